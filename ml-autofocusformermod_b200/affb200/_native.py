@@ -1,0 +1,82 @@
+"""ctypes binding of libaffb200.so (C ABI in include/affb200.h).
+
+There is deliberately no CPU or pure-PyTorch fallback here: if the shared library is missing the import raises,
+mirroring the reference's behaviour when its extension cannot be imported (reference clusten/clusten.py:8-14).
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libaffb200.so")
+
+_i64 = ctypes.c_int64
+_ptr = ctypes.c_void_p
+_int = ctypes.c_int
+
+# name -> (restype, argtypes); kept in one table so tests can check it against include/affb200.h
+SIGNATURES = {
+    "affb200_abi_version": (_int, []),
+    "affb200_last_error": (ctypes.c_char_p, []),
+    "affb200_target_arch": (ctypes.c_char_p, []),
+    "affb200_csr_off_bytes": (ctypes.c_size_t, [_i64, _i64]),
+    "affb200_csr_ent_bytes": (ctypes.c_size_t, [_i64, _i64, _i64]),
+    "affb200_csr_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
+    "affb200_csr_build": (_int, [_ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _int, _ptr]),
+    "affb200_qk_fwd": (_int, [_ptr, _ptr, _ptr, _ptr] + [_i64] * 6 + [_int, _ptr]),
+    "affb200_qk_bwd": (_int, [_ptr] * 8 + [_i64] * 6 + [_int, _ptr]),
+    "affb200_av_fwd": (_int, [_ptr, _ptr, _ptr, _ptr] + [_i64] * 6 + [_int, _ptr]),
+    "affb200_av_bwd": (_int, [_ptr] * 8 + [_i64] * 6 + [_int, _ptr]),
+    "affb200_wf_fwd": (_int, [_ptr, _ptr, _ptr, _ptr] + [_i64] * 6 + [_int, _ptr]),
+    "affb200_wf_bwd": (_int, [_ptr] * 8 + [_i64] * 6 + [_int, _ptr]),
+}
+
+DTYPE_ENUM = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2, torch.float64: 3}
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "Could not load CLUSTEN CUDA extension. libaffb200.so is missing at %s; build it with "
+            "`python -c 'import __graft_entry__ as g; g.build()'` or `make -C ml-autofocusformermod_b200/csrc`."
+            % LIB_PATH)
+    try:
+        lib = ctypes.CDLL(LIB_PATH)
+    except OSError as e:  # pragma: no cover - depends on the machine
+        raise RuntimeError("Could not load CLUSTEN CUDA extension. " + str(e))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    if lib.affb200_abi_version() != 1:
+        raise RuntimeError("libaffb200.so ABI version mismatch")
+    return lib
+
+
+LIB = _load()
+
+
+def last_error():
+    return LIB.affb200_last_error().decode()
+
+
+def check(code, what):
+    if code != 0:
+        raise RuntimeError("%s failed (%d): %s" % (what, code, last_error()))
+
+
+def dtype_enum(t):
+    try:
+        return DTYPE_ENUM[t.dtype]
+    except KeyError:
+        raise RuntimeError('"%s" not implemented for \'%s\'' % ("clusten", str(t.dtype).replace("torch.", "")))
+
+
+def stream_ptr(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def p(t):
+    """device pointer of a tensor (None -> NULL)"""
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
