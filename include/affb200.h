@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define AFFB200_ABI_VERSION 1
+#define AFFB200_ABI_VERSION 2
 
 typedef enum {
     AFFB200_F32 = 0,
@@ -51,18 +51,64 @@ const char *affb200_last_error(void);
 const char *affb200_target_arch(void);
 
 /* ------------------------------------------------------------------------------------------------------------
- * Transposed neighbour index ("who references key row r"), used by the scatter halves of the backward passes
- * instead of the reference's atomics (clustenqk_cuda_kernel.cu:125, clustenav_cuda_kernel.cu:121,
- * clustenwf_cuda_kernel.cu:129).  CSR per batch element:
- *   off[b][0..Nk]      int32, off[b][r]..off[b][r+1] = range of entries referencing key row r
- *   ent[b][0..Nq*M)    int32, entry e = i*M + j  (query token i, neighbour slot j), ascending within a row
- * `work` is scratch of affb200_csr_work_bytes() bytes.  nbhd_idx: [B][Nq][M] int64.
+ * Index plans.  nbhd_idx is constant across the 2..18 blocks of a stage (reference models/aff_transformer.py:489-495
+ * passes the same member_idx to every block), so structures derived from it are built once per tensor and handed
+ * to every forward/backward call through affb200_nbhd_plan (all members are DEVICE pointers, the struct itself
+ * lives on the host and is read during the call only).
+ *
+ * (1) Transposed index ("who references key row r"), used by the generic scatter halves of the backward passes
+ *     instead of the reference's atomics (clustenqk_cuda_kernel.cu:125, clustenav_cuda_kernel.cu:121,
+ *     clustenwf_cuda_kernel.cu:129).  CSR per batch element:
+ *       off[b][0..Nk]      int32, off[b][r]..off[b][r+1] = range of entries referencing key row r
+ *       ent[b][0..Nq*M)    int32, entry e = i*M + j  (query token i, neighbour slot j), ascending within a row
+ *     `work` is scratch of affb200_csr_work_bytes() bytes.  nbhd_idx: [B][Nq][M] int64.
+ *
+ * (2) Tile plans for the dense-tile kernels (f16/bf16, head dim 16 or 32).  T = tokens per tile (16, 32 or 64).
+ *     Query tiles (tile t covers query tokens [t*T, t*T+T)):
+ *       q_hdr [B][ceil(Nq/T)]            int32: U = number of distinct key rows the tile references, or-ed with
+ *                                        AFFB200_PLAN_DUP (a token lists one row twice) / AFFB200_PLAN_OVERFLOW (U > 256)
+ *       q_rows[B][ceil(Nq/T)][256]       int32: those rows ascending, padded with -1 to a multiple of 16
+ *       q_loc [B][Nq][M]                 uint8: position of nbhd_idx[b,i,j] in its tile's q_rows
+ *     Key tiles (tile t covers key rows [t*T, t*T+T)):
+ *       k_hdr [B][ceil(Nk/T)]            int32: Uq = number of distinct query tokens referencing the tile (+ flags)
+ *       k_utok[B][ceil(Nk/T)][256]       int32: those tokens ascending, padded with -1 to a multiple of 16
+ *       k_rloc[B][ceil(Nk/T)][256][M]    uint8: nbhd_idx[b,utok[u],j] - t*T, or 0xFF when outside the tile
+ *     stats[4] int32 (caller-zeroed): {query tiles overflowed, query tiles with DUP, key tiles overflowed, key tiles
+ *     with DUP}.  A plan with an overflow count > 0 must not be passed to the operators (use the generic path).
  * ---------------------------------------------------------------------------------------------------------- */
+#define AFFB200_PLAN_UMAX 256
+#define AFFB200_PLAN_MAX_NK 131072
+#define AFFB200_PLAN_MAX_M 192
+#define AFFB200_PLAN_DUP 0x20000000
+#define AFFB200_PLAN_OVERFLOW 0x40000000
+#define AFFB200_PLAN_COUNT_MASK 0x0fffffff
+
+typedef struct {
+    const int32_t *csr_off; /* (1), may be NULL when k_hdr is given */
+    const int32_t *csr_ent;
+    int32_t tq;             /* query-tile size, 0 = no query-tile plan */
+    const int32_t *q_hdr;
+    const int32_t *q_rows;
+    const uint8_t *q_loc;
+    int32_t tk;             /* key-tile size, 0 = no key-tile plan */
+    const int32_t *k_hdr;
+    const int32_t *k_utok;
+    const uint8_t *k_rloc;
+} affb200_nbhd_plan;
+
 size_t affb200_csr_off_bytes(int64_t B, int64_t Nk);
 size_t affb200_csr_ent_bytes(int64_t B, int64_t Nq, int64_t M);
 size_t affb200_csr_work_bytes(int64_t B, int64_t Nk);
 int affb200_csr_build(const int64_t *nbhd_idx, int64_t B, int64_t Nq, int64_t Nk, int64_t M,
                       int32_t *off, int32_t *ent, void *work, int sorted, void *stream);
+
+int64_t affb200_plan_tiles(int64_t n, int64_t T);
+int affb200_qplan_build(const int64_t *nbhd_idx, int64_t B, int64_t Nq, int64_t Nk, int64_t M, int64_t T,
+                        int32_t *hdr, int32_t *rows, uint8_t *loc, int32_t *stats, void *stream);
+/* cnt_work: scratch of B*ceil(Nk/T) int32 */
+int affb200_kplan_build(const int64_t *nbhd_idx, int64_t B, int64_t Nq, int64_t Nk, int64_t M, int64_t T,
+                        int32_t *hdr, int32_t *utok, uint8_t *rloc, int32_t *cnt_work, int32_t *stats,
+                        void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * QK: replaces clustenqk_cuda.forward / .backward (clustenqk_cuda.cpp:25-45, clustenqk_cuda_kernel.cu:18-178).
@@ -70,12 +116,14 @@ int affb200_csr_build(const int64_t *nbhd_idx, int64_t B, int64_t Nq, int64_t Nk
  *   q [B][H][Nq][c], k [B][H][Nk][c] (NOT pre-transposed: clusten.py:30's permute is not needed),
  *   idx [B][Nq][M] int64, attn [B][H][Nq][M].
  * Backward: d_q[b,h,i,c] = sum_j k[idx]*d_attn ; d_k[b,h,r,c] = sum_{(i,j): idx[b,i,j]=r} q[b,h,i,c]*d_attn[b,h,i,j]
+ * `plan` (host pointer) may be NULL for the forward calls (generic kernels); the backward calls need either the
+ * transposed index (1) or a key-tile plan (2).  With a tile plan, f16/bf16 and c in {16,32} the dense-tile kernels run.
  * ---------------------------------------------------------------------------------------------------------- */
-int affb200_qk_fwd(const void *q, const void *k, const int64_t *idx, void *attn,
+int affb200_qk_fwd(const void *q, const void *k, const int64_t *idx, const affb200_nbhd_plan *plan, void *attn,
                    int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c,
                    int dtype, void *stream);
 int affb200_qk_bwd(const void *d_attn, const void *q, const void *k, const int64_t *idx,
-                   const int32_t *csr_off, const int32_t *csr_ent,
+                   const affb200_nbhd_plan *plan,
                    void *d_q, void *d_k,
                    int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c,
                    int dtype, void *stream);
@@ -85,11 +133,11 @@ int affb200_qk_bwd(const void *d_attn, const void *q, const void *k, const int64
  *   out[b,h,i,c] = sum_j attn[b,h,i,j] * v[b,h,idx[b,i,j],c]
  * Backward: d_attn[b,h,i,j] = sum_c v[idx]*d_out ; d_v[b,h,r,c] = sum_{(i,j)->r} attn[b,h,i,j]*d_out[b,h,i,c]
  * ---------------------------------------------------------------------------------------------------------- */
-int affb200_av_fwd(const void *attn, const void *v, const int64_t *idx, void *out,
+int affb200_av_fwd(const void *attn, const void *v, const int64_t *idx, const affb200_nbhd_plan *plan, void *out,
                    int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c,
                    int dtype, void *stream);
 int affb200_av_bwd(const void *d_out, const void *attn, const void *v, const int64_t *idx,
-                   const int32_t *csr_off, const int32_t *csr_ent,
+                   const affb200_nbhd_plan *plan,
                    void *d_attn, void *d_v,
                    int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c,
                    int dtype, void *stream);
@@ -100,11 +148,11 @@ int affb200_av_bwd(const void *d_out, const void *attn, const void *v, const int
  *   w [B][Nq][M][IC], f [B][Nk][C], idx [B][Nq][M] int64, out [B][Nq][IC][C].
  * Backward: d_w[b,i,j,ic] = sum_c f[idx]*d_out[b,i,ic,c] ; d_f[b,r,c] = sum_{(i,j)->r} sum_ic d_out[b,i,ic,c]*w[b,i,j,ic]
  * ---------------------------------------------------------------------------------------------------------- */
-int affb200_wf_fwd(const void *w, const void *f, const int64_t *idx, void *out,
+int affb200_wf_fwd(const void *w, const void *f, const int64_t *idx, const affb200_nbhd_plan *plan, void *out,
                    int64_t B, int64_t Nq, int64_t Nk, int64_t M, int64_t IC, int64_t C,
                    int dtype, void *stream);
 int affb200_wf_bwd(const void *d_out, const void *w, const void *f, const int64_t *idx,
-                   const int32_t *csr_off, const int32_t *csr_ent,
+                   const affb200_nbhd_plan *plan,
                    void *d_w, void *d_f,
                    int64_t B, int64_t Nq, int64_t Nk, int64_t M, int64_t IC, int64_t C,
                    int dtype, void *stream);

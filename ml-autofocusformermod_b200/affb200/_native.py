@@ -15,6 +15,21 @@ _i64 = ctypes.c_int64
 _ptr = ctypes.c_void_p
 _int = ctypes.c_int
 
+
+
+class NbhdPlanStruct(ctypes.Structure):
+    """affb200_nbhd_plan (include/affb200.h): device pointers of the structures derived from one nbhd_idx tensor."""
+    _fields_ = [("csr_off", _ptr), ("csr_ent", _ptr),
+                ("tq", ctypes.c_int32), ("q_hdr", _ptr), ("q_rows", _ptr), ("q_loc", _ptr),
+                ("tk", ctypes.c_int32), ("k_hdr", _ptr), ("k_utok", _ptr), ("k_rloc", _ptr)]
+
+
+_plan_p = ctypes.POINTER(NbhdPlanStruct)
+
+PLAN_UMAX = 256
+PLAN_MAX_NK = 131072
+PLAN_MAX_M = 192
+
 # name -> (restype, argtypes); kept in one table so tests can check it against include/affb200.h
 SIGNATURES = {
     "affb200_abi_version": (_int, []),
@@ -24,12 +39,15 @@ SIGNATURES = {
     "affb200_csr_ent_bytes": (ctypes.c_size_t, [_i64, _i64, _i64]),
     "affb200_csr_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
     "affb200_csr_build": (_int, [_ptr, _i64, _i64, _i64, _i64, _ptr, _ptr, _ptr, _int, _ptr]),
-    "affb200_qk_fwd": (_int, [_ptr, _ptr, _ptr, _ptr] + [_i64] * 6 + [_int, _ptr]),
-    "affb200_qk_bwd": (_int, [_ptr] * 8 + [_i64] * 6 + [_int, _ptr]),
-    "affb200_av_fwd": (_int, [_ptr, _ptr, _ptr, _ptr] + [_i64] * 6 + [_int, _ptr]),
-    "affb200_av_bwd": (_int, [_ptr] * 8 + [_i64] * 6 + [_int, _ptr]),
-    "affb200_wf_fwd": (_int, [_ptr, _ptr, _ptr, _ptr] + [_i64] * 6 + [_int, _ptr]),
-    "affb200_wf_bwd": (_int, [_ptr] * 8 + [_i64] * 6 + [_int, _ptr]),
+    "affb200_plan_tiles": (_i64, [_i64, _i64]),
+    "affb200_qplan_build": (_int, [_ptr] + [_i64] * 5 + [_ptr] * 5),
+    "affb200_kplan_build": (_int, [_ptr] + [_i64] * 5 + [_ptr] * 6),
+    "affb200_qk_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
+    "affb200_qk_bwd": (_int, [_ptr] * 4 + [_plan_p] + [_ptr] * 2 + [_i64] * 6 + [_int, _ptr]),
+    "affb200_av_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
+    "affb200_av_bwd": (_int, [_ptr] * 4 + [_plan_p] + [_ptr] * 2 + [_i64] * 6 + [_int, _ptr]),
+    "affb200_wf_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
+    "affb200_wf_bwd": (_int, [_ptr] * 4 + [_plan_p] + [_ptr] * 2 + [_i64] * 6 + [_int, _ptr]),
 }
 
 DTYPE_ENUM = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2, torch.float64: 3}
@@ -49,7 +67,7 @@ def _load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.affb200_abi_version() != 1:
+    if lib.affb200_abi_version() != 2:
         raise RuntimeError("libaffb200.so ABI version mismatch")
     return lib
 

@@ -30,6 +30,11 @@ def _check_cuda(**tensors):
     return dev
 
 
+def _dense(t, c):
+    """dtype / head dim combinations served by the dense-tile tensor-core kernels (csrc/clusten_dense.cu)"""
+    return t.dtype in (torch.float16, torch.bfloat16) and c in (16, 32)
+
+
 def _check_idx(nbhd_idx, B, Nq):
     if nbhd_idx.dtype != torch.int64:
         raise RuntimeError("nbhd_idx must be an int64 tensor")
@@ -54,7 +59,8 @@ class CLUSTENQKFunction(Function):
         M = nbhd_idx.shape[2]
         with torch.cuda.device(dev):
             attn = torch.empty((B, H, Nq, M), dtype=query.dtype, device=dev)
-            N.check(N.LIB.affb200_qk_fwd(N.p(query), N.p(key), N.p(nbhd_idx), N.p(attn), B, H, Nq, Nk, M, c,
+            plan = get_plan(nbhd_idx).struct(nbhd_idx, Nk, _dense(query, c), False)
+            N.check(N.LIB.affb200_qk_fwd(N.p(query), N.p(key), N.p(nbhd_idx), plan, N.p(attn), B, H, Nq, Nk, M, c,
                                          N.dtype_enum(query), N.stream_ptr(dev)), "clusten_qk_forward")
         ctx.save_for_backward(query, key, nbhd_idx)
         return attn
@@ -70,10 +76,10 @@ class CLUSTENQKFunction(Function):
         Nk = key.shape[2]
         M = nbhd_idx.shape[2]
         with torch.cuda.device(dev):
-            off, ent = get_plan(nbhd_idx).csr(nbhd_idx, Nk)
+            plan = get_plan(nbhd_idx).struct(nbhd_idx, Nk, _dense(query, c), True)
             d_query = torch.empty_like(query)
             d_key = torch.empty_like(key)
-            N.check(N.LIB.affb200_qk_bwd(N.p(grad_attn), N.p(query), N.p(key), N.p(nbhd_idx), N.p(off), N.p(ent),
+            N.check(N.LIB.affb200_qk_bwd(N.p(grad_attn), N.p(query), N.p(key), N.p(nbhd_idx), plan,
                                          N.p(d_query), N.p(d_key), B, H, Nq, Nk, M, c, N.dtype_enum(query),
                                          N.stream_ptr(dev)), "clusten_qk_backward")
         return d_query, d_key, None
@@ -95,7 +101,8 @@ class CLUSTENAVFunction(Function):
         _check_idx(nbhd_idx, B, Nq)
         with torch.cuda.device(dev):
             feat = torch.empty((B, H, Nq, c), dtype=attn.dtype, device=dev)
-            N.check(N.LIB.affb200_av_fwd(N.p(attn), N.p(v), N.p(nbhd_idx), N.p(feat), B, H, Nq, Nk, M, c,
+            plan = get_plan(nbhd_idx).struct(nbhd_idx, Nk, _dense(attn, c), False)
+            N.check(N.LIB.affb200_av_fwd(N.p(attn), N.p(v), N.p(nbhd_idx), plan, N.p(feat), B, H, Nq, Nk, M, c,
                                          N.dtype_enum(attn), N.stream_ptr(dev)), "clusten_av_forward")
         ctx.save_for_backward(attn, v, nbhd_idx)
         return feat
@@ -110,10 +117,10 @@ class CLUSTENAVFunction(Function):
         B, H, Nq, M = attn.shape
         Nk, c = v.shape[2], v.shape[3]
         with torch.cuda.device(dev):
-            off, ent = get_plan(nbhd_idx).csr(nbhd_idx, Nk)
+            plan = get_plan(nbhd_idx).struct(nbhd_idx, Nk, _dense(attn, c), True)
             d_attn = torch.empty_like(attn)
             d_v = torch.empty_like(v)
-            N.check(N.LIB.affb200_av_bwd(N.p(grad_feat), N.p(attn), N.p(v), N.p(nbhd_idx), N.p(off), N.p(ent),
+            N.check(N.LIB.affb200_av_bwd(N.p(grad_feat), N.p(attn), N.p(v), N.p(nbhd_idx), plan,
                                          N.p(d_attn), N.p(d_v), B, H, Nq, Nk, M, c, N.dtype_enum(attn),
                                          N.stream_ptr(dev)), "clusten_av_backward")
         return d_attn, d_v, None
@@ -135,7 +142,7 @@ class CLUSTENWFFunction(Function):
         _check_idx(nbhd_idx, B, Nq)
         with torch.cuda.device(dev):
             feat_new = torch.empty((B, Nq, IC, C), dtype=weights.dtype, device=dev)
-            N.check(N.LIB.affb200_wf_fwd(N.p(weights), N.p(feat), N.p(nbhd_idx), N.p(feat_new), B, Nq, Nk, M, IC, C,
+            N.check(N.LIB.affb200_wf_fwd(N.p(weights), N.p(feat), N.p(nbhd_idx), None, N.p(feat_new), B, Nq, Nk, M, IC, C,
                                          N.dtype_enum(weights), N.stream_ptr(dev)), "clusten_wf_forward")
         ctx.save_for_backward(weights, feat, nbhd_idx)
         return feat_new
@@ -150,10 +157,10 @@ class CLUSTENWFFunction(Function):
         B, Nq, M, IC = weights.shape
         Nk, C = feat.shape[1], feat.shape[2]
         with torch.cuda.device(dev):
-            off, ent = get_plan(nbhd_idx).csr(nbhd_idx, Nk)
+            plan = get_plan(nbhd_idx).struct(nbhd_idx, Nk, False, True)
             d_weights = torch.empty_like(weights)
             d_feat = torch.empty_like(feat)
-            N.check(N.LIB.affb200_wf_bwd(N.p(grad_feat_new), N.p(weights), N.p(feat), N.p(nbhd_idx), N.p(off),
-                                         N.p(ent), N.p(d_weights), N.p(d_feat), B, Nq, Nk, M, IC, C,
+            N.check(N.LIB.affb200_wf_bwd(N.p(grad_feat_new), N.p(weights), N.p(feat), N.p(nbhd_idx), plan,
+                                         N.p(d_weights), N.p(d_feat), B, Nq, Nk, M, IC, C,
                                          N.dtype_enum(weights), N.stream_ptr(dev)), "clusten_wf_backward")
         return d_weights, d_feat, None

@@ -4,12 +4,16 @@
 `member_idx` tensor to every block), so derived index structures are built once and shared by every forward and
 backward call that receives the same tensor object:
 
-  * the transposed index (CSR: key row -> referencing (token, slot) entries) that turns the scatter halves of the
-    backward passes into gathers (affb200_csr_build in include/affb200.h).
+  * tile plans (csrc/tileplan.cu): per tile of T consecutive tokens the union of referenced key rows plus 1-byte
+    positions, and the transposed form per tile of key rows — what the dense-tile f16/bf16 kernels consume;
+  * the transposed index (CSR: key row -> referencing (token, slot) entries) for the generic scatter halves of the
+    backward passes (affb200_csr_build).
 
 Plans are looked up by tensor identity and die with the tensor (weakref), and are invalidated by in-place writes
-(`Tensor._version`).
+(`Tensor._version`).  Building a tile plan reads back one 16-byte counter block (tiles whose union exceeded 256
+rows): a plan with overflowed tiles is discarded and the generic kernels are used for that tensor.
 """
+import ctypes
 import threading
 import weakref
 
@@ -20,15 +24,31 @@ from . import _native as N
 _lock = threading.Lock()
 _plans = {}  # id(tensor) -> (weakref, version, NbhdPlan)
 
+NUM_SMS = 148
+
+
+def pick_tile(B, n, M):
+    """Tokens per tile: 64 when that still gives >= 4 CTAs per SM-wave and the neighbourhood is small enough for
+    the union of a tile to stay under 256 rows; smaller tiles for small problems and wide neighbourhoods."""
+    t = 64 if M <= 64 else (32 if M <= 96 else 16)
+    while t > 16 and B * ((n + t - 1) // t) < 4 * NUM_SMS:
+        t //= 2
+    return t
+
 
 class NbhdPlan:
     """Derived structures of one nbhd_idx tensor [B, Nq, M] (int64, CUDA, contiguous)."""
 
     def __init__(self, idx):
         self.shape = tuple(idx.shape)
-        self._csr = {}  # Nk -> (off, ent)
+        self._csr = {}    # Nk -> (off, ent)
+        self._q = {}      # Nk -> (T, hdr, rows, loc) or None when not tileable
+        self._k = {}      # Nk -> (T, hdr, utok, rloc) or None
+        self._structs = {}
         self._lock = threading.Lock()
+        self.stats = {}
 
+    # -- transposed index -------------------------------------------------------------------------------
     def csr(self, idx, Nk, sorted_entries=True):
         """(off [B, Nk+1] int32, ent [B, Nq*M] int32) for key-row count Nk; built on first use."""
         with self._lock:
@@ -43,10 +63,100 @@ class NbhdPlan:
                 work = torch.empty(max(1, N.LIB.affb200_csr_work_bytes(B, Nk)), dtype=torch.uint8, device=dev)
                 N.check(N.LIB.affb200_csr_build(N.p(idx), B, Nq, Nk, M, N.p(off), N.p(ent), N.p(work),
                                                 1 if sorted_entries else 0, N.stream_ptr(dev)), "csr_build")
-                # `work` is only used by the kernels just enqueued on the current stream; the caching allocator
-                # keeps it stream-ordered, so dropping the reference here is safe.
             self._csr[Nk] = (off, ent)
+            self._structs.clear()
             return off, ent
+
+    # -- tile plans -------------------------------------------------------------------------------------
+    def _tileable(self, Nk):
+        B, Nq, M = self.shape
+        return (0 < B <= 65535 and Nq > 0 and 1 <= M <= N.PLAN_MAX_M and 0 < Nk <= N.PLAN_MAX_NK
+                and Nq * M < 2 ** 31)
+
+    def qplan(self, idx, Nk):
+        with self._lock:
+            if Nk in self._q:
+                return self._q[Nk]
+            res = None
+            if self._tileable(Nk):
+                B, Nq, M = self.shape
+                dev = idx.device
+                T = pick_tile(B, Nq, M)
+                with torch.cuda.device(dev):
+                    while True:
+                        nt = (Nq + T - 1) // T
+                        hdr = torch.empty((B, nt), dtype=torch.int32, device=dev)
+                        rows = torch.empty((B, nt, N.PLAN_UMAX), dtype=torch.int32, device=dev)
+                        loc = torch.empty(B * Nq * M + 16, dtype=torch.uint8, device=dev)  # +16: vector tail reads
+                        stats = torch.zeros(4, dtype=torch.int32, device=dev)
+                        N.check(N.LIB.affb200_qplan_build(N.p(idx), B, Nq, Nk, M, T, N.p(hdr), N.p(rows), N.p(loc),
+                                                          N.p(stats), N.stream_ptr(dev)), "qplan_build")
+                        st = stats.tolist()
+                        if st[0] == 0:
+                            res = (T, hdr, rows, loc)
+                            self.stats["q"] = dict(T=T, overflow=0, dup_tiles=st[1], tiles=B * nt)
+                            break
+                        if T == 16:
+                            self.stats["q"] = dict(T=T, overflow=st[0], tiles=B * nt)
+                            break
+                        T //= 2
+            self._q[Nk] = res
+            self._structs.clear()
+            return res
+
+    def kplan(self, idx, Nk):
+        with self._lock:
+            if Nk in self._k:
+                return self._k[Nk]
+            res = None
+            if self._tileable(Nk):
+                B, Nq, M = self.shape
+                dev = idx.device
+                T = pick_tile(B, Nk, M)
+                with torch.cuda.device(dev):
+                    while True:
+                        nt = (Nk + T - 1) // T
+                        hdr = torch.empty((B, nt), dtype=torch.int32, device=dev)
+                        utok = torch.empty((B, nt, N.PLAN_UMAX), dtype=torch.int32, device=dev)
+                        rloc = torch.empty((B, nt, N.PLAN_UMAX, M), dtype=torch.uint8, device=dev)
+                        cnt = torch.empty(B * nt, dtype=torch.int32, device=dev)
+                        stats = torch.zeros(4, dtype=torch.int32, device=dev)
+                        N.check(N.LIB.affb200_kplan_build(N.p(idx), B, Nq, Nk, M, T, N.p(hdr), N.p(utok), N.p(rloc),
+                                                          N.p(cnt), N.p(stats), N.stream_ptr(dev)), "kplan_build")
+                        st = stats.tolist()
+                        if st[2] == 0:
+                            res = (T, hdr, utok, rloc)
+                            self.stats["k"] = dict(T=T, overflow=0, dup_tiles=st[3], tiles=B * nt)
+                            break
+                        if T == 16:
+                            self.stats["k"] = dict(T=T, overflow=st[2], tiles=B * nt)
+                            break
+                        T //= 2
+            self._k[Nk] = res
+            self._structs.clear()
+            return res
+
+    # -- what the C ABI receives ------------------------------------------------------------------------
+    def struct(self, idx, Nk, dense, backward):
+        """ctypes affb200_nbhd_plan for a call on key-row count Nk.  `dense`: the call's dtype/head-dim can use
+        the dense-tile kernels.  `backward`: the scatter half needs a key-tile plan or the transposed index."""
+        q = self.qplan(idx, Nk) if dense else None
+        k = self.kplan(idx, Nk) if (dense and backward) else None
+        need_csr = backward and k is None
+        csr = self.csr(idx, Nk) if need_csr else self._csr.get(Nk)
+        key = (Nk, q is not None, k is not None, csr is not None)
+        with self._lock:
+            s = self._structs.get(key)
+            if s is None:
+                s = N.NbhdPlanStruct()
+                if csr is not None:
+                    s.csr_off, s.csr_ent = csr[0].data_ptr(), csr[1].data_ptr()
+                if q is not None:
+                    s.tq, s.q_hdr, s.q_rows, s.q_loc = q[0], q[1].data_ptr(), q[2].data_ptr(), q[3].data_ptr()
+                if k is not None:
+                    s.tk, s.k_hdr, s.k_utok, s.k_rloc = k[0], k[1].data_ptr(), k[2].data_ptr(), k[3].data_ptr()
+                self._structs[key] = s
+            return ctypes.byref(s)
 
 
 def get_plan(idx):

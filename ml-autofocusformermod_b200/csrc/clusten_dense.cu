@@ -1,0 +1,487 @@
+// clusten_dense.cu — dense-tile CLUSTEN kernels for f16/bf16 with head dim 16 or 32 (sm_100a).
+//
+// With a tile plan (tileplan.cu) a tile of T consecutive tokens and the UNION of the U <= 256 rows it touches turn
+// the gather ops into small dense contractions on the tensor cores, the only place the path is a real contraction
+// (per-cluster (tokens x head_dim)·(head_dim x neighbourhood) tiles):
+//   gather-dot   S[T x U]  = X[T x c] · Y_U[U x c]^T ; out[t, j] = S[t, loc[t, j]]          QK fwd, AV bwd (d_attn)
+//   gather-wsum  out[T x c] = P[T x U] · Y_U[U x c],  P[t, loc[t, j]] = w[t, j]              AV fwd, QK bwd (d_q)
+//   scatter-wsum dY[T x c]  = P'[T x Uq] · X_Uq[Uq x c], P'[rloc[u, j], u] = w[utok[u], j]   QK bwd (d_k), AV bwd (d_v)
+// Every union row is fetched from L2/HBM once per tile and head with 16-byte cp.async into padded shared memory
+// (conflict-free ldmatrix), instead of once per (token, slot) as a row gather would (~6x fewer bytes through L1),
+// the 8-byte indices are replaced by the plan's 1-byte positions, outputs leave as 16-byte streaming stores, and
+// all sums are fp32 MMA accumulators combined in a fixed order (run-to-run deterministic, no atomics).
+#include "common.cuh"
+
+namespace affb200 {
+
+constexpr int kDT = 256;              // threads per CTA (8 warps)
+constexpr int kSS = kUMaxDense + 8;   // element stride of the [T][U] operand matrices: (2*kSS/16) is odd
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void cp_async16(void *dst, const void *src, bool valid) {
+    const int sz = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void *p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void *p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
+}
+
+template <typename T> __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <> __device__ __forceinline__ void mma16816<__nv_bfloat16>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <> __device__ __forceinline__ void mma16816<__half>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+template <typename T> __device__ __forceinline__ uint32_t pack2(float lo, float hi);
+template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+template <> __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
+    __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+// stage `n_rows` rows of C elements into padded shared memory rows; row_of(i) gives the global row or -1 (zero-fill)
+template <typename T, int C, typename RowOf>
+__device__ __forceinline__ void stage_rows(T *dst, const T *__restrict__ src_base, int n_rows, RowOf row_of) {
+    constexpr int CS = C + 8;
+    constexpr int CH = C * 2 / 16;
+    for (int q = threadIdx.x; q < n_rows * CH; q += kDT) {
+        const int i = q / CH, ch = q - i * CH;
+        const int r = row_of(i);
+        cp_async16(dst + i * CS + ch * 8, src_base + int64_t(r < 0 ? 0 : r) * C + ch * 8, r >= 0);
+    }
+}
+
+struct TileSmem {
+    int *rows;        // [256]
+    uint8_t *loc;     // [T*M] (padded to 16 bytes)
+    void *xs;         // [T][C+8]          (gather-dot only)
+    void *ys;         // [256][C+8]
+    void *ps;         // [T][kSS]
+    float *os;        // [8*16*(16+... )]  fp32 partial outputs (wsum kernels)
+};
+
+template <int C> __host__ __device__ constexpr int os_floats() { return 8 * 16 * 16 * (C + 8) / C; }
+
+// =========================================================================================================
+// gather-dot
+// =========================================================================================================
+template <typename T, int C>
+__global__ void __launch_bounds__(kDT)
+gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const int32_t *__restrict__ q_hdr,
+                        const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc, T *__restrict__ out,
+                        int H, int Nq, int Nk, int M, int TT) {
+    constexpr int CS = C + 8;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    int *rows_s = reinterpret_cast<int *>(smem_raw);
+    T *ys = reinterpret_cast<T *>(smem_raw + 1024);
+    T *ss = ys + kUMaxDense * CS;
+    T *xs = ss + TT * kSS;
+    uint8_t *loc_s = reinterpret_cast<uint8_t *>(xs + TT * CS);
+
+    const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x;
+    const int t0 = tile * TT;
+    const int ti = min(TT, Nq - t0);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int U = q_hdr[int64_t(b) * n_tiles + tile] & AFFB200_PLAN_COUNT_MASK;
+    const int Upad = (U + 15) & ~15;
+    const int n_ent = ti * M;
+
+    const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * kUMaxDense;
+    for (int u = tid; u < Upad; u += kDT) rows_s[u] = rg[u];
+    const uint8_t *lg = q_loc + (int64_t(b) * Nq + t0) * M;
+    if ((reinterpret_cast<uintptr_t>(lg) & 15) == 0) {
+        for (int p = tid; p < (n_ent + 15) / 16; p += kDT)
+            reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(reinterpret_cast<const uint4 *>(lg) + p);  // tail over-read stays inside the [B][Nq][M] array + 16-byte slack kept by the host
+    } else {
+        for (int p = tid; p < n_ent; p += kDT) loc_s[p] = lg[p];
+    }
+    __syncthreads();
+
+    const int MT = TT >> 4;
+    const int mt = warp % MT;
+    const int nstep = 8 / MT;  // warps sharing one m-tile
+    const int g = lane >> 2, q4 = lane & 3;
+    const bool vec_out = (M % 8 == 0);
+
+    for (int h = 0; h < H; ++h) {
+        const int64_t z = int64_t(b) * H + h;
+        stage_rows<T, C>(xs, x + (z * Nq + t0) * C, TT, [&](int i) { return i < ti ? i : -1; });
+        stage_rows<T, C>(ys, y + z * Nk * C, Upad, [&](int i) { return rows_s[i]; });
+        cp_async_commit();
+        cp_async_wait_all();
+        __syncthreads();
+
+        // A fragments of this warp's m-tile
+        uint32_t a[C / 16][4];
+#pragma unroll
+        for (int ks = 0; ks < C / 16; ++ks)
+            ldsm_x4(a[ks], xs + (mt * 16 + (lane & 15)) * CS + ks * 16 + (lane >> 4) * 8);
+        if constexpr (C == 32) {
+            for (int nt = warp / MT; nt < Upad / 8; nt += nstep) {
+                uint32_t bf[4];  // (k 0-7, 8-15, 16-23, 24-31) of keys nt*8 .. nt*8+7
+                ldsm_x4(bf, ys + (nt * 8 + (lane & 7)) * CS + (lane >> 3) * 8);
+                float d[4] = {0.f, 0.f, 0.f, 0.f};
+                mma16816<T>(d, a[0], bf[0], bf[1]);
+                mma16816<T>(d, a[1], bf[2], bf[3]);
+                T *sp = ss + (mt * 16 + g) * kSS + nt * 8 + q4 * 2;
+                *reinterpret_cast<uint32_t *>(sp) = pack2<T>(d[0], d[1]);
+                *reinterpret_cast<uint32_t *>(sp + 8 * kSS) = pack2<T>(d[2], d[3]);
+            }
+        } else {
+            for (int np = warp / MT; np < Upad / 16; np += nstep) {
+                uint32_t bf[4];  // keys np*16..+7: k 0-7, 8-15 ; keys np*16+8..+15: k 0-7, 8-15
+                ldsm_x4(bf, ys + (np * 16 + (lane & 7) + (lane >> 4) * 8) * CS + ((lane >> 3) & 1) * 8);
+                float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+                mma16816<T>(d0, a[0], bf[0], bf[1]);
+                mma16816<T>(d1, a[0], bf[2], bf[3]);
+                T *sp = ss + (mt * 16 + g) * kSS + np * 16 + q4 * 2;
+                *reinterpret_cast<uint32_t *>(sp) = pack2<T>(d0[0], d0[1]);
+                *reinterpret_cast<uint32_t *>(sp + 8 * kSS) = pack2<T>(d0[2], d0[3]);
+                *reinterpret_cast<uint32_t *>(sp + 8) = pack2<T>(d1[0], d1[1]);
+                *reinterpret_cast<uint32_t *>(sp + 8 * kSS + 8) = pack2<T>(d1[2], d1[3]);
+            }
+        }
+        __syncthreads();
+
+        T *og = out + (z * Nq + t0) * M;
+        if (vec_out && (reinterpret_cast<uintptr_t>(og) & 15) == 0) {
+            for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {
+                const int p = p8 * 8;
+                const int t = p / M;
+                const uint2 lc = *reinterpret_cast<const uint2 *>(loc_s + p);
+                const T *srow = ss + t * kSS;
+                const uint8_t *l8 = reinterpret_cast<const uint8_t *>(&lc);
+                uint4 v;
+                uint16_t *e = reinterpret_cast<uint16_t *>(&v);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) e[k] = *reinterpret_cast<const uint16_t *>(srow + l8[k]);
+                st_cs_u4(og + p, v);
+            }
+        } else {
+            for (int p = tid; p < n_ent; p += kDT) og[p] = ss[(p / M) * kSS + loc_s[p]];
+        }
+        __syncthreads();
+    }
+}
+
+// =========================================================================================================
+// shared tail of the two wsum kernels: out[T x C] = A[T x Kpad] (smem, stride kSS) · Bm[Kpad x C] (smem, stride C+8)
+// K is split over the warps that share an output item; partials meet in `os` and are summed in slice order.
+// =========================================================================================================
+template <typename T, int C>
+__device__ __forceinline__ void wsum_mma_store(const T *ps, const T *bs, float *os, T *__restrict__ og, int TT,
+                                                int Kpad, int n_valid_rows) {
+    constexpr int CS = C + 8;
+    constexpr int OS = C + 8;  // fp32 row stride of the partial-output buffer
+    constexpr int NP = C / 16;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int MT = TT >> 4;
+    const int items = MT * NP;
+    const int nslices = 8 / items;
+    const int item = warp % items, slice = warp / items;
+    const int mt = item % MT, np = item / MT;
+    const int g = lane >> 2, q4 = lane & 3;
+
+    float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int ks = slice; ks < Kpad / 16; ks += nslices) {
+        uint32_t a[4], bf[4];
+        ldsm_x4(a, ps + (mt * 16 + (lane & 15)) * kSS + ks * 16 + (lane >> 4) * 8);
+        // B stored [k][n]: matrices (k 0-7, n 0-7), (k 8-15, n 0-7), (k 0-7, n 8-15), (k 8-15, n 8-15), transposed on load
+        ldsm_x4_t(bf, bs + (ks * 16 + (lane & 15)) * CS + np * 16 + (lane >> 4) * 8);
+        mma16816<T>(d0, a, bf[0], bf[1]);
+        mma16816<T>(d1, a, bf[2], bf[3]);
+    }
+    float *op = os + (slice * TT + mt * 16 + g) * OS + np * 16 + q4 * 2;
+    *reinterpret_cast<float2 *>(op) = make_float2(d0[0], d0[1]);
+    *reinterpret_cast<float2 *>(op + 8 * OS) = make_float2(d0[2], d0[3]);
+    *reinterpret_cast<float2 *>(op + 8) = make_float2(d1[0], d1[1]);
+    *reinterpret_cast<float2 *>(op + 8 * OS + 8) = make_float2(d1[2], d1[3]);
+    __syncthreads();
+    // 8 consecutive channels per thread -> one 16-byte store; the tile's rows are contiguous in global memory
+    for (int e = tid; e < n_valid_rows * (C / 8); e += kDT) {
+        const int row = e / (C / 8), c0 = (e - row * (C / 8)) * 8;
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        for (int s = 0; s < nslices; ++s) {
+            const float4 v0 = *reinterpret_cast<const float4 *>(os + (s * TT + row) * OS + c0);
+            const float4 v1 = *reinterpret_cast<const float4 *>(os + (s * TT + row) * OS + c0 + 4);
+            acc[0] += v0.x; acc[1] += v0.y; acc[2] += v0.z; acc[3] += v0.w;
+            acc[4] += v1.x; acc[5] += v1.y; acc[6] += v1.z; acc[7] += v1.w;
+        }
+        uint4 v;
+        v.x = pack2<T>(acc[0], acc[1]); v.y = pack2<T>(acc[2], acc[3]);
+        v.z = pack2<T>(acc[4], acc[5]); v.w = pack2<T>(acc[6], acc[7]);
+        *reinterpret_cast<uint4 *>(og + row * C + c0) = v;
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ void zero_operand(T *ps, int n_rows, int Kpad) {
+    const int chunks = Kpad / 8;  // 16-byte chunks per row
+    for (int q = threadIdx.x; q < n_rows * chunks; q += kDT) {
+        const int r = q / chunks, ch = q - r * chunks;
+        *reinterpret_cast<uint4 *>(ps + r * kSS + ch * 8) = make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+
+// =========================================================================================================
+// gather-wsum
+// =========================================================================================================
+template <typename T, int C>
+__global__ void __launch_bounds__(kDT)
+gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const int32_t *__restrict__ q_hdr,
+                         const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc, T *__restrict__ out,
+                         int H, int Nq, int Nk, int M, int TT) {
+    constexpr int CS = C + 8;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    int *rows_s = reinterpret_cast<int *>(smem_raw);
+    T *ys = reinterpret_cast<T *>(smem_raw + 1024);
+    T *ps = ys + kUMaxDense * CS;
+    float *os = reinterpret_cast<float *>(ps + TT * kSS);
+    uint8_t *loc_s = reinterpret_cast<uint8_t *>(os + os_floats<C>());
+
+    const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x;
+    const int t0 = tile * TT;
+    const int ti = min(TT, Nq - t0);
+    const int tid = threadIdx.x;
+    const int hdr = q_hdr[int64_t(b) * n_tiles + tile];
+    const int U = hdr & AFFB200_PLAN_COUNT_MASK;
+    const bool dup = (hdr & AFFB200_PLAN_DUP) != 0;
+    const int Upad = (U + 15) & ~15;
+    const int n_ent = ti * M;
+
+    const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * kUMaxDense;
+    for (int u = tid; u < Upad; u += kDT) rows_s[u] = rg[u];
+    const uint8_t *lg = q_loc + (int64_t(b) * Nq + t0) * M;
+    if ((reinterpret_cast<uintptr_t>(lg) & 15) == 0) {
+        for (int p = tid; p < (n_ent + 15) / 16; p += kDT)
+            reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(reinterpret_cast<const uint4 *>(lg) + p);
+    } else {
+        for (int p = tid; p < n_ent; p += kDT) loc_s[p] = lg[p];
+    }
+    __syncthreads();
+
+    for (int h = 0; h < H; ++h) {
+        const int64_t z = int64_t(b) * H + h;
+        stage_rows<T, C>(ys, y + z * Nk * C, Upad, [&](int i) { return rows_s[i]; });
+        cp_async_commit();
+        zero_operand<T>(ps, TT, Upad);
+        __syncthreads();
+        const T *wg = w + (z * Nq + t0) * M;
+        if (!dup) {
+            if (M % 8 == 0 && (reinterpret_cast<uintptr_t>(wg) & 15) == 0) {
+                for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {
+                    const int p = p8 * 8;
+                    const uint4 wv = __ldg(reinterpret_cast<const uint4 *>(wg + p));
+                    const uint2 lc = *reinterpret_cast<const uint2 *>(loc_s + p);
+                    const uint16_t *e = reinterpret_cast<const uint16_t *>(&wv);
+                    const uint8_t *l8 = reinterpret_cast<const uint8_t *>(&lc);
+                    uint16_t *prow = reinterpret_cast<uint16_t *>(ps + (p / M) * kSS);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) prow[l8[k]] = e[k];
+                }
+            } else {
+                for (int p = tid; p < n_ent; p += kDT) ps[(p / M) * kSS + loc_s[p]] = wg[p];
+            }
+        } else if (tid < ti) {
+            // a token lists a row more than once: accumulate that token's operand row in slot order
+            T *prow = ps + tid * kSS;
+            for (int j = 0; j < M; ++j) {
+                const int l = loc_s[tid * M + j];
+                prow[l] = Elem<T>::from_acc(Elem<T>::to_acc(prow[l]) + Elem<T>::to_acc(wg[tid * M + j]));
+            }
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        wsum_mma_store<T, C>(ps, ys, os, out + (z * Nq + t0) * C, TT, Upad, ti);
+        __syncthreads();
+    }
+}
+
+// =========================================================================================================
+// scatter-wsum over key tiles: dY[r0 + r, :] = sum_{u, j : rloc[u][j] == r} w[utok[u], j] * x[utok[u], :]
+// =========================================================================================================
+template <typename T, int C>
+__global__ void __launch_bounds__(kDT)
+scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, const int32_t *__restrict__ k_hdr,
+                          const int32_t *__restrict__ k_utok, const uint8_t *__restrict__ k_rloc,
+                          T *__restrict__ dy, int H, int Nq, int Nk, int M, int TT) {
+    constexpr int CS = C + 8;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    int *tok_s = reinterpret_cast<int *>(smem_raw);
+    T *xs = reinterpret_cast<T *>(smem_raw + 1024);
+    T *ps = xs + kUMaxDense * CS;
+    float *os = reinterpret_cast<float *>(ps + TT * kSS);
+
+    const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x;
+    const int r0 = tile * TT;
+    const int ri = min(TT, Nk - r0);
+    const int tid = threadIdx.x;
+    const int64_t tix = int64_t(b) * n_tiles + tile;
+    const int hdr = k_hdr[tix];
+    const int Uq = hdr & AFFB200_PLAN_COUNT_MASK;
+    const bool dup = (hdr & AFFB200_PLAN_DUP) != 0;
+    const int Upad = (Uq + 15) & ~15;
+    const int n_ent = Uq * M;
+
+    const int32_t *ug = k_utok + tix * kUMaxDense;
+    for (int u = tid; u < Upad; u += kDT) tok_s[u] = ug[u];
+    __syncthreads();
+    const uint8_t *rl = k_rloc + tix * int64_t(kUMaxDense) * M;
+
+    for (int h = 0; h < H; ++h) {
+        const int64_t z = int64_t(b) * H + h;
+        stage_rows<T, C>(xs, x + z * Nq * C, Upad, [&](int i) { return tok_s[i]; });
+        cp_async_commit();
+        zero_operand<T>(ps, TT, Upad);
+        __syncthreads();
+        const T *wz = w + z * Nq * M;
+        if (!dup) {
+            if (M % 8 == 0 && (reinterpret_cast<uintptr_t>(wz) & 15) == 0 && (reinterpret_cast<uintptr_t>(rl) & 7) == 0) {
+                for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {
+                    const int p = p8 * 8;
+                    const int u = p / M, j = p - u * M;
+                    const uint2 lc = __ldg(reinterpret_cast<const uint2 *>(rl + p));
+                    if (lc.x == 0xffffffffu && lc.y == 0xffffffffu) continue;
+                    const uint4 wv = __ldg(reinterpret_cast<const uint4 *>(wz + int64_t(tok_s[u]) * M + j));
+                    const uint16_t *e = reinterpret_cast<const uint16_t *>(&wv);
+                    const uint8_t *l8 = reinterpret_cast<const uint8_t *>(&lc);
+                    uint16_t *pcol = reinterpret_cast<uint16_t *>(ps) + u;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                        if (l8[k] != 0xFF) pcol[l8[k] * kSS] = e[k];
+                }
+            } else {
+                for (int p = tid; p < n_ent; p += kDT) {
+                    const int r = rl[p];
+                    if (r != 0xFF) {
+                        const int u = p / M;
+                        ps[r * kSS + u] = wz[int64_t(tok_s[u]) * M + (p - u * M)];
+                    }
+                }
+            }
+        } else if (tid < Uq) {
+            const T *wr = wz + int64_t(tok_s[tid]) * M;
+            for (int j = 0; j < M; ++j) {
+                const int r = rl[tid * M + j];
+                if (r != 0xFF) {
+                    T *pe = ps + r * kSS + tid;
+                    *pe = Elem<T>::from_acc(Elem<T>::to_acc(*pe) + Elem<T>::to_acc(wr[j]));
+                }
+            }
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        wsum_mma_store<T, C>(ps, xs, os, dy + (z * Nk + r0) * C, TT, Upad, ri);
+        __syncthreads();
+    }
+}
+
+// =========================================================================================================
+// launchers
+// =========================================================================================================
+static size_t smem_gather_dot(int C, int T, int M) {
+    return 1024 + size_t(kUMaxDense) * (C + 8) * 2 + size_t(T) * kSS * 2 + size_t(T) * (C + 8) * 2 +
+           ((size_t(T) * M + 15) & ~size_t(15));
+}
+static size_t smem_gather_wsum(int C, int T, int M) {
+    return 1024 + size_t(kUMaxDense) * (C + 8) * 2 + size_t(T) * kSS * 2 + size_t(8 * 16 * 16 * (C + 8) / C) * 4 +
+           ((size_t(T) * M + 15) & ~size_t(15));
+}
+static size_t smem_scatter_wsum(int C, int T) {
+    return 1024 + size_t(kUMaxDense) * (C + 8) * 2 + size_t(T) * kSS * 2 + size_t(8 * 16 * 16 * (C + 8) / C) * 4;
+}
+
+template <typename K> static int set_smem(K kern, size_t smem) {
+    if (smem > 48 * 1024 &&
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)) != cudaSuccess)
+        return check_launch("cudaFuncSetAttribute");
+    return AFFB200_OK;
+}
+
+template <typename T>
+int launch_gather_dot_dense(const T *x, const T *y, const affb200_nbhd_plan *pl, T *out, int64_t B, int64_t H,
+                            int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
+    const int TT = pl->tq;
+    dim3 grid(unsigned((Nq + TT - 1) / TT), unsigned(B));
+    const size_t smem = smem_gather_dot(int(c), TT, int(M));
+#define AFF_L(C_)                                                                                               \
+    do {                                                                                                        \
+        auto kern = gather_dot_dense_kernel<T, C_>;                                                             \
+        if (int e = set_smem(kern, smem)) return e;                                                             \
+        kern<<<grid, kDT, smem, st>>>(x, y, pl->q_hdr, pl->q_rows, pl->q_loc, out, int(H), int(Nq), int(Nk),    \
+                                      int(M), TT);                                                              \
+    } while (0)
+    if (c == 32) AFF_L(32); else AFF_L(16);
+#undef AFF_L
+    return check_launch("gather_dot_dense");
+}
+
+template <typename T>
+int launch_gather_wsum_dense(const T *w, const T *y, const affb200_nbhd_plan *pl, T *out, int64_t B, int64_t H,
+                             int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
+    const int TT = pl->tq;
+    dim3 grid(unsigned((Nq + TT - 1) / TT), unsigned(B));
+    const size_t smem = smem_gather_wsum(int(c), TT, int(M));
+#define AFF_L(C_)                                                                                               \
+    do {                                                                                                        \
+        auto kern = gather_wsum_dense_kernel<T, C_>;                                                            \
+        if (int e = set_smem(kern, smem)) return e;                                                             \
+        kern<<<grid, kDT, smem, st>>>(w, y, pl->q_hdr, pl->q_rows, pl->q_loc, out, int(H), int(Nq), int(Nk),    \
+                                      int(M), TT);                                                              \
+    } while (0)
+    if (c == 32) AFF_L(32); else AFF_L(16);
+#undef AFF_L
+    return check_launch("gather_wsum_dense");
+}
+
+template <typename T>
+int launch_scatter_wsum_dense(const T *w, const T *x, const affb200_nbhd_plan *pl, T *dy, int64_t B, int64_t H,
+                              int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
+    const int TT = pl->tk;
+    dim3 grid(unsigned((Nk + TT - 1) / TT), unsigned(B));
+    const size_t smem = smem_scatter_wsum(int(c), TT);
+#define AFF_L(C_)                                                                                               \
+    do {                                                                                                        \
+        auto kern = scatter_wsum_dense_kernel<T, C_>;                                                           \
+        if (int e = set_smem(kern, smem)) return e;                                                             \
+        kern<<<grid, kDT, smem, st>>>(w, x, pl->k_hdr, pl->k_utok, pl->k_rloc, dy, int(H), int(Nq), int(Nk),    \
+                                      int(M), TT);                                                              \
+    } while (0)
+    if (c == 32) AFF_L(32); else AFF_L(16);
+#undef AFF_L
+    return check_launch("scatter_wsum_dense");
+}
+
+#define AFF_INST(T)                                                                                                 \
+    template int launch_gather_dot_dense<T>(const T *, const T *, const affb200_nbhd_plan *, T *, int64_t, int64_t,   \
+                                            int64_t, int64_t, int64_t, int64_t, cudaStream_t);                        \
+    template int launch_gather_wsum_dense<T>(const T *, const T *, const affb200_nbhd_plan *, T *, int64_t, int64_t,  \
+                                             int64_t, int64_t, int64_t, int64_t, cudaStream_t);                       \
+    template int launch_scatter_wsum_dense<T>(const T *, const T *, const affb200_nbhd_plan *, T *, int64_t, int64_t, \
+                                              int64_t, int64_t, int64_t, int64_t, cudaStream_t);
+AFF_INST(__half)
+AFF_INST(__nv_bfloat16)
+#undef AFF_INST
+
+}  // namespace affb200

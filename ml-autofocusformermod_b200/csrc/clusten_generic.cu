@@ -507,62 +507,114 @@ using namespace affb200;
         }                                              \
     } while (0)
 
-extern "C" int affb200_qk_fwd(const void *q, const void *k, const int64_t *idx, void *attn, int64_t B, int64_t H,
-                              int64_t Nq, int64_t Nk, int64_t M, int64_t c, int dtype, void *stream) {
+template <typename T> struct IsDenseType { static constexpr bool value = false; };
+template <> struct IsDenseType<__half> { static constexpr bool value = true; };
+template <> struct IsDenseType<__nv_bfloat16> { static constexpr bool value = true; };
+
+static bool dense_shape_ok(int64_t M, int64_t c, const void *a, const void *b, const void *o) {
+    return (c == 16 || c == 32) && M >= 1 && M <= AFFB200_PLAN_MAX_M && aligned16(a) && aligned16(b) && aligned16(o);
+}
+static bool has_qplan(const affb200_nbhd_plan *p) { return p && p->tq > 0 && p->q_hdr && p->q_rows && p->q_loc; }
+static bool has_kplan(const affb200_nbhd_plan *p) { return p && p->tk > 0 && p->k_hdr && p->k_utok && p->k_rloc; }
+static bool has_csr(const affb200_nbhd_plan *p) { return p && p->csr_off && p->csr_ent; }
+
+// out[z,i,j] = sum_c x[z,i,c]*y[z,idx,c]
+template <typename T>
+static int run_gather_dot(const T *x, const T *y, const int64_t *idx, const affb200_nbhd_plan *plan, T *out,
+                          int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
+    if constexpr (IsDenseType<T>::value) {
+        if (has_qplan(plan) && dense_shape_ok(M, c, x, y, out) && B * H * Nq > 0)
+            return launch_gather_dot_dense<T>(x, y, plan, out, B, H, Nq, Nk, M, c, st);
+    }
+    return launch_gather_dot<T>(x, y, idx, out, B, H, Nq, Nk, M, c, st);
+}
+// out[z,i,c] = sum_j w[z,i,j]*y[z,idx,c]
+template <typename T>
+static int run_gather_wsum(const T *w, const T *y, const int64_t *idx, const affb200_nbhd_plan *plan, T *out,
+                           int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
+    if constexpr (IsDenseType<T>::value) {
+        if (has_qplan(plan) && dense_shape_ok(M, c, w, y, out) && B * H * Nq > 0)
+            return launch_gather_wsum_dense<T>(w, y, plan, out, B, H, Nq, Nk, M, c, st);
+    }
+    return launch_gather_wsum<T>(w, y, idx, out, B, H, Nq, Nk, M, c, st);
+}
+// dy[z,r,c] = sum_{(i,j)->r} w[z,i,j]*x[z,i,c]
+template <typename T>
+static int run_scatter_wsum(const char *op, const T *w, const T *x, const affb200_nbhd_plan *plan, T *dy, int64_t B,
+                            int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
+    if constexpr (IsDenseType<T>::value) {
+        if (has_kplan(plan) && dense_shape_ok(M, c, w, x, dy) && B * H * Nk > 0 && Nq > 0)
+            return launch_scatter_wsum_dense<T>(w, x, plan, dy, B, H, Nq, Nk, M, c, st);
+    }
+    if (!has_csr(plan) && B * Nq * M > 0) {
+        set_error("%s: the plan holds neither a usable key-tile plan nor the transposed index (csr_off/csr_ent)", op);
+        return AFFB200_E_ARG;
+    }
+    return launch_csr_wsum<T>(w, x, plan ? plan->csr_off : nullptr, plan ? plan->csr_ent : nullptr, dy, B, H, Nq, Nk,
+                              M, c, st);
+}
+
+extern "C" int affb200_qk_fwd(const void *q, const void *k, const int64_t *idx, const affb200_nbhd_plan *plan,
+                              void *attn, int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c,
+                              int dtype, void *stream) {
     if (int e = check_dims("qk_fwd", B, H, Nq, Nk, M, c)) return e;
-    AFF_REQUIRE(B * H * Nq * M == 0 || (q && k && idx && attn), "null pointer");
+    AFF_REQUIRE(B * H * Nq * M == 0 || (attn && idx && (c == 0 || (q && k))), "null pointer");
     return dispatch_dtype(dtype, [&](auto tag) {
         using T = decltype(tag);
-        return launch_gather_dot<T>((const T *)q, (const T *)k, idx, (T *)attn, B, H, Nq, Nk, M, c,
-                                    (cudaStream_t)stream);
+        return run_gather_dot<T>((const T *)q, (const T *)k, idx, plan, (T *)attn, B, H, Nq, Nk, M, c,
+                                 (cudaStream_t)stream);
     });
 }
 
 extern "C" int affb200_qk_bwd(const void *d_attn, const void *q, const void *k, const int64_t *idx,
-                              const int32_t *csr_off, const int32_t *csr_ent, void *d_q, void *d_k, int64_t B,
+                              const affb200_nbhd_plan *plan, void *d_q, void *d_k, int64_t B,
                               int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c, int dtype, void *stream) {
     if (int e = check_dims("qk_bwd", B, H, Nq, Nk, M, c)) return e;
-    AFF_REQUIRE(B * H * Nq * M * c == 0 || (d_attn && q && k && idx && d_q && d_k), "null pointer");
-    AFF_REQUIRE(B * Nq * M == 0 || (csr_off && csr_ent), "transposed index (csr_off/csr_ent) is required");
+    AFF_REQUIRE(B * H * Nq * M * c == 0 || (d_attn && q && k && idx), "null pointer");
+    AFF_REQUIRE(B * H * Nq * c == 0 || d_q, "null pointer");
+    AFF_REQUIRE(B * H * Nk * c == 0 || d_k, "null pointer");
     return dispatch_dtype(dtype, [&](auto tag) {
         using T = decltype(tag);
         auto st = (cudaStream_t)stream;
-        if (int e = launch_gather_wsum<T>((const T *)d_attn, (const T *)k, idx, (T *)d_q, B, H, Nq, Nk, M, c, st))
+        if (int e = run_gather_wsum<T>((const T *)d_attn, (const T *)k, idx, plan, (T *)d_q, B, H, Nq, Nk, M, c, st))
             return e;
-        return launch_csr_wsum<T>((const T *)d_attn, (const T *)q, csr_off, csr_ent, (T *)d_k, B, H, Nq, Nk, M, c, st);
+        return run_scatter_wsum<T>("qk_bwd", (const T *)d_attn, (const T *)q, plan, (T *)d_k, B, H, Nq, Nk, M, c, st);
     });
 }
 
-extern "C" int affb200_av_fwd(const void *attn, const void *v, const int64_t *idx, void *out, int64_t B, int64_t H,
-                              int64_t Nq, int64_t Nk, int64_t M, int64_t c, int dtype, void *stream) {
+extern "C" int affb200_av_fwd(const void *attn, const void *v, const int64_t *idx, const affb200_nbhd_plan *plan,
+                              void *out, int64_t B, int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c,
+                              int dtype, void *stream) {
     if (int e = check_dims("av_fwd", B, H, Nq, Nk, M, c)) return e;
-    AFF_REQUIRE(B * H * Nq * c == 0 || (attn && v && idx && out), "null pointer");
+    AFF_REQUIRE(B * H * Nq * c == 0 || (out && (M == 0 || (attn && v && idx))), "null pointer");
     return dispatch_dtype(dtype, [&](auto tag) {
         using T = decltype(tag);
-        return launch_gather_wsum<T>((const T *)attn, (const T *)v, idx, (T *)out, B, H, Nq, Nk, M, c,
-                                     (cudaStream_t)stream);
+        return run_gather_wsum<T>((const T *)attn, (const T *)v, idx, plan, (T *)out, B, H, Nq, Nk, M, c,
+                                  (cudaStream_t)stream);
     });
 }
 
 extern "C" int affb200_av_bwd(const void *d_out, const void *attn, const void *v, const int64_t *idx,
-                              const int32_t *csr_off, const int32_t *csr_ent, void *d_attn, void *d_v, int64_t B,
+                              const affb200_nbhd_plan *plan, void *d_attn, void *d_v, int64_t B,
                               int64_t H, int64_t Nq, int64_t Nk, int64_t M, int64_t c, int dtype, void *stream) {
     if (int e = check_dims("av_bwd", B, H, Nq, Nk, M, c)) return e;
-    AFF_REQUIRE(B * H * Nq * M * c == 0 || (d_out && attn && v && idx && d_attn && d_v), "null pointer");
-    AFF_REQUIRE(B * Nq * M == 0 || (csr_off && csr_ent), "transposed index (csr_off/csr_ent) is required");
+    AFF_REQUIRE(B * H * Nq * M * c == 0 || (d_out && attn && v && idx && d_attn), "null pointer");
+    AFF_REQUIRE(B * H * Nk * c == 0 || d_v, "null pointer");
     return dispatch_dtype(dtype, [&](auto tag) {
         using T = decltype(tag);
         auto st = (cudaStream_t)stream;
-        if (int e = launch_gather_dot<T>((const T *)d_out, (const T *)v, idx, (T *)d_attn, B, H, Nq, Nk, M, c, st))
+        if (int e = run_gather_dot<T>((const T *)d_out, (const T *)v, idx, plan, (T *)d_attn, B, H, Nq, Nk, M, c, st))
             return e;
-        return launch_csr_wsum<T>((const T *)attn, (const T *)d_out, csr_off, csr_ent, (T *)d_v, B, H, Nq, Nk, M, c, st);
+        return run_scatter_wsum<T>("av_bwd", (const T *)attn, (const T *)d_out, plan, (T *)d_v, B, H, Nq, Nk, M, c, st);
     });
 }
 
-extern "C" int affb200_wf_fwd(const void *w, const void *f, const int64_t *idx, void *out, int64_t B, int64_t Nq,
-                              int64_t Nk, int64_t M, int64_t IC, int64_t C, int dtype, void *stream) {
+extern "C" int affb200_wf_fwd(const void *w, const void *f, const int64_t *idx, const affb200_nbhd_plan *plan,
+                              void *out, int64_t B, int64_t Nq, int64_t Nk, int64_t M, int64_t IC, int64_t C,
+                              int dtype, void *stream) {
+    (void)plan;
     if (int e = check_dims("wf_fwd", B, IC, Nq, Nk, M, C)) return e;
-    AFF_REQUIRE(B * Nq * IC * C == 0 || (w && f && idx && out), "null pointer");
+    AFF_REQUIRE(B * Nq * IC * C == 0 || (out && (M == 0 || (w && f && idx))), "null pointer");
     return dispatch_dtype(dtype, [&](auto tag) {
         using T = decltype(tag);
         return launch_wf_fwd<T>((const T *)w, (const T *)f, idx, (T *)out, B, Nq, Nk, M, IC, C, (cudaStream_t)stream);
@@ -570,16 +622,18 @@ extern "C" int affb200_wf_fwd(const void *w, const void *f, const int64_t *idx, 
 }
 
 extern "C" int affb200_wf_bwd(const void *d_out, const void *w, const void *f, const int64_t *idx,
-                              const int32_t *csr_off, const int32_t *csr_ent, void *d_w, void *d_f, int64_t B,
+                              const affb200_nbhd_plan *plan, void *d_w, void *d_f, int64_t B,
                               int64_t Nq, int64_t Nk, int64_t M, int64_t IC, int64_t C, int dtype, void *stream) {
     if (int e = check_dims("wf_bwd", B, IC, Nq, Nk, M, C)) return e;
-    AFF_REQUIRE(B * Nq * M * IC * C == 0 || (d_out && w && f && idx && d_w && d_f), "null pointer");
-    AFF_REQUIRE(B * Nq * M == 0 || (csr_off && csr_ent), "transposed index (csr_off/csr_ent) is required");
+    AFF_REQUIRE(B * Nq * M * IC * C == 0 || (d_out && w && f && idx && d_w), "null pointer");
+    AFF_REQUIRE(B * Nk * C == 0 || d_f, "null pointer");
+    AFF_REQUIRE(B * Nq * M == 0 || has_csr(plan), "transposed index (csr_off/csr_ent) is required");
     return dispatch_dtype(dtype, [&](auto tag) {
         using T = decltype(tag);
         auto st = (cudaStream_t)stream;
         if (int e = launch_wf_bwd_w<T>((const T *)d_out, (const T *)f, idx, (T *)d_w, B, Nq, Nk, M, IC, C, st))
             return e;
-        return launch_wf_bwd_f<T>((const T *)d_out, (const T *)w, csr_off, csr_ent, (T *)d_f, B, Nq, Nk, M, IC, C, st);
+        return launch_wf_bwd_f<T>((const T *)d_out, (const T *)w, plan ? plan->csr_off : nullptr,
+                                  plan ? plan->csr_ent : nullptr, (T *)d_f, B, Nq, Nk, M, IC, C, st);
     });
 }

@@ -17,6 +17,7 @@ void set_error(const char *fmt, ...);
 int check_launch(const char *what);
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+constexpr int kUMaxDense = AFFB200_PLAN_UMAX;
 
 // ---- element traits: storage type T, accumulator type, 16-byte vector width ------------------------------
 template <typename T> struct Elem;
@@ -114,5 +115,16 @@ template <typename F> inline int dispatch_dtype(int dtype, F &&f) {
 }
 
 inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// dense-tile launchers (clusten_dense.cu), instantiated for __half and __nv_bfloat16
+template <typename T>
+int launch_gather_dot_dense(const T *x, const T *y, const affb200_nbhd_plan *pl, T *out, int64_t B, int64_t H,
+                            int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st);
+template <typename T>
+int launch_gather_wsum_dense(const T *w, const T *y, const affb200_nbhd_plan *pl, T *out, int64_t B, int64_t H,
+                             int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st);
+template <typename T>
+int launch_scatter_wsum_dense(const T *w, const T *x, const affb200_nbhd_plan *pl, T *dy, int64_t B, int64_t H,
+                              int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st);
 
 }  // namespace affb200

@@ -56,9 +56,33 @@ def test_argument_errors_are_reported_without_a_gpu():
     """Bad arguments are rejected before any CUDA call, with a message in affb200_last_error()."""
     ensure_built()
     from affb200 import _native as N
-    rc = N.LIB.affb200_qk_fwd(None, None, None, None, 1, 1, -1, 1, 1, 1, 0, None)
+    rc = N.LIB.affb200_qk_fwd(None, None, None, None, None, 1, 1, -1, 1, 1, 1, 0, None)
     assert rc == -1 and "negative" in N.last_error()
-    rc = N.LIB.affb200_qk_fwd(None, None, None, None, 1, 1, 4, 4, 4, 4, 0, None)
+    rc = N.LIB.affb200_qk_fwd(None, None, None, None, None, 1, 1, 4, 4, 4, 4, 0, None)
     assert rc == -1 and "null" in N.last_error()
-    rc = N.LIB.affb200_qk_fwd(None, None, None, None, 0, 1, 4, 4, 4, 4, 99, None)
+    rc = N.LIB.affb200_qk_fwd(None, None, None, None, None, 0, 1, 4, 4, 4, 4, 99, None)
     assert rc == -1 and "dtype" in N.last_error()
+    rc = N.LIB.affb200_qplan_build(None, 1, 8, 8, 4, 48, None, None, None, None, None)
+    assert rc == -1 and "unsupported dimensions" in N.last_error()
+
+
+def test_plan_struct_layout_matches_header():
+    """The ctypes mirror of affb200_nbhd_plan has the header's field order and the C layout (gcc sizeof)."""
+    import subprocess
+    import tempfile
+    from affb200 import _native as N
+    fields = [f[0] for f in N.NbhdPlanStruct._fields_]
+    src = open(HEADER).read()
+    body = src[src.index("typedef struct {"):src.index("} affb200_nbhd_plan;")]
+    order = re.findall(r"\b(\w+);", re.sub(r"/\*.*?\*/", "", body, flags=re.S))
+    assert order == fields
+    with tempfile.TemporaryDirectory() as d:
+        c = os.path.join(d, "s.c")
+        open(c, "w").write('#include <stdio.h>\n#include "affb200.h"\nint main(){printf("%zu %zu %zu",'
+                           'sizeof(affb200_nbhd_plan),__builtin_offsetof(affb200_nbhd_plan,q_hdr),'
+                           '__builtin_offsetof(affb200_nbhd_plan,k_rloc));return 0;}')
+        exe = os.path.join(d, "s")
+        subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe], check=True)
+        size, o1, o2 = map(int, subprocess.run([exe], capture_output=True, text=True).stdout.split())
+    assert size == ctypes.sizeof(N.NbhdPlanStruct)
+    assert o1 == N.NbhdPlanStruct.q_hdr.offset and o2 == N.NbhdPlanStruct.k_rloc.offset

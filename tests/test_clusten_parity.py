@@ -72,6 +72,58 @@ def test_reference_test_shape_mean_loss(op):
     check(op, dims, torch.bfloat16, seed=8, oracle_device="cuda")
 
 
+DENSE_CASES = [
+    # (B, H, Nq, Nk, M, c, m) — local-attention stage shapes of BASELINE configs 2-5 at reduced batch
+    (4, 2, 3136, 3136, 48, 32, 8),    # AFF-Tiny stage 1
+    (4, 2, 3136, 3136, 48, 16, 8),    # AFF-Mini stage 1 (head dim 16)
+    (8, 4, 627, 627, 48, 32, 8),      # AFF-Tiny-1/5 stage 2: N % 8 != 0 -> padded last cluster, duplicate row 0
+    (40, 8, 125, 125, 48, 32, 8),     # stage 3
+    (2, 4, 2304, 2304, 144, 32, 24),  # AFF-Base 384 stage 2 (nbhd 144)
+    (1, 2, 30720, 30720, 48, 32, 8),  # maskfiner j=3 (largest token count)
+    (3, 2, 100, 333, 40, 32, 8),      # Nq != Nk, partial last tile
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("op", ["qk", "av"])
+def test_dense_tile_path_on_clustered_indices(op, dtype):
+    """Clustered neighbourhoods (the model's regime) take the dense-tile tensor-core kernels: the tile plans must
+    build without overflow, and outputs/gradients must match the fp64 oracle within the bf16/fp16 tolerance."""
+    from tests.util import clustered_idx
+    from affb200.plan import get_plan
+    for s, (B, H, Nq, Nk, M, c, m) in enumerate(DENSE_CASES):
+        a, b, _, go = make_inputs(op, (B, H, Nq, Nk, M, c), dtype, 40 + s, device="cuda")
+        idx = clustered_idx(B, Nq, Nk, M, m, 50 + s).cuda()
+        out, ga, gb = run_ours(op, a, b, idx, go)
+        st = get_plan(idx).stats
+        assert st["q"]["overflow"] == 0 and st["k"]["overflow"] == 0, st
+        if Nk % m:
+            assert st["q"]["dup_tiles"] > 0  # padded slots all point at row 0
+        ro, rga, rgb = run_oracle(op, a, b, idx, go, "cuda")
+        assert_close(out, ro, dtype, "%s fwd %s" % (op, DENSE_CASES[s]))
+        assert_close(ga, rga, dtype, "%s grad_a %s" % (op, DENSE_CASES[s]))
+        assert_close(gb, rgb, dtype, "%s grad_b %s" % (op, DENSE_CASES[s]))
+
+
+def test_dense_and_generic_paths_agree():
+    """Same bf16 inputs through the dense-tile kernels and through the generic row-gather kernels (fp32 math on
+    the same rounded operands): both round an fp32 sum once, so they agree to ~1 ulp of bf16."""
+    from tests.util import clustered_idx
+    from affb200 import _native as N
+    from affb200.plan import get_plan
+    B, H, Nn, M, c = 4, 2, 784, 48, 32
+    q, k, _, _ = make_inputs("qk", (B, H, Nn, Nn, M, c), torch.bfloat16, 77, device="cuda")
+    idx = clustered_idx(B, Nn, Nn, M, 8, 78).cuda()
+    o1, o2 = torch.empty(B, H, Nn, M, device="cuda", dtype=torch.bfloat16), torch.empty(B, H, Nn, M, device="cuda", dtype=torch.bfloat16)
+    pl = get_plan(idx)
+    A = (B, H, Nn, Nn, M, c, N.dtype_enum(q), N.stream_ptr(q.device))
+    N.check(N.LIB.affb200_qk_fwd(N.p(q), N.p(k), N.p(idx), pl.struct(idx, Nn, True, False), N.p(o1), *A), "dense")
+    N.check(N.LIB.affb200_qk_fwd(N.p(q), N.p(k), N.p(idx), None, N.p(o2), *A), "generic")
+    assert pl.stats["q"]["overflow"] == 0
+    assert rel_err(o1, o2) < 4e-3
+    assert (o1 == o2).float().mean() > 0.9
+
+
 RAGGED = {
     "qk": [(1, 1, 1, 1, 1, 1), (3, 2, 17, 5, 7, 3), (2, 3, 33, 70, 13, 8), (1, 5, 64, 64, 48, 24),
            (2, 1, 100, 9, 144, 32), (1, 2, 40, 40, 50, 20), (2, 2, 9, 300, 6, 128), (1, 16, 25, 25, 25, 32)],

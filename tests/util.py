@@ -46,3 +46,24 @@ def make_inputs(op, dims, dtype, seed, device="cpu", idx_mode="uniform"):
         idx = torch.zeros((B, Nq, M), dtype=torch.int64)
     go = torch.randn(out_shape, generator=g)
     return a.to(dtype).to(device), b.to(dtype).to(device), idx.to(device), go.to(dtype).to(device)
+
+
+def clustered_idx(B, Nq, Nk, M, m, seed, pad_to_zero=True):
+    """Block-structured neighbourhoods like the model builds (reference aff_transformer.py:476-480):
+    nbhd_idx[b,i,q*m+r] = cluster[b,i,q]*m + r for M//m clusters near the token's own position, with a per-batch
+    random choice among nearby clusters; rows >= Nk (padded last cluster) become 0 as in point_utils.py:204."""
+    g = torch.Generator().manual_seed(seed)
+    nnc = max(1, M // m)
+    k = (Nk + m - 1) // m
+    own = (torch.arange(Nq) * Nk // max(Nq, 1)) // m
+    jitter = torch.randint(-2, 3, (B, Nq, 1), generator=g)
+    base = own[None, :, None] + jitter
+    # nnc distinct clusters around base: a random subset of a window of nnc+3 clusters
+    win = nnc + 3
+    perm = torch.rand(B, Nq, win, generator=g).argsort(-1)[..., :nnc]
+    cl = (base + perm - win // 2).clamp_(0, k - 1)
+    idx = (cl[..., None] * m + torch.arange(m)).reshape(B, Nq, nnc * m)
+    if idx.shape[-1] < M:
+        idx = torch.cat([idx, idx[..., : M - idx.shape[-1]]], -1)
+    idx = torch.where(idx >= Nk, torch.zeros_like(idx) if pad_to_zero else idx.clamp(max=Nk - 1), idx)
+    return idx.contiguous()

@@ -62,6 +62,7 @@ def make_idx(B, Nq, Nk, M, mode, dev, m=8):
 
 
 _flush = None
+NO_DENSE = False
 
 
 def flush_l2():
@@ -99,19 +100,22 @@ def bench_qkav(name, S, dtype, mode, iters):
     idx = make_idx(B, Nn, Nn, M, mode, dev, m=8 if M % 8 == 0 and M != 144 else 24)
     o_attn, o_feat = torch.empty_like(attn), torch.empty_like(q)
     d_q, d_k = torch.empty_like(q), torch.empty_like(k)
-    off, ent = get_plan(idx).csr(idx, Nn)
+    pl = get_plan(idx)
+    dense = dtype in (torch.float16, torch.bfloat16) and c in (16, 32) and not NO_DENSE
+    pf, pb = pl.struct(idx, Nn, dense, False), pl.struct(idx, Nn, dense, True)
+    print(json.dumps(dict(shape=name, idx=mode, plan=pl.stats)), flush=True)
     st = N.stream_ptr(dev)
     de = N.dtype_enum(q)
     A = (B, H, Nn, Nn, M, c, de, st)
     ops = {
-        "qk_fwd": (lambda: N.check(N.LIB.affb200_qk_fwd(N.p(q), N.p(k), N.p(idx), N.p(o_attn), *A), "qk"),
+        "qk_fwd": (lambda: N.check(N.LIB.affb200_qk_fwd(N.p(q), N.p(k), N.p(idx), pf, N.p(o_attn), *A), "qk"),
                    s * (2 * B * H * Nn * c + B * H * Nn * M) + 8 * B * Nn * M),
-        "qk_bwd": (lambda: N.check(N.LIB.affb200_qk_bwd(N.p(attn), N.p(q), N.p(k), N.p(idx), N.p(off), N.p(ent),
+        "qk_bwd": (lambda: N.check(N.LIB.affb200_qk_bwd(N.p(attn), N.p(q), N.p(k), N.p(idx), pb,
                                                          N.p(d_q), N.p(d_k), *A), "qkb"),
                    s * (B * H * Nn * M + 4 * B * H * Nn * c) + 8 * B * Nn * M),
-        "av_fwd": (lambda: N.check(N.LIB.affb200_av_fwd(N.p(attn), N.p(k), N.p(idx), N.p(o_feat), *A), "av"),
+        "av_fwd": (lambda: N.check(N.LIB.affb200_av_fwd(N.p(attn), N.p(k), N.p(idx), pf, N.p(o_feat), *A), "av"),
                    s * (B * H * Nn * M + 2 * B * H * Nn * c) + 8 * B * Nn * M),
-        "av_bwd": (lambda: N.check(N.LIB.affb200_av_bwd(N.p(q), N.p(attn), N.p(k), N.p(idx), N.p(off), N.p(ent),
+        "av_bwd": (lambda: N.check(N.LIB.affb200_av_bwd(N.p(q), N.p(attn), N.p(k), N.p(idx), pb,
                                                          N.p(o_attn), N.p(d_k), *A), "avb"),
                    s * (2 * B * H * Nn * M + 4 * B * H * Nn * c) + 8 * B * Nn * M),
     }
@@ -128,13 +132,13 @@ def bench_wf(name, S, dtype, mode, iters):
     out = torch.empty(B, Nq, IC, C, device=dev, dtype=dtype)
     go = torch.randn_like(out)
     d_w, d_f = torch.empty_like(w), torch.empty_like(f)
-    off, ent = get_plan(idx).csr(idx, Nk)
+    pb = get_plan(idx).struct(idx, Nk, False, True)
     st = N.stream_ptr(dev)
     A = (B, Nq, Nk, M, IC, C, N.dtype_enum(w), st)
     ops = {
-        "wf_fwd": (lambda: N.check(N.LIB.affb200_wf_fwd(N.p(w), N.p(f), N.p(idx), N.p(out), *A), "wf"),
+        "wf_fwd": (lambda: N.check(N.LIB.affb200_wf_fwd(N.p(w), N.p(f), N.p(idx), None, N.p(out), *A), "wf"),
                    s * (B * Nq * M * IC + B * Nk * C + B * Nq * IC * C) + 8 * B * Nq * M),
-        "wf_bwd": (lambda: N.check(N.LIB.affb200_wf_bwd(N.p(go), N.p(w), N.p(f), N.p(idx), N.p(off), N.p(ent),
+        "wf_bwd": (lambda: N.check(N.LIB.affb200_wf_bwd(N.p(go), N.p(w), N.p(f), N.p(idx), pb,
                                                          N.p(d_w), N.p(d_f), *A), "wfb"),
                    s * (B * Nq * IC * C + 2 * B * Nq * M * IC + 2 * B * Nk * C) + 8 * B * Nq * M),
     }
@@ -163,7 +167,10 @@ def main():
     ap.add_argument("--idx", default="S,U")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", default="")
+    ap.add_argument("--no-dense", action="store_true", help="force the generic (row-gather) kernels")
     a = ap.parse_args()
+    global NO_DENSE
+    NO_DENSE = a.no_dense
     rows = []
     for dt in a.dtype.split(","):
         for mode in a.idx.split(","):
