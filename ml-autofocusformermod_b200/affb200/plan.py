@@ -14,6 +14,7 @@ Plans are looked up by tensor identity and die with the tensor (weakref), and ar
 rows): a plan with overflowed tiles is discarded and the generic kernels are used for that tensor.
 """
 import ctypes
+import os
 import threading
 import weakref
 
@@ -30,6 +31,9 @@ NUM_SMS = 148
 def pick_tile(B, n, M):
     """Tokens per tile: 64 when that still gives >= 4 CTAs per SM-wave and the neighbourhood is small enough for
     the union of a tile to stay under 256 rows; smaller tiles for small problems and wide neighbourhoods."""
+    forced = os.environ.get("AFFB200_TILE")
+    if forced:
+        return int(forced)
     t = 64 if M <= 64 else (32 if M <= 96 else 16)
     while t > 16 and B * ((n + t - 1) // t) < 4 * NUM_SMS:
         t //= 2

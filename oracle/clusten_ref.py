@@ -36,7 +36,7 @@ def wf_ref(weights, feat, nbhd_idx):
     """feat_new[b,i,ic,c] = sum_j weights[b,i,j,ic] * feat[b,nbhd_idx[b,i,j],c]"""
     b, n_, m, ic = weights.shape
     c = feat.shape[-1]
-    feat_gather = feat.gather(index=nbhd_idx.reshape(b, -1, 1).expand(-1, -1, c), dim=1).reshape(b, n_, m, c)
+    feat_gather = feat.gather(index=nbhd_idx.reshape(b, n_ * m, 1).expand(-1, -1, c), dim=1).reshape(b, n_, m, c)
     return weights.transpose(-1, -2) @ feat_gather
 
 

@@ -56,10 +56,10 @@ def clustered_idx(B, Nq, Nk, M, m, seed, pad_to_zero=True):
     nnc = max(1, M // m)
     k = (Nk + m - 1) // m
     own = (torch.arange(Nq) * Nk // max(Nq, 1)) // m
-    jitter = torch.randint(-2, 3, (B, Nq, 1), generator=g)
+    jitter = torch.randint(-1, 2, (B, Nq, 1), generator=g)
     base = own[None, :, None] + jitter
-    # nnc distinct clusters around base: a random subset of a window of nnc+3 clusters
-    win = nnc + 3
+    # nnc distinct clusters around base: a random subset of a window of nnc+1 clusters
+    win = nnc + 1
     perm = torch.rand(B, Nq, win, generator=g).argsort(-1)[..., :nnc]
     cl = (base + perm - win // 2).clamp_(0, k - 1)
     idx = (cl[..., None] * m + torch.arange(m)).reshape(B, Nq, nnc * m)

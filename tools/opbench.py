@@ -63,6 +63,7 @@ def make_idx(B, Nq, Nk, M, mode, dev, m=8):
 
 _flush = None
 NO_DENSE = False
+WARM = 5
 
 
 def flush_l2():
@@ -150,7 +151,7 @@ def run_ops(name, ops, dtype, mode, iters, S):
     rows = []
     for op, (fn, nbytes) in ops.items():
         flush = nbytes < (512 << 20)
-        med, best = time_call(fn, iters, 5, flush)
+        med, best = time_call(fn, iters, WARM, flush)
         gbs = nbytes / (med * 1e-3) / 1e9
         row = dict(shape=name, op=op, dtype=str(dtype).replace("torch.", ""), idx=mode, ms=round(med, 4),
                    ms_best=round(best, 4), alg_MB=round(nbytes / 1e6, 2), GBps=round(gbs, 1),
@@ -167,10 +168,12 @@ def main():
     ap.add_argument("--idx", default="S,U")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", default="")
+    ap.add_argument("--warm", type=int, default=5)
     ap.add_argument("--no-dense", action="store_true", help="force the generic (row-gather) kernels")
     a = ap.parse_args()
-    global NO_DENSE
+    global NO_DENSE, WARM
     NO_DENSE = a.no_dense
+    WARM = a.warm
     rows = []
     for dt in a.dtype.split(","):
         for mode in a.idx.split(","):
