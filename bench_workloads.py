@@ -1,0 +1,167 @@
+"""Workloads of bench.py.  Each workload offers
+    build(B, device, world) -> run   with  run.make_host_batch(i) / run.to_device(host) / run.step(dev) -> loss
+                                           run.roofline(peak, src) -> dict
+    cpu_reference(sample_b) -> callable   (oracle port on the host cores; the only oracle use besides tests/smoke)
+    config(B, world), metric, unit, dtype_name, default_batch
+"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+# AFF-Tiny-1/5 (reference configs/aff_tiny_1_5th.yaml:6-13): local-attention stages (N, C, heads, depth) and the
+# three merges N -> N' = int(N*0.2) (aff_transformer.py:292).  Stage 4 (25 tokens) is global/dense attention.
+TINY15_STAGES = [(3136, 64, 2, 3), (627, 128, 4, 4), (125, 256, 8, 18)]
+TINY15_MERGES = [(627, 3136, 64), (125, 627, 128), (25, 125, 256)]
+NBHD, CLUSTER, INNER = 48, 8, 4
+
+
+def block_structured_idx(B, Nq, Nk, M, m, device, seed):
+    """Neighbourhoods of the model's form (aff_transformer.py:480): nnc = M/m nearest clusters x m consecutive rows;
+    cluster choice jittered per token; rows >= Nk (padded last cluster) -> 0 (point_utils.py:204)."""
+    g = torch.Generator().manual_seed(seed)
+    nnc = M // m
+    k = (Nk + m - 1) // m
+    own = (torch.arange(Nq) * Nk // max(Nq, 1)) // m
+    win = nnc + 2
+    perm = torch.rand(B, Nq, win, generator=g).argsort(-1)[..., :nnc]
+    cl = (own[None, :, None] + perm - win // 2).clamp_(0, k - 1)
+    idx = (cl[..., None] * m + torch.arange(m)).reshape(B, Nq, M)
+    idx = torch.where(idx >= Nk, torch.zeros_like(idx), idx)
+    return idx.contiguous().to(device)
+
+
+class ClustenChain:
+    """v0 workload: every CLUSTEN call of one AFF-Tiny-1/5 forward+backward (25 blocks of QK -> softmax -> AV, and
+    the three WF merges) at the model's shapes, driven through the autograd.Function surface.  The linears, MLPs and
+    index builders of the full model are not part of this workload."""
+    metric = "AFF-Tiny-1/5 224x224 off-grid attention path (CLUSTEN QK/AV/WF fwd+bwd) img/s"
+    unit = "img/s"
+    dtype_name = "bf16"
+    default_batch = 256
+
+    def config(self, B, world):
+        return {"workload": "clusten_chain_aff_tiny_1_5th_224", "batch_per_gpu": B, "global_batch": B * world,
+                "stages": TINY15_STAGES, "merges": TINY15_MERGES, "nbhd": NBHD, "cluster_size": CLUSTER,
+                "parallelism": "dp%d" % world, "l2": "inputs larger than L2 (stage-1 working set 0.67 GB)",
+                "idx": "block-structured synthetic neighbourhoods (int64)"}
+
+    def build(self, B, device, world):
+        return _ChainRun(B, device, torch.bfloat16)
+
+    def cpu_reference(self, sample_b):
+        from oracle import clusten_ref as R  # the checker, timed here as the CPU baseline only
+        run = _ChainRun(sample_b, torch.device("cpu"), torch.float32, fns=(R.qk_ref, R.av_ref, R.wf_ref))
+        host = run.make_host_batch(0)
+
+        def go():
+            run.step(host)
+        return go
+
+
+class _ChainRun:
+    def __init__(self, B, device, dtype, fns=None):
+        self.B, self.device, self.dtype = B, device, dtype
+        if fns is None:
+            from clusten import CLUSTENQKFunction, CLUSTENAVFunction, CLUSTENWFFunction
+            fns = (CLUSTENQKFunction.apply, CLUSTENAVFunction.apply, CLUSTENWFFunction.apply)
+        self.qk, self.av, self.wf = fns
+        self.idx = [block_structured_idx(B, n, n, NBHD, CLUSTER, device, 10 + s)
+                    for s, (n, _, _, _) in enumerate(TINY15_STAGES)]
+        self.idx_m = [block_structured_idx(B, nq, nk, NBHD, CLUSTER, device, 20 + s)
+                      for s, (nq, nk, _) in enumerate(TINY15_MERGES)]
+        g = torch.Generator().manual_seed(5)
+        self.w = [torch.randn(B, nq, NBHD, INNER, generator=g).to(dtype).to(device).requires_grad_(True)
+                  for (nq, _, _) in TINY15_MERGES]
+
+    def make_host_batch(self, i):
+        g = torch.Generator().manual_seed(100 + i)
+        ts = [torch.randn(self.B, n, c, generator=g).to(self.dtype) for (n, c, _, _) in TINY15_STAGES]
+        return [t.pin_memory() if self.device.type == "cuda" else t for t in ts]
+
+    def to_device(self, host):
+        return [t.to(self.device, non_blocking=True) for t in host]
+
+    def step(self, feats):
+        loss = None
+        for s, (n, c, h, depth) in enumerate(TINY15_STAGES):
+            x = feats[s].detach().requires_grad_(True)
+            kv = x.view(self.B, n, h, c // h).permute(0, 2, 1, 3)
+            q = kv * (c // h) ** -0.5
+            for _ in range(depth):
+                attn = self.qk(q, kv, self.idx[s]).float().softmax(-1).to(self.dtype)
+                q = q + self.av(attn, kv, self.idx[s])
+            merged = self.wf(self.w[s], x, self.idx_m[s])
+            l = q.float().square().mean() + merged.float().square().mean()
+            loss = l if loss is None else loss + l
+        loss.backward()
+        return loss
+
+    def roofline(self, peak, peak_src):
+        """Per-op CUDA-event times at every stage shape (through the C ABI, on the current stream); the headline
+        entry is the op with the largest share of the step (time x calls per step).  Algorithmic bytes are
+        SURVEY.md §8(d)'s: every API-visible input read once + output written once, nbhd_idx at 8 B/element."""
+        return clusten_roofline(self.B, self.device, self.dtype, self.idx, peak, peak_src)
+
+
+def _time_op(fn, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def clusten_roofline(B, device, dtype, idx_list, peak, peak_src):
+    from affb200 import _native as N
+    from affb200.plan import get_plan
+    s = torch.empty((), dtype=dtype).element_size()
+    rows = []
+    for st, (n, c_full, h, depth) in enumerate(TINY15_STAGES):
+        c, M = c_full // h, NBHD
+        idx = idx_list[st]
+        q = torch.randn(B, h, n, c, device=device).to(dtype)
+        k = torch.randn(B, h, n, c, device=device).to(dtype)
+        attn = torch.softmax(torch.randn(B, h, n, M, device=device), -1).to(dtype)
+        o_attn, o_feat, d_q, d_k = torch.empty_like(attn), torch.empty_like(q), torch.empty_like(q), torch.empty_like(k)
+        pl = get_plan(idx)
+        dense = dtype in (torch.float16, torch.bfloat16) and c in (16, 32)
+        pf, pb = pl.struct(idx, n, dense, False), pl.struct(idx, n, dense, True)
+        A = (B, h, n, n, M, c, N.dtype_enum(q), N.stream_ptr(device))
+        P = N.p
+        ops = {
+            "qk_fwd": (lambda: N.LIB.affb200_qk_fwd(P(q), P(k), P(idx), pf, P(o_attn), *A),
+                       s * (2 * B * h * n * c + B * h * n * M) + 8 * B * n * M),
+            "qk_bwd": (lambda: N.LIB.affb200_qk_bwd(P(attn), P(q), P(k), P(idx), pb, P(d_q), P(d_k), *A),
+                       s * (B * h * n * M + 4 * B * h * n * c) + 8 * B * n * M),
+            "av_fwd": (lambda: N.LIB.affb200_av_fwd(P(attn), P(k), P(idx), pf, P(o_feat), *A),
+                       s * (B * h * n * M + 2 * B * h * n * c) + 8 * B * n * M),
+            "av_bwd": (lambda: N.LIB.affb200_av_bwd(P(q), P(attn), P(k), P(idx), pb, P(o_attn), P(d_k), *A),
+                       s * (2 * B * h * n * M + 4 * B * h * n * c) + 8 * B * n * M),
+        }
+        for name, (fn, nbytes) in ops.items():
+            ms = _time_op(fn)
+            rows.append({"kernel": "%s@stage%d" % (name, st + 1), "ms": ms, "calls_per_step": depth,
+                         "bytes": nbytes, "GBps": nbytes / ms / 1e6})
+        del q, k, attn, o_attn, o_feat, d_q, d_k
+    top = max(rows, key=lambda r: r["ms"] * r["calls_per_step"])
+    return {"bound": "hbm", "kernel": top["kernel"], "achieved": top["GBps"], "peak": peak, "unit": "GB/s",
+            "frac": top["GBps"] / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": top["bytes"], "avg_launch_ms": top["ms"],
+            "all": [{"kernel": r["kernel"], "ms": round(r["ms"], 4), "GBps": round(r["GBps"], 1),
+                     "frac": round(r["GBps"] / peak, 3), "calls_per_step": r["calls_per_step"]} for r in rows]}
+
+
+WORKLOADS = {"clusten_chain": ClustenChain}
+DEFAULT = "clusten_chain"
+
+
+def get(name):
+    return WORKLOADS[name or DEFAULT]()

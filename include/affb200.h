@@ -49,6 +49,8 @@ int affb200_abi_version(void);
 const char *affb200_last_error(void);
 /* Compile-time target of the kernels in this library, e.g. "sm_100a". */
 const char *affb200_target_arch(void);
+/* Number of CUDA kernels this library has enqueued in this process so far (bench.py's gpu_launches is a delta). */
+int64_t affb200_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Index plans.  nbhd_idx is constant across the 2..18 blocks of a stage (reference models/aff_transformer.py:489-495

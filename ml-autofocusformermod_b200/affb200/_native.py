@@ -35,6 +35,7 @@ SIGNATURES = {
     "affb200_abi_version": (_int, []),
     "affb200_last_error": (ctypes.c_char_p, []),
     "affb200_target_arch": (ctypes.c_char_p, []),
+    "affb200_launch_count": (_i64, []),
     "affb200_csr_off_bytes": (ctypes.c_size_t, [_i64, _i64]),
     "affb200_csr_ent_bytes": (ctypes.c_size_t, [_i64, _i64, _i64]),
     "affb200_csr_work_bytes": (ctypes.c_size_t, [_i64, _i64]),

@@ -14,7 +14,8 @@
 namespace affb200 {
 
 void set_error(const char *fmt, ...);
-int check_launch(const char *what);
+int check_launch(const char *what, int n_kernels = 1);  // also counts kernels enqueued (affb200_launch_count)
+void count_launches(int n);
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 constexpr int kUMaxDense = AFFB200_PLAN_UMAX;

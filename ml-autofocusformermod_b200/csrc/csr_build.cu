@@ -179,5 +179,5 @@ extern "C" int affb200_csr_build(const int64_t *nbhd_idx, int64_t B, int64_t Nq,
             off, ent, NqM, int(Nk), n_rows, long_count, long_rows);
         csr_sort_long_kernel<<<kNumSMs, 1024, 0, st>>>(off, ent, NqM, int(Nk), long_count, long_rows);
     }
-    return check_launch("csr_build");
+    return check_launch("csr_build", sorted ? 5 : 3);
 }
