@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define AFFB200_ABI_VERSION 2
+#define AFFB200_ABI_VERSION 3
 
 typedef enum {
     AFFB200_F32 = 0,
@@ -158,6 +158,56 @@ int affb200_wf_bwd(const void *d_out, const void *w, const void *f, const int64_
                    void *d_w, void *d_f,
                    int64_t B, int64_t Nq, int64_t Nk, int64_t M, int64_t IC, int64_t C,
                    int dtype, void *stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Index builders.  Integer outputs are bit-exact with the reference's (library ordering rules included); fp32
+ * arithmetic follows the reference's operation order without FMA contraction.  pos arrays are [B][N][2] fp32 (x, y).
+ * `work` is caller-allocated device scratch of the matching *_work_bytes() size.
+ * ---------------------------------------------------------------------------------------------------------- */
+
+/* Replaces space_filling_cluster(pos, m, h, w, no_reorder=False) in its default variant (sf_type='', use_anchor=True)
+ * (reference models/point_utils.py:61-208; call sites models/aff_transformer.py:463,470, models/mixres_neighbour.py:512).
+ *   ranking   [B][N]  int64   pos_ranking: ranking[b][r] = original index of the token of rank r (stable ascending key)
+ *   pos_sorted[B][N][2] fp32  pos gathered by ranking
+ *   mean      [B][K][2] fp32  cluster centres, K = ceil(N/m); the last cluster averages its N-(K-1)m real members
+ * member_idx / cluster_mask are pure functions of (N, m) (point_utils.py:186-189,203-206) and are formed by the
+ * caller (or implicitly by affb200_nbhd_build).  NB the key uses a maximum over the WHOLE [B][N] batch (:158). */
+size_t affb200_sfc_work_bytes(int64_t B, int64_t N);
+int affb200_sfc_cluster(const float *pos, int64_t B, int64_t N, int64_t m, int64_t h, int64_t w,
+                        int64_t *ranking, float *pos_sorted, float *mean, void *work, void *stream);
+
+/* Stable argsort of fp32 rows: order[b][r] = index of the r-th element; replaces torch.sort(...)[1] on CUDA
+ * (reference models/mixres_neighbour.py:735, models/point_utils.py:159). */
+size_t affb200_argsort_work_bytes(int64_t B, int64_t N);
+int affb200_argsort_f32(const float *x, int64_t B, int64_t N, int descending, int64_t *order, void *work,
+                        void *stream);
+
+/* Replaces knn_keops(query, database, k, return_dist) for 2-D points (reference models/point_utils.py:27-58;
+ * pykeops 2.1.1 argKmin / Kmin_argKmin): the k <= 32 smallest fp32 sqrt(dx^2+dy^2) per query, ascending, equal
+ * distances in ascending database index.  idx [B][Nq][k] int64; dist [B][Nq][k] fp32 or NULL. */
+int affb200_knn2d(const float *query, const float *database, int64_t B, int64_t Nq, int64_t Nd, int64_t k,
+                  int64_t *idx, float *dist, void *stream);
+
+/* Replaces the neighbourhood build of BasicLayer.forward (reference models/aff_transformer.py:478-487;
+ * models/mixres_neighbour.py:521-528 with clamp=1): nearest [B][N][nnc] int64 cluster ids ->
+ *   nbhd_idx [B][N][nnc*m] int64, mask [B][N][nnc*m] int64 (NULL when N % m == 0), pe_idx [B][N][nnc*m] int64. */
+int affb200_nbhd_build(const float *pos, const int64_t *nearest, int64_t B, int64_t N, int64_t m, int64_t nnc,
+                       int64_t rel_pos_width, int64_t table_width, int clamp,
+                       int64_t *nbhd_idx, int64_t *mask, int64_t *pe_idx, void *stream);
+
+/* Replaces the selection half of ClusterMerging.forward (reference models/aff_transformer.py:295-326): grid prior,
+ * final_prob = grid + alpha*lp - 100*reserve_mask, torch.topk(sample, sorted=False) in its CUDA output order, reserved
+ * tokens appended ascending.  lp [B][N] of lp_dtype (NULL: no importance term); final_prob [B][N] fp32 (out);
+ * idx_out [B][sample + (reserve_on ? reserve_num : 0)] int64; status [B] int32 (bit 0: reserved count != reserve_num,
+ * bit 1: adaptive stride 0 = duplicate positions). */
+size_t affb200_merge_select_work_bytes(int64_t B, int64_t N);
+int affb200_merge_select(const float *pos, const void *lp, int lp_dtype, int64_t B, int64_t N, int64_t stride,
+                         double alpha, int64_t sample, int64_t reserve_num, int reserve_on,
+                         float *final_prob, int64_t *idx_out, int32_t *status, void *work, void *stream);
+
+/* dst[b][k][:] = src[b][idx[b][k]][:] for int64 rows of even length M (aff_transformer.py:335-338). */
+int affb200_gather_rows_i64(const int64_t *src, const int64_t *idx, int64_t B, int64_t N, int64_t K, int64_t M,
+                            int64_t *dst, void *stream);
 
 #ifdef __cplusplus
 }

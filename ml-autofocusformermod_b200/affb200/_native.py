@@ -43,6 +43,15 @@ SIGNATURES = {
     "affb200_plan_tiles": (_i64, [_i64, _i64]),
     "affb200_qplan_build": (_int, [_ptr] + [_i64] * 5 + [_ptr] * 5),
     "affb200_kplan_build": (_int, [_ptr] + [_i64] * 5 + [_ptr] * 6),
+    "affb200_sfc_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
+    "affb200_sfc_cluster": (_int, [_ptr] + [_i64] * 5 + [_ptr] * 5),
+    "affb200_argsort_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
+    "affb200_argsort_f32": (_int, [_ptr, _i64, _i64, _int, _ptr, _ptr, _ptr]),
+    "affb200_knn2d": (_int, [_ptr, _ptr] + [_i64] * 4 + [_ptr] * 3),
+    "affb200_nbhd_build": (_int, [_ptr, _ptr] + [_i64] * 6 + [_int] + [_ptr] * 4),
+    "affb200_merge_select_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
+    "affb200_merge_select": (_int, [_ptr, _ptr, _int, _i64, _i64, _i64, ctypes.c_double, _i64, _i64, _int] + [_ptr] * 5),
+    "affb200_gather_rows_i64": (_int, [_ptr, _ptr] + [_i64] * 4 + [_ptr, _ptr]),
     "affb200_qk_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
     "affb200_qk_bwd": (_int, [_ptr] * 4 + [_plan_p] + [_ptr] * 2 + [_i64] * 6 + [_int, _ptr]),
     "affb200_av_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
@@ -68,7 +77,7 @@ def _load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.affb200_abi_version() != 2:
+    if lib.affb200_abi_version() != 3:
         raise RuntimeError("libaffb200.so ABI version mismatch")
     return lib
 

@@ -1,0 +1,157 @@
+"""Index builders of the off-grid attention path, host side (mirrors reference models/point_utils.py and the index
+code inlined in models/aff_transformer.py / models/mixres_neighbour.py).  Every function enqueues hand-written
+sm_100a kernels of libaffb200.so on the current CUDA stream (C ABI: include/affb200.h); there is no CPU path.
+
+  space_filling_cluster(pos, m, h, w, no_reorder=False)      reference point_utils.py:61-208 (default variant)
+  knn_keops(query, database, k, return_dist=False)           reference point_utils.py:27-58
+  argsort_stable(x, descending=False)                        torch.sort(...)[1] on CUDA (mixres_neighbour.py:735)
+  build_nbhd(pos, cluster_mean_pos, m, nbhd_size, rel_pos_width, clamp=False)
+                                                             reference aff_transformer.py:446-487
+  select_merge_centers(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on=True)
+                                                             reference aff_transformer.py:289-326
+  gather_rows(src, idx)                                      reference aff_transformer.py:335-338
+"""
+import math
+
+import torch
+
+from . import _native as N
+
+
+def _f32_pos(pos, name="pos"):
+    if not pos.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor" % name)
+    if pos.dim() != 3 or pos.shape[2] != 2:
+        raise RuntimeError("%s must have shape [B, N, 2]" % name)
+    pos = pos.detach()
+    if pos.dtype != torch.float32:
+        pos = pos.to(torch.float32)  # point_utils.py:87-88 / :45-48
+    return pos.contiguous()
+
+
+def _work(nbytes, dev):
+    return torch.empty(max(16, nbytes), dtype=torch.uint8, device=dev)
+
+
+def space_filling_cluster(pos, m, h, w, no_reorder=False, sf_type='', use_anchor=True):
+    """Balanced clustering along a space-filling scan of an anchor grid.  Returns, like the reference,
+    (pos_sorted b×n×2 fp32, cluster_mean_pos b×k×2 fp32, member_idx b×k×m int64, cluster_mask b×k×m int64 | None,
+    pos_ranking b×n×1 int64)."""
+    if no_reorder or sf_type != '' or not use_anchor:
+        raise NotImplementedError("only the variant the models call is implemented: no_reorder=False, sf_type='', "
+                                  "use_anchor=True (reference aff_transformer.py:463,470; mixres_neighbour.py:512)")
+    pos = _f32_pos(pos)
+    b, n, _ = pos.shape
+    dev = pos.device
+    k = int(math.ceil(n / m))
+    with torch.cuda.device(dev):
+        ranking = torch.empty((b, n), dtype=torch.int64, device=dev)
+        pos_sorted = torch.empty_like(pos)
+        mean = torch.empty((b, k, 2), dtype=torch.float32, device=dev)
+        work = _work(N.LIB.affb200_sfc_work_bytes(b, n), dev)
+        N.check(N.LIB.affb200_sfc_cluster(N.p(pos), b, n, m, h, w, N.p(ranking), N.p(pos_sorted), N.p(mean),
+                                          N.p(work), N.stream_ptr(dev)), "space_filling_cluster")
+        member_idx = torch.arange(k * m, device=dev)
+        if k * m == n:
+            cluster_mask = None
+        else:
+            member_idx[n:] = 0
+            cluster_mask = (torch.arange(k * m, device=dev) < n).long().reshape(1, k, m).expand(b, -1, -1)
+        member_idx = member_idx.reshape(1, k, m).expand(b, -1, -1)
+    return pos_sorted, mean, member_idx, cluster_mask, ranking.unsqueeze(2)
+
+
+def knn_keops(query, database, k, return_dist=False):
+    """k nearest database points per query (2-D, fp32 Euclidean distance, ascending, ties -> lowest index)."""
+    query = _f32_pos(query, "query")
+    database = _f32_pos(database, "database")
+    b, nq, _ = query.shape
+    nd = database.shape[1]
+    dev = query.device
+    with torch.cuda.device(dev):
+        idx = torch.empty((b, nq, k), dtype=torch.int64, device=dev)
+        dist = torch.empty((b, nq, k), dtype=torch.float32, device=dev) if return_dist else None
+        N.check(N.LIB.affb200_knn2d(N.p(query), N.p(database), b, nq, nd, k, N.p(idx), N.p(dist), N.stream_ptr(dev)),
+                "knn")
+    if return_dist:
+        return idx, dist
+    return idx
+
+
+def argsort_stable(x, descending=False):
+    """Stable argsort along dim 1 of a [B, N] fp32 tensor."""
+    if not x.is_cuda:
+        raise RuntimeError("x must be a CUDA tensor")
+    x = x.detach().to(torch.float32).contiguous()
+    b, n = x.shape
+    dev = x.device
+    with torch.cuda.device(dev):
+        order = torch.empty((b, n), dtype=torch.int64, device=dev)
+        work = _work(N.LIB.affb200_argsort_work_bytes(b, n), dev)
+        N.check(N.LIB.affb200_argsort_f32(N.p(x), b, n, 1 if descending else 0, N.p(order), N.p(work),
+                                          N.stream_ptr(dev)), "argsort")
+    return order
+
+
+def build_nbhd(pos, cluster_mean_pos, m, nbhd_size, rel_pos_width, clamp=False):
+    """Neighbourhood of every token = the members of its nnc nearest clusters.  pos must be in cluster order.
+    Returns (nbhd_idx b×n×M int64, cluster_mask b×n×M int64 | None, pe_idx b×n×M int64, nearest_cluster b×n×nnc)."""
+    pos = _f32_pos(pos)
+    b, n, _ = pos.shape
+    dev = pos.device
+    k = int(math.ceil(n / float(m)))
+    nnc = min(int(round(nbhd_size / float(m))), k)
+    M = m * nnc
+    nearest = knn_keops(pos, cluster_mean_pos, nnc)
+    with torch.cuda.device(dev):
+        nbhd = torch.empty((b, n, M), dtype=torch.int64, device=dev)
+        pe_idx = torch.empty((b, n, M), dtype=torch.int64, device=dev)
+        mask = torch.empty((b, n, M), dtype=torch.int64, device=dev) if k * m != n else None
+        N.check(N.LIB.affb200_nbhd_build(N.p(pos), N.p(nearest), b, n, m, nnc, rel_pos_width, 2 * rel_pos_width + 1,
+                                         1 if clamp else 0, N.p(nbhd), N.p(mask), N.p(pe_idx), N.stream_ptr(dev)),
+                "nbhd_build")
+    return nbhd, mask, pe_idx, nearest
+
+
+def select_merge_centers(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on=True, check=False):
+    """Indices of the tokens kept by adaptive downsampling, in the reference's order: the topk-sampled centres
+    (torch CUDA topk(sorted=False) order) followed by the reserved coarse-grid tokens (ascending).
+    Returns (idx b×keep int64, final_prob b×n fp32).  `check=True` synchronises and raises when the number of
+    reserved grid tokens differs from reserve_num (the reference's reshape would raise: aff_transformer.py:323)."""
+    pos = _f32_pos(pos)
+    b, n, _ = pos.shape
+    dev = pos.device
+    keep = int(n * ds_rate)
+    sample = keep - reserve_num if reserve_on else keep
+    lp = None
+    if learned_prob is not None:
+        lp = learned_prob.detach().reshape(b, n).contiguous()
+        if not lp.is_cuda:
+            raise RuntimeError("learned_prob must be a CUDA tensor")
+    with torch.cuda.device(dev):
+        idx = torch.empty((b, keep), dtype=torch.int64, device=dev)
+        final = torch.empty((b, n), dtype=torch.float32, device=dev)
+        status = torch.empty((b,), dtype=torch.int32, device=dev)
+        work = _work(N.LIB.affb200_merge_select_work_bytes(b, n), dev) if stride != 2 else None
+        N.check(N.LIB.affb200_merge_select(N.p(pos), N.p(lp), N.dtype_enum(lp) if lp is not None else 0, b, n, stride,
+                                           float(alpha), sample, reserve_num, 1 if reserve_on else 0, N.p(final),
+                                           N.p(idx), N.p(status), N.p(work), N.stream_ptr(dev)), "merge_select")
+    if check and int(status.max().item()) != 0:
+        raise RuntimeError("merge_select: reserved-token count differs from reserve_num, or duplicate positions")
+    return idx, final
+
+
+def gather_rows(src, idx):
+    """src [B, N, M] int64, idx [B, K] int64 -> [B, K, M]  (member_idx / pe_idx / mask at the merge centres)."""
+    b, n, M = src.shape
+    K = idx.shape[1]
+    if M % 2:
+        return src.gather(1, idx.unsqueeze(2).expand(-1, -1, M))
+    src = src.contiguous()
+    idx = idx.contiguous()
+    dev = src.device
+    with torch.cuda.device(dev):
+        out = torch.empty((b, K, M), dtype=torch.int64, device=dev)
+        N.check(N.LIB.affb200_gather_rows_i64(N.p(src), N.p(idx), b, n, K, M, N.p(out), N.stream_ptr(dev)),
+                "gather_rows")
+    return out
