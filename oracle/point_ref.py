@@ -110,7 +110,7 @@ def knn_ref(query, database, k, return_dist=False):
     d2 = diff[..., 0] * diff[..., 0]
     for t in range(1, diff.shape[-1]):
         d2 = d2 + diff[..., t] * diff[..., t]
-    dist = d2.sqrt()
+    dist = d2.double().sqrt().float()   # IEEE correctly rounded fp32 sqrt (torch's CPU fp32 sqrt is not: 1 ulp off)
     sd, si = dist.sort(dim=2, stable=True)
     if return_dist:
         return si[..., :k].contiguous(), sd[..., :k].contiguous()

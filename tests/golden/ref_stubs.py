@@ -35,7 +35,7 @@ class _Lazy:
         if p == 2:
             return _Lazy(self.t * self.t)
         if p == 0.5:
-            return _Lazy(self.t.sqrt())
+            return _Lazy(self.t.double().sqrt().float())  # correctly rounded, as sqrtf on the GPU
         raise NotImplementedError(p)
 
     def sum(self, dim):

@@ -36,7 +36,10 @@ def test_sfc_matches_reference_golden():
         p_s, mean, member, mask, ranking = space_filling_cluster(pos, c["m"], c["h"], c["w"])
         assert ranking.dtype == torch.int64 and ranking.shape == (pos.shape[0], pos.shape[1], 1)
         assert torch.equal(ranking.squeeze(2).cpu().to(torch.int32), c["ranking"]), name
-        assert torch.equal(mean.cpu(), c["mean"]), name
+        if c["ordering_rule_imposed"]:   # integer positions: sums are exact in fp32, centres are bit-exact
+            assert torch.equal(mean.cpu(), c["mean"]), name
+        else:                            # fractional positions: fp32 centre within 1e-5 relative (summation order)
+            assert torch.allclose(mean.cpu(), c["mean"], rtol=1e-5, atol=0), name
         assert (mask is not None) == c["has_mask"], name
         assert torch.equal(p_s, pos.gather(1, ranking.expand(-1, -1, 2))), name
 
@@ -95,7 +98,9 @@ def test_knn_matches_oracle(case):
     idx, dist = knn_keops(q.cuda(), d.cuda(), k, return_dist=True)
     ridx, rdist = O.knn_ref(q, d, k, return_dist=True)
     assert torch.equal(idx.cpu(), ridx)
-    assert torch.equal(dist.cpu(), rdist)
+    bad = (dist.cpu() != rdist)
+    assert not bad.any(), (int(bad.sum()), dist.cpu()[bad][:4].tolist(), rdist[bad][:4].tolist(),
+                           (dist.cpu()[bad][:4] ** 2).tolist())
     assert torch.equal(knn_keops(q.cuda(), d.cuda(), k).cpu(), ridx)
 
 
@@ -162,7 +167,7 @@ def test_argsort_and_gather_rows():
     g = torch.Generator().manual_seed(0)
     for (B, n) in [(2, 2048), (1, 8192), (3, 4096), (4, 77)]:
         x = torch.randn(B, n, generator=g)
-        x[:, ::7] = x[:, 1::7][:, : x[:, ::7].shape[1]]  # ties
+        x[:, 0:n - 7:7] = x[:, 1:n - 6:7]  # ties
         for desc in (False, True):
             assert torch.equal(argsort_stable(x.cuda(), desc).cpu(), x.sort(dim=1, descending=desc, stable=True)[1])
     src = torch.randint(0, 1000, (3, 50, 48), generator=g)
