@@ -1,0 +1,50 @@
+"""Operator set of the CPU oracle, shaped like affb200.aff_transformer.CudaOps.  TEST INFRASTRUCTURE (see
+oracle/__init__.py): tests and bench.py's cpu_baseline / `--impl reference` legs inject it into the host glue
+(`AutoFocusFormer(ops=OracleOps())`) to run the reference's pure-PyTorch path on the host cores."""
+import torch
+
+from . import clusten_ref as R
+from . import point_ref as P
+
+
+class OracleOps:
+    fused_attention = None
+
+    qk = staticmethod(R.qk_ref)
+    av = staticmethod(R.av_ref)
+    wf = staticmethod(R.wf_ref)
+
+    @staticmethod
+    def space_filling_cluster(pos, m, h, w, no_reorder=False):
+        assert not no_reorder
+        return P.sfc_ref(pos, m, h, w)
+
+    @staticmethod
+    def build_nbhd(pos, mean, m, nbhd_size, rel_pos_width, clamp=False):
+        return P.nbhd_ref(pos, mean, m, nbhd_size, rel_pos_width, clamp)
+
+    @staticmethod
+    def select_merge_centers(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on=True):
+        return P.select_ref(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on)
+
+    @staticmethod
+    def gather_rows(src, idx):
+        return src.gather(1, idx.unsqueeze(2).expand(-1, -1, src.shape[2]))
+
+
+def fill_parameters_by_name(model, seed=0, scale=0.25):
+    """Deterministic weights that do not depend on construction order: every parameter is drawn from a generator
+    seeded by (seed, crc32(name)).  Norm weights stay near 1.  Used by the model golden and its test on both sides."""
+    import zlib
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            g = torch.Generator().manual_seed((seed * 1000003 + zlib.crc32(name.encode())) % (2 ** 31))
+            r = torch.randn(p.shape, generator=g)
+            if p.dim() >= 2:
+                fan_in = p[0].numel()
+                v = r * (scale / fan_in ** 0.5) * 4
+            elif "norm" in name and name.endswith("weight") or name.endswith("bn.weight") or ".weight_net.1.weight" in name:
+                v = 1 + 0.1 * r
+            else:
+                v = 0.1 * r
+            p.copy_(v.to(p.dtype))

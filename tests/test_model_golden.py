@@ -1,0 +1,111 @@
+"""The host glue (affb200/aff_transformer.py) against the golden produced by the REFERENCE's own AutoFocusFormer
+(tests/golden/model_aff_small.pt, generator tests/golden/make_model_golden.py):
+  * CPU: glue + the oracle's operator set reproduces logits, gradients and every stage's index tensors;
+  * GPU: glue + the CUDA operator set (C ABI kernels) does, in fp32 (1e-5 relative on outputs, 1e-4 on gradients,
+    integer tensors bit-exact), and in bf16 autocast within 1e-2 on the logits."""
+import os
+
+import pytest
+import torch
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "model_aff_small.pt")
+
+
+def _load():
+    g = torch.load(GOLD)
+    x = torch.randn(*g["x_shape"], generator=torch.Generator().manual_seed(g["x_seed"]))
+    assert abs(x.double().sum().item() - g["x_sum"]) < 1e-6
+    return g, x
+
+
+def _run(model, x, capture, autocast=False):
+    hooks = []
+    for li, layer in enumerate(model.layers):
+        def pre(mod, args, li=li):
+            if ("stage%d" % li) not in capture:
+                capture["stage%d" % li] = {"member_idx": args[1], "cluster_mask": args[2], "pe_idx": args[3]}
+        hooks.append(layer.blocks[0].register_forward_pre_hook(pre))
+        if layer.downsample is not None:
+            def post(mod, args, out, li=li):
+                capture["merge%d_pos" % li] = out[0].detach()
+            hooks.append(layer.downsample.register_forward_hook(post))
+    x = x.clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+        logits = model(x)
+    w = torch.linspace(-1, 1, logits.numel(), device=logits.device).reshape(logits.shape)
+    (logits.float() * w).sum().backward()
+    for h in hooks:
+        h.remove()
+    return logits.detach().float().cpu(), x.grad.detach().cpu(), {k: p.grad.detach().float().cpu() for k, p in model.named_parameters()}
+
+
+def _check_index(cap, gold):
+    for k, v in gold["index"].items():
+        if isinstance(v, dict):
+            for kk, vv in v.items():
+                got = cap[k][kk]
+                assert (vv is None) == (got is None), (k, kk)
+                if vv is not None:
+                    assert got.dtype == torch.int64
+                    assert torch.equal(got.cpu().to(torch.int16), vv), (k, kk)
+        else:
+            assert torch.equal(cap[k].float().cpu(), v), k
+
+
+def rel(a, b):
+    return ((a - b).norm() / b.norm()).item()
+
+
+def test_glue_with_oracle_ops_reproduces_reference_model():
+    from affb200.aff_transformer import AutoFocusFormer
+    from oracle.aff_ops_ref import OracleOps, fill_parameters_by_name
+    g, x = _load()
+    model = AutoFocusFormer(ops=OracleOps(), **g["cfg"])
+    fill_parameters_by_name(model, seed=g["seed"])
+    model.train()
+    cap = {}
+    logits, dx, grads = _run(model, x, cap)
+    _check_index(cap, g)
+    assert rel(logits, g["logits"]) < 1e-6 and rel(dx, g["dx"]) < 1e-5
+    for k, v in g["grads"].items():
+        assert rel(grads[k], v) < 1e-5, k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fused", [False, True])
+def test_cuda_model_matches_reference_golden_fp32(fused):
+    from affb200.aff_transformer import AutoFocusFormer, CudaOps
+    from oracle.aff_ops_ref import fill_parameters_by_name
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g, x = _load()
+    ops = CudaOps()
+    if fused:
+        fa = pytest.importorskip("affb200.fused")
+        ops.fused_attention = fa.fused_cluster_attention
+    model = AutoFocusFormer(ops=ops, **g["cfg"])
+    fill_parameters_by_name(model, seed=g["seed"])
+    model.cuda().train()
+    cap = {}
+    logits, dx, grads = _run(model, x.cuda(), cap)
+    _check_index(cap, g)
+    assert rel(logits, g["logits"]) < 1e-5, rel(logits, g["logits"])
+    assert rel(dx, g["dx"]) < 1e-4
+    for k, v in g["grads"].items():
+        assert rel(grads[k], v) < 1e-4, (k, rel(grads[k], v))
+
+
+@pytest.mark.gpu
+def test_cuda_model_bf16_autocast_close_to_reference():
+    from affb200.aff_transformer import AutoFocusFormer
+    from oracle.aff_ops_ref import fill_parameters_by_name
+    g, x = _load()
+    model = AutoFocusFormer(**g["cfg"])
+    fill_parameters_by_name(model, seed=g["seed"])
+    model.cuda().train()
+    cap = {}
+    logits, dx, grads = _run(model, x.cuda(), cap, autocast=True)
+    # stage-1 indices do not depend on features; later stages depend on bf16-rounded importance scores
+    for kk, vv in g["index"]["stage0"].items():
+        assert vv is None or torch.equal(cap["stage0"][kk].cpu().to(torch.int16), vv)
+    assert rel(logits, g["logits"]) < 5e-2, rel(logits, g["logits"])
