@@ -125,8 +125,8 @@ def clusten_roofline(B, device, dtype, idx_list, peak, peak_src):
     s = torch.empty((), dtype=dtype).element_size()
     rows = []
     for st, (n, c_full, h, depth) in enumerate(TINY15_STAGES):
-        c, M = c_full // h, NBHD
         idx = idx_list[st]
+        c, M, n = c_full // h, idx.shape[2], idx.shape[1]
         q = torch.randn(B, h, n, c, device=device).to(dtype)
         k = torch.randn(B, h, n, c, device=device).to(dtype)
         attn = torch.softmax(torch.randn(B, h, n, M, device=device), -1).to(dtype)
@@ -165,3 +165,99 @@ DEFAULT = "clusten_chain"
 
 def get(name):
     return WORKLOADS[name or DEFAULT]()
+
+
+class AffTrain:
+    """The workload BASELINE.json's metric is quoted on: AFF-Tiny-1/5 224x224 forward + backward (+ AdamW step) in
+    bf16 autocast, random-init weights, synthetic images, per-GPU batch 256 (configs/aff_tiny_1_5th.yaml:17),
+    batch-sharded DDP for N > 1 (reference main.py:102)."""
+    model_name = "aff_tiny_1_5th"
+    metric = "AFF-Tiny-1/5 224x224 fwd+bwd img/s"
+    unit = "img/s"
+    dtype_name = "bf16"
+    default_batch = 256
+    img = 224
+
+    def config(self, B, world):
+        return {"workload": "%s_%d_train_step" % (self.model_name, self.img), "batch_per_gpu": B,
+                "global_batch": B * world, "parallelism": "dp%d" % world,
+                "step": "forward + cross-entropy + backward + AdamW step, bf16 autocast, drop_path as configured",
+                "l2": "activations per step (GBs) far exceed the 126 MB L2; inputs alternate between two batches",
+                "attention": os.environ.get("AFFB200_ATTN", "fused")}
+
+    def build(self, B, device, world):
+        return _AffRun(self, B, device, world)
+
+    def cpu_reference(self, sample_b):
+        from affb200.aff_transformer import build_aff
+        from oracle.aff_ops_ref import OracleOps  # the checker, timed here as the CPU baseline only
+        torch.manual_seed(0)
+        model = build_aff(self.model_name, ops=OracleOps()).train()
+        g = torch.Generator().manual_seed(1)
+        x = torch.randn(sample_b, 3, self.img, self.img, generator=g)
+        y = torch.randint(0, 1000, (sample_b,), generator=g)
+
+        def go():
+            model.zero_grad(set_to_none=True)
+            torch.nn.functional.cross_entropy(model(x), y).backward()
+        return go
+
+
+class _AffRun:
+    def __init__(self, wl, B, device, world):
+        from affb200.aff_transformer import build_aff, CudaOps
+        self.wl, self.B, self.device, self.world = wl, B, device, world
+        ops = CudaOps()
+        if os.environ.get("AFFB200_ATTN", "fused") == "fused":
+            try:
+                from affb200 import fused
+                ops.fused_attention = fused.fused_cluster_attention
+            except ImportError:
+                pass
+        self.ops = ops
+        model = build_aff(wl.model_name, ops=ops).to(device).train()
+        self.model = model
+        if world > 1:
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            model = DDP(model, device_ids=[device.index], broadcast_buffers=False, gradient_as_bucket_view=True)
+        self.net = model
+        self.opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.05, fused=True)
+
+    def make_host_batch(self, i):
+        g = torch.Generator().manual_seed(1000 + i)
+        x = torch.randn(self.B, 3, self.wl.img, self.wl.img, generator=g).pin_memory()
+        y = torch.randint(0, 1000, (self.B,), generator=g).pin_memory()
+        return [x, y]
+
+    def to_device(self, host):
+        return [t.to(self.device, non_blocking=True) for t in host]
+
+    def step(self, batch):
+        x, y = batch
+        self.opt.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            logits = self.net(x)
+        loss = torch.nn.functional.cross_entropy(logits.float(), y)
+        loss.backward()
+        self.opt.step()
+        return loss
+
+    def roofline(self, peak, peak_src):
+        """CLUSTEN kernels at this model's stage shapes with the model's own neighbourhoods (captured from a forward)."""
+        idx = []
+        hooks = [layer.blocks[0].register_forward_pre_hook(lambda m, a: idx.append(a[1]))
+                 for layer in self.model.layers[:3]]
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            self.model(torch.randn(self.B, 3, self.wl.img, self.wl.img, device=self.device))
+        for h in hooks:
+            h.remove()
+        return clusten_roofline(self.B, self.device, torch.bfloat16, idx, peak, peak_src)
+
+
+class AffTinyTrain(AffTrain):
+    model_name = "aff_tiny"
+    metric = "AFF-Tiny 224x224 fwd+bwd img/s"
+
+
+WORKLOADS.update({"aff_tiny_1_5th": AffTrain, "aff_tiny": AffTinyTrain})
+DEFAULT = "aff_tiny_1_5th"
