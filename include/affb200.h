@@ -209,6 +209,19 @@ int affb200_merge_select(const float *pos, const void *lp, int lp_dtype, int64_t
 int affb200_gather_rows_i64(const int64_t *src, const int64_t *idx, int64_t B, int64_t N, int64_t K, int64_t M,
                             int64_t *dst, void *stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Relative-position bias of ClusterAttention (reference models/aff_transformer.py:126-137), in place on the QK output:
+ *   attn[b,h,i,j] += table[pe_idx[b,i,j]][h]  (+ -100 where mask[b,i,j] == 0; mask may be NULL)
+ * table [P][H] fp32, pe_idx / mask [B][N][M] int64, attn [B][H][N][M] of `dtype`.
+ * affb200_attn_bias_bwd: d_table[p][h] = sum of d_vals over the elements whose pe_idx is p (fp32, fully written).
+ *   channel_last = 0: d_vals is [B][H][N][M] (gradient of attn); 1: d_vals is [B][N][M][H] (gradient of the
+ *   PointConv weights gathered from weight_net's table, models/aff_transformer.py:343-349).
+ * ---------------------------------------------------------------------------------------------------------- */
+int affb200_attn_bias_add(void *attn, const float *table, const int64_t *pe_idx, const int64_t *mask,
+                          int64_t B, int64_t H, int64_t N, int64_t M, int dtype, void *stream);
+int affb200_attn_bias_bwd(const void *d_vals, const int64_t *pe_idx, int64_t B, int64_t H, int64_t N, int64_t M,
+                          int64_t P, int channel_last, float *d_table, int dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

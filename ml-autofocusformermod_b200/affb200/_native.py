@@ -52,6 +52,8 @@ SIGNATURES = {
     "affb200_merge_select_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
     "affb200_merge_select": (_int, [_ptr, _ptr, _int, _i64, _i64, _i64, ctypes.c_double, _i64, _i64, _int] + [_ptr] * 5),
     "affb200_gather_rows_i64": (_int, [_ptr, _ptr] + [_i64] * 4 + [_ptr, _ptr]),
+    "affb200_attn_bias_add": (_int, [_ptr] * 4 + [_i64] * 4 + [_int, _ptr]),
+    "affb200_attn_bias_bwd": (_int, [_ptr, _ptr] + [_i64] * 5 + [_int, _ptr, _int, _ptr]),
     "affb200_qk_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
     "affb200_qk_bwd": (_int, [_ptr] * 4 + [_plan_p] + [_ptr] * 2 + [_i64] * 6 + [_int, _ptr]),
     "affb200_av_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),

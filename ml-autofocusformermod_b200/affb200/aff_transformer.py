@@ -27,6 +27,9 @@ class CudaOps:
     def __init__(self):
         from .clusten import CLUSTENQKFunction, CLUSTENAVFunction, CLUSTENWFFunction
         from . import point_utils as P
+        from . import attn_ops as A
+        self.attn_bias_add = A.attn_bias_add
+        self.table_gather = A.table_gather
         self.qk = CLUSTENQKFunction.apply
         self.av = CLUSTENAVFunction.apply
         self.wf = CLUSTENWFFunction.apply
@@ -116,14 +119,10 @@ class ClusterAttention(nn.Module):
             return self.proj_drop(self.proj(feat))
         if global_attn:
             attn = q @ key.transpose(-1, -2)
-            mask = None
         else:
             attn = ops.qk(q, key, member_idx)                      # b h n m
-            mask = cluster_mask.reshape(b, 1, n, -1) if cluster_mask is not None else None
-        pos_embed = pe_table[pe_idx.reshape(-1)].reshape(*pe_idx.shape, h).permute(0, 3, 1, 2)
-        attn = attn + pos_embed
-        if mask is not None:
-            attn = attn + (1 - mask) * (-100)
+        # attn += pe_table[pe_idx] (+ -100 at padded slots): one in-place pass (reference :126-137)
+        attn = ops.attn_bias_add(attn, pe_table, pe_idx, None if global_attn else cluster_mask)
         blank_attn = (q * self.blank_k.reshape(1, h, 1, c_)).sum(-1, keepdim=True)
         attn = torch.cat([attn, blank_attn], dim=-1).softmax(dim=-1)
         attn = self.attn_drop(attn)
@@ -188,7 +187,7 @@ class ClusterMerging(nn.Module):
             cluster_mask = ops.gather_rows(cluster_mask, idx)
         m = member_idx.shape[-1]
         weights_table = self.weight_net(pre_table)                                       # T*T x ic
-        weights = weights_table[pe_idx.reshape(-1)].reshape(b, n_new, m, -1)
+        weights = ops.table_gather(weights_table, pe_idx)                                # b x n' x m x ic
         if learned_prob is not None:
             lp = learned_prob.gather(1, member_idx.reshape(b, -1, 1)).reshape(b, n_new, m, 1)
             if cluster_mask is not None:

@@ -1,0 +1,138 @@
+// attn_glue.cu — the relative-position bias of ClusterAttention as one in-place pass and its table gradient.
+//
+// Reference (models/aff_transformer.py:126-137): pe_table = Linear(5->H)(pre_table)  [P x H];
+//   pos_embed = pe_table.gather(pe_idx) -> [B,N,M,H] -> permute -> [B,H,N,M];  attn = attn + pos_embed;
+//   attn = attn + (1 - mask) * (-100).
+// Forward here: attn[b,h,i,j] += table[pe_idx[b,i,j], h] (+ -100 where mask == 0), in place on the QK output, one
+// read and one write of attn, pe_idx/mask read once for all heads.
+// Backward: d_attn passes through; d_table[p,h] = sum over {(b,i,j): pe_idx = p} of d_attn[b,h,i,j].  The reference
+// gets this from autograd's scatter-add / index_put (one global atomic or a sort per element).  Here each CTA keeps a
+// private fp32 copy of one head's table column in shared memory (P floats, 49 KB at 224x224), accumulates its share
+// of the (b,i,j) range with shared-memory atomics, and flushes only the entries it touched — neighbourhoods are
+// local, so a CTA touches a few hundred distinct offsets — with one global atomic each.
+#include "common.cuh"
+#include <algorithm>
+
+namespace affb200 {
+
+constexpr int kBT = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(kBT)
+attn_bias_add_kernel(T *__restrict__ attn, const float *__restrict__ table_f32, const int64_t *__restrict__ pe_idx,
+                     const int64_t *__restrict__ mask, int H, int64_t NM, int64_t total /* B*N*M */) {
+    const int64_t t = int64_t(blockIdx.x) * kBT + threadIdx.x;
+    if (t >= total) return;
+    const int64_t b = t / NM;
+    const int64_t r = t - b * NM;
+    const int64_t p = __ldg(pe_idx + t);
+    const float mterm = (mask && __ldg(mask + t) == 0) ? -100.f : 0.f;
+    for (int h = 0; h < H; ++h) {
+        T *a = attn + (b * H + h) * NM + r;
+        // same rounding sequence as the reference's two adds in the tensor dtype
+        float v = Elem<T>::to_acc(*a);
+        v = Elem<T>::to_acc(Elem<T>::from_acc(v + __ldg(table_f32 + p * H + h)));
+        if (mask) v = Elem<T>::to_acc(Elem<T>::from_acc(v + mterm));
+        *a = Elem<T>::from_acc(v);
+    }
+}
+
+// grid (chunks, H); dynamic smem: P floats + P/32 touched-bitmap words
+template <typename T>
+__global__ void __launch_bounds__(kBT)
+attn_bias_bwd_kernel(const T *__restrict__ d_attn, const int64_t *__restrict__ pe_idx, int H, int64_t NM,
+                     int64_t total, int P, int channel_last, float *__restrict__ d_table /* [P][H], pre-zeroed */) {
+    extern __shared__ float hist[];
+    uint32_t *touched = reinterpret_cast<uint32_t *>(hist + P);
+    const int nw = (P + 31) >> 5;
+    const int h = blockIdx.y;
+    for (int p = threadIdx.x; p < P; p += kBT) hist[p] = 0.f;
+    for (int w = threadIdx.x; w < nw; w += kBT) touched[w] = 0u;
+    __syncthreads();
+    const int64_t per = (total + gridDim.x - 1) / gridDim.x;
+    const int64_t t0 = int64_t(blockIdx.x) * per, t1 = min(total, t0 + per);
+    for (int64_t t = t0 + threadIdx.x; t < t1; t += kBT) {
+        const int64_t b = t / NM;
+        const int64_t r = t - b * NM;
+        const int p = int(__ldg(pe_idx + t));
+        // [B][H][N*M] (attention logits) or [B][N*M][H] (PointConv weights, aff_transformer.py:349)
+        const float g = Elem<T>::to_acc(__ldg(d_attn + (channel_last ? t * H + h : (b * H + h) * NM + r)));
+        atomicAdd(hist + p, g);
+        atomicOr(touched + (p >> 5), 1u << (p & 31));
+    }
+    __syncthreads();
+    for (int w = threadIdx.x; w < nw; w += kBT) {
+        uint32_t bits = touched[w];
+        while (bits) {
+            const int bit = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const int p = (w << 5) + bit;
+            atomicAdd(d_table + int64_t(p) * H + h, hist[p]);
+        }
+    }
+}
+
+// fallback for tables that do not fit in shared memory (MixRes: 1023^2 entries): direct global atomics
+template <typename T>
+__global__ void __launch_bounds__(kBT)
+attn_bias_bwd_global_kernel(const T *__restrict__ d_attn, const int64_t *__restrict__ pe_idx, int H, int64_t NM,
+                            int64_t total, int channel_last, float *__restrict__ d_table) {
+    const int64_t t = int64_t(blockIdx.x) * kBT + threadIdx.x;
+    if (t >= total) return;
+    const int64_t b = t / NM;
+    const int64_t r = t - b * NM;
+    const int64_t p = __ldg(pe_idx + t);
+    for (int h = 0; h < H; ++h)
+        atomicAdd(d_table + p * H + h,
+                  Elem<T>::to_acc(__ldg(d_attn + (channel_last ? t * H + h : (b * H + h) * NM + r))));
+}
+
+}  // namespace affb200
+
+using namespace affb200;
+
+extern "C" int affb200_attn_bias_add(void *attn, const float *table, const int64_t *pe_idx, const int64_t *mask,
+                                     int64_t B, int64_t H, int64_t N, int64_t M, int dtype, void *stream) {
+    if (B < 0 || H < 0 || N < 0 || M < 0 || H >= (1 << 16)) { set_error("attn_bias_add: bad dimensions"); return AFFB200_E_ARG; }
+    const int64_t total = B * N * M;
+    if (total * H == 0) return AFFB200_OK;
+    if (!attn || !table || !pe_idx) { set_error("attn_bias_add: null pointer"); return AFFB200_E_ARG; }
+    return dispatch_dtype(dtype, [&](auto tag) {
+        using T = decltype(tag);
+        attn_bias_add_kernel<T><<<unsigned((total + kBT - 1) / kBT), kBT, 0, (cudaStream_t)stream>>>(
+            (T *)attn, table, pe_idx, mask, int(H), N * M, total);
+        return check_launch("attn_bias_add");
+    });
+}
+
+extern "C" int affb200_attn_bias_bwd(const void *d_attn, const int64_t *pe_idx, int64_t B, int64_t H, int64_t N,
+                                     int64_t M, int64_t P, int channel_last, float *d_table, int dtype, void *stream) {
+    if (B < 0 || H < 0 || N < 0 || M < 0 || P < 0 || H >= 65536 || P >= (int64_t(1) << 31)) {
+        set_error("attn_bias_bwd: bad dimensions");
+        return AFFB200_E_ARG;
+    }
+    auto st = (cudaStream_t)stream;
+    if (P * H == 0) return AFFB200_OK;
+    if (!d_table) { set_error("attn_bias_bwd: null pointer"); return AFFB200_E_ARG; }
+    if (cudaMemsetAsync(d_table, 0, size_t(P * H) * 4, st) != cudaSuccess) return check_launch("attn_bias_bwd memset", 0);
+    const int64_t total = B * N * M;
+    if (total == 0) return AFFB200_OK;
+    if (!d_attn || !pe_idx) { set_error("attn_bias_bwd: null pointer"); return AFFB200_E_ARG; }
+    const size_t smem = size_t(P) * 4 + size_t((P + 31) / 32) * 4;
+    return dispatch_dtype(dtype, [&](auto tag) {
+        using T = decltype(tag);
+        if (smem <= 200 * 1024) {
+            auto kern = attn_bias_bwd_kernel<T>;
+            if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+            const int per_sm = smem > 100 * 1024 ? 1 : 2;
+            int chunks = int(std::max<int64_t>(1, (int64_t(kNumSMs) * per_sm) / H));
+            chunks = int(std::min<int64_t>(chunks, (total + 4095) / 4096));
+            kern<<<dim3(unsigned(chunks), unsigned(H)), kBT, smem, st>>>((const T *)d_attn, pe_idx, int(H), N * M,
+                                                                         total, int(P), channel_last, d_table);
+        } else {
+            attn_bias_bwd_global_kernel<T><<<unsigned((total + kBT - 1) / kBT), kBT, 0, st>>>(
+                (const T *)d_attn, pe_idx, int(H), N * M, total, channel_last, d_table);
+        }
+        return check_launch("attn_bias_bwd");
+    });
+}

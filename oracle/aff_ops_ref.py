@@ -28,6 +28,22 @@ class OracleOps:
         return P.select_ref(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on)
 
     @staticmethod
+    def attn_bias_add(attn, pe_table, pe_idx, mask=None):
+        """reference aff_transformer.py:131-137"""
+        h = attn.shape[1]
+        pos_embed = pe_table.gather(index=pe_idx.reshape(-1, 1).expand(-1, h), dim=0).reshape(*pe_idx.shape, h)
+        attn = attn + pos_embed.permute(0, 3, 1, 2)
+        if mask is not None:
+            attn = attn + (1 - mask.reshape(mask.shape[0], 1, mask.shape[1], -1)) * (-100)
+        return attn
+
+    @staticmethod
+    def table_gather(table, pe_idx):
+        """reference aff_transformer.py:347-349"""
+        ic = table.shape[-1]
+        return table.gather(index=pe_idx.reshape(-1, 1).expand(-1, ic), dim=0).reshape(*pe_idx.shape, ic)
+
+    @staticmethod
     def gather_rows(src, idx):
         return src.gather(1, idx.unsqueeze(2).expand(-1, -1, src.shape[2]))
 
