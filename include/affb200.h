@@ -75,8 +75,8 @@ int64_t affb200_launch_count(void);
  *       k_hdr [B][ceil(Nk/T)]            int32: Uq = number of distinct query tokens referencing the tile (+ flags)
  *       k_utok[B][ceil(Nk/T)][256]       int32: those tokens ascending, padded with -1 to a multiple of 16
  *       k_rloc[B][ceil(Nk/T)][256][M]    uint8: nbhd_idx[b,utok[u],j] - t*T, or 0xFF when outside the tile
- *     stats[4] int32 (caller-zeroed): {query tiles overflowed, query tiles with DUP, key tiles overflowed, key tiles
- *     with DUP}.  A plan with an overflow count > 0 must not be passed to the operators (use the generic path).
+ *     stats[8] int32 (caller-zeroed): {query tiles overflowed, query tiles with DUP, key tiles overflowed, key tiles
+ *     with DUP, max U over query tiles, max Uq over key tiles, 0, 0}.  A plan with an overflow count > 0 must not be passed to the operators (use the generic path).
  * ---------------------------------------------------------------------------------------------------------- */
 #define AFFB200_PLAN_UMAX 256
 #define AFFB200_PLAN_MAX_NK 131072
@@ -221,6 +221,38 @@ int affb200_attn_bias_add(void *attn, const float *table, const int64_t *pe_idx,
                           int64_t B, int64_t H, int64_t N, int64_t M, int dtype, void *stream);
 int affb200_attn_bias_bwd(const void *d_vals, const int64_t *pe_idx, int64_t B, int64_t H, int64_t N, int64_t M,
                           int64_t P, int channel_last, float *d_table, int dtype, void *stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Fused neighbourhood attention: everything between the q/kv Linears and the output projection of ClusterAttention
+ * (reference models/aff_transformer.py:103-156) in one kernel (f16/bf16, head dim 16 or 32):
+ *   S[i,j] = scale*q_i.k_nbhd[i,j] + table[pe_idx[i,j]][h] + (mask ? 0 : -100);  S[i,M] = scale*q_i.blank_k[h]
+ *   P = softmax_{M+1}(S);  out_i = sum_j P[i,j] v_nbhd[i,j] + P[i,M] blank_v[h]
+ * Operands are strided [B][N][H][c] views of the Linear outputs (element (b,i,h,0) at p + b*sB + i*sN + h*sH, the c
+ * elements contiguous, every row 16-byte aligned), so q = Linear(feat) viewed [B,N,H,c], k/v = the two halves of
+ * Linear(feat) viewed [B,N,H,2,c], out [B,N,H*c].  table [P][H] fp32, blank_k/blank_v [H][c] fp32, lse [B][H][N] fp32.
+ * plan: query-tile plan of nbhd_idx (and key-tile plan for the backward); q_pe: affb200_fused_attn_pack_pe output
+ * (pe_idx | masked<<15, needs P <= 32768; `bad` counts out-of-range indices); umax = max distinct rows per tile <= 255.
+ * Backward writes dq/dk/dv (strided views, fully overwritten), d_table [P][H] fp32 and per-tile partial sums of the
+ * blank-token gradients blank_part [B][ceil(N/tq)][H][2][c] fp32 (sum over the first two axes -> d blank_k, d blank_v);
+ * ds_work / p_work: scratch [B][H][N][M] of `dtype`.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct {
+    const void *p;
+    int64_t sB, sN, sH;
+} affb200_view;
+
+int affb200_fused_attn_pack_pe(const int64_t *pe_idx, const int64_t *mask, int64_t total, uint16_t *out, int32_t *bad,
+                               void *stream);
+int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view *k, const affb200_view *v, const affb200_view *out,
+                           const float *table, const float *blank_k, const float *blank_v,
+                           const affb200_nbhd_plan *plan, const uint16_t *q_pe, int32_t umax, float *lse,
+                           int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype, void *stream);
+int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const affb200_view *v, const affb200_view *out,
+                           const affb200_view *dout, const affb200_view *dq, const affb200_view *dk,
+                           const affb200_view *dv, const float *table, const float *blank_k, const float *blank_v,
+                           const affb200_nbhd_plan *plan, const uint16_t *q_pe, int32_t umax, const float *lse,
+                           void *ds_work, void *p_work, float *blank_part, float *d_table, int64_t P,
+                           int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype, void *stream);
 
 #ifdef __cplusplus
 }

@@ -54,6 +54,11 @@ SIGNATURES = {
     "affb200_gather_rows_i64": (_int, [_ptr, _ptr] + [_i64] * 4 + [_ptr, _ptr]),
     "affb200_attn_bias_add": (_int, [_ptr] * 4 + [_i64] * 4 + [_int, _ptr]),
     "affb200_attn_bias_bwd": (_int, [_ptr, _ptr] + [_i64] * 5 + [_int, _ptr, _int, _ptr]),
+    "affb200_fused_attn_pack_pe": (_int, [_ptr, _ptr, _i64, _ptr, _ptr, _ptr]),
+    "affb200_fused_attn_fwd": (_int, [_ptr] * 4 + [_ptr] * 3 + [_plan_p, _ptr, ctypes.c_int32, _ptr] + [_i64] * 5
+                               + [ctypes.c_float, _int, _ptr]),
+    "affb200_fused_attn_bwd": (_int, [_ptr] * 8 + [_ptr] * 3 + [_plan_p, _ptr, ctypes.c_int32, _ptr] + [_ptr] * 4
+                               + [_i64] * 6 + [ctypes.c_float, _int, _ptr]),
     "affb200_qk_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
     "affb200_qk_bwd": (_int, [_ptr] * 4 + [_plan_p] + [_ptr] * 2 + [_i64] * 6 + [_int, _ptr]),
     "affb200_av_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),

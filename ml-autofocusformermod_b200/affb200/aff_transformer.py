@@ -105,18 +105,17 @@ class ClusterAttention(nn.Module):
         b, n, c = feat.shape
         h = self.num_heads
         c_ = c // h
-        q = self.q(feat) * self.scale
+        q_lin = self.q(feat)
         kv = self.kv(feat)
         pe_table = self.pos_embed(pre_table)                       # T*T x h
-        q = q.reshape(b, n, h, c_).permute(0, 2, 1, 3)             # b h n c_
+        if not global_attn and ops.fused_attention is not None and self.attn_drop.p == 0.:
+            out = ops.fused_attention(q_lin, kv, h, self.scale, member_idx, pe_idx, cluster_mask, pe_table,
+                                      self.blank_k, self.blank_v)   # b n c, or None when unsupported
+            if out is not None:
+                return self.proj_drop(self.proj(out))
+        q = (q_lin * self.scale).reshape(b, n, h, c_).permute(0, 2, 1, 3)   # b h n c_
         kv = kv.view(b, n, h, 2, c_).permute(3, 0, 2, 1, 4)        # 2 b h n c_
         key, v = kv[0], kv[1]
-        use_fused = (not global_attn and ops.fused_attention is not None and self.attn_drop.p == 0.)
-        if use_fused:
-            out = ops.fused_attention(q, key, v, member_idx, pe_idx, cluster_mask, pe_table,
-                                      self.blank_k.view(h, c_), self.blank_v.view(h, c_))   # b h n c_
-            feat = out.permute(0, 2, 1, 3).reshape(b, n, c)
-            return self.proj_drop(self.proj(feat))
         if global_attn:
             attn = q @ key.transpose(-1, -2)
         else:

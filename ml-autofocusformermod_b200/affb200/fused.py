@@ -1,0 +1,135 @@
+"""Fused neighbourhood attention (csrc/fused_attn.cu): the whole of ClusterAttention between the q/kv Linears and the
+output projection (reference models/aff_transformer.py:103-156) as one autograd.Function.
+
+    out = fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, pe_table,
+                                  blank_k, blank_v)            # -> [B, N, H*c], or None when the case is unsupported
+
+q_lin [B,N,H*c] and kv_lin [B,N,2*H*c] are the Linear outputs themselves (kv laid out [H][2][c] per token as in
+`kv.view(b, n, h, 2, c_)`, aff_transformer.py:115); no permuted copies are made in either direction.  Supported:
+f16/bf16 activations, head dim 16 or 32, bias table of at most 32768 rows, neighbourhoods whose tiles reference at
+most 255 distinct rows (any clustered index tensor).  Everything else returns None and the caller uses the unfused
+operators.
+"""
+import ctypes
+
+import torch
+from torch.autograd import Function
+
+from . import _native as N
+from .plan import get_plan
+
+
+class _View(ctypes.Structure):
+    _fields_ = [("p", ctypes.c_void_p), ("sB", ctypes.c_int64), ("sN", ctypes.c_int64), ("sH", ctypes.c_int64)]
+
+
+def _view(t, sB, sN, sH, offset_elems=0):
+    return ctypes.byref(_View(t.data_ptr() + offset_elems * t.element_size(), sB, sN, sH))
+
+
+def _packed_pe(plan, pe_idx, mask):
+    """uint16 bias indices (pe | masked << 15), built once per (pe_idx, mask) pair and cached on the plan."""
+    key = (id(pe_idx), pe_idx._version, None if mask is None else id(mask))
+    hit = plan._pe.get(key) if hasattr(plan, "_pe") else None
+    if hit is not None and hit[0]() is pe_idx:
+        return hit[1]
+    import weakref
+    dev = pe_idx.device
+    pe_c = pe_idx.contiguous()
+    mask_c = mask.contiguous() if mask is not None else None
+    with torch.cuda.device(dev):
+        out = torch.empty(pe_c.shape, dtype=torch.int16, device=dev)
+        bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        N.check(N.LIB.affb200_fused_attn_pack_pe(N.p(pe_c), N.p(mask_c), pe_c.numel(), N.p(out), N.p(bad),
+                                                 N.stream_ptr(dev)), "pack_pe")
+        res = out if int(bad.item()) == 0 else None
+    if not hasattr(plan, "_pe"):
+        plan._pe = {}
+    plan._pe.clear()
+    plan._pe[key] = (weakref.ref(pe_idx), res)
+    return res
+
+
+class FusedClusterAttention(Function):
+    @staticmethod
+    def forward(ctx, q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe, meta):
+        H, scale, umax = meta
+        B, n, hc = q_lin.shape
+        c = hc // H
+        M = nbhd_idx.shape[2]
+        dev = q_lin.device
+        q_lin = q_lin.contiguous()
+        kv_lin = kv_lin.contiguous()
+        table = pe_table.detach().float().contiguous()
+        bk = blank_k.detach().float().contiguous()
+        bv = blank_v.detach().float().contiguous()
+        plan = get_plan(nbhd_idx)
+        with torch.cuda.device(dev):
+            out = torch.empty_like(q_lin)
+            lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+            st = plan.struct(nbhd_idx, n, True, False)
+            N.check(N.LIB.affb200_fused_attn_fwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), N.p(table), N.p(bk), N.p(bv), st,
+                N.p(q_pe), umax, N.p(lse), B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)),
+                "fused_attn_fwd")
+        ctx.save_for_backward(q_lin, kv_lin, out, lse, table, bk, bv, nbhd_idx, q_pe)
+        ctx.meta = (H, scale, umax, pe_table.dtype, blank_k.dtype, pe_table.shape[0])
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        q_lin, kv_lin, out, lse, table, bk, bv, nbhd_idx, q_pe = ctx.saved_tensors
+        H, scale, umax, table_dt, blank_dt, P = ctx.meta
+        B, n, hc = q_lin.shape
+        c = hc // H
+        M = nbhd_idx.shape[2]
+        dev = q_lin.device
+        d_out = d_out.contiguous()
+        if d_out.dtype != q_lin.dtype:
+            d_out = d_out.to(q_lin.dtype)
+        plan = get_plan(nbhd_idx)
+        with torch.cuda.device(dev):
+            st = plan.struct(nbhd_idx, n, True, True)
+            T = plan.stats["q"]["T"]
+            nt = (n + T - 1) // T
+            dq = torch.empty_like(q_lin)
+            dkv = torch.empty_like(kv_lin)
+            ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+            pw = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+            blank_part = torch.empty((B, nt, H, 2, c), dtype=torch.float32, device=dev)
+            d_table = torch.empty((P, H), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_fused_attn_bwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
+                _view(dq, n * hc, hc, c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c, c),
+                N.p(table), N.p(bk), N.p(bv), st, N.p(q_pe), umax, N.p(lse), N.p(ds), N.p(pw), N.p(blank_part),
+                N.p(d_table), P, B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)), "fused_attn_bwd")
+            db = blank_part.sum(dim=(0, 1))  # [H, 2, c]
+        return (dq, dkv, d_table.to(table_dt), db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt),
+                None, None, None)
+
+
+_ctypes_sigs_done = False
+
+
+def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k,
+                            blank_v):
+    """Returns out [B, N, H*c], or None when this case must take the unfused operators."""
+    if not q_lin.is_cuda or q_lin.dtype not in (torch.float16, torch.bfloat16) or kv_lin.dtype != q_lin.dtype:
+        return None
+    B, n, hc = q_lin.shape
+    c = hc // num_heads
+    if c not in (16, 32) or pe_table.shape[0] > 32768 or nbhd_idx.shape[2] > N.PLAN_MAX_M:
+        return None
+    plan = get_plan(nbhd_idx)
+    if plan.qplan(nbhd_idx, n) is None or plan.kplan(nbhd_idx, n) is None:
+        return None
+    umax = plan.stats["q"]["umax"]
+    if umax > N.PLAN_UMAX - 1:
+        return None
+    q_pe = _packed_pe(plan, pe_idx, cluster_mask)
+    if q_pe is None:
+        return None
+    return FusedClusterAttention.apply(q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe,
+                                       (num_heads, scale, umax))

@@ -92,13 +92,13 @@ class NbhdPlan:
                         hdr = torch.empty((B, nt), dtype=torch.int32, device=dev)
                         rows = torch.empty((B, nt, N.PLAN_UMAX), dtype=torch.int32, device=dev)
                         loc = torch.empty(B * Nq * M + 16, dtype=torch.uint8, device=dev)  # +16: vector tail reads
-                        stats = torch.zeros(4, dtype=torch.int32, device=dev)
+                        stats = torch.zeros(8, dtype=torch.int32, device=dev)
                         N.check(N.LIB.affb200_qplan_build(N.p(idx), B, Nq, Nk, M, T, N.p(hdr), N.p(rows), N.p(loc),
                                                           N.p(stats), N.stream_ptr(dev)), "qplan_build")
                         st = stats.tolist()
                         if st[0] == 0:
                             res = (T, hdr, rows, loc)
-                            self.stats["q"] = dict(T=T, overflow=0, dup_tiles=st[1], tiles=B * nt)
+                            self.stats["q"] = dict(T=T, overflow=0, dup_tiles=st[1], tiles=B * nt, umax=st[4])
                             break
                         if T == 16:
                             self.stats["q"] = dict(T=T, overflow=st[0], tiles=B * nt)
@@ -124,13 +124,13 @@ class NbhdPlan:
                         utok = torch.empty((B, nt, N.PLAN_UMAX), dtype=torch.int32, device=dev)
                         rloc = torch.empty((B, nt, N.PLAN_UMAX, M), dtype=torch.uint8, device=dev)
                         cnt = torch.empty(B * nt, dtype=torch.int32, device=dev)
-                        stats = torch.zeros(4, dtype=torch.int32, device=dev)
+                        stats = torch.zeros(8, dtype=torch.int32, device=dev)
                         N.check(N.LIB.affb200_kplan_build(N.p(idx), B, Nq, Nk, M, T, N.p(hdr), N.p(utok), N.p(rloc),
                                                           N.p(cnt), N.p(stats), N.stream_ptr(dev)), "kplan_build")
                         st = stats.tolist()
                         if st[2] == 0:
                             res = (T, hdr, utok, rloc)
-                            self.stats["k"] = dict(T=T, overflow=0, dup_tiles=st[3], tiles=B * nt)
+                            self.stats["k"] = dict(T=T, overflow=0, dup_tiles=st[3], tiles=B * nt, umax=st[5])
                             break
                         if T == 16:
                             self.stats["k"] = dict(T=T, overflow=st[2], tiles=B * nt)

@@ -60,13 +60,14 @@ template <> __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi
 
 // stage `n_rows` rows of C elements into padded shared memory rows; row_of(i) gives the global row or -1 (zero-fill)
 template <typename T, int C, typename RowOf>
-__device__ __forceinline__ void stage_rows(T *dst, const T *__restrict__ src_base, int n_rows, RowOf row_of) {
+__device__ __forceinline__ void stage_rows(T *dst, const T *__restrict__ src_base, int n_rows, RowOf row_of,
+                                           int64_t row_stride = C) {
     constexpr int CS = C + 8;
     constexpr int CH = C * 2 / 16;
     for (int q = threadIdx.x; q < n_rows * CH; q += kDT) {
         const int i = q / CH, ch = q - i * CH;
         const int r = row_of(i);
-        cp_async16(dst + i * CS + ch * 8, src_base + int64_t(r < 0 ? 0 : r) * C + ch * 8, r >= 0);
+        cp_async16(dst + i * CS + ch * 8, src_base + int64_t(r < 0 ? 0 : r) * row_stride + ch * 8, r >= 0);
     }
 }
 
@@ -77,6 +78,11 @@ struct TileSmem {
     void *ys;         // [256][C+8]
     void *ps;         // [T][kSS]
     float *os;        // [8*16*(16+... )]  fp32 partial outputs (wsum kernels)
+};
+
+// strides (in elements) of a [B][H][N][C]-indexed tensor whose memory layout may differ (e.g. a [B][N][H][C] buffer)
+struct StridedRows {
+    int64_t sB, sH, sN;
 };
 
 template <int C> __host__ __device__ constexpr int os_floats() { return 8 * 16 * 16 * (C + 8) / C; }
@@ -189,7 +195,7 @@ gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const 
 // =========================================================================================================
 template <typename T, int C>
 __device__ __forceinline__ void wsum_mma_store(const T *ps, const T *bs, float *os, T *__restrict__ og, int TT,
-                                                int Kpad, int n_valid_rows) {
+                                                int Kpad, int n_valid_rows, int64_t out_stride = C, float alpha = 1.f) {
     constexpr int CS = C + 8;
     constexpr int OS = C + 8;  // fp32 row stride of the partial-output buffer
     constexpr int NP = C / 16;
@@ -229,9 +235,9 @@ __device__ __forceinline__ void wsum_mma_store(const T *ps, const T *bs, float *
             acc[4] += v1.x; acc[5] += v1.y; acc[6] += v1.z; acc[7] += v1.w;
         }
         uint4 v;
-        v.x = pack2<T>(acc[0], acc[1]); v.y = pack2<T>(acc[2], acc[3]);
-        v.z = pack2<T>(acc[4], acc[5]); v.w = pack2<T>(acc[6], acc[7]);
-        *reinterpret_cast<uint4 *>(og + row * C + c0) = v;
+        v.x = pack2<T>(acc[0] * alpha, acc[1] * alpha); v.y = pack2<T>(acc[2] * alpha, acc[3] * alpha);
+        v.z = pack2<T>(acc[4] * alpha, acc[5] * alpha); v.w = pack2<T>(acc[6] * alpha, acc[7] * alpha);
+        *reinterpret_cast<uint4 *>(og + int64_t(row) * out_stride + c0) = v;
     }
 }
 
@@ -325,7 +331,8 @@ template <typename T, int C>
 __global__ void __launch_bounds__(kDT)
 scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, const int32_t *__restrict__ k_hdr,
                           const int32_t *__restrict__ k_utok, const uint8_t *__restrict__ k_rloc,
-                          T *__restrict__ dy, int H, int Nq, int Nk, int M, int TT) {
+                          T *__restrict__ dy, int H, int Nq, int Nk, int M, int TT, StridedRows xs_, StridedRows ys_,
+                          float alpha) {
     constexpr int CS = C + 8;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     int *tok_s = reinterpret_cast<int *>(smem_raw);
@@ -351,7 +358,7 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
 
     for (int h = 0; h < H; ++h) {
         const int64_t z = int64_t(b) * H + h;
-        stage_rows<T, C>(xs, x + z * Nq * C, Upad, [&](int i) { return tok_s[i]; });
+        stage_rows<T, C>(xs, x + int64_t(b) * xs_.sB + int64_t(h) * xs_.sH, Upad, [&](int i) { return tok_s[i]; }, xs_.sN);
         cp_async_commit();
         zero_operand<T>(ps, TT, Upad);
         __syncthreads();
@@ -392,7 +399,8 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
         }
         cp_async_wait_all();
         __syncthreads();
-        wsum_mma_store<T, C>(ps, xs, os, dy + (z * Nk + r0) * C, TT, Upad, ri);
+        wsum_mma_store<T, C>(ps, xs, os, dy + int64_t(b) * ys_.sB + int64_t(h) * ys_.sH + int64_t(r0) * ys_.sN, TT, Upad,
+                             ri, ys_.sN, alpha);
         __syncthreads();
     }
 }
@@ -458,6 +466,15 @@ int launch_gather_wsum_dense(const T *w, const T *y, const affb200_nbhd_plan *pl
 template <typename T>
 int launch_scatter_wsum_dense(const T *w, const T *x, const affb200_nbhd_plan *pl, T *dy, int64_t B, int64_t H,
                               int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
+    const int64_t xs[3] = {H * Nq * c, Nq * c, c}, ys[3] = {H * Nk * c, Nk * c, c};
+    return launch_scatter_wsum_dense_strided<T>(w, x, pl, dy, B, H, Nq, Nk, M, c, xs, ys, 1.f, st);
+}
+
+template <typename T>
+int launch_scatter_wsum_dense_strided(const T *w, const T *x, const affb200_nbhd_plan *pl, T *dy, int64_t B, int64_t H,
+                                      int64_t Nq, int64_t Nk, int64_t M, int64_t c, const int64_t *x_str,
+                                      const int64_t *y_str, float alpha, cudaStream_t st) {
+    const StridedRows xs_{x_str[0], x_str[1], x_str[2]}, ys_{y_str[0], y_str[1], y_str[2]};
     const int TT = pl->tk;
     dim3 grid(unsigned((Nk + TT - 1) / TT), unsigned(B));
     const size_t smem = smem_scatter_wsum(int(c), TT);
@@ -466,7 +483,7 @@ int launch_scatter_wsum_dense(const T *w, const T *x, const affb200_nbhd_plan *p
         auto kern = scatter_wsum_dense_kernel<T, C_>;                                                           \
         if (int e = set_smem(kern, smem)) return e;                                                             \
         kern<<<grid, kDT, smem, st>>>(w, x, pl->k_hdr, pl->k_utok, pl->k_rloc, dy, int(H), int(Nq), int(Nk),    \
-                                      int(M), TT);                                                              \
+                                      int(M), TT, xs_, ys_, alpha);                                             \
     } while (0)
     if (c == 32) AFF_L(32); else AFF_L(16);
 #undef AFF_L
@@ -479,7 +496,10 @@ int launch_scatter_wsum_dense(const T *w, const T *x, const affb200_nbhd_plan *p
     template int launch_gather_wsum_dense<T>(const T *, const T *, const affb200_nbhd_plan *, T *, int64_t, int64_t,  \
                                              int64_t, int64_t, int64_t, int64_t, cudaStream_t);                       \
     template int launch_scatter_wsum_dense<T>(const T *, const T *, const affb200_nbhd_plan *, T *, int64_t, int64_t, \
-                                              int64_t, int64_t, int64_t, int64_t, cudaStream_t);
+                                              int64_t, int64_t, int64_t, int64_t, cudaStream_t);                      \
+    template int launch_scatter_wsum_dense_strided<T>(const T *, const T *, const affb200_nbhd_plan *, T *, int64_t,  \
+                                                      int64_t, int64_t, int64_t, int64_t, int64_t, const int64_t *,   \
+                                                      const int64_t *, float, cudaStream_t);
 AFF_INST(__half)
 AFF_INST(__nv_bfloat16)
 #undef AFF_INST

@@ -128,4 +128,13 @@ template <typename T>
 int launch_scatter_wsum_dense(const T *w, const T *x, const affb200_nbhd_plan *pl, T *dy, int64_t B, int64_t H,
                               int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st);
 
+// x / dy addressed as [b][h][row] with element strides {sB, sH, sN}; dy = alpha * sum(...)
+template <typename T>
+int launch_scatter_wsum_dense_strided(const T *w, const T *x, const affb200_nbhd_plan *pl, T *dy, int64_t B, int64_t H,
+                                      int64_t Nq, int64_t Nk, int64_t M, int64_t c, const int64_t *x_str,
+                                      const int64_t *y_str, float alpha, cudaStream_t st);
+// d_table[p][h] from d_vals [B][H][N*M] indexed by packed uint16 bias indices (attn_glue.cu)
+int launch_table_grad_u16(const void *d_vals, const uint16_t *pe, int64_t B, int64_t H, int64_t NM, int64_t P,
+                          float *d_table, int dtype, cudaStream_t st);
+
 }  // namespace affb200

@@ -1,0 +1,612 @@
+// fused_attn.cu — fused neighbourhood attention of ClusterAttention (reference models/aff_transformer.py:103-156):
+//
+//   S[i,j]   = scale * q_i · k_{nbhd[i,j]} + table[pe_idx[i,j], h] + (mask[i,j] ? 0 : -100)      j < M
+//   S[i,M]   = scale * q_i · blank_k[h]                                                           (blank token)
+//   P        = softmax over the M+1 logits
+//   out_i    = sum_j P[i,j] v_{nbhd[i,j]} + P[i,M] blank_v[h]
+//
+// One kernel replaces QK -> bias gather/permute/add -> mask add -> blank logit -> cat -> softmax -> split -> AV ->
+// blank_v add (8+ launches and 5-6 round trips of the [B,H,N,M] tensor).  It reads q/k/v straight out of the Linear
+// outputs ([B,N,H*c] and [B,N,H,2,c]: no permute copies, no q*scale pass) and writes out as [B,N,H*c].
+//
+// Per CTA: a tile of T consecutive tokens (query-tile plan of tileplan.cu).  The union of the U <= 255 key rows the
+// tile references is staged once per head in shared memory (K_U and V_U, 16-byte cp.async, padded rows), with the
+// blank token appended as row U, so the blank logit and the blank_v term fall out of the same two tensor-core
+// contractions:  S = Q·K_U^T (fp32, kept dense in shared memory), per-row softmax over the gathered entries,
+// P scattered back into a dense bf16 tile that aliases S row by row, then O = P·V_U.
+// Backward (fused_attn_bwd_kernel): recomputes S and P from the saved log-sum-exp, forms dP = dO·V_U^T,
+// dS = P∘(dP − δ), dQ = scale·dS·K_U, and emits dS and P (bf16, [B,H,N,M]) for the key-tile scatter kernels
+// (clusten_dense.cu) that produce dK and dV without atomics, and for the table-gradient kernel.
+#include "common.cuh"
+#include <type_traits>
+
+namespace affb200 {
+
+constexpr int kFT = 256;  // threads per CTA
+
+__device__ __forceinline__ uint32_t f_smem_u32(const void *p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void f_cp_async16(void *dst, const void *src, bool valid) {
+    const int sz = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(f_smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void f_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void f_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void f_ldsm_x4(uint32_t (&r)[4], const void *p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(f_smem_u32(p)));
+}
+__device__ __forceinline__ void f_ldsm_x4_t(uint32_t (&r)[4], const void *p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(f_smem_u32(p)));
+}
+template <typename T> __device__ __forceinline__ void f_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <> __device__ __forceinline__ void f_mma<__nv_bfloat16>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <> __device__ __forceinline__ void f_mma<__half>(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <typename T> __device__ __forceinline__ uint32_t f_pack2(float lo, float hi);
+template <> __device__ __forceinline__ uint32_t f_pack2<__nv_bfloat16>(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+template <> __device__ __forceinline__ uint32_t f_pack2<__half>(float lo, float hi) {
+    __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+// strided [B][N][H][c] view of a Linear output: element (b, i, h, 0) at base + b*sB + i*sN + h*sH
+template <typename T> struct View {
+    const T *p;
+    int64_t sB, sN, sH;
+    __device__ __forceinline__ const T *row(int64_t b, int64_t i, int h) const { return p + b * sB + i * sN + h * sH; }
+};
+template <typename T> struct ViewW {
+    T *p;
+    int64_t sB, sN, sH;
+    __device__ __forceinline__ T *row(int64_t b, int64_t i, int h) const { return p + b * sB + i * sN + h * sH; }
+};
+
+// compact per-(token, slot) bias index: pe | (masked << 15) — built once per stage from pe_idx / cluster_mask
+__global__ void __launch_bounds__(256)
+pe_pack_kernel(const int64_t *__restrict__ pe_idx, const int64_t *__restrict__ mask, int64_t total,
+               uint16_t *__restrict__ out, int32_t *__restrict__ bad) {
+    const int64_t t = int64_t(blockIdx.x) * 256 + threadIdx.x;
+    if (t >= total) return;
+    const int64_t p = __ldg(pe_idx + t);
+    if (p < 0 || p >= 32768) { atomicAdd(bad, 1); out[t] = 0; return; }
+    out[t] = uint16_t(p) | ((mask && __ldg(mask + t) == 0) ? 0x8000u : 0u);
+}
+
+// ---- shared-memory carve-up (all offsets multiples of 16 bytes) --------------------------------------------
+struct FusedSmem {
+    int UC;       // row capacity of the K/V staging buffers (multiple of 32, >= U+1)
+    int RS;       // byte stride of an S/P row: UC*4 + 16  (== 16 mod 128: conflict-free ldmatrix on the bf16 view)
+    size_t rows, ks, vs, xs, dos, sp, dp, loc, pe, os, bl, total;
+};
+__host__ __device__ inline FusedSmem fused_smem(int UC, int TT, int C, int M, bool bwd) {
+    FusedSmem s;
+    s.UC = UC;
+    s.RS = UC * 4 + 16;
+    size_t o = 0;
+    s.rows = o; o += size_t(UC) * 4;
+    s.ks = o;   o += size_t(UC) * (C + 8) * 2;
+    s.vs = o;   o += size_t(UC) * (C + 8) * 2;
+    s.xs = o;   o += size_t(TT) * (C + 8) * 2;
+    s.dos = o;  o += bwd ? size_t(TT) * (C + 8) * 2 : 0;
+    s.sp = o;   o += size_t(TT) * s.RS;
+    s.dp = o;   o += bwd ? size_t(TT) * s.RS : 0;
+    s.loc = o;  o += (size_t(TT) * M + 15) & ~size_t(15);
+    s.pe = o;   o += (size_t(TT) * M * 2 + 15) & ~size_t(15);
+    s.os = o;   o += size_t(8 * 16 * 16 * (C + 8) / C) * 4;
+    s.bl = o;   o += bwd ? size_t(8) * 2 * C * 4 : 0;
+    s.total = o;
+    return s;
+}
+
+// stage n_rows rows of C elements (row_ptr(i) == nullptr -> zero fill; row `skip` is left alone) into padded rows
+// of stride C+8.  `safe` is any valid global address (cp.async with src-size 0 never dereferences it).
+template <typename T, int C, typename RowPtr>
+__device__ __forceinline__ void f_stage_rows(T *dst, int n_rows, int skip, const T *safe, RowPtr row_ptr) {
+    constexpr int CS = C + 8;
+    constexpr int CH = C * 2 / 16;
+    for (int q = threadIdx.x; q < n_rows * CH; q += kFT) {
+        const int i = q / CH, ch = q - i * CH;
+        if (i == skip) continue;
+        const T *src = row_ptr(i);
+        f_cp_async16(dst + i * CS + ch * 8, src ? src + ch * 8 : safe, src != nullptr);
+    }
+}
+
+// S[TT x Upad] (fp32, smem row stride RS bytes) = alpha * X[TT x C] · Y[Upad x C]^T
+template <typename T, int C>
+__device__ __forceinline__ void f_mma_xyT(const T *xs, const T *ys, unsigned char *sp, int RS, int TT, int Upad,
+                                          float alpha) {
+    constexpr int CS = C + 8;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int MT = TT >> 4;
+    const int mt = warp % MT;
+    const int nstep = 8 / MT;
+    const int g = lane >> 2, q4 = lane & 3;
+    uint32_t a[C / 16][4];
+#pragma unroll
+    for (int ks = 0; ks < C / 16; ++ks)
+        f_ldsm_x4(a[ks], xs + (mt * 16 + (lane & 15)) * CS + ks * 16 + (lane >> 4) * 8);
+    if constexpr (C == 32) {
+        for (int nt = warp / MT; nt < Upad / 8; nt += nstep) {
+            uint32_t bf[4];
+            f_ldsm_x4(bf, ys + (nt * 8 + (lane & 7)) * CS + (lane >> 3) * 8);
+            float d[4] = {0.f, 0.f, 0.f, 0.f};
+            f_mma<T>(d, a[0], bf[0], bf[1]);
+            f_mma<T>(d, a[1], bf[2], bf[3]);
+            float *r0 = reinterpret_cast<float *>(sp + size_t(mt * 16 + g) * RS) + nt * 8 + q4 * 2;
+            float *r1 = reinterpret_cast<float *>(sp + size_t(mt * 16 + g + 8) * RS) + nt * 8 + q4 * 2;
+            *reinterpret_cast<float2 *>(r0) = make_float2(d[0] * alpha, d[1] * alpha);
+            *reinterpret_cast<float2 *>(r1) = make_float2(d[2] * alpha, d[3] * alpha);
+        }
+    } else {
+        for (int np = warp / MT; np < Upad / 16; np += nstep) {
+            uint32_t bf[4];
+            f_ldsm_x4(bf, ys + (np * 16 + (lane & 7) + (lane >> 4) * 8) * CS + ((lane >> 3) & 1) * 8);
+            float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+            f_mma<T>(d0, a[0], bf[0], bf[1]);
+            f_mma<T>(d1, a[0], bf[2], bf[3]);
+            float *r0 = reinterpret_cast<float *>(sp + size_t(mt * 16 + g) * RS) + np * 16 + q4 * 2;
+            float *r1 = reinterpret_cast<float *>(sp + size_t(mt * 16 + g + 8) * RS) + np * 16 + q4 * 2;
+            *reinterpret_cast<float2 *>(r0) = make_float2(d0[0] * alpha, d0[1] * alpha);
+            *reinterpret_cast<float2 *>(r1) = make_float2(d0[2] * alpha, d0[3] * alpha);
+            *reinterpret_cast<float2 *>(r0 + 8) = make_float2(d1[0] * alpha, d1[1] * alpha);
+            *reinterpret_cast<float2 *>(r1 + 8) = make_float2(d1[2] * alpha, d1[3] * alpha);
+        }
+    }
+}
+
+// out[TT x C] = alpha * A[TT x Kpad] (bf16/f16 view of the S/P buffer, row stride RS bytes) · Bm[Kpad x C]
+// K is split over the warps that share an output item; partials meet in `os` and are summed in slice order.
+template <typename T, int C>
+__device__ __forceinline__ void f_mma_pv_store(const unsigned char *sp, int RS, const T *bs, float *os, int TT,
+                                               int Kpad, int n_valid, float alpha, T *out_base, int64_t out_stride) {
+    constexpr int CS = C + 8;
+    constexpr int OS = C + 8;
+    constexpr int NP = C / 16;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int MT = TT >> 4;
+    const int items = MT * NP;
+    const int nslices = 8 / items;
+    const int item = warp % items, slice = warp / items;
+    const int mt = item % MT, np = item / MT;
+    const int g = lane >> 2, q4 = lane & 3;
+    float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int ks = slice; ks < Kpad / 16; ks += nslices) {
+        uint32_t a[4], bf[4];
+        f_ldsm_x4(a, sp + size_t(mt * 16 + (lane & 15)) * RS + (ks * 16 + (lane >> 4) * 8) * 2);
+        f_ldsm_x4_t(bf, bs + (ks * 16 + (lane & 15)) * CS + np * 16 + (lane >> 4) * 8);
+        f_mma<T>(d0, a, bf[0], bf[1]);
+        f_mma<T>(d1, a, bf[2], bf[3]);
+    }
+    float *op = os + (slice * TT + mt * 16 + g) * OS + np * 16 + q4 * 2;
+    *reinterpret_cast<float2 *>(op) = make_float2(d0[0], d0[1]);
+    *reinterpret_cast<float2 *>(op + 8 * OS) = make_float2(d0[2], d0[3]);
+    *reinterpret_cast<float2 *>(op + 8) = make_float2(d1[0], d1[1]);
+    *reinterpret_cast<float2 *>(op + 8 * OS + 8) = make_float2(d1[2], d1[3]);
+    __syncthreads();
+    for (int e = tid; e < n_valid * (C / 8); e += kFT) {
+        const int row = e / (C / 8), c0 = (e - row * (C / 8)) * 8;
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        for (int s = 0; s < nslices; ++s) {
+            const float4 v0 = *reinterpret_cast<const float4 *>(os + (s * TT + row) * OS + c0);
+            const float4 v1 = *reinterpret_cast<const float4 *>(os + (s * TT + row) * OS + c0 + 4);
+            acc[0] += v0.x; acc[1] += v0.y; acc[2] += v0.z; acc[3] += v0.w;
+            acc[4] += v1.x; acc[5] += v1.y; acc[6] += v1.z; acc[7] += v1.w;
+        }
+        uint4 v;
+        v.x = f_pack2<T>(acc[0] * alpha, acc[1] * alpha); v.y = f_pack2<T>(acc[2] * alpha, acc[3] * alpha);
+        v.z = f_pack2<T>(acc[4] * alpha, acc[5] * alpha); v.w = f_pack2<T>(acc[6] * alpha, acc[7] * alpha);
+        *reinterpret_cast<uint4 *>(out_base + int64_t(row) * out_stride + c0) = v;
+    }
+}
+
+constexpr int kNE = 7;  // logits per lane: ceil((192 + 1) / 32)
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct TileHdr {
+    int U, Upad, ti, t0;
+    bool dup;
+};
+
+// common prologue: tile header, union rows, 1-byte positions and packed bias indices -> shared memory
+__device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32_t *q_rows, const uint8_t *q_loc,
+                                               const uint16_t *q_pe, int N, int M, int TT, int UC, int *rows_s,
+                                               uint8_t *loc_s, uint16_t *pe_s) {
+    TileHdr t;
+    const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x, tid = threadIdx.x;
+    t.t0 = tile * TT;
+    t.ti = min(TT, N - t.t0);
+    const int hdr = q_hdr[int64_t(b) * n_tiles + tile];
+    t.U = hdr & AFFB200_PLAN_COUNT_MASK;
+    t.dup = (hdr & AFFB200_PLAN_DUP) != 0;
+    t.Upad = (t.U + 1 + 15) & ~15;
+    const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * AFFB200_PLAN_UMAX;
+    for (int u = tid; u < UC; u += kFT) rows_s[u] = u < t.U ? rg[u] : -1;
+    const int n_ent = t.ti * M;
+    const uint8_t *lg = q_loc + (int64_t(b) * N + t.t0) * M;
+    const uint16_t *pg = q_pe + (int64_t(b) * N + t.t0) * M;
+    for (int p = tid; p < n_ent; p += kFT) { loc_s[p] = lg[p]; pe_s[p] = pg[p]; }
+    return t;
+}
+
+// softmax of one token's M+1 logits, read from its dense fp32 S row; returns normalised probabilities in pv[] and
+// their column positions in col[]; lse = log-sum-exp
+__device__ __forceinline__ void f_row_softmax(const float *srow, const uint8_t *loc_r, const uint16_t *pe_r,
+                                              const float *__restrict__ table, int H, int h, int M, int U, int lane,
+                                              float (&pv)[kNE], int (&col)[kNE], float &lse) {
+    float mx = -INFINITY;
+#pragma unroll
+    for (int e = 0; e < kNE; ++e) {
+        const int j = lane + 32 * e;
+        float s = -INFINITY;
+        int c = 0;
+        if (j < M) {
+            c = loc_r[j];
+            const uint32_t pe = pe_r[j];
+            s = srow[c] + __ldg(table + int64_t(pe & 0x7fffu) * H + h) + ((pe & 0x8000u) ? -100.f : 0.f);
+        } else if (j == M) {
+            c = U;
+            s = srow[U];
+        }
+        pv[e] = s;
+        col[e] = c;
+        mx = fmaxf(mx, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+#pragma unroll
+    for (int e = 0; e < kNE; ++e) {
+        pv[e] = exp2f((pv[e] - mx) * kLog2e);  // exp2f(-inf) = 0 for the unused lanes
+        sum += pv[e];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.f / sum;
+#pragma unroll
+    for (int e = 0; e < kNE; ++e) pv[e] *= inv;
+    lse = mx + logf(sum);
+}
+
+// write one token's values into its dense operand row (bf16/f16 view at the start of the S row), zero elsewhere
+template <typename T>
+__device__ __forceinline__ void f_scatter_row(T *prow, int Upad, int M, bool dup, int lane, const float (&pv)[kNE],
+                                              const int (&col)[kNE]) {
+    for (int w = lane; w < Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
+    __syncwarp();
+    if (!dup) {
+#pragma unroll
+        for (int e = 0; e < kNE; ++e)
+            if (lane + 32 * e <= M) prow[col[e]] = Elem<T>::from_acc(pv[e]);
+    } else {  // a token lists a row more than once (padded slots all point at row 0): accumulate in slot order
+#pragma unroll
+        for (int e = 0; e < kNE; ++e)
+            for (int l = 0; l < 32; ++l) {
+                if (lane == l && l + 32 * e <= M)
+                    prow[col[e]] = Elem<T>::from_acc(Elem<T>::to_acc(prow[col[e]]) + pv[e]);
+                __syncwarp();
+            }
+    }
+}
+
+template <typename T, int C>
+__global__ void __launch_bounds__(kFT)
+fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float *__restrict__ table,
+                      const float *__restrict__ blank_k, const float *__restrict__ blank_v,
+                      const int32_t *__restrict__ q_hdr, const int32_t *__restrict__ q_rows,
+                      const uint8_t *__restrict__ q_loc, const uint16_t *__restrict__ q_pe, float *__restrict__ lse,
+                      int H, int N, int M, int TT, float scale, FusedSmem L) {
+    constexpr int CS = C + 8;
+    extern __shared__ __align__(128) unsigned char smem[];
+    int *rows_s = reinterpret_cast<int *>(smem + L.rows);
+    T *ks = reinterpret_cast<T *>(smem + L.ks);
+    T *vs = reinterpret_cast<T *>(smem + L.vs);
+    T *xs = reinterpret_cast<T *>(smem + L.xs);
+    unsigned char *sp = smem + L.sp;
+    uint8_t *loc_s = smem + L.loc;
+    uint16_t *pe_s = reinterpret_cast<uint16_t *>(smem + L.pe);
+    float *os = reinterpret_cast<float *>(smem + L.os);
+
+    const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, rows_s, loc_s, pe_s);
+    __syncthreads();
+
+    for (int h = 0; h < H; ++h) {
+        f_stage_rows<T, C>(xs, TT, -1, q.p, [&](int i) { return i < t.ti ? q.row(b, t.t0 + i, h) : nullptr; });
+        f_stage_rows<T, C>(ks, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? k.row(b, rows_s[i], h) : nullptr; });
+        f_stage_rows<T, C>(vs, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? v.row(b, rows_s[i], h) : nullptr; });
+        f_cp_async_commit();
+        if (tid < C) {  // the blank token is key/value row U
+            ks[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_k + h * C + tid));
+            vs[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_v + h * C + tid));
+        }
+        f_cp_async_wait_all();
+        __syncthreads();
+        f_mma_xyT<T, C>(xs, ks, sp, L.RS, TT, t.Upad, scale);
+        __syncthreads();
+        for (int i = warp; i < TT; i += 8) {
+            T *prow = reinterpret_cast<T *>(sp + size_t(i) * L.RS);
+            if (i >= t.ti) {
+                for (int w = lane; w < t.Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
+                continue;
+            }
+            float pv[kNE], l;
+            int col[kNE];
+            f_row_softmax(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
+                          pv, col, l);
+            if (lane == 0) lse[(int64_t(b) * H + h) * N + t.t0 + i] = l;
+            __syncwarp();
+            f_scatter_row<T>(prow, t.Upad, M, t.dup, lane, pv, col);
+        }
+        __syncthreads();
+        f_mma_pv_store<T, C>(sp, L.RS, vs, os, TT, t.Upad, t.ti, 1.f, out.row(b, t.t0, h), out.sN);
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Backward, query-tile half.  Emits dQ, and dS / P in [B][H][N][M] for the key-tile scatter kernels and the table
+// gradient; per-tile partial sums of the blank-token gradients go to blank_part [B][tiles][H][2][C] (fp32).
+// ---------------------------------------------------------------------------------------------------------
+template <typename T, int C>
+__global__ void __launch_bounds__(kFT)
+fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout, ViewW<T> dq,
+                      const float *__restrict__ table, const float *__restrict__ blank_k,
+                      const float *__restrict__ blank_v, const int32_t *__restrict__ q_hdr,
+                      const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc,
+                      const uint16_t *__restrict__ q_pe, const float *__restrict__ lse, T *__restrict__ ds_out,
+                      T *__restrict__ p_out, float *__restrict__ blank_part, int H, int N, int M, int TT, float scale,
+                      FusedSmem L) {
+    constexpr int CS = C + 8;
+    extern __shared__ __align__(128) unsigned char smem[];
+    int *rows_s = reinterpret_cast<int *>(smem + L.rows);
+    T *ks = reinterpret_cast<T *>(smem + L.ks);
+    T *vs = reinterpret_cast<T *>(smem + L.vs);
+    T *xs = reinterpret_cast<T *>(smem + L.xs);
+    T *dos = reinterpret_cast<T *>(smem + L.dos);
+    unsigned char *sp = smem + L.sp;
+    unsigned char *dp = smem + L.dp;
+    uint8_t *loc_s = smem + L.loc;
+    uint16_t *pe_s = reinterpret_cast<uint16_t *>(smem + L.pe);
+    float *os = reinterpret_cast<float *>(smem + L.os);
+    float *bl = reinterpret_cast<float *>(smem + L.bl);  // [8 warps][2][C]
+
+    const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, rows_s, loc_s, pe_s);
+    __syncthreads();
+    const int e_blank = M >> 5, l_blank = M & 31;  // (slot, lane) that owns the blank logit
+
+    for (int h = 0; h < H; ++h) {
+        f_stage_rows<T, C>(xs, TT, -1, q.p, [&](int i) { return i < t.ti ? q.row(b, t.t0 + i, h) : nullptr; });
+        f_stage_rows<T, C>(dos, TT, -1, q.p, [&](int i) { return i < t.ti ? dout.row(b, t.t0 + i, h) : nullptr; });
+        f_stage_rows<T, C>(ks, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? k.row(b, rows_s[i], h) : nullptr; });
+        f_stage_rows<T, C>(vs, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? v.row(b, rows_s[i], h) : nullptr; });
+        f_cp_async_commit();
+        if (tid < C) {
+            ks[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_k + h * C + tid));
+            vs[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_v + h * C + tid));
+        }
+        f_cp_async_wait_all();
+        __syncthreads();
+        f_mma_xyT<T, C>(xs, ks, sp, L.RS, TT, t.Upad, scale);   // S
+        f_mma_xyT<T, C>(dos, vs, dp, L.RS, TT, t.Upad, 1.f);    // dP = dO · V_U^T
+        __syncthreads();
+
+        float acc_bk = 0.f, acc_bv = 0.f;  // lane c < C: this warp's share of d blank_k[h][c], d blank_v[h][c]
+        for (int i = warp; i < TT; i += 8) {
+            T *prow = reinterpret_cast<T *>(sp + size_t(i) * L.RS);
+            if (i >= t.ti) {
+                for (int w = lane; w < t.Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
+                continue;
+            }
+            const int64_t tok = t.t0 + i;
+            // delta = dO_i · O_i
+            float dl = 0.f, qv = 0.f, dov = 0.f;
+            if (lane < C) {
+                dov = Elem<T>::to_acc(dos[i * CS + lane]);
+                qv = Elem<T>::to_acc(xs[i * CS + lane]);
+                dl = dov * Elem<T>::to_acc(__ldg(out.row(b, tok, h) + lane));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) dl += __shfl_xor_sync(0xffffffffu, dl, o);
+            float pv[kNE], l;
+            int col[kNE];
+            f_row_softmax(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
+                          pv, col, l);
+            // (the recomputed log-sum-exp equals the saved one up to rounding; the saved value is not needed)
+            const float *dprow = reinterpret_cast<const float *>(dp + size_t(i) * L.RS);
+            float dsv[kNE];
+            T *pg = p_out + ((int64_t(b) * H + h) * N + tok) * M;
+            T *dg = ds_out + ((int64_t(b) * H + h) * N + tok) * M;
+#pragma unroll
+            for (int e = 0; e < kNE; ++e) {
+                const int j = lane + 32 * e;
+                dsv[e] = (j <= M) ? pv[e] * (dprow[col[e]] - dl) : 0.f;
+                if (j < M) {
+                    pg[j] = Elem<T>::from_acc(pv[e]);
+                    dg[j] = Elem<T>::from_acc(dsv[e]);
+                }
+            }
+            // blank-token gradients
+            float pb = 0.f, dsb = 0.f;
+#pragma unroll
+            for (int e = 0; e < kNE; ++e)
+                if (e == e_blank) { pb = pv[e]; dsb = dsv[e]; }
+            pb = __shfl_sync(0xffffffffu, pb, l_blank);
+            dsb = __shfl_sync(0xffffffffu, dsb, l_blank);
+            acc_bk += scale * dsb * qv;
+            acc_bv += pb * dov;
+            __syncwarp();
+            f_scatter_row<T>(prow, t.Upad, M, t.dup, lane, dsv, col);
+        }
+        if (lane < C) {
+            bl[(warp * 2 + 0) * C + lane] = acc_bk;
+            bl[(warp * 2 + 1) * C + lane] = acc_bv;
+        }
+        __syncthreads();
+        if (tid < 2 * C) {
+            float sacc = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) sacc += bl[w * 2 * C + tid];
+            blank_part[((int64_t(b) * gridDim.x + blockIdx.x) * H + h) * 2 * C + tid] = sacc;
+        }
+        f_mma_pv_store<T, C>(sp, L.RS, ks, os, TT, t.Upad, t.ti, scale, dq.row(b, t.t0, h), dq.sN);  // dQ = scale·dS·K_U
+        __syncthreads();
+    }
+}
+
+}  // namespace affb200
+
+// =========================================================================================================
+// C ABI
+// =========================================================================================================
+using namespace affb200;
+
+template <typename T> static View<T> mk_view(const affb200_view *v) { return View<T>{(const T *)v->p, v->sB, v->sN, v->sH}; }
+template <typename T> static ViewW<T> mk_vieww(const affb200_view *v) { return ViewW<T>{(T *)v->p, v->sB, v->sN, v->sH}; }
+
+static bool view_ok(const affb200_view *v, int64_t c) {
+    // rows must be 16-byte aligned for cp.async / 128-bit stores
+    return v && v->p && (reinterpret_cast<uintptr_t>(v->p) & 15) == 0 && (v->sB * 2) % 16 == 0 && (v->sN * 2) % 16 == 0 &&
+           (v->sH * 2) % 16 == 0 && (c == 16 || c == 32);
+}
+
+static int fused_common_check(const char *what, const affb200_nbhd_plan *plan, const uint16_t *q_pe, int64_t B, int64_t H,
+                              int64_t N, int64_t M, int64_t c, int umax, int dtype) {
+    if (B <= 0 || H <= 0 || N <= 0 || M <= 0 || B > 65535 || M > AFFB200_PLAN_MAX_M || H > 65535) {
+        set_error("%s: unsupported dimensions", what);
+        return AFFB200_E_ARG;
+    }
+    if (dtype != AFFB200_F16 && dtype != AFFB200_BF16) { set_error("%s: f16 / bf16 only", what); return AFFB200_E_ARG; }
+    if (c != 16 && c != 32) { set_error("%s: head dim must be 16 or 32", what); return AFFB200_E_ARG; }
+    if (!plan || plan->tq <= 0 || !plan->q_hdr || !plan->q_rows || !plan->q_loc || !q_pe) {
+        set_error("%s: a query-tile plan and packed bias indices are required", what);
+        return AFFB200_E_ARG;
+    }
+    if (umax < 0 || umax > AFFB200_PLAN_UMAX - 1) {
+        set_error("%s: a tile references %d distinct rows; the fused kernel holds at most %d plus the blank token", what,
+                  umax, AFFB200_PLAN_UMAX - 1);
+        return AFFB200_E_ARG;
+    }
+    return AFFB200_OK;
+}
+
+extern "C" int affb200_fused_attn_pack_pe(const int64_t *pe_idx, const int64_t *mask, int64_t total, uint16_t *out,
+                                          int32_t *bad, void *stream) {
+    if (total < 0) { set_error("pack_pe: negative size"); return AFFB200_E_ARG; }
+    if (total == 0) return AFFB200_OK;
+    if (!pe_idx || !out || !bad) { set_error("pack_pe: null pointer"); return AFFB200_E_ARG; }
+    pe_pack_kernel<<<unsigned((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pe_idx, mask, total, out, bad);
+    return check_launch("pack_pe");
+}
+
+extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view *k, const affb200_view *v,
+                                      const affb200_view *out, const float *table, const float *blank_k,
+                                      const float *blank_v, const affb200_nbhd_plan *plan, const uint16_t *q_pe,
+                                      int32_t umax, float *lse, int64_t B, int64_t H, int64_t N, int64_t M, int64_t c,
+                                      float scale, int dtype, void *stream) {
+    if (int e = fused_common_check("fused_attn_fwd", plan, q_pe, B, H, N, M, c, umax, dtype)) return e;
+    if (!view_ok(q, c) || !view_ok(k, c) || !view_ok(v, c) || !view_ok(out, c) || !table || !blank_k || !blank_v || !lse) {
+        set_error("fused_attn_fwd: null or misaligned operand (rows must be 16-byte aligned)");
+        return AFFB200_E_ARG;
+    }
+    const int TT = plan->tq;
+    const int UC = (umax + 1 + 31) & ~31;
+    const FusedSmem L = fused_smem(UC, TT, int(c), int(M), false);
+    if (L.total > 227 * 1024) { set_error("fused_attn_fwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
+    dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
+    auto st = (cudaStream_t)stream;
+    return dispatch_dtype(dtype, [&](auto tag) -> int {
+        using T0 = decltype(tag);
+        if constexpr (std::is_same<T0, __half>::value || std::is_same<T0, __nv_bfloat16>::value) {
+            using T = T0;
+#define AFF_F(C_)                                                                                                  \
+    do {                                                                                                           \
+        auto kern = fused_attn_fwd_kernel<T, C_>;                                                                  \
+        if (L.total > 48 * 1024 &&                                                                                 \
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.total)) != cudaSuccess)  \
+            return check_launch("cudaFuncSetAttribute", 0);                                                        \
+        kern<<<grid, kFT, L.total, st>>>(mk_view<T>(q), mk_view<T>(k), mk_view<T>(v), mk_vieww<T>(out), table,     \
+                                         blank_k, blank_v, plan->q_hdr, plan->q_rows, plan->q_loc, q_pe, lse,      \
+                                         int(H), int(N), int(M), TT, scale, L);                                    \
+    } while (0)
+            if (c == 32) AFF_F(32); else AFF_F(16);
+#undef AFF_F
+            return check_launch("fused_attn_fwd");
+        } else {
+            return AFFB200_E_ARG;
+        }
+    });
+}
+
+extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const affb200_view *v,
+                                      const affb200_view *out, const affb200_view *dout, const affb200_view *dq,
+                                      const affb200_view *dk, const affb200_view *dv, const float *table,
+                                      const float *blank_k, const float *blank_v, const affb200_nbhd_plan *plan,
+                                      const uint16_t *q_pe, int32_t umax, const float *lse, void *ds_work, void *p_work,
+                                      float *blank_part, float *d_table, int64_t P, int64_t B, int64_t H, int64_t N,
+                                      int64_t M, int64_t c, float scale, int dtype, void *stream) {
+    if (int e = fused_common_check("fused_attn_bwd", plan, q_pe, B, H, N, M, c, umax, dtype)) return e;
+    if (!view_ok(q, c) || !view_ok(k, c) || !view_ok(v, c) || !view_ok(out, c) || !view_ok(dout, c) || !view_ok(dq, c) ||
+        !view_ok(dk, c) || !view_ok(dv, c) || !table || !blank_k || !blank_v || !lse || !ds_work || !p_work ||
+        !blank_part || !d_table) {
+        set_error("fused_attn_bwd: null or misaligned operand");
+        return AFFB200_E_ARG;
+    }
+    if (plan->tk <= 0 || !plan->k_hdr || !plan->k_utok || !plan->k_rloc) {
+        set_error("fused_attn_bwd: a key-tile plan is required");
+        return AFFB200_E_ARG;
+    }
+    if (P <= 0 || P > 32768) { set_error("fused_attn_bwd: bias table must have 1..32768 rows"); return AFFB200_E_ARG; }
+    const int TT = plan->tq;
+    const int UC = (umax + 1 + 31) & ~31;
+    const FusedSmem L = fused_smem(UC, TT, int(c), int(M), true);
+    if (L.total > 227 * 1024) { set_error("fused_attn_bwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
+    dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
+    auto st = (cudaStream_t)stream;
+    return dispatch_dtype(dtype, [&](auto tag) -> int {
+        using T0 = decltype(tag);
+        if constexpr (std::is_same<T0, __half>::value || std::is_same<T0, __nv_bfloat16>::value) {
+            using T = T0;
+#define AFF_B(C_)                                                                                                  \
+    do {                                                                                                           \
+        auto kern = fused_attn_bwd_kernel<T, C_>;                                                                  \
+        if (L.total > 48 * 1024 &&                                                                                 \
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.total)) != cudaSuccess)  \
+            return check_launch("cudaFuncSetAttribute", 0);                                                        \
+        kern<<<grid, kFT, L.total, st>>>(mk_view<T>(q), mk_view<T>(k), mk_view<T>(v), mk_view<T>(out),             \
+                                         mk_view<T>(dout), mk_vieww<T>(dq), table, blank_k, blank_v, plan->q_hdr,  \
+                                         plan->q_rows, plan->q_loc, q_pe, lse, (T *)ds_work, (T *)p_work,          \
+                                         blank_part, int(H), int(N), int(M), TT, scale, L);                        \
+    } while (0)
+            if (c == 32) AFF_B(32); else AFF_B(16);
+#undef AFF_B
+            if (int e = check_launch("fused_attn_bwd")) return e;
+            // dK = scale * scatter(dS, Q) ; dV = scatter(P, dO): key-tile ownership, no atomics
+            const int64_t qs[3] = {q->sB, q->sH, q->sN}, dos_[3] = {dout->sB, dout->sH, dout->sN};
+            const int64_t dks[3] = {dk->sB, dk->sH, dk->sN}, dvs[3] = {dv->sB, dv->sH, dv->sN};
+            if (int e = launch_scatter_wsum_dense_strided<T>((const T *)ds_work, (const T *)q->p, plan, (T *)dk->p, B, H, N,
+                                                             N, M, c, qs, dks, scale, st))
+                return e;
+            if (int e = launch_scatter_wsum_dense_strided<T>((const T *)p_work, (const T *)dout->p, plan, (T *)dv->p, B, H,
+                                                             N, N, M, c, dos_, dvs, 1.f, st))
+                return e;
+            return launch_table_grad_u16(ds_work, q_pe, B, H, N * M, P, d_table, dtype, st);
+        } else {
+            return AFFB200_E_ARG;
+        }
+    });
+}

@@ -134,6 +134,7 @@ qplan_kernel(const int64_t *__restrict__ idx, int Nq, int Nk, int M, int T, int3
     if (tid == 0) {
         *h = U | (dup_flag ? AFFB200_PLAN_DUP : 0);
         if (dup_flag) atomicAdd(stats + 1, 1);
+        atomicMax(stats + 4, U);
     }
 }
 
@@ -243,6 +244,7 @@ kplan_finish_kernel(const int64_t *__restrict__ idx, int Nq, int Nk, int M, int 
     if (tid == 0) {
         hdr[tix] = n | (dup_flag ? AFFB200_PLAN_DUP : 0);
         if (dup_flag) atomicAdd(stats + 3, 1);
+        atomicMax(stats + 5, n);
     }
 }
 
