@@ -243,15 +243,49 @@ class _AffRun:
         return loss
 
     def roofline(self, peak, peak_src):
-        """CLUSTEN kernels at this model's stage shapes with the model's own neighbourhoods (captured from a forward)."""
-        idx = []
-        hooks = [layer.blocks[0].register_forward_pre_hook(lambda m, a: idx.append(a[1]))
+        """The attention kernels at this model's stage shapes with the model's own neighbourhoods (captured from a
+        forward): the fused neighbourhood-attention forward kernel and backward kernel group (what the step runs),
+        followed by the unfused CLUSTEN operators for reference.  Algorithmic bytes of the fused op = its API-visible
+        operands once: fwd q + kv + out at s bytes, nbhd_idx + pe_idx (+ mask) at 8 B; bwd q, kv, out, d_out read and
+        d_q, d_kv written, plus the same index tensors."""
+        cap = []
+        hooks = [layer.blocks[0].register_forward_pre_hook(lambda m, a: cap.append((a[1], a[2], a[3])))
                  for layer in self.model.layers[:3]]
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
             self.model(torch.randn(self.B, 3, self.wl.img, self.wl.img, device=self.device))
         for h in hooks:
             h.remove()
-        return clusten_roofline(self.B, self.device, torch.bfloat16, idx, peak, peak_src)
+        rows = []
+        if self.ops.fused_attention is not None:
+            from affb200 import fused
+            for st, (nbhd, mask, pe_idx) in enumerate(cap):
+                layer = self.model.layers[st]
+                attn = layer.blocks[0].attn
+                B, n, M = nbhd.shape
+                H, hc = attn.num_heads, attn.dim
+                q = torch.randn(B, n, hc, device=self.device).bfloat16()
+                kv = torch.randn(B, n, 2 * hc, device=self.device).bfloat16()
+                table = torch.randn(self.model.pre_table.shape[0], H, device=self.device).bfloat16()
+                calls = fused.raw_calls(q, kv, H, attn.scale, nbhd, pe_idx, mask, table, attn.blank_k, attn.blank_v)
+                if calls is None:
+                    continue
+                nidx = 8 * B * n * M * (3 if mask is not None else 2)
+                for nm, fn, nbytes in (("fused_attn_fwd", calls[0], 2 * 4 * B * n * hc + nidx),
+                                       ("fused_attn_bwd", calls[1], 2 * 8 * B * n * hc + nidx)):
+                    ms = _time_op(fn)
+                    rows.append({"kernel": "%s@stage%d" % (nm, st + 1), "ms": ms, "calls_per_step": layer.depth,
+                                 "bytes": nbytes, "GBps": nbytes / ms / 1e6})
+                del q, kv, calls
+        top = max(rows, key=lambda r: r["ms"] * r["calls_per_step"]) if rows else None
+        unfused = clusten_roofline(self.B, self.device, torch.bfloat16, [c[0] for c in cap], peak, peak_src)
+        if top is None:
+            return unfused
+        fmt = lambda r: {"kernel": r["kernel"], "ms": round(r["ms"], 4), "GBps": round(r["GBps"], 1),
+                         "frac": round(r["GBps"] / peak, 3), "calls_per_step": r["calls_per_step"]}
+        return {"bound": "hbm", "kernel": top["kernel"], "achieved": top["GBps"], "peak": peak, "unit": "GB/s",
+                "frac": top["GBps"] / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": top["bytes"], "avg_launch_ms": top["ms"],
+                "all": [fmt(r) for r in rows], "unfused_clusten_ops": unfused["all"]}
 
 
 class AffTinyTrain(AffTrain):

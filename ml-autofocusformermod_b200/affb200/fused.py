@@ -133,3 +133,48 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
         return None
     return FusedClusterAttention.apply(q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe,
                                        (num_heads, scale, umax))
+
+
+def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v):
+    """(fwd, bwd) closures that enqueue the forward kernel / the backward kernel group through the C ABI on
+    preallocated buffers (no autograd, no allocation) — what bench.py times for the roofline entries."""
+    B, n, hc = q_lin.shape
+    H = num_heads
+    c = hc // H
+    M = nbhd_idx.shape[2]
+    dev = q_lin.device
+    plan = get_plan(nbhd_idx)
+    if plan.qplan(nbhd_idx, n) is None or plan.kplan(nbhd_idx, n) is None:
+        return None
+    umax = plan.stats["q"]["umax"]
+    q_pe = _packed_pe(plan, pe_idx, cluster_mask)
+    if q_pe is None or umax > N.PLAN_UMAX - 1:
+        return None
+    st_f = plan.struct(nbhd_idx, n, True, False)
+    st_b = plan.struct(nbhd_idx, n, True, True)
+    T = plan.stats["q"]["T"]
+    table = pe_table.detach().float().contiguous()
+    bk, bv = blank_k.detach().float().contiguous(), blank_v.detach().float().contiguous()
+    out, dq, dkv, dout = torch.empty_like(q_lin), torch.empty_like(q_lin), torch.empty_like(kv_lin), torch.randn_like(q_lin)
+    lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+    ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+    pw = torch.empty_like(ds)
+    blank_part = torch.empty((B, (n + T - 1) // T, H, 2, c), dtype=torch.float32, device=dev)
+    d_table = torch.empty((table.shape[0], H), dtype=torch.float32, device=dev)
+    de, sp = N.dtype_enum(q_lin), N.stream_ptr(dev)
+    keep = (plan, q_pe, table, bk, bv, out, dq, dkv, dout, lse, ds, pw, blank_part, d_table)
+    V = lambda t, off=0, kv=False: _view(t, n * (2 * hc if kv else hc), 2 * hc if kv else hc, 2 * c if kv else c, off)
+
+    def fwd():
+        N.check(N.LIB.affb200_fused_attn_fwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), N.p(table),
+                                             N.p(bk), N.p(bv), st_f, N.p(q_pe), umax, N.p(lse), B, H, n, M, c,
+                                             float(scale), de, sp), "fused_attn_fwd")
+
+    def bwd():
+        N.check(N.LIB.affb200_fused_attn_bwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), V(dout), V(dq),
+                                             V(dkv, 0, True), V(dkv, c, True), N.p(table), N.p(bk), N.p(bv), st_b,
+                                             N.p(q_pe), umax, N.p(lse), N.p(ds), N.p(pw), N.p(blank_part), N.p(d_table),
+                                             table.shape[0], B, H, n, M, c, float(scale), de, sp), "fused_attn_bwd")
+
+    fwd._keep = keep
+    return fwd, bwd

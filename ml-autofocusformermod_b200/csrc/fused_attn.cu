@@ -213,7 +213,7 @@ __device__ __forceinline__ void f_mma_pv_store(const unsigned char *sp, int RS, 
     }
 }
 
-constexpr int kNE = 7;  // logits per lane: ceil((192 + 1) / 32)
+// NE = logits per lane = ceil((M + 1) / 32): 2 for nbhd 48, 5 for nbhd 144, 7 up to M = 192
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct TileHdr {
@@ -244,6 +244,7 @@ __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32
 
 // softmax of one token's M+1 logits, read from its dense fp32 S row; returns normalised probabilities in pv[] and
 // their column positions in col[]; lse = log-sum-exp
+template <int kNE>
 __device__ __forceinline__ void f_row_softmax(const float *srow, const uint8_t *loc_r, const uint16_t *pe_r,
                                               const float *__restrict__ table, int H, int h, int M, int U, int lane,
                                               float (&pv)[kNE], int (&col)[kNE], float &lse) {
@@ -281,28 +282,37 @@ __device__ __forceinline__ void f_row_softmax(const float *srow, const uint8_t *
     lse = mx + logf(sum);
 }
 
-// write one token's values into its dense operand row (bf16/f16 view at the start of the S row), zero elsewhere
-template <typename T>
+// write one token's values into its dense operand row (bf16/f16 view at the start of the S row), zero elsewhere.
+// Tiles in which a token lists a row twice (the padded slots of the last cluster all point at row 0) accumulate in
+// fp32 with shared-memory atomics over the row's fp32 footprint and convert in place afterwards.
+template <typename T, int kNE>
 __device__ __forceinline__ void f_scatter_row(T *prow, int Upad, int M, bool dup, int lane, const float (&pv)[kNE],
                                               const int (&col)[kNE]) {
-    for (int w = lane; w < Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
-    __syncwarp();
     if (!dup) {
+        for (int w = lane; w < Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
+        __syncwarp();
 #pragma unroll
         for (int e = 0; e < kNE; ++e)
             if (lane + 32 * e <= M) prow[col[e]] = Elem<T>::from_acc(pv[e]);
-    } else {  // a token lists a row more than once (padded slots all point at row 0): accumulate in slot order
+    } else {
+        float *frow = reinterpret_cast<float *>(prow);
+        for (int w = lane; w < Upad; w += 32) frow[w] = 0.f;
+        __syncwarp();
 #pragma unroll
         for (int e = 0; e < kNE; ++e)
-            for (int l = 0; l < 32; ++l) {
-                if (lane == l && l + 32 * e <= M)
-                    prow[col[e]] = Elem<T>::from_acc(Elem<T>::to_acc(prow[col[e]]) + pv[e]);
-                __syncwarp();
-            }
+            if (lane + 32 * e <= M) atomicAdd(frow + col[e], pv[e]);
+        __syncwarp();
+        float tmp[8];  // Upad <= 256
+#pragma unroll
+        for (int k = 0; k < 8; ++k) tmp[k] = (lane + 32 * k < Upad) ? frow[lane + 32 * k] : 0.f;
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            if (lane + 32 * k < Upad) prow[lane + 32 * k] = Elem<T>::from_acc(tmp[k]);
     }
 }
 
-template <typename T, int C>
+template <typename T, int C, int kNE>
 __global__ void __launch_bounds__(kFT)
 fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float *__restrict__ table,
                       const float *__restrict__ blank_k, const float *__restrict__ blank_v,
@@ -345,11 +355,11 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
             }
             float pv[kNE], l;
             int col[kNE];
-            f_row_softmax(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
+            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
                           pv, col, l);
             if (lane == 0) lse[(int64_t(b) * H + h) * N + t.t0 + i] = l;
             __syncwarp();
-            f_scatter_row<T>(prow, t.Upad, M, t.dup, lane, pv, col);
+            f_scatter_row<T, kNE>(prow, t.Upad, M, t.dup, lane, pv, col);
         }
         __syncthreads();
         f_mma_pv_store<T, C>(sp, L.RS, vs, os, TT, t.Upad, t.ti, 1.f, out.row(b, t.t0, h), out.sN);
@@ -361,7 +371,7 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
 // Backward, query-tile half.  Emits dQ, and dS / P in [B][H][N][M] for the key-tile scatter kernels and the table
 // gradient; per-tile partial sums of the blank-token gradients go to blank_part [B][tiles][H][2][C] (fp32).
 // ---------------------------------------------------------------------------------------------------------
-template <typename T, int C>
+template <typename T, int C, int kNE>
 __global__ void __launch_bounds__(kFT)
 fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout, ViewW<T> dq,
                       const float *__restrict__ table, const float *__restrict__ blank_k,
@@ -424,7 +434,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
             for (int o = 16; o > 0; o >>= 1) dl += __shfl_xor_sync(0xffffffffu, dl, o);
             float pv[kNE], l;
             int col[kNE];
-            f_row_softmax(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
+            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
                           pv, col, l);
             // (the recomputed log-sum-exp equals the saved one up to rounding; the saved value is not needed)
             const float *dprow = reinterpret_cast<const float *>(dp + size_t(i) * L.RS);
@@ -450,7 +460,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
             acc_bk += scale * dsb * qv;
             acc_bv += pb * dov;
             __syncwarp();
-            f_scatter_row<T>(prow, t.Upad, M, t.dup, lane, dsv, col);
+            f_scatter_row<T, kNE>(prow, t.Upad, M, t.dup, lane, dsv, col);
         }
         if (lane < C) {
             bl[(warp * 2 + 0) * C + lane] = acc_bk;
@@ -533,9 +543,9 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
         using T0 = decltype(tag);
         if constexpr (std::is_same<T0, __half>::value || std::is_same<T0, __nv_bfloat16>::value) {
             using T = T0;
-#define AFF_F(C_)                                                                                                  \
+#define AFF_F(C_, NE_)                                                                                                  \
     do {                                                                                                           \
-        auto kern = fused_attn_fwd_kernel<T, C_>;                                                                  \
+        auto kern = fused_attn_fwd_kernel<T, C_, NE_>;                                                             \
         if (L.total > 48 * 1024 &&                                                                                 \
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.total)) != cudaSuccess)  \
             return check_launch("cudaFuncSetAttribute", 0);                                                        \
@@ -543,7 +553,9 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
                                          blank_k, blank_v, plan->q_hdr, plan->q_rows, plan->q_loc, q_pe, lse,      \
                                          int(H), int(N), int(M), TT, scale, L);                                    \
     } while (0)
-            if (c == 32) AFF_F(32); else AFF_F(16);
+            const int ne = int((M + 1 + 31) / 32);
+            if (c == 32) { if (ne <= 2) AFF_F(32, 2); else if (ne <= 5) AFF_F(32, 5); else AFF_F(32, 7); }
+            else { if (ne <= 2) AFF_F(16, 2); else if (ne <= 5) AFF_F(16, 5); else AFF_F(16, 7); }
 #undef AFF_F
             return check_launch("fused_attn_fwd");
         } else {
@@ -581,9 +593,9 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
         using T0 = decltype(tag);
         if constexpr (std::is_same<T0, __half>::value || std::is_same<T0, __nv_bfloat16>::value) {
             using T = T0;
-#define AFF_B(C_)                                                                                                  \
+#define AFF_B(C_, NE_)                                                                                                  \
     do {                                                                                                           \
-        auto kern = fused_attn_bwd_kernel<T, C_>;                                                                  \
+        auto kern = fused_attn_bwd_kernel<T, C_, NE_>;                                                             \
         if (L.total > 48 * 1024 &&                                                                                 \
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.total)) != cudaSuccess)  \
             return check_launch("cudaFuncSetAttribute", 0);                                                        \
@@ -592,7 +604,9 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
                                          plan->q_rows, plan->q_loc, q_pe, lse, (T *)ds_work, (T *)p_work,          \
                                          blank_part, int(H), int(N), int(M), TT, scale, L);                        \
     } while (0)
-            if (c == 32) AFF_B(32); else AFF_B(16);
+            const int ne = int((M + 1 + 31) / 32);
+            if (c == 32) { if (ne <= 2) AFF_B(32, 2); else if (ne <= 5) AFF_B(32, 5); else AFF_B(32, 7); }
+            else { if (ne <= 2) AFF_B(16, 2); else if (ne <= 5) AFF_B(16, 5); else AFF_B(16, 7); }
 #undef AFF_B
             if (int e = check_launch("fused_attn_bwd")) return e;
             // dK = scale * scatter(dS, Q) ; dV = scatter(P, dO): key-tile ownership, no atomics
