@@ -88,35 +88,44 @@ attn_bias_bwd_global_kernel(const T *__restrict__ d_attn, const int64_t *__restr
 }
 
 // same histogram scheme, indices taken from the fused-attention plan's packed uint16 form (bit 15 = masked slot)
+constexpr int kTG = 512;
 template <typename T>
-__global__ void __launch_bounds__(kBT)
+__global__ void __launch_bounds__(kTG)
 table_grad_u16_kernel(const T *__restrict__ d_vals, const uint16_t *__restrict__ pe, int H, int64_t NM, int64_t total,
                       int P, float *__restrict__ d_table) {
     extern __shared__ float hist[];
-    uint32_t *touched = reinterpret_cast<uint32_t *>(hist + P);
-    const int nw = (P + 31) >> 5;
     const int h = blockIdx.y;
-    for (int p = threadIdx.x; p < P; p += kBT) hist[p] = 0.f;
-    for (int w = threadIdx.x; w < nw; w += kBT) touched[w] = 0u;
+    for (int p = threadIdx.x; p < P; p += kTG) hist[p] = 0.f;
     __syncthreads();
-    const int64_t per = (total + gridDim.x - 1) / gridDim.x;
-    const int64_t t0 = int64_t(blockIdx.x) * per, t1 = min(total, t0 + per);
-    for (int64_t t = t0 + threadIdx.x; t < t1; t += kBT) {
-        const int64_t b = t / NM;
-        const int64_t r = t - b * NM;
-        const int p = int(__ldg(pe + t) & 0x7fffu);
-        atomicAdd(hist + p, Elem<T>::to_acc(__ldg(d_vals + (b * H + h) * NM + r)));
-        atomicOr(touched + (p >> 5), 1u << (p & 31));
+    // chunk boundaries are multiples of 8 entries so that every thread handles 8 consecutive entries with one
+    // 16-byte load of the indices and one of the values (NM is a multiple of 8 whenever M is)
+    const int64_t groups = (total + 7) / 8;
+    const int64_t per = (groups + gridDim.x - 1) / gridDim.x;
+    const int64_t g0 = int64_t(blockIdx.x) * per, g1 = min(groups, g0 + per);
+    const bool vec = (NM % 8 == 0) && sizeof(T) == 2;
+    for (int64_t g = g0 + threadIdx.x; g < g1; g += kTG) {
+        const int64_t t = g * 8;
+        if (vec) {
+            const int64_t b = t / NM;
+            const int64_t r = t - b * NM;
+            const uint4 pv = __ldg(reinterpret_cast<const uint4 *>(pe + t));
+            const uint4 dv = __ldg(reinterpret_cast<const uint4 *>(d_vals + (b * H + h) * NM + r));
+            const uint16_t *p8 = reinterpret_cast<const uint16_t *>(&pv);
+            const T *d8 = reinterpret_cast<const T *>(&dv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) atomicAdd(hist + (p8[k] & 0x7fffu), Elem<T>::to_acc(d8[k]));
+        } else {
+            for (int k = 0; k < 8 && t + k < total; ++k) {
+                const int64_t b = (t + k) / NM;
+                const int64_t r = (t + k) - b * NM;
+                atomicAdd(hist + (__ldg(pe + t + k) & 0x7fffu), Elem<T>::to_acc(__ldg(d_vals + (b * H + h) * NM + r)));
+            }
+        }
     }
     __syncthreads();
-    for (int w = threadIdx.x; w < nw; w += kBT) {
-        uint32_t bits = touched[w];
-        while (bits) {
-            const int bit = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const int p = (w << 5) + bit;
-            atomicAdd(d_table + int64_t(p) * H + h, hist[p]);
-        }
+    for (int p = threadIdx.x; p < P; p += kTG) {
+        const float v = hist[p];
+        if (v != 0.f) atomicAdd(d_table + int64_t(p) * H + h, v);
     }
 }
 
@@ -125,7 +134,7 @@ int launch_table_grad_u16(const void *d_vals, const uint16_t *pe, int64_t B, int
     if (cudaMemsetAsync(d_table, 0, size_t(P * H) * 4, st) != cudaSuccess) return check_launch("table_grad memset", 0);
     const int64_t total = B * NM;
     if (total == 0) return AFFB200_OK;
-    const size_t smem = size_t(P) * 4 + size_t((P + 31) / 32) * 4;  // P <= 32768 -> <= 132 KB
+    const size_t smem = size_t(P) * 4;  // P <= 32768 -> <= 128 KB
     return dispatch_dtype(dtype, [&](auto tag) {
         using T = decltype(tag);
         auto kern = table_grad_u16_kernel<T>;
@@ -133,7 +142,7 @@ int launch_table_grad_u16(const void *d_vals, const uint16_t *pe, int64_t B, int
         const int per_sm = smem > 100 * 1024 ? 1 : 2;
         int chunks = int(std::max<int64_t>(1, (int64_t(kNumSMs) * per_sm) / H));
         chunks = int(std::min<int64_t>(chunks, (total + 4095) / 4096));
-        kern<<<dim3(unsigned(chunks), unsigned(H)), kBT, smem, st>>>((const T *)d_vals, pe, int(H), NM, total, int(P),
+        kern<<<dim3(unsigned(chunks), unsigned(H)), kTG, smem, st>>>((const T *)d_vals, pe, int(H), NM, total, int(P),
                                                                      d_table);
         return check_launch("table_grad_u16");
     });

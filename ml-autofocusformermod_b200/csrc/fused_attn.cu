@@ -109,17 +109,28 @@ __host__ __device__ inline FusedSmem fused_smem(int UC, int TT, int C, int M, bo
     return s;
 }
 
-// stage n_rows rows of C elements (row_ptr(i) == nullptr -> zero fill; row `skip` is left alone) into padded rows
-// of stride C+8.  `safe` is any valid global address (cp.async with src-size 0 never dereferences it).
-template <typename T, int C, typename RowPtr>
-__device__ __forceinline__ void f_stage_rows(T *dst, int n_rows, int skip, const T *safe, RowPtr row_ptr) {
+// Staging (16-byte cp.async into padded rows of stride C+8).  All address arithmetic per chunk is 32-bit: the caller
+// passes a base pointer that already includes the batch and head offsets.
+//   f_stage_gather: row i comes from base + off_s[i] (element offset, < 0 -> zero fill); row `skip` is left alone
+//   f_stage_tile:   row i comes from base + i*stride for i < n_valid, zero fill above
+template <typename T, int C>
+__device__ __forceinline__ void f_stage_gather(T *dst, int n_rows, int skip, const T *base, const int *off_s) {
     constexpr int CS = C + 8;
-    constexpr int CH = C * 2 / 16;
+    constexpr int CH = C / 8;
     for (int q = threadIdx.x; q < n_rows * CH; q += kFT) {
-        const int i = q / CH, ch = q - i * CH;
+        const int i = q / CH, ch = q % CH;
         if (i == skip) continue;
-        const T *src = row_ptr(i);
-        f_cp_async16(dst + i * CS + ch * 8, src ? src + ch * 8 : safe, src != nullptr);
+        const int off = off_s[i];
+        f_cp_async16(dst + i * CS + ch * 8, base + (off < 0 ? 0 : off) + ch * 8, off >= 0);
+    }
+}
+template <typename T, int C>
+__device__ __forceinline__ void f_stage_tile(T *dst, int n_rows, int n_valid, const T *base, int stride) {
+    constexpr int CS = C + 8;
+    constexpr int CH = C / 8;
+    for (int q = threadIdx.x; q < n_rows * CH; q += kFT) {
+        const int i = q / CH, ch = q % CH;
+        f_cp_async16(dst + i * CS + ch * 8, base + (i < n_valid ? i * stride : 0) + ch * 8, i < n_valid);
     }
 }
 
@@ -221,10 +232,11 @@ struct TileHdr {
     bool dup;
 };
 
-// common prologue: tile header, union rows, 1-byte positions and packed bias indices -> shared memory
+// common prologue: tile header, union rows (as element offsets row*kv_stride, -1 = none), 1-byte positions and
+// packed bias indices -> shared memory
 __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32_t *q_rows, const uint8_t *q_loc,
-                                               const uint16_t *q_pe, int N, int M, int TT, int UC, int *rows_s,
-                                               uint8_t *loc_s, uint16_t *pe_s) {
+                                               const uint16_t *q_pe, int N, int M, int TT, int UC, int kv_stride,
+                                               int *rows_s, uint8_t *loc_s, uint16_t *pe_s) {
     TileHdr t;
     const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x, tid = threadIdx.x;
     t.t0 = tile * TT;
@@ -234,11 +246,18 @@ __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32
     t.dup = (hdr & AFFB200_PLAN_DUP) != 0;
     t.Upad = (t.U + 1 + 15) & ~15;
     const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * AFFB200_PLAN_UMAX;
-    for (int u = tid; u < UC; u += kFT) rows_s[u] = u < t.U ? rg[u] : -1;
+    for (int u = tid; u < UC; u += kFT) rows_s[u] = u < t.U ? rg[u] * kv_stride : -1;
     const int n_ent = t.ti * M;
     const uint8_t *lg = q_loc + (int64_t(b) * N + t.t0) * M;
     const uint16_t *pg = q_pe + (int64_t(b) * N + t.t0) * M;
-    for (int p = tid; p < n_ent; p += kFT) { loc_s[p] = lg[p]; pe_s[p] = pg[p]; }
+    if ((M & 15) == 0) {  // 16-byte aligned rows: vector loads
+        const uint4 *l4 = reinterpret_cast<const uint4 *>(lg);
+        const uint4 *p4 = reinterpret_cast<const uint4 *>(pg);
+        for (int p = tid; p < n_ent / 16; p += kFT) reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(l4 + p);
+        for (int p = tid; p < n_ent / 8; p += kFT) reinterpret_cast<uint4 *>(pe_s)[p] = __ldg(p4 + p);
+    } else {
+        for (int p = tid; p < n_ent; p += kFT) { loc_s[p] = lg[p]; pe_s[p] = pg[p]; }
+    }
     return t;
 }
 
@@ -246,7 +265,7 @@ __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32
 // their column positions in col[]; lse = log-sum-exp
 template <int kNE>
 __device__ __forceinline__ void f_row_softmax(const float *srow, const uint8_t *loc_r, const uint16_t *pe_r,
-                                              const float *__restrict__ table, int H, int h, int M, int U, int lane,
+                                              const float *__restrict__ table_h /* table + h */, int H, int M, int U, int lane,
                                               float (&pv)[kNE], int (&col)[kNE], float &lse) {
     float mx = -INFINITY;
 #pragma unroll
@@ -257,7 +276,7 @@ __device__ __forceinline__ void f_row_softmax(const float *srow, const uint8_t *
         if (j < M) {
             c = loc_r[j];
             const uint32_t pe = pe_r[j];
-            s = srow[c] + __ldg(table + int64_t(pe & 0x7fffu) * H + h) + ((pe & 0x8000u) ? -100.f : 0.f);
+            s = srow[c] + __ldg(table_h + int(pe & 0x7fffu) * H) + ((pe & 0x8000u) ? -100.f : 0.f);
         } else if (j == M) {
             c = U;
             s = srow[U];
@@ -276,10 +295,10 @@ __device__ __forceinline__ void f_row_softmax(const float *srow, const uint8_t *
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    const float inv = 1.f / sum;
+    const float inv = __fdividef(1.f, sum);
 #pragma unroll
     for (int e = 0; e < kNE; ++e) pv[e] *= inv;
-    lse = mx + logf(sum);
+    lse = mx + __logf(sum);
 }
 
 // write one token's values into its dense operand row (bf16/f16 view at the start of the S row), zero elsewhere.
@@ -289,7 +308,7 @@ template <typename T, int kNE>
 __device__ __forceinline__ void f_scatter_row(T *prow, int Upad, int M, bool dup, int lane, const float (&pv)[kNE],
                                               const int (&col)[kNE]) {
     if (!dup) {
-        for (int w = lane; w < Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
+        if (lane < Upad / 8) reinterpret_cast<uint4 *>(prow)[lane] = make_uint4(0u, 0u, 0u, 0u);  // Upad <= 256
         __syncwarp();
 #pragma unroll
         for (int e = 0; e < kNE; ++e)
@@ -331,13 +350,13 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
     float *os = reinterpret_cast<float *>(smem + L.os);
 
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, rows_s, loc_s, pe_s);
+    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, int(k.sN), rows_s, loc_s, pe_s);
     __syncthreads();
 
     for (int h = 0; h < H; ++h) {
-        f_stage_rows<T, C>(xs, TT, -1, q.p, [&](int i) { return i < t.ti ? q.row(b, t.t0 + i, h) : nullptr; });
-        f_stage_rows<T, C>(ks, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? k.row(b, rows_s[i], h) : nullptr; });
-        f_stage_rows<T, C>(vs, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? v.row(b, rows_s[i], h) : nullptr; });
+        f_stage_tile<T, C>(xs, TT, t.ti, q.row(b, t.t0, h), int(q.sN));
+        f_stage_gather<T, C>(ks, t.Upad, t.U, k.row(b, 0, h), rows_s);
+        f_stage_gather<T, C>(vs, t.Upad, t.U, v.row(b, 0, h), rows_s);
         f_cp_async_commit();
         if (tid < C) {  // the blank token is key/value row U
             ks[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_k + h * C + tid));
@@ -350,12 +369,12 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
         for (int i = warp; i < TT; i += 8) {
             T *prow = reinterpret_cast<T *>(sp + size_t(i) * L.RS);
             if (i >= t.ti) {
-                for (int w = lane; w < t.Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
+                if (lane < t.Upad / 8) reinterpret_cast<uint4 *>(prow)[lane] = make_uint4(0u, 0u, 0u, 0u);
                 continue;
             }
             float pv[kNE], l;
             int col[kNE];
-            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
+            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table + h, H, M, t.U, lane,
                           pv, col, l);
             if (lane == 0) lse[(int64_t(b) * H + h) * N + t.t0 + i] = l;
             __syncwarp();
@@ -395,15 +414,15 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
     float *bl = reinterpret_cast<float *>(smem + L.bl);  // [8 warps][2][C]
 
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, rows_s, loc_s, pe_s);
+    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, int(k.sN), rows_s, loc_s, pe_s);
     __syncthreads();
     const int e_blank = M >> 5, l_blank = M & 31;  // (slot, lane) that owns the blank logit
 
     for (int h = 0; h < H; ++h) {
-        f_stage_rows<T, C>(xs, TT, -1, q.p, [&](int i) { return i < t.ti ? q.row(b, t.t0 + i, h) : nullptr; });
-        f_stage_rows<T, C>(dos, TT, -1, q.p, [&](int i) { return i < t.ti ? dout.row(b, t.t0 + i, h) : nullptr; });
-        f_stage_rows<T, C>(ks, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? k.row(b, rows_s[i], h) : nullptr; });
-        f_stage_rows<T, C>(vs, t.Upad, t.U, q.p, [&](int i) { return rows_s[i] >= 0 ? v.row(b, rows_s[i], h) : nullptr; });
+        f_stage_tile<T, C>(xs, TT, t.ti, q.row(b, t.t0, h), int(q.sN));
+        f_stage_tile<T, C>(dos, TT, t.ti, dout.row(b, t.t0, h), int(dout.sN));
+        f_stage_gather<T, C>(ks, t.Upad, t.U, k.row(b, 0, h), rows_s);
+        f_stage_gather<T, C>(vs, t.Upad, t.U, v.row(b, 0, h), rows_s);
         f_cp_async_commit();
         if (tid < C) {
             ks[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_k + h * C + tid));
@@ -419,7 +438,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
         for (int i = warp; i < TT; i += 8) {
             T *prow = reinterpret_cast<T *>(sp + size_t(i) * L.RS);
             if (i >= t.ti) {
-                for (int w = lane; w < t.Upad / 2; w += 32) reinterpret_cast<uint32_t *>(prow)[w] = 0u;
+                if (lane < t.Upad / 8) reinterpret_cast<uint4 *>(prow)[lane] = make_uint4(0u, 0u, 0u, 0u);
                 continue;
             }
             const int64_t tok = t.t0 + i;
@@ -434,7 +453,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
             for (int o = 16; o > 0; o >>= 1) dl += __shfl_xor_sync(0xffffffffu, dl, o);
             float pv[kNE], l;
             int col[kNE];
-            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table, H, h, M, t.U, lane,
+            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table + h, H, M, t.U, lane,
                           pv, col, l);
             // (the recomputed log-sum-exp equals the saved one up to rounding; the saved value is not needed)
             const float *dprow = reinterpret_cast<const float *>(dp + size_t(i) * L.RS);
@@ -488,6 +507,10 @@ using namespace affb200;
 template <typename T> static View<T> mk_view(const affb200_view *v) { return View<T>{(const T *)v->p, v->sB, v->sN, v->sH}; }
 template <typename T> static ViewW<T> mk_vieww(const affb200_view *v) { return ViewW<T>{(T *)v->p, v->sB, v->sN, v->sH}; }
 
+static bool kv_ok(const affb200_view *k, const affb200_view *v, int64_t N) {
+    // the kernels index gathered rows with 32-bit element offsets row * sN shared by k and v
+    return k->sN == v->sN && k->sN > 0 && N * k->sN < (int64_t(1) << 31);
+}
 static bool view_ok(const affb200_view *v, int64_t c) {
     // rows must be 16-byte aligned for cp.async / 128-bit stores
     return v && v->p && (reinterpret_cast<uintptr_t>(v->p) & 15) == 0 && (v->sB * 2) % 16 == 0 && (v->sN * 2) % 16 == 0 &&
@@ -506,6 +529,7 @@ static int fused_common_check(const char *what, const affb200_nbhd_plan *plan, c
         set_error("%s: a query-tile plan and packed bias indices are required", what);
         return AFFB200_E_ARG;
     }
+    if (N > AFFB200_PLAN_MAX_NK) { set_error("%s: N > %d", what, AFFB200_PLAN_MAX_NK); return AFFB200_E_ARG; }
     if (umax < 0 || umax > AFFB200_PLAN_UMAX - 1) {
         set_error("%s: a tile references %d distinct rows; the fused kernel holds at most %d plus the blank token", what,
                   umax, AFFB200_PLAN_UMAX - 1);
@@ -533,6 +557,7 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
         set_error("fused_attn_fwd: null or misaligned operand (rows must be 16-byte aligned)");
         return AFFB200_E_ARG;
     }
+    if (!kv_ok(k, v, N) || N * q->sN >= (int64_t(1) << 31)) { set_error("fused_attn_fwd: k/v token strides must match and fit int32"); return AFFB200_E_ARG; }
     const int TT = plan->tq;
     const int UC = (umax + 1 + 31) & ~31;
     const FusedSmem L = fused_smem(UC, TT, int(c), int(M), false);
@@ -578,6 +603,7 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
         set_error("fused_attn_bwd: null or misaligned operand");
         return AFFB200_E_ARG;
     }
+    if (!kv_ok(k, v, N) || N * q->sN >= (int64_t(1) << 31) || N * dout->sN >= (int64_t(1) << 31)) { set_error("fused_attn_bwd: k/v token strides must match and fit int32"); return AFFB200_E_ARG; }
     if (plan->tk <= 0 || !plan->k_hdr || !plan->k_utok || !plan->k_rloc) {
         set_error("fused_attn_bwd: a key-tile plan is required");
         return AFFB200_E_ARG;
