@@ -224,7 +224,8 @@ __device__ __forceinline__ void f_mma_pv_store(const unsigned char *sp, int RS, 
     }
 }
 
-// NE = logits per lane = ceil((M + 1) / 32): 2 for nbhd 48, 5 for nbhd 144, 7 up to M = 192
+// Row phase mapping: TPR = 256 / TT threads share one token row (a contiguous lane group); thread `sub` owns the
+// logits j = sub + TPR*e, e < NE, NE >= ceil((M + 1) / TPR).  All TT rows of the tile are processed in one pass.
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct TileHdr {
@@ -261,84 +262,105 @@ __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32
     return t;
 }
 
-// softmax of one token's M+1 logits, read from its dense fp32 S row; returns normalised probabilities in pv[] and
-// their column positions in col[]; lse = log-sum-exp
-template <int kNE>
-__device__ __forceinline__ void f_row_softmax(const float *srow, const uint8_t *loc_r, const uint16_t *pe_r,
-                                              const float *__restrict__ table_h /* table + h */, int H, int M, int U, int lane,
-                                              float (&pv)[kNE], int (&col)[kNE], float &lse) {
+__device__ __forceinline__ float f_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+template <int TPR> __device__ __forceinline__ float f_group_max(float v) {
+#pragma unroll
+    for (int o = TPR / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+template <int TPR> __device__ __forceinline__ float f_group_sum(float v) {
+#pragma unroll
+    for (int o = TPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// softmax of one token's M+1 logits by its TPR threads: gathers S[row][loc] + bias (+ -100 at padded slots), the blank
+// logit S[row][U]; leaves the normalised probabilities of this thread's slots in pv[] and returns the log-sum-exp
+template <int TPR, int NE>
+__device__ __forceinline__ float f_row_softmax(const float *srow, const uint8_t *loc_r, const uint16_t *pe_r,
+                                               const float *__restrict__ table_h, int H, int M, int U, int sub,
+                                               bool live, float (&pv)[NE]) {
     float mx = -INFINITY;
 #pragma unroll
-    for (int e = 0; e < kNE; ++e) {
-        const int j = lane + 32 * e;
+    for (int e = 0; e < NE; ++e) {
+        const int j = sub + TPR * e;
         float s = -INFINITY;
-        int c = 0;
-        if (j < M) {
-            c = loc_r[j];
-            const uint32_t pe = pe_r[j];
-            s = srow[c] + __ldg(table_h + int(pe & 0x7fffu) * H) + ((pe & 0x8000u) ? -100.f : 0.f);
-        } else if (j == M) {
-            c = U;
-            s = srow[U];
+        if (live) {
+            if (j < M) {
+                const uint32_t pe = pe_r[j];
+                s = srow[loc_r[j]] + __ldg(table_h + int(pe & 0x7fffu) * H) + ((pe & 0x8000u) ? -100.f : 0.f);
+            } else if (j == M) {
+                s = srow[U];
+            }
         }
         pv[e] = s;
-        col[e] = c;
         mx = fmaxf(mx, s);
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mx = f_group_max<TPR>(mx);
+    if (!live) mx = 0.f;
     float sum = 0.f;
 #pragma unroll
-    for (int e = 0; e < kNE; ++e) {
-        pv[e] = exp2f((pv[e] - mx) * kLog2e);  // exp2f(-inf) = 0 for the unused lanes
+    for (int e = 0; e < NE; ++e) {
+        pv[e] = f_ex2((pv[e] - mx) * kLog2e);  // ex2(-inf) = 0 for the unused slots
         sum += pv[e];
     }
+    sum = f_group_sum<TPR>(sum);
+    const float inv = live ? __fdividef(1.f, sum) : 0.f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    const float inv = __fdividef(1.f, sum);
-#pragma unroll
-    for (int e = 0; e < kNE; ++e) pv[e] *= inv;
-    lse = mx + __logf(sum);
+    for (int e = 0; e < NE; ++e) pv[e] *= inv;
+    return mx + __logf(sum);
 }
 
-// write one token's values into its dense operand row (bf16/f16 view at the start of the S row), zero elsewhere.
+// write a token's values into its dense operand row (bf16/f16 view at the start of its S row), zero elsewhere.
 // Tiles in which a token lists a row twice (the padded slots of the last cluster all point at row 0) accumulate in
 // fp32 with shared-memory atomics over the row's fp32 footprint and convert in place afterwards.
-template <typename T, int kNE>
-__device__ __forceinline__ void f_scatter_row(T *prow, int Upad, int M, bool dup, int lane, const float (&pv)[kNE],
-                                              const int (&col)[kNE]) {
+template <typename T, int TPR, int NE>
+__device__ __forceinline__ void f_scatter_row(T *prow, const uint8_t *loc_r, int Upad, int M, int U, bool dup, int sub,
+                                              bool live, const float (&pv)[NE]) {
     if (!dup) {
-        if (lane < Upad / 8) reinterpret_cast<uint4 *>(prow)[lane] = make_uint4(0u, 0u, 0u, 0u);  // Upad <= 256
+        for (int w = sub; w < Upad / 8; w += TPR) reinterpret_cast<uint4 *>(prow)[w] = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();
+        if (live) {
 #pragma unroll
-        for (int e = 0; e < kNE; ++e)
-            if (lane + 32 * e <= M) prow[col[e]] = Elem<T>::from_acc(pv[e]);
+            for (int e = 0; e < NE; ++e) {
+                const int j = sub + TPR * e;
+                if (j <= M) prow[j < M ? loc_r[j] : U] = Elem<T>::from_acc(pv[e]);
+            }
+        }
     } else {
         float *frow = reinterpret_cast<float *>(prow);
-        for (int w = lane; w < Upad; w += 32) frow[w] = 0.f;
+        for (int w = sub; w < Upad; w += TPR) frow[w] = 0.f;
         __syncwarp();
+        if (live) {
 #pragma unroll
-        for (int e = 0; e < kNE; ++e)
-            if (lane + 32 * e <= M) atomicAdd(frow + col[e], pv[e]);
+            for (int e = 0; e < NE; ++e) {
+                const int j = sub + TPR * e;
+                if (j <= M) atomicAdd(frow + (j < M ? loc_r[j] : U), pv[e]);
+            }
+        }
         __syncwarp();
-        float tmp[8];  // Upad <= 256
-#pragma unroll
-        for (int k = 0; k < 8; ++k) tmp[k] = (lane + 32 * k < Upad) ? frow[lane + 32 * k] : 0.f;
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-            if (lane + 32 * k < Upad) prow[lane + 32 * k] = Elem<T>::from_acc(tmp[k]);
+        for (int base = 0; base < Upad; base += TPR) {  // in-place fp32 -> T, front to back
+            const float vv = frow[base + sub];
+            __syncwarp();
+            prow[base + sub] = Elem<T>::from_acc(vv);
+            __syncwarp();
+        }
     }
 }
 
-template <typename T, int C, int kNE>
+template <typename T, int C, int TT, int NE>
 __global__ void __launch_bounds__(kFT)
 fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float *__restrict__ table,
                       const float *__restrict__ blank_k, const float *__restrict__ blank_v,
                       const int32_t *__restrict__ q_hdr, const int32_t *__restrict__ q_rows,
                       const uint8_t *__restrict__ q_loc, const uint16_t *__restrict__ q_pe, float *__restrict__ lse,
-                      int H, int N, int M, int TT, float scale, FusedSmem L) {
+                      int H, int N, int M, float scale, FusedSmem L) {
     constexpr int CS = C + 8;
+    constexpr int TPR = kFT / TT;
     extern __shared__ __align__(128) unsigned char smem[];
     int *rows_s = reinterpret_cast<int *>(smem + L.rows);
     T *ks = reinterpret_cast<T *>(smem + L.ks);
@@ -349,9 +371,12 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
     uint16_t *pe_s = reinterpret_cast<uint16_t *>(smem + L.pe);
     float *os = reinterpret_cast<float *>(smem + L.os);
 
-    const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.y, tid = threadIdx.x;
     const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, int(k.sN), rows_s, loc_s, pe_s);
     __syncthreads();
+    const int i = tid / TPR, sub = tid % TPR;  // this thread's token row and its position in the row's group
+    const bool live = i < t.ti;
+    T *prow = reinterpret_cast<T *>(sp + i * L.RS);
 
     for (int h = 0; h < H; ++h) {
         f_stage_tile<T, C>(xs, TT, t.ti, q.row(b, t.t0, h), int(q.sN));
@@ -366,19 +391,13 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
         __syncthreads();
         f_mma_xyT<T, C>(xs, ks, sp, L.RS, TT, t.Upad, scale);
         __syncthreads();
-        for (int i = warp; i < TT; i += 8) {
-            T *prow = reinterpret_cast<T *>(sp + size_t(i) * L.RS);
-            if (i >= t.ti) {
-                if (lane < t.Upad / 8) reinterpret_cast<uint4 *>(prow)[lane] = make_uint4(0u, 0u, 0u, 0u);
-                continue;
-            }
-            float pv[kNE], l;
-            int col[kNE];
-            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table + h, H, M, t.U, lane,
-                          pv, col, l);
-            if (lane == 0) lse[(int64_t(b) * H + h) * N + t.t0 + i] = l;
+        {
+            float pv[NE];
+            const float l = f_row_softmax<TPR, NE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M,
+                                                   table + h, H, M, t.U, sub, live, pv);
+            if (live && sub == 0) lse[(int64_t(b) * H + h) * N + t.t0 + i] = l;
             __syncwarp();
-            f_scatter_row<T, kNE>(prow, t.Upad, M, t.dup, lane, pv, col);
+            f_scatter_row<T, TPR, NE>(prow, loc_s + i * M, t.Upad, M, t.U, t.dup, sub, live, pv);
         }
         __syncthreads();
         f_mma_pv_store<T, C>(sp, L.RS, vs, os, TT, t.Upad, t.ti, 1.f, out.row(b, t.t0, h), out.sN);
@@ -390,16 +409,18 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
 // Backward, query-tile half.  Emits dQ, and dS / P in [B][H][N][M] for the key-tile scatter kernels and the table
 // gradient; per-tile partial sums of the blank-token gradients go to blank_part [B][tiles][H][2][C] (fp32).
 // ---------------------------------------------------------------------------------------------------------
-template <typename T, int C, int kNE>
+template <typename T, int C, int TT, int NE>
 __global__ void __launch_bounds__(kFT)
 fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout, ViewW<T> dq,
                       const float *__restrict__ table, const float *__restrict__ blank_k,
                       const float *__restrict__ blank_v, const int32_t *__restrict__ q_hdr,
                       const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc,
                       const uint16_t *__restrict__ q_pe, const float *__restrict__ lse, T *__restrict__ ds_out,
-                      T *__restrict__ p_out, float *__restrict__ blank_part, int H, int N, int M, int TT, float scale,
+                      T *__restrict__ p_out, float *__restrict__ blank_part, int H, int N, int M, float scale,
                       FusedSmem L) {
     constexpr int CS = C + 8;
+    constexpr int TPR = kFT / TT;
+    constexpr int CPT = (C + TPR - 1) / TPR;  // channels per thread in the per-row channel reductions
     extern __shared__ __align__(128) unsigned char smem[];
     int *rows_s = reinterpret_cast<int *>(smem + L.rows);
     T *ks = reinterpret_cast<T *>(smem + L.ks);
@@ -416,7 +437,13 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, int(k.sN), rows_s, loc_s, pe_s);
     __syncthreads();
-    const int e_blank = M >> 5, l_blank = M & 31;  // (slot, lane) that owns the blank logit
+    const int i = tid / TPR, sub = tid % TPR;
+    const bool live = i < t.ti;
+    T *prow = reinterpret_cast<T *>(sp + i * L.RS);
+    const float *dprow = reinterpret_cast<const float *>(dp + i * L.RS);
+    const uint8_t *loc_r = loc_s + i * M;
+    const int e_blank = M / TPR, s_blank = M % TPR;  // (slot, group position) that owns the blank logit
+    const int64_t tok = t.t0 + i;
 
     for (int h = 0; h < H; ++h) {
         f_stage_tile<T, C>(xs, TT, t.ti, q.row(b, t.t0, h), int(q.sN));
@@ -434,56 +461,65 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
         f_mma_xyT<T, C>(dos, vs, dp, L.RS, TT, t.Upad, 1.f);    // dP = dO · V_U^T
         __syncthreads();
 
-        float acc_bk = 0.f, acc_bv = 0.f;  // lane c < C: this warp's share of d blank_k[h][c], d blank_v[h][c]
-        for (int i = warp; i < TT; i += 8) {
-            T *prow = reinterpret_cast<T *>(sp + size_t(i) * L.RS);
-            if (i >= t.ti) {
-                if (lane < t.Upad / 8) reinterpret_cast<uint4 *>(prow)[lane] = make_uint4(0u, 0u, 0u, 0u);
-                continue;
-            }
-            const int64_t tok = t.t0 + i;
-            // delta = dO_i · O_i
-            float dl = 0.f, qv = 0.f, dov = 0.f;
-            if (lane < C) {
-                dov = Elem<T>::to_acc(dos[i * CS + lane]);
-                qv = Elem<T>::to_acc(xs[i * CS + lane]);
-                dl = dov * Elem<T>::to_acc(__ldg(out.row(b, tok, h) + lane));
-            }
+        float acc_bk[CPT], acc_bv[CPT];
+        {
+            // delta = dO_i · O_i over this thread's channels, then over the row's group
+            float dl = 0.f, qv[CPT], dov[CPT];
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) dl += __shfl_xor_sync(0xffffffffu, dl, o);
-            float pv[kNE], l;
-            int col[kNE];
-            f_row_softmax<kNE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M, table + h, H, M, t.U, lane,
-                          pv, col, l);
-            // (the recomputed log-sum-exp equals the saved one up to rounding; the saved value is not needed)
-            const float *dprow = reinterpret_cast<const float *>(dp + size_t(i) * L.RS);
-            float dsv[kNE];
-            T *pg = p_out + ((int64_t(b) * H + h) * N + tok) * M;
-            T *dg = ds_out + ((int64_t(b) * H + h) * N + tok) * M;
-#pragma unroll
-            for (int e = 0; e < kNE; ++e) {
-                const int j = lane + 32 * e;
-                dsv[e] = (j <= M) ? pv[e] * (dprow[col[e]] - dl) : 0.f;
-                if (j < M) {
-                    pg[j] = Elem<T>::from_acc(pv[e]);
-                    dg[j] = Elem<T>::from_acc(dsv[e]);
+            for (int cc = 0; cc < CPT; ++cc) {
+                const int c = sub * CPT + cc;
+                qv[cc] = dov[cc] = 0.f;
+                if (live && c < C) {
+                    dov[cc] = Elem<T>::to_acc(dos[i * CS + c]);
+                    qv[cc] = Elem<T>::to_acc(xs[i * CS + c]);
+                    dl += dov[cc] * Elem<T>::to_acc(__ldg(out.row(b, tok, h) + c));
                 }
             }
-            // blank-token gradients
+            dl = f_group_sum<TPR>(dl);
+            float pv[NE];
+            f_row_softmax<TPR, NE>(reinterpret_cast<const float *>(prow), loc_r, pe_s + i * M, table + h, H, M, t.U, sub,
+                                   live, pv);
+            T *pg = p_out + ((int64_t(b) * H + h) * N + tok) * M;
+            T *dg = ds_out + ((int64_t(b) * H + h) * N + tok) * M;
             float pb = 0.f, dsb = 0.f;
 #pragma unroll
-            for (int e = 0; e < kNE; ++e)
-                if (e == e_blank) { pb = pv[e]; dsb = dsv[e]; }
-            pb = __shfl_sync(0xffffffffu, pb, l_blank);
-            dsb = __shfl_sync(0xffffffffu, dsb, l_blank);
-            acc_bk += scale * dsb * qv;
-            acc_bv += pb * dov;
+            for (int e = 0; e < NE; ++e) {
+                const int j = sub + TPR * e;
+                const float p = pv[e];
+                float ds = 0.f;
+                if (live && j <= M) ds = p * (dprow[j < M ? loc_r[j] : t.U] - dl);
+                if (live && j < M) {
+                    pg[j] = Elem<T>::from_acc(p);
+                    dg[j] = Elem<T>::from_acc(ds);
+                }
+                if (e == e_blank) { pb = p; dsb = ds; }
+                pv[e] = ds;
+            }
+            // blank-token gradients: broadcast the blank slot's (p, ds) within the row's group
+            const int src = (lane & ~(TPR - 1)) | s_blank;
+            pb = __shfl_sync(0xffffffffu, pb, src);
+            dsb = __shfl_sync(0xffffffffu, dsb, src);
+#pragma unroll
+            for (int cc = 0; cc < CPT; ++cc) {
+                acc_bk[cc] = scale * dsb * qv[cc];
+                acc_bv[cc] = pb * dov[cc];
+            }
             __syncwarp();
-            f_scatter_row<T, kNE>(prow, t.Upad, M, t.dup, lane, dsv, col);
+            f_scatter_row<T, TPR, NE>(prow, loc_r, t.Upad, M, t.U, t.dup, sub, live, pv);
         }
-        if (lane < C) {
-            bl[(warp * 2 + 0) * C + lane] = acc_bk;
-            bl[(warp * 2 + 1) * C + lane] = acc_bv;
+        // sum the blank partials over the rows of this warp (lanes with equal `sub`), then over the warps
+#pragma unroll
+        for (int cc = 0; cc < CPT; ++cc) {
+#pragma unroll
+            for (int o = TPR; o < 32; o <<= 1) {
+                acc_bk[cc] += __shfl_xor_sync(0xffffffffu, acc_bk[cc], o);
+                acc_bv[cc] += __shfl_xor_sync(0xffffffffu, acc_bv[cc], o);
+            }
+            const int c = sub * CPT + cc;
+            if (lane < TPR && c < C) {
+                bl[(warp * 2 + 0) * C + c] = acc_bk[cc];
+                bl[(warp * 2 + 1) * C + c] = acc_bv[cc];
+            }
         }
         __syncthreads();
         if (tid < 2 * C) {
@@ -568,19 +604,28 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
         using T0 = decltype(tag);
         if constexpr (std::is_same<T0, __half>::value || std::is_same<T0, __nv_bfloat16>::value) {
             using T = T0;
-#define AFF_F(C_, NE_)                                                                                                  \
+#define AFF_F(C_, TT_, NE_)                                                                                                 \
     do {                                                                                                           \
-        auto kern = fused_attn_fwd_kernel<T, C_, NE_>;                                                             \
+        auto kern = fused_attn_fwd_kernel<T, C_, TT_, NE_>;                                                        \
         if (L.total > 48 * 1024 &&                                                                                 \
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.total)) != cudaSuccess)  \
             return check_launch("cudaFuncSetAttribute", 0);                                                        \
         kern<<<grid, kFT, L.total, st>>>(mk_view<T>(q), mk_view<T>(k), mk_view<T>(v), mk_vieww<T>(out), table,     \
                                          blank_k, blank_v, plan->q_hdr, plan->q_rows, plan->q_loc, q_pe, lse,      \
-                                         int(H), int(N), int(M), TT, scale, L);                                    \
+                                         int(H), int(N), int(M), scale, L);                                        \
     } while (0)
-            const int ne = int((M + 1 + 31) / 32);
-            if (c == 32) { if (ne <= 2) AFF_F(32, 2); else if (ne <= 5) AFF_F(32, 5); else AFF_F(32, 7); }
-            else { if (ne <= 2) AFF_F(16, 2); else if (ne <= 5) AFF_F(16, 5); else AFF_F(16, 7); }
+            // (tile size, slots per thread): 256/TT threads per row, NE*256/TT >= M+1
+            const int need = int(M) + 1;
+#define AFF_FC(C_)                                                                                   \
+    do {                                                                                             \
+        if (TT == 16 && need <= 13 * 16) AFF_F(C_, 16, 13);                                          \
+        else if (TT == 32 && need <= 7 * 8) AFF_F(C_, 32, 7);                                        \
+        else if (TT == 32 && need <= 13 * 8) AFF_F(C_, 32, 13);                                      \
+        else if (TT == 64 && need <= 17 * 4) AFF_F(C_, 64, 17);                                      \
+        else { set_error("fused_attn: tile size %d does not support M = %d", TT, int(M)); return AFFB200_E_ARG; } \
+    } while (0)
+            if (c == 32) AFF_FC(32); else AFF_FC(16);
+#undef AFF_FC
 #undef AFF_F
             return check_launch("fused_attn_fwd");
         } else {
@@ -619,20 +664,29 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
         using T0 = decltype(tag);
         if constexpr (std::is_same<T0, __half>::value || std::is_same<T0, __nv_bfloat16>::value) {
             using T = T0;
-#define AFF_B(C_, NE_)                                                                                                  \
+#define AFF_B(C_, TT_, NE_)                                                                                                 \
     do {                                                                                                           \
-        auto kern = fused_attn_bwd_kernel<T, C_, NE_>;                                                             \
+        auto kern = fused_attn_bwd_kernel<T, C_, TT_, NE_>;                                                        \
         if (L.total > 48 * 1024 &&                                                                                 \
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(L.total)) != cudaSuccess)  \
             return check_launch("cudaFuncSetAttribute", 0);                                                        \
         kern<<<grid, kFT, L.total, st>>>(mk_view<T>(q), mk_view<T>(k), mk_view<T>(v), mk_view<T>(out),             \
                                          mk_view<T>(dout), mk_vieww<T>(dq), table, blank_k, blank_v, plan->q_hdr,  \
                                          plan->q_rows, plan->q_loc, q_pe, lse, (T *)ds_work, (T *)p_work,          \
-                                         blank_part, int(H), int(N), int(M), TT, scale, L);                        \
+                                         blank_part, int(H), int(N), int(M), scale, L);                            \
     } while (0)
-            const int ne = int((M + 1 + 31) / 32);
-            if (c == 32) { if (ne <= 2) AFF_B(32, 2); else if (ne <= 5) AFF_B(32, 5); else AFF_B(32, 7); }
-            else { if (ne <= 2) AFF_B(16, 2); else if (ne <= 5) AFF_B(16, 5); else AFF_B(16, 7); }
+            // (tile size, slots per thread): 256/TT threads per row, NE*256/TT >= M+1
+            const int need = int(M) + 1;
+#define AFF_BC(C_)                                                                                   \
+    do {                                                                                             \
+        if (TT == 16 && need <= 13 * 16) AFF_B(C_, 16, 13);                                          \
+        else if (TT == 32 && need <= 7 * 8) AFF_B(C_, 32, 7);                                        \
+        else if (TT == 32 && need <= 13 * 8) AFF_B(C_, 32, 13);                                      \
+        else if (TT == 64 && need <= 17 * 4) AFF_B(C_, 64, 17);                                      \
+        else { set_error("fused_attn: tile size %d does not support M = %d", TT, int(M)); return AFFB200_E_ARG; } \
+    } while (0)
+            if (c == 32) AFF_BC(32); else AFF_BC(16);
+#undef AFF_BC
 #undef AFF_B
             if (int e = check_launch("fused_attn_bwd")) return e;
             // dK = scale * scatter(dS, Q) ; dV = scatter(P, dO): key-tile ownership, no atomics
