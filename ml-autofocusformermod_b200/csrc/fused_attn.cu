@@ -267,6 +267,28 @@ __device__ __forceinline__ float f_ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// n contiguous elements (n*sizeof(T) in {2,4,8,16} bytes, naturally aligned) -> fp32
+template <typename T, int n> __device__ __forceinline__ void f_load_n(const T *p, float (&o)[n]) {
+    static_assert(sizeof(T) == 2 && (n == 1 || n == 2 || n == 4 || n == 8), "2-byte elements");
+    if constexpr (n == 1) {
+        o[0] = Elem<T>::to_acc(*p);
+    } else if constexpr (n == 2) {
+        const uint32_t r = *reinterpret_cast<const uint32_t *>(p);
+        const T *e = reinterpret_cast<const T *>(&r);
+        o[0] = Elem<T>::to_acc(e[0]); o[1] = Elem<T>::to_acc(e[1]);
+    } else if constexpr (n == 4) {
+        const uint2 r = *reinterpret_cast<const uint2 *>(p);
+        const T *e = reinterpret_cast<const T *>(&r);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) o[k] = Elem<T>::to_acc(e[k]);
+    } else {
+        const uint4 r = *reinterpret_cast<const uint4 *>(p);
+        const T *e = reinterpret_cast<const T *>(&r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = Elem<T>::to_acc(e[k]);
+    }
+}
+
 template <int TPR> __device__ __forceinline__ float f_group_max(float v) {
 #pragma unroll
     for (int o = TPR / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
@@ -464,17 +486,16 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
         float acc_bk[CPT], acc_bv[CPT];
         {
             // delta = dO_i · O_i over this thread's channels, then over the row's group
-            float dl = 0.f, qv[CPT], dov[CPT];
+            float dl = 0.f, qv[CPT], dov[CPT], ov[CPT];
 #pragma unroll
-            for (int cc = 0; cc < CPT; ++cc) {
-                const int c = sub * CPT + cc;
-                qv[cc] = dov[cc] = 0.f;
-                if (live && c < C) {
-                    dov[cc] = Elem<T>::to_acc(dos[i * CS + c]);
-                    qv[cc] = Elem<T>::to_acc(xs[i * CS + c]);
-                    dl += dov[cc] * Elem<T>::to_acc(__ldg(out.row(b, tok, h) + c));
-                }
+            for (int cc = 0; cc < CPT; ++cc) qv[cc] = dov[cc] = ov[cc] = 0.f;
+            if (live && sub * CPT < C) {
+                f_load_n<T, CPT>(dos + i * CS + sub * CPT, dov);
+                f_load_n<T, CPT>(xs + i * CS + sub * CPT, qv);
+                f_load_n<T, CPT>(out.row(b, tok, h) + sub * CPT, ov);
             }
+#pragma unroll
+            for (int cc = 0; cc < CPT; ++cc) dl += dov[cc] * ov[cc];
             dl = f_group_sum<TPR>(dl);
             float pv[NE];
             f_row_softmax<TPR, NE>(reinterpret_cast<const float *>(prow), loc_r, pe_s + i * M, table + h, H, M, t.U, sub,
