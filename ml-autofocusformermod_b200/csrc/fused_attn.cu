@@ -60,6 +60,7 @@ template <> __device__ __forceinline__ uint32_t f_pack2<__half>(float lo, float 
     return *reinterpret_cast<uint32_t *>(&v);
 }
 
+
 // strided [B][N][H][c] view of a Linear output: element (b, i, h, 0) at base + b*sB + i*sN + h*sH
 template <typename T> struct View {
     const T *p;
@@ -84,54 +85,93 @@ pe_pack_kernel(const int64_t *__restrict__ pe_idx, const int64_t *__restrict__ m
 }
 
 // ---- shared-memory carve-up (all offsets multiples of 16 bytes) --------------------------------------------
+// rows   union rows of the tile as element offsets into the k/v slab of one (batch, head)
+// ks/vs  K_U / V_U of the current head (padded rows of C+8); the backward keeps two K buffers so that the next
+//        head's keys load while dQ = dS·K_U still reads the current ones
+// xs/dos/outs  the tile's own Q / dO / O rows
+// sp     S (fp32) and, aliased row by row, P or dS (bf16);  dp  dP (fp32);  os  split-K partials of the output
+//        contraction (the backward lays it over dp, which is dead by then);  bl  blank-gradient partials
 struct FusedSmem {
     int UC;       // row capacity of the K/V staging buffers (multiple of 32, >= U+1)
-    int RS;       // byte stride of an S/P row: UC*4 + 16  (== 16 mod 128: conflict-free ldmatrix on the bf16 view)
-    size_t rows, ks, vs, xs, dos, sp, dp, loc, pe, os, bl, total;
+    int RS;       // byte stride of an S/P row: UC*4 + 16  (== 16 mod 128: conflict-free ldmatrix on the bf16 view;
+                  // the 4 spare floats hold the row's sentinel for unused slots)
+    size_t rows, ks, ks2, vs, xs, dos, outs, sp, dp, os, bl, total;
 };
-__host__ __device__ inline FusedSmem fused_smem(int UC, int TT, int C, int M, bool bwd) {
+__host__ __device__ inline FusedSmem fused_smem(int UC, int TT, int C, bool bwd) {
     FusedSmem s;
     s.UC = UC;
     s.RS = UC * 4 + 16;
+    const size_t kv = size_t(UC) * (C + 8) * 2, tile = size_t(TT) * (C + 8) * 2, srow = size_t(TT) * s.RS;
+    const size_t osz = size_t(8 * 16 * 16 * (C + 8) / C) * 4;
     size_t o = 0;
     s.rows = o; o += size_t(UC) * 4;
-    s.ks = o;   o += size_t(UC) * (C + 8) * 2;
-    s.vs = o;   o += size_t(UC) * (C + 8) * 2;
-    s.xs = o;   o += size_t(TT) * (C + 8) * 2;
-    s.dos = o;  o += bwd ? size_t(TT) * (C + 8) * 2 : 0;
-    s.sp = o;   o += size_t(TT) * s.RS;
-    s.dp = o;   o += bwd ? size_t(TT) * s.RS : 0;
-    s.loc = o;  o += (size_t(TT) * M + 15) & ~size_t(15);
-    s.pe = o;   o += (size_t(TT) * M * 2 + 15) & ~size_t(15);
-    s.os = o;   o += size_t(8 * 16 * 16 * (C + 8) / C) * 4;
+    s.ks = o;   o += kv;
+    s.ks2 = o;  o += bwd ? kv : 0;
+    s.vs = o;   o += kv;
+    s.xs = o;   o += tile;
+    s.dos = o;  o += bwd ? tile : 0;
+    s.outs = o; o += bwd ? tile : 0;
+    s.sp = o;   o += srow;
+    if (bwd) {
+        s.dp = o; s.os = o; o += srow > osz ? srow : osz;
+    } else {
+        s.dp = o; s.os = o; o += osz;
+    }
     s.bl = o;   o += bwd ? size_t(8) * 2 * C * 4 : 0;
     s.total = o;
     return s;
 }
 
-// Staging (16-byte cp.async into padded rows of stride C+8).  All address arithmetic per chunk is 32-bit: the caller
-// passes a base pointer that already includes the batch and head offsets.
-//   f_stage_gather: row i comes from base + off_s[i] (element offset, < 0 -> zero fill); row `skip` is left alone
-//   f_stage_tile:   row i comes from base + i*stride for i < n_valid, zero fill above
+// ---- staging ---------------------------------------------------------------------------------------------------
+// 16-byte cp.async into padded rows of stride C+8.  ptxas separates an LDGSTS from earlier shared-memory traffic
+// with three filler instructions, so the copies of one batch are issued back to back from offsets that already sit
+// in registers: each thread owns chunk `ch` of rows r0, r0+RPP, r0+2·RPP, ... and keeps their element offsets for
+// the whole tile (K and V of every head are gathered with the same offsets).
 template <typename T, int C>
-__device__ __forceinline__ void f_stage_gather(T *dst, int n_rows, int skip, const T *base, const int *off_s) {
-    constexpr int CS = C + 8;
-    constexpr int CH = C / 8;
-    for (int q = threadIdx.x; q < n_rows * CH; q += kFT) {
-        const int i = q / CH, ch = q % CH;
-        if (i == skip) continue;
-        const int off = off_s[i];
-        f_cp_async16(dst + i * CS + ch * 8, base + (off < 0 ? 0 : off) + ch * 8, off >= 0);
+struct GatherStager {
+    static constexpr int CS = C + 8;
+    static constexpr int CH = C / 8;         // 16-byte chunks per row
+    static constexpr int RPP = kFT / CH;     // rows per pass of the CTA
+    static constexpr int KMAX = AFFB200_PLAN_UMAX / RPP;
+    int off[KMAX];   // element offset of this thread's chunk (row offset + ch*8); < 0: nothing to copy
+    uint32_t dst0;   // byte offset of the chunk inside a staging buffer, row r0
+
+    __device__ __forceinline__ void init(const int *rows_s, int U) {
+        const int r0 = threadIdx.x / CH, ch = threadIdx.x % CH;
+        dst0 = uint32_t(r0 * CS + ch * 8) * 2u;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            const int row = r0 + k * RPP;
+            off[k] = row < U ? rows_s[row] + ch * 8 : -1;
+        }
     }
+    __device__ __forceinline__ void issue(uint32_t buf_addr, const T *slab) const {
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k)
+            if (off[k] >= 0)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(buf_addr + dst0 + uint32_t(k * RPP * CS * 2)),
+                             "l"(slab + off[k]) : "memory");
+    }
+};
+
+// the tile's own rows: row i from base + i*stride, i < n_valid (TT*CH <= 256 chunks: at most one per thread)
+template <typename T, int C, int TT>
+__device__ __forceinline__ void f_stage_tile(uint32_t buf_addr, const T *base, int stride, int n_valid) {
+    constexpr int CS = C + 8, CH = C / 8;
+    static_assert(TT * CH <= kFT, "one chunk per thread");
+    const int row = threadIdx.x / CH, ch = threadIdx.x % CH;
+    if (threadIdx.x < TT * CH && row < n_valid)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(buf_addr + uint32_t(row * CS + ch * 8) * 2u),
+                     "l"(base + row * stride + ch * 8) : "memory");
 }
+template <int n> __device__ __forceinline__ void f_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(n) : "memory"); }
+
+// rows [r_lo, r_hi) of a padded staging buffer <- 0 (the C payload elements of each row)
 template <typename T, int C>
-__device__ __forceinline__ void f_stage_tile(T *dst, int n_rows, int n_valid, const T *base, int stride) {
-    constexpr int CS = C + 8;
-    constexpr int CH = C / 8;
-    for (int q = threadIdx.x; q < n_rows * CH; q += kFT) {
-        const int i = q / CH, ch = q % CH;
-        f_cp_async16(dst + i * CS + ch * 8, base + (i < n_valid ? i * stride : 0) + ch * 8, i < n_valid);
-    }
+__device__ __forceinline__ void f_zero_rows(T *buf, int r_lo, int r_hi) {
+    constexpr int CS = C + 8, CH = C / 8;
+    for (int q = threadIdx.x; q < (r_hi - r_lo) * CH; q += kFT)
+        *reinterpret_cast<uint4 *>(buf + (r_lo + q / CH) * CS + (q % CH) * 8) = make_uint4(0u, 0u, 0u, 0u);
 }
 
 // S[TT x Upad] (fp32, smem row stride RS bytes) = alpha * X[TT x C] · Y[Upad x C]^T
@@ -224,20 +264,22 @@ __device__ __forceinline__ void f_mma_pv_store(const unsigned char *sp, int RS, 
     }
 }
 
-// Row phase mapping: TPR = 256 / TT threads share one token row (a contiguous lane group); thread `sub` owns the
-// logits j = sub + TPR*e, e < NE, NE >= ceil((M + 1) / TPR).  All TT rows of the tile are processed in one pass.
+// Row phase mapping: TPR = 256 / TT threads share one token row (a contiguous lane group).  Thread `sub` owns the
+// PER = NE-1 consecutive neighbour slots j = sub*PER + e and, for sub == 0, the blank logit as slot NE-1; all TT rows
+// of the tile are processed in one pass.  What a slot needs is packed once per tile into a 32-bit descriptor held
+// in registers for every head:  bits 0-8 column of S (the slot's position in the union, or UC = the row's sentinel
+// column for unused slots), bits 9-23 bias-table row, bit 24 masked slot (-100), bit 31 unused slot.
 constexpr float kLog2e = 1.4426950408889634f;
+constexpr uint32_t kSlotUnused = 0x80000000u;
 
 struct TileHdr {
     int U, Upad, ti, t0;
     bool dup;
 };
 
-// common prologue: tile header, union rows (as element offsets row*kv_stride, -1 = none), 1-byte positions and
-// packed bias indices -> shared memory
-__device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32_t *q_rows, const uint8_t *q_loc,
-                                               const uint16_t *q_pe, int N, int M, int TT, int UC, int kv_stride,
-                                               int *rows_s, uint8_t *loc_s, uint16_t *pe_s) {
+// common prologue: tile header and union rows (as element offsets row*kv_stride, -1 above U) -> shared memory
+__device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32_t *q_rows, int N, int TT, int UC,
+                                               int kv_stride, int *rows_s) {
     TileHdr t;
     const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x, tid = threadIdx.x;
     t.t0 = tile * TT;
@@ -248,18 +290,33 @@ __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32
     t.Upad = (t.U + 1 + 15) & ~15;
     const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * AFFB200_PLAN_UMAX;
     for (int u = tid; u < UC; u += kFT) rows_s[u] = u < t.U ? rg[u] * kv_stride : -1;
-    const int n_ent = t.ti * M;
-    const uint8_t *lg = q_loc + (int64_t(b) * N + t.t0) * M;
-    const uint16_t *pg = q_pe + (int64_t(b) * N + t.t0) * M;
-    if ((M & 15) == 0) {  // 16-byte aligned rows: vector loads
-        const uint4 *l4 = reinterpret_cast<const uint4 *>(lg);
-        const uint4 *p4 = reinterpret_cast<const uint4 *>(pg);
-        for (int p = tid; p < n_ent / 16; p += kFT) reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(l4 + p);
-        for (int p = tid; p < n_ent / 8; p += kFT) reinterpret_cast<uint4 *>(pe_s)[p] = __ldg(p4 + p);
-    } else {
-        for (int p = tid; p < n_ent; p += kFT) { loc_s[p] = lg[p]; pe_s[p] = pg[p]; }
-    }
     return t;
+}
+
+// slot descriptors of this thread, straight from the plan's 1-byte positions and the packed bias indices
+template <int PER>
+__device__ __forceinline__ void f_load_desc(const uint8_t *__restrict__ loc_r, const uint16_t *__restrict__ pe_r, int M,
+                                            int sub, bool live, int UC, uint32_t (&desc)[PER]) {
+    const int j0 = sub * PER;
+    auto mk = [](uint32_t loc, uint32_t pe) { return loc | ((pe & 0x7fffu) << 9) | ((pe >> 15) << 24); };
+    if ((PER % 2 == 0) && (M % 2 == 0)) {  // slots come in aligned pairs that are valid together
+#pragma unroll
+        for (int e = 0; e < PER; e += 2) {
+            desc[e] = desc[e + 1] = kSlotUnused | uint32_t(UC);
+            if (live && j0 + e < M) {
+                const uint32_t l2 = __ldg(reinterpret_cast<const uint16_t *>(loc_r + j0 + e));
+                const uint32_t p2 = __ldg(reinterpret_cast<const uint32_t *>(pe_r + j0 + e));
+                desc[e] = mk(l2 & 0xffu, p2 & 0xffffu);
+                desc[e + 1] = mk(l2 >> 8, p2 >> 16);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < PER; ++e) {
+            desc[e] = kSlotUnused | uint32_t(UC);
+            if (live && j0 + e < M) desc[e] = mk(__ldg(loc_r + j0 + e), __ldg(pe_r + j0 + e));
+        }
+    }
 }
 
 __device__ __forceinline__ float f_ex2(float x) {
@@ -300,28 +357,26 @@ template <int TPR> __device__ __forceinline__ float f_group_sum(float v) {
     return v;
 }
 
-// softmax of one token's M+1 logits by its TPR threads: gathers S[row][loc] + bias (+ -100 at padded slots), the blank
-// logit S[row][U]; leaves the normalised probabilities of this thread's slots in pv[] and returns the log-sum-exp
+// the M+1 logits of one token, gathered by its TPR threads: S[row][col] + bias (+ -100 at masked slots); the blank
+// logit S[row][U] is slot NE-1 of the group's first thread.  Unused slots read the row's -inf sentinel.
+template <int NE>
+__device__ __forceinline__ void f_row_logits(const float *srow, const uint32_t (&desc)[NE - 1],
+                                             const float *__restrict__ table_h, int H, int U, bool has_blank,
+                                             float (&pv)[NE]) {
+#pragma unroll
+    for (int e = 0; e < NE - 1; ++e) {
+        const uint32_t d = desc[e];
+        pv[e] = srow[d & 511u] + __ldg(table_h + ((d >> 9) & 0x7fffu) * H) + ((d & (1u << 24)) ? -100.f : 0.f);
+    }
+    pv[NE - 1] = has_blank ? srow[U] : -INFINITY;
+}
+
+// softmax over the row's group; leaves the probabilities in pv[] and returns the log-sum-exp
 template <int TPR, int NE>
-__device__ __forceinline__ float f_row_softmax(const float *srow, const uint8_t *loc_r, const uint16_t *pe_r,
-                                               const float *__restrict__ table_h, int H, int M, int U, int sub,
-                                               bool live, float (&pv)[NE]) {
+__device__ __forceinline__ float f_row_softmax(bool live, float (&pv)[NE]) {
     float mx = -INFINITY;
 #pragma unroll
-    for (int e = 0; e < NE; ++e) {
-        const int j = sub + TPR * e;
-        float s = -INFINITY;
-        if (live) {
-            if (j < M) {
-                const uint32_t pe = pe_r[j];
-                s = srow[loc_r[j]] + __ldg(table_h + int(pe & 0x7fffu) * H) + ((pe & 0x8000u) ? -100.f : 0.f);
-            } else if (j == M) {
-                s = srow[U];
-            }
-        }
-        pv[e] = s;
-        mx = fmaxf(mx, s);
-    }
+    for (int e = 0; e < NE; ++e) mx = fmaxf(mx, pv[e]);
     mx = f_group_max<TPR>(mx);
     if (!live) mx = 0.f;
     float sum = 0.f;
@@ -341,29 +396,23 @@ __device__ __forceinline__ float f_row_softmax(const float *srow, const uint8_t 
 // Tiles in which a token lists a row twice (the padded slots of the last cluster all point at row 0) accumulate in
 // fp32 with shared-memory atomics over the row's fp32 footprint and convert in place afterwards.
 template <typename T, int TPR, int NE>
-__device__ __forceinline__ void f_scatter_row(T *prow, const uint8_t *loc_r, int Upad, int M, int U, bool dup, int sub,
-                                              bool live, const float (&pv)[NE]) {
+__device__ __forceinline__ void f_scatter_row(T *prow, const uint32_t (&desc)[NE - 1], int Upad, int U, bool dup,
+                                              int sub, bool has_blank, const float (&pv)[NE]) {
     if (!dup) {
         for (int w = sub; w < Upad / 8; w += TPR) reinterpret_cast<uint4 *>(prow)[w] = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();
-        if (live) {
 #pragma unroll
-            for (int e = 0; e < NE; ++e) {
-                const int j = sub + TPR * e;
-                if (j <= M) prow[j < M ? loc_r[j] : U] = Elem<T>::from_acc(pv[e]);
-            }
-        }
+        for (int e = 0; e < NE - 1; ++e)
+            if (int(desc[e]) >= 0) prow[desc[e] & 511u] = Elem<T>::from_acc(pv[e]);
+        if (has_blank) prow[U] = Elem<T>::from_acc(pv[NE - 1]);
     } else {
         float *frow = reinterpret_cast<float *>(prow);
         for (int w = sub; w < Upad; w += TPR) frow[w] = 0.f;
         __syncwarp();
-        if (live) {
 #pragma unroll
-            for (int e = 0; e < NE; ++e) {
-                const int j = sub + TPR * e;
-                if (j <= M) atomicAdd(frow + (j < M ? loc_r[j] : U), pv[e]);
-            }
-        }
+        for (int e = 0; e < NE - 1; ++e)
+            if (int(desc[e]) >= 0) atomicAdd(frow + (desc[e] & 511u), pv[e]);
+        if (has_blank) atomicAdd(frow + U, pv[NE - 1]);
         __syncwarp();
         for (int base = 0; base < Upad; base += TPR) {  // in-place fp32 -> T, front to back
             const float vv = frow[base + sub];
@@ -374,6 +423,15 @@ __device__ __forceinline__ void f_scatter_row(T *prow, const uint8_t *loc_r, int
     }
 }
 
+// blank token of head h -> row U of a K or V staging buffer
+template <typename T, int C>
+__device__ __forceinline__ void f_put_blank(T *buf, int U, const float *__restrict__ blank, int h) {
+    if (threadIdx.x < C) buf[U * (C + 8) + threadIdx.x] = Elem<T>::from_acc(__ldg(blank + h * C + threadIdx.x));
+}
+
+// Forward.  Loads run one head ahead of the math: Q and K of head h+1 are requested as soon as S = Q·K^T of head h
+// has left the staging buffers, V of head h+1 as soon as O = P·V of head h has; every wait is "all but the newest
+// group" (cp.async groups retire in order: ... QK_h, V_h, QK_h+1, V_h+1 ...).
 template <typename T, int C, int TT, int NE>
 __global__ void __launch_bounds__(kFT)
 fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float *__restrict__ table,
@@ -381,7 +439,6 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
                       const int32_t *__restrict__ q_hdr, const int32_t *__restrict__ q_rows,
                       const uint8_t *__restrict__ q_loc, const uint16_t *__restrict__ q_pe, float *__restrict__ lse,
                       int H, int N, int M, float scale, FusedSmem L) {
-    constexpr int CS = C + 8;
     constexpr int TPR = kFT / TT;
     extern __shared__ __align__(128) unsigned char smem[];
     int *rows_s = reinterpret_cast<int *>(smem + L.rows);
@@ -389,47 +446,75 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
     T *vs = reinterpret_cast<T *>(smem + L.vs);
     T *xs = reinterpret_cast<T *>(smem + L.xs);
     unsigned char *sp = smem + L.sp;
-    uint8_t *loc_s = smem + L.loc;
-    uint16_t *pe_s = reinterpret_cast<uint16_t *>(smem + L.pe);
     float *os = reinterpret_cast<float *>(smem + L.os);
+    const uint32_t ks_a = f_smem_u32(ks), vs_a = f_smem_u32(vs), xs_a = f_smem_u32(xs);
 
     const int b = blockIdx.y, tid = threadIdx.x;
-    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, int(k.sN), rows_s, loc_s, pe_s);
-    __syncthreads();
+    const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
     const int i = tid / TPR, sub = tid % TPR;  // this thread's token row and its position in the row's group
-    const bool live = i < t.ti;
+    const bool live = i < t.ti, has_blank = live && sub == 0;
+    uint32_t desc[NE - 1];
+    {
+        const int64_t r = (int64_t(b) * N + t.t0 + (live ? i : 0)) * M;
+        f_load_desc<NE - 1>(q_loc + r, q_pe + r, M, sub, live, L.UC, desc);
+    }
     T *prow = reinterpret_cast<T *>(sp + i * L.RS);
+    const float *srow = reinterpret_cast<const float *>(prow);
+    if (sub == 0) reinterpret_cast<float *>(prow)[L.UC] = -INFINITY;  // what unused slots read
+    f_zero_rows<T, C>(ks, t.U + 1, t.Upad);
+    f_zero_rows<T, C>(vs, t.U + 1, t.Upad);
+    f_zero_rows<T, C>(xs, t.ti, TT);
+    __syncthreads();
+
+    GatherStager<T, C> st;
+    st.init(rows_s, t.U);
+    const T *qb = q.row(b, t.t0, 0), *kb = k.row(b, 0, 0), *vb = v.row(b, 0, 0);
+    f_stage_tile<T, C, TT>(xs_a, qb, int(q.sN), t.ti);
+    st.issue(ks_a, kb);
+    f_cp_async_commit();
+    st.issue(vs_a, vb);
+    f_cp_async_commit();
+    f_put_blank<T, C>(ks, t.U, blank_k, 0);
+    f_put_blank<T, C>(vs, t.U, blank_v, 0);
 
     for (int h = 0; h < H; ++h) {
-        f_stage_tile<T, C>(xs, TT, t.ti, q.row(b, t.t0, h), int(q.sN));
-        f_stage_gather<T, C>(ks, t.Upad, t.U, k.row(b, 0, h), rows_s);
-        f_stage_gather<T, C>(vs, t.Upad, t.U, v.row(b, 0, h), rows_s);
-        f_cp_async_commit();
-        if (tid < C) {  // the blank token is key/value row U
-            ks[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_k + h * C + tid));
-            vs[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_v + h * C + tid));
-        }
-        f_cp_async_wait_all();
+        f_cp_async_wait<1>();  // Q_h, K_h
         __syncthreads();
         f_mma_xyT<T, C>(xs, ks, sp, L.RS, TT, t.Upad, scale);
         __syncthreads();
+        if (h + 1 < H) {
+            f_stage_tile<T, C, TT>(xs_a, qb + (h + 1) * q.sH, int(q.sN), t.ti);
+            st.issue(ks_a, kb + (h + 1) * k.sH);
+            f_put_blank<T, C>(ks, t.U, blank_k, h + 1);
+        }
+        f_cp_async_commit();
         {
             float pv[NE];
-            const float l = f_row_softmax<TPR, NE>(reinterpret_cast<const float *>(prow), loc_s + i * M, pe_s + i * M,
-                                                   table + h, H, M, t.U, sub, live, pv);
-            if (live && sub == 0) lse[(int64_t(b) * H + h) * N + t.t0 + i] = l;
+            f_row_logits<NE>(srow, desc, table + h, H, t.U, has_blank, pv);
+            const float l = f_row_softmax<TPR, NE>(live, pv);
+            if (has_blank) lse[(int64_t(b) * H + h) * N + t.t0 + i] = l;
             __syncwarp();
-            f_scatter_row<T, TPR, NE>(prow, loc_s + i * M, t.Upad, M, t.U, t.dup, sub, live, pv);
+            f_scatter_row<T, TPR, NE>(prow, desc, t.Upad, t.U, t.dup, sub, has_blank, pv);
         }
+        f_cp_async_wait<1>();  // V_h
         __syncthreads();
         f_mma_pv_store<T, C>(sp, L.RS, vs, os, TT, t.Upad, t.ti, 1.f, out.row(b, t.t0, h), out.sN);
         __syncthreads();
+        if (h + 1 < H) {
+            st.issue(vs_a, vb + (h + 1) * v.sH);
+            f_put_blank<T, C>(vs, t.U, blank_v, h + 1);
+        }
+        f_cp_async_commit();
     }
+    f_cp_async_wait<0>();
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // Backward, query-tile half.  Emits dQ, and dS / P in [B][H][N][M] for the key-tile scatter kernels and the table
 // gradient; per-tile partial sums of the blank-token gradients go to blank_part [B][tiles][H][2][C] (fp32).
+// Per head: S = Q·K_U^T and dP = dO·V_U^T on the tensor cores, then per row P = exp(S + bias − lse),
+// dS = P∘(dP − δ) with δ = dO·O, then dQ = scale·dS·K_U.  V and K of head h+1 (second K buffer) are requested right
+// after the two contractions of head h, Q/dO/O of head h+1 right after its row phase.
 // ---------------------------------------------------------------------------------------------------------
 template <typename T, int C, int TT, int NE>
 __global__ void __launch_bounds__(kFT)
@@ -442,46 +527,74 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
                       FusedSmem L) {
     constexpr int CS = C + 8;
     constexpr int TPR = kFT / TT;
+    constexpr int PER = NE - 1;
     constexpr int CPT = (C + TPR - 1) / TPR;  // channels per thread in the per-row channel reductions
     extern __shared__ __align__(128) unsigned char smem[];
     int *rows_s = reinterpret_cast<int *>(smem + L.rows);
-    T *ks = reinterpret_cast<T *>(smem + L.ks);
+    T *ks0 = reinterpret_cast<T *>(smem + L.ks);
+    T *ks1 = reinterpret_cast<T *>(smem + L.ks2);
     T *vs = reinterpret_cast<T *>(smem + L.vs);
     T *xs = reinterpret_cast<T *>(smem + L.xs);
     T *dos = reinterpret_cast<T *>(smem + L.dos);
+    T *outs = reinterpret_cast<T *>(smem + L.outs);
     unsigned char *sp = smem + L.sp;
     unsigned char *dp = smem + L.dp;
-    uint8_t *loc_s = smem + L.loc;
-    uint16_t *pe_s = reinterpret_cast<uint16_t *>(smem + L.pe);
-    float *os = reinterpret_cast<float *>(smem + L.os);
+    float *os = reinterpret_cast<float *>(smem + L.os);  // over dp: dP is dead when the dQ partials are written
     float *bl = reinterpret_cast<float *>(smem + L.bl);  // [8 warps][2][C]
+    const uint32_t vs_a = f_smem_u32(vs), xs_a = f_smem_u32(xs), dos_a = f_smem_u32(dos), outs_a = f_smem_u32(outs);
 
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const TileHdr t = f_load_tile(q_hdr, q_rows, q_loc, q_pe, N, M, TT, L.UC, int(k.sN), rows_s, loc_s, pe_s);
-    __syncthreads();
+    const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
     const int i = tid / TPR, sub = tid % TPR;
-    const bool live = i < t.ti;
+    const bool live = i < t.ti, has_blank = live && sub == 0;
+    const int64_t tok = t.t0 + (live ? i : 0);
+    uint32_t desc[PER];
+    {
+        const int64_t r = (int64_t(b) * N + tok) * M;
+        f_load_desc<PER>(q_loc + r, q_pe + r, M, sub, live, L.UC, desc);
+    }
     T *prow = reinterpret_cast<T *>(sp + i * L.RS);
+    const float *srow = reinterpret_cast<const float *>(prow);
     const float *dprow = reinterpret_cast<const float *>(dp + i * L.RS);
-    const uint8_t *loc_r = loc_s + i * M;
-    const int e_blank = M / TPR, s_blank = M % TPR;  // (slot, group position) that owns the blank logit
-    const int64_t tok = t.t0 + i;
+    if (sub == 0) reinterpret_cast<float *>(prow)[L.UC] = -INFINITY;  // unused slots: P = 0 ...
+    // ... and dP = 0 (set again per head below, the dQ partials overwrite it)
+    f_zero_rows<T, C>(ks0, t.U + 1, t.Upad);
+    f_zero_rows<T, C>(ks1, t.U + 1, t.Upad);
+    f_zero_rows<T, C>(vs, t.U + 1, t.Upad);
+    f_zero_rows<T, C>(xs, t.ti, TT);
+    f_zero_rows<T, C>(dos, t.ti, TT);
+    f_zero_rows<T, C>(outs, t.ti, TT);
+    __syncthreads();
+
+    GatherStager<T, C> st;
+    st.init(rows_s, t.U);
+    const T *qb = q.row(b, t.t0, 0), *dob = dout.row(b, t.t0, 0), *ob = out.row(b, t.t0, 0);
+    const T *kb = k.row(b, 0, 0), *vb = v.row(b, 0, 0);
+    f_stage_tile<T, C, TT>(xs_a, qb, int(q.sN), t.ti);
+    f_stage_tile<T, C, TT>(dos_a, dob, int(dout.sN), t.ti);
+    f_stage_tile<T, C, TT>(outs_a, ob, int(out.sN), t.ti);
+    st.issue(f_smem_u32(ks0), kb);
+    st.issue(vs_a, vb);
+    f_cp_async_commit();
+    f_put_blank<T, C>(ks0, t.U, blank_k, 0);
+    f_put_blank<T, C>(vs, t.U, blank_v, 0);
+    const bool pair_ok = (PER % 2 == 0) && (M % 2 == 0);
 
     for (int h = 0; h < H; ++h) {
-        f_stage_tile<T, C>(xs, TT, t.ti, q.row(b, t.t0, h), int(q.sN));
-        f_stage_tile<T, C>(dos, TT, t.ti, dout.row(b, t.t0, h), int(dout.sN));
-        f_stage_gather<T, C>(ks, t.Upad, t.U, k.row(b, 0, h), rows_s);
-        f_stage_gather<T, C>(vs, t.Upad, t.U, v.row(b, 0, h), rows_s);
-        f_cp_async_commit();
-        if (tid < C) {
-            ks[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_k + h * C + tid));
-            vs[t.U * CS + tid] = Elem<T>::from_acc(__ldg(blank_v + h * C + tid));
+        T *kcur = (h & 1) ? ks1 : ks0, *knext = (h & 1) ? ks0 : ks1;
+        f_cp_async_wait<0>();
+        __syncthreads();
+        f_mma_xyT<T, C>(xs, kcur, sp, L.RS, TT, t.Upad, scale);  // S
+        f_mma_xyT<T, C>(dos, vs, dp, L.RS, TT, t.Upad, 1.f);     // dP = dO · V_U^T
+        if (sub == 0) const_cast<float *>(dprow)[L.UC] = 0.f;
+        __syncthreads();
+        if (h + 1 < H) {
+            st.issue(f_smem_u32(knext), kb + (h + 1) * k.sH);
+            st.issue(vs_a, vb + (h + 1) * v.sH);
+            f_put_blank<T, C>(knext, t.U, blank_k, h + 1);
+            f_put_blank<T, C>(vs, t.U, blank_v, h + 1);
         }
-        f_cp_async_wait_all();
-        __syncthreads();
-        f_mma_xyT<T, C>(xs, ks, sp, L.RS, TT, t.Upad, scale);   // S
-        f_mma_xyT<T, C>(dos, vs, dp, L.RS, TT, t.Upad, 1.f);    // dP = dO · V_U^T
-        __syncthreads();
+        f_cp_async_commit();
 
         float acc_bk[CPT], acc_bv[CPT];
         {
@@ -489,35 +602,48 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
             float dl = 0.f, qv[CPT], dov[CPT], ov[CPT];
 #pragma unroll
             for (int cc = 0; cc < CPT; ++cc) qv[cc] = dov[cc] = ov[cc] = 0.f;
-            if (live && sub * CPT < C) {
+            if (sub * CPT < C) {  // rows past the end of the tile are zero in all three buffers
                 f_load_n<T, CPT>(dos + i * CS + sub * CPT, dov);
                 f_load_n<T, CPT>(xs + i * CS + sub * CPT, qv);
-                f_load_n<T, CPT>(out.row(b, tok, h) + sub * CPT, ov);
+                f_load_n<T, CPT>(outs + i * CS + sub * CPT, ov);
             }
 #pragma unroll
             for (int cc = 0; cc < CPT; ++cc) dl += dov[cc] * ov[cc];
             dl = f_group_sum<TPR>(dl);
+            // P from the saved log-sum-exp: no max / sum reductions
+            const float nl = live ? -__ldg(lse + (int64_t(b) * H + h) * N + tok) * kLog2e : 0.f;
             float pv[NE];
-            f_row_softmax<TPR, NE>(reinterpret_cast<const float *>(prow), loc_r, pe_s + i * M, table + h, H, M, t.U, sub,
-                                   live, pv);
-            T *pg = p_out + ((int64_t(b) * H + h) * N + tok) * M;
-            T *dg = ds_out + ((int64_t(b) * H + h) * N + tok) * M;
-            float pb = 0.f, dsb = 0.f;
+            f_row_logits<NE>(srow, desc, table + h, H, t.U, has_blank, pv);
+            T *pg = p_out + ((int64_t(b) * H + h) * N + tok) * M + sub * PER;
+            T *dg = ds_out + ((int64_t(b) * H + h) * N + tok) * M + sub * PER;
+            if (pair_ok) {
 #pragma unroll
-            for (int e = 0; e < NE; ++e) {
-                const int j = sub + TPR * e;
-                const float p = pv[e];
-                float ds = 0.f;
-                if (live && j <= M) ds = p * (dprow[j < M ? loc_r[j] : t.U] - dl);
-                if (live && j < M) {
-                    pg[j] = Elem<T>::from_acc(p);
-                    dg[j] = Elem<T>::from_acc(ds);
+                for (int e = 0; e + 1 < PER; e += 2) {
+                    const float p0 = f_ex2(fmaf(pv[e], kLog2e, nl)), p1 = f_ex2(fmaf(pv[e + 1], kLog2e, nl));
+                    const float d0 = p0 * (dprow[desc[e] & 511u] - dl), d1 = p1 * (dprow[desc[e + 1] & 511u] - dl);
+                    if (int(desc[e]) >= 0) {
+                        *reinterpret_cast<uint32_t *>(pg + e) = f_pack2<T>(p0, p1);
+                        *reinterpret_cast<uint32_t *>(dg + e) = f_pack2<T>(d0, d1);
+                    }
+                    pv[e] = d0; pv[e + 1] = d1;
                 }
-                if (e == e_blank) { pb = p; dsb = ds; }
-                pv[e] = ds;
+            } else {
+#pragma unroll
+                for (int e = 0; e < PER; ++e) {
+                    const float p0 = f_ex2(fmaf(pv[e], kLog2e, nl));
+                    const float d0 = p0 * (dprow[desc[e] & 511u] - dl);
+                    if (int(desc[e]) >= 0) {
+                        pg[e] = Elem<T>::from_acc(p0);
+                        dg[e] = Elem<T>::from_acc(d0);
+                    }
+                    pv[e] = d0;
+                }
             }
+            float pb = f_ex2(fmaf(pv[NE - 1], kLog2e, nl));  // 0 unless this thread holds the blank slot
+            float dsb = has_blank ? pb * (dprow[t.U] - dl) : 0.f;
+            pv[NE - 1] = dsb;
             // blank-token gradients: broadcast the blank slot's (p, ds) within the row's group
-            const int src = (lane & ~(TPR - 1)) | s_blank;
+            const int src = lane & ~(TPR - 1);
             pb = __shfl_sync(0xffffffffu, pb, src);
             dsb = __shfl_sync(0xffffffffu, dsb, src);
 #pragma unroll
@@ -526,7 +652,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
                 acc_bv[cc] = pb * dov[cc];
             }
             __syncwarp();
-            f_scatter_row<T, TPR, NE>(prow, loc_r, t.Upad, M, t.U, t.dup, sub, live, pv);
+            f_scatter_row<T, TPR, NE>(prow, desc, t.Upad, t.U, t.dup, sub, has_blank, pv);
         }
         // sum the blank partials over the rows of this warp (lanes with equal `sub`), then over the warps
 #pragma unroll
@@ -543,15 +669,22 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
             }
         }
         __syncthreads();
+        if (h + 1 < H) {
+            f_stage_tile<T, C, TT>(xs_a, qb + (h + 1) * q.sH, int(q.sN), t.ti);
+            f_stage_tile<T, C, TT>(dos_a, dob + (h + 1) * dout.sH, int(dout.sN), t.ti);
+            f_stage_tile<T, C, TT>(outs_a, ob + (h + 1) * out.sH, int(out.sN), t.ti);
+        }
+        f_cp_async_commit();
         if (tid < 2 * C) {
             float sacc = 0.f;
 #pragma unroll
             for (int w = 0; w < 8; ++w) sacc += bl[w * 2 * C + tid];
             blank_part[((int64_t(b) * gridDim.x + blockIdx.x) * H + h) * 2 * C + tid] = sacc;
         }
-        f_mma_pv_store<T, C>(sp, L.RS, ks, os, TT, t.Upad, t.ti, scale, dq.row(b, t.t0, h), dq.sN);  // dQ = scale·dS·K_U
+        f_mma_pv_store<T, C>(sp, L.RS, kcur, os, TT, t.Upad, t.ti, scale, dq.row(b, t.t0, h), dq.sN);  // dQ = scale·dS·K_U
         __syncthreads();
     }
+    f_cp_async_wait<0>();
 }
 
 }  // namespace affb200
@@ -617,7 +750,7 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
     if (!kv_ok(k, v, N) || N * q->sN >= (int64_t(1) << 31)) { set_error("fused_attn_fwd: k/v token strides must match and fit int32"); return AFFB200_E_ARG; }
     const int TT = plan->tq;
     const int UC = (umax + 1 + 31) & ~31;
-    const FusedSmem L = fused_smem(UC, TT, int(c), int(M), false);
+    const FusedSmem L = fused_smem(UC, TT, int(c), false);
     if (L.total > 227 * 1024) { set_error("fused_attn_fwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
     dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
     auto st = (cudaStream_t)stream;
@@ -635,14 +768,14 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
                                          blank_k, blank_v, plan->q_hdr, plan->q_rows, plan->q_loc, q_pe, lse,      \
                                          int(H), int(N), int(M), scale, L);                                        \
     } while (0)
-            // (tile size, slots per thread): 256/TT threads per row, NE*256/TT >= M+1
-            const int need = int(M) + 1;
+            // (tile size, slots per thread): 256/TT threads per row, each NE-1 neighbour slots: (NE-1)*256/TT >= M
+            const int need = int(M);
 #define AFF_FC(C_)                                                                                   \
     do {                                                                                             \
-        if (TT == 16 && need <= 13 * 16) AFF_F(C_, 16, 13);                                          \
-        else if (TT == 32 && need <= 7 * 8) AFF_F(C_, 32, 7);                                        \
-        else if (TT == 32 && need <= 13 * 8) AFF_F(C_, 32, 13);                                      \
-        else if (TT == 64 && need <= 17 * 4) AFF_F(C_, 64, 17);                                      \
+        if (TT == 16 && need <= 12 * 16) AFF_F(C_, 16, 13);                                          \
+        else if (TT == 32 && need <= 6 * 8) AFF_F(C_, 32, 7);                                        \
+        else if (TT == 32 && need <= 12 * 8) AFF_F(C_, 32, 13);                                      \
+        else if (TT == 64 && need <= 16 * 4) AFF_F(C_, 64, 17);                                      \
         else { set_error("fused_attn: tile size %d does not support M = %d", TT, int(M)); return AFFB200_E_ARG; } \
     } while (0)
             if (c == 32) AFF_FC(32); else AFF_FC(16);
@@ -677,7 +810,7 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
     if (P <= 0 || P > 32768) { set_error("fused_attn_bwd: bias table must have 1..32768 rows"); return AFFB200_E_ARG; }
     const int TT = plan->tq;
     const int UC = (umax + 1 + 31) & ~31;
-    const FusedSmem L = fused_smem(UC, TT, int(c), int(M), true);
+    const FusedSmem L = fused_smem(UC, TT, int(c), true);
     if (L.total > 227 * 1024) { set_error("fused_attn_bwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
     dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
     auto st = (cudaStream_t)stream;
@@ -696,14 +829,14 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
                                          plan->q_rows, plan->q_loc, q_pe, lse, (T *)ds_work, (T *)p_work,          \
                                          blank_part, int(H), int(N), int(M), scale, L);                            \
     } while (0)
-            // (tile size, slots per thread): 256/TT threads per row, NE*256/TT >= M+1
-            const int need = int(M) + 1;
+            // (tile size, slots per thread): 256/TT threads per row, each NE-1 neighbour slots: (NE-1)*256/TT >= M
+            const int need = int(M);
 #define AFF_BC(C_)                                                                                   \
     do {                                                                                             \
-        if (TT == 16 && need <= 13 * 16) AFF_B(C_, 16, 13);                                          \
-        else if (TT == 32 && need <= 7 * 8) AFF_B(C_, 32, 7);                                        \
-        else if (TT == 32 && need <= 13 * 8) AFF_B(C_, 32, 13);                                      \
-        else if (TT == 64 && need <= 17 * 4) AFF_B(C_, 64, 17);                                      \
+        if (TT == 16 && need <= 12 * 16) AFF_B(C_, 16, 13);                                          \
+        else if (TT == 32 && need <= 6 * 8) AFF_B(C_, 32, 7);                                        \
+        else if (TT == 32 && need <= 12 * 8) AFF_B(C_, 32, 13);                                      \
+        else if (TT == 64 && need <= 16 * 4) AFF_B(C_, 64, 17);                                      \
         else { set_error("fused_attn: tile size %d does not support M = %d", TT, int(M)); return AFFB200_E_ARG; } \
     } while (0)
             if (c == 32) AFF_BC(32); else AFF_BC(16);
