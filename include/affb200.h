@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define AFFB200_ABI_VERSION 3
+#define AFFB200_ABI_VERSION 4
 
 typedef enum {
     AFFB200_F32 = 0,
@@ -253,6 +253,20 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
                            const affb200_nbhd_plan *plan, const uint16_t *q_pe, int32_t umax, const float *lse,
                            void *ds_work, void *p_work, float *blank_part, float *d_table, int64_t P,
                            int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype, void *stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * LayerNorm over the channel dim of token rows [R][C] (the norm on either side of the attention and in
+ * ClusterMerging; reference models/aff_transformer.py:199-200,223-229,284,362 = nn.LayerNorm, which autocast runs in
+ * fp32 between two dtype copies).  x in `in_dtype`, y in `out_dtype` (f32/f16/bf16 each), gamma/beta/mean/rstd fp32,
+ * statistics in fp32.  C multiple of 8; forward C <= 2048, backward C <= 1024.  Backward: dx in x's dtype, dgamma /
+ * dbeta fp32 [C] (overwritten), work = affb200_layer_norm_bwd_work_floats(R, C) floats of scratch.
+ * ---------------------------------------------------------------------------------------------------------- */
+int affb200_layer_norm_fwd(const void *x, const float *gamma, const float *beta, void *y, float *mean, float *rstd,
+                           int64_t R, int64_t C, float eps, int in_dtype, int out_dtype, void *stream);
+int64_t affb200_layer_norm_bwd_work_floats(int64_t R, int64_t C);
+int affb200_layer_norm_bwd(const void *dy, const void *x, const float *gamma, const float *mean, const float *rstd,
+                           void *dx, float *dgamma, float *dbeta, float *work, int64_t R, int64_t C, int x_dtype,
+                           int dy_dtype, void *stream);
 
 #ifdef __cplusplus
 }

@@ -28,6 +28,8 @@ class CudaOps:
         from .clusten import CLUSTENQKFunction, CLUSTENAVFunction, CLUSTENWFFunction
         from . import point_utils as P
         from . import attn_ops as A
+        from . import norm_ops as L
+        self.layer_norm = L.layer_norm
         self.attn_bias_add = A.attn_bias_add
         self.table_gather = A.table_gather
         self.qk = CLUSTENQKFunction.apply
@@ -61,6 +63,11 @@ def build_pe_lookup(img_size):
     table = torch.stack([xs, ys, dis, ys / dis, xs / dis], dim=2)
     table[~torch.isfinite(table)] = 0
     return rel_pos_width, table_width, table.reshape(-1, 5)
+
+
+def _ln(ops, mod, x):
+    """nn.LayerNorm `mod` applied through the operator set (one fused pass on the product path)."""
+    return ops.layer_norm(x, mod.weight, mod.bias, mod.eps)
 
 
 def drop_path(x, p, training):
@@ -151,11 +158,11 @@ class ClusterTransformerBlock(nn.Module):
             self.gamma2 = nn.Parameter(layer_scale * torch.ones(dim))
 
     def forward(self, feat, member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops):
-        x = self.attn(self.norm1(feat), member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops)
+        x = self.attn(_ln(ops, self.norm1, feat), member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops)
         if self.layer_scale:
             x = self.gamma1 * x
         feat = feat + drop_path(x, self.drop_path_p, self.training)
-        x = self.mlp(self.norm2(feat))
+        x = self.mlp(_ln(ops, self.norm2, feat))
         if self.layer_scale:
             x = self.gamma2 * x
         return feat + drop_path(x, self.drop_path_p, self.training)
@@ -195,7 +202,7 @@ class ClusterMerging(nn.Module):
         elif cluster_mask is not None:
             weights = weights * cluster_mask.unsqueeze(3)
         feat = ops.wf(weights, feat, member_idx).reshape(b, n_new, -1)                   # b x n' x ic*c
-        return pos, self.linear(self.norm(feat))
+        return pos, self.linear(_ln(ops, self.norm, feat))
 
 
 class BasicLayer(nn.Module):

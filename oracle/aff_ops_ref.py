@@ -28,6 +28,11 @@ class OracleOps:
         return P.select_ref(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on)
 
     @staticmethod
+    def layer_norm(x, weight, bias, eps=1e-5):
+        """nn.LayerNorm as the reference applies it (aff_transformer.py:199-200,284)"""
+        return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)
+
+    @staticmethod
     def attn_bias_add(attn, pe_table, pe_idx, mask=None):
         """reference aff_transformer.py:131-137"""
         h = attn.shape[1]
