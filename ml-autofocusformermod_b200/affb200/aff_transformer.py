@@ -29,7 +29,9 @@ class CudaOps:
         from . import point_utils as P
         from . import attn_ops as A
         from . import norm_ops as L
+        from . import linear_ops as LI
         self.layer_norm = L.layer_norm
+        self.linear = LI.linear
         self.attn_bias_add = A.attn_bias_add
         self.table_gather = A.table_gather
         self.qk = CLUSTENQKFunction.apply
@@ -70,6 +72,11 @@ def _ln(ops, mod, x):
     return ops.layer_norm(x, mod.weight, mod.bias, mod.eps)
 
 
+def _lin(ops, mod, x):
+    """nn.Linear `mod` applied through the operator set (bias gradient as one column-sum pass on the product path)."""
+    return ops.linear(x, mod.weight, mod.bias)
+
+
 def drop_path(x, p, training):
     """Stochastic depth per sample (timm DropPath semantics: scale kept paths by 1/(1-p))."""
     if p == 0. or not training:
@@ -87,8 +94,8 @@ class Mlp(nn.Module):
         self.fc2 = nn.Linear(hidden_features, in_features)
         self.drop = nn.Dropout(drop)
 
-    def forward(self, x):
-        return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
+    def forward(self, x, ops):
+        return self.drop(_lin(ops, self.fc2, self.drop(self.act(_lin(ops, self.fc1, x)))))
 
 
 class ClusterAttention(nn.Module):
@@ -112,14 +119,14 @@ class ClusterAttention(nn.Module):
         b, n, c = feat.shape
         h = self.num_heads
         c_ = c // h
-        q_lin = self.q(feat)
-        kv = self.kv(feat)
+        q_lin = _lin(ops, self.q, feat)
+        kv = _lin(ops, self.kv, feat)
         pe_table = self.pos_embed(pre_table)                       # T*T x h
         if not global_attn and ops.fused_attention is not None and self.attn_drop.p == 0.:
             out = ops.fused_attention(q_lin, kv, h, self.scale, member_idx, pe_idx, cluster_mask, pe_table,
                                       self.blank_k, self.blank_v)   # b n c, or None when unsupported
             if out is not None:
-                return self.proj_drop(self.proj(out))
+                return self.proj_drop(_lin(ops, self.proj, out))
         q = (q_lin * self.scale).reshape(b, n, h, c_).permute(0, 2, 1, 3)   # b h n c_
         kv = kv.view(b, n, h, 2, c_).permute(3, 0, 2, 1, 4)        # 2 b h n c_
         key, v = kv[0], kv[1]
@@ -141,7 +148,7 @@ class ClusterAttention(nn.Module):
             # Here the probabilities are rounded to v's dtype so that AV stays on the bf16 tensor-core path.
             out = ops.av(attn.to(v.dtype), v, member_idx)
         feat = (out + blank_v.to(out.dtype)).permute(0, 2, 1, 3).reshape(b, n, c)
-        return self.proj_drop(self.proj(feat))
+        return self.proj_drop(_lin(ops, self.proj, feat))
 
 
 class ClusterTransformerBlock(nn.Module):
@@ -162,7 +169,7 @@ class ClusterTransformerBlock(nn.Module):
         if self.layer_scale:
             x = self.gamma1 * x
         feat = feat + drop_path(x, self.drop_path_p, self.training)
-        x = self.mlp(_ln(ops, self.norm2, feat))
+        x = self.mlp(_ln(ops, self.norm2, feat), ops)
         if self.layer_scale:
             x = self.gamma2 * x
         return feat + drop_path(x, self.drop_path_p, self.training)
@@ -202,7 +209,7 @@ class ClusterMerging(nn.Module):
         elif cluster_mask is not None:
             weights = weights * cluster_mask.unsqueeze(3)
         feat = ops.wf(weights, feat, member_idx).reshape(b, n_new, -1)                   # b x n' x ic*c
-        return pos, self.linear(_ln(ops, self.norm, feat))
+        return pos, _lin(ops, self.linear, _ln(ops, self.norm, feat))
 
 
 class BasicLayer(nn.Module):
@@ -278,6 +285,11 @@ class PatchEmbed(nn.Module):
         self.norm = nn.LayerNorm(embed_dim) if patch_norm else None
 
     def forward(self, x):
+        if x.is_cuda:
+            # NHWC through the stem: cuDNN's native layout (no NCHW<->NHWC conversion kernels around the convs), the
+            # per-channel BatchNorm reductions run over contiguous channel vectors, and the token matrix [b, h*w, c]
+            # below is then a view instead of a transpose copy
+            x = x.contiguous(memory_format=torch.channels_last)
         x = self.proj2(self.act1(self.bn(self.proj1(x))))
         b, c, h, w = x.shape
         x = x.flatten(2).transpose(1, 2)

@@ -28,6 +28,11 @@ class OracleOps:
         return P.select_ref(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on)
 
     @staticmethod
+    def linear(x, weight, bias=None):
+        """nn.Linear (aff_transformer.py:85-100,285)"""
+        return torch.nn.functional.linear(x, weight, bias)
+
+    @staticmethod
     def layer_norm(x, weight, bias, eps=1e-5):
         """nn.LayerNorm as the reference applies it (aff_transformer.py:199-200,284)"""
         return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)

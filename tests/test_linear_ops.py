@@ -1,0 +1,58 @@
+"""GPU parity of the column-sum bias gradient (csrc/col_sum.cu) and of the Linear operator built on it against
+nn.functional.linear evaluated in float64 on the same inputs (reference layers: aff_transformer.py:85-100,285)."""
+import pytest
+import torch
+
+from tests.util import assert_close
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(1, 64), (37, 64), (5000, 64), (100003, 128), (777, 96), (4096, 256), (300, 1024),
+                                   (64, 2048), (9, 8)])
+def test_col_sum(shape, dtype):
+    from affb200.linear_ops import col_sum
+    g = torch.Generator().manual_seed(shape[0] + shape[1])
+    x = torch.randn(shape, generator=g).to(dtype)
+    out = col_sum(x.cuda())
+    assert out.dtype == torch.float32 and out.shape == (shape[1],)
+    assert_close(out, x.double().sum(0), torch.float32, "col_sum")
+    # fixed summation order: bit-reproducible
+    assert torch.equal(out, col_sum(x.cuda()))
+
+
+def test_col_sum_edge_cases():
+    from affb200.linear_ops import col_sum
+    assert torch.equal(col_sum(torch.zeros(0, 64, device="cuda")), torch.zeros(64, device="cuda"))
+    x = torch.randn(50, 12, device="cuda")   # width not a multiple of 8 -> stock reduction
+    assert torch.allclose(col_sum(x), x.sum(0))
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        col_sum(torch.zeros(4, 8))
+
+
+@pytest.mark.parametrize("autocast", [False, True])
+@pytest.mark.parametrize("shape", [(4, 300, 64, 192), (2, 125, 256, 512), (3, 25, 1024, 512), (8, 64, 8)])
+def test_linear_matches_nn_linear(shape, autocast):
+    from affb200.linear_ops import linear
+    *lead, cin, cout = shape
+    g = torch.Generator().manual_seed(cin + cout)
+    x = torch.randn(*lead, cin, generator=g)
+    w = torch.randn(cout, cin, generator=g) / cin ** 0.5
+    b = torch.randn(cout, generator=g)
+    go = torch.randn(*lead, cout, generator=g)
+
+    def run(fn):
+        xs, ws, bs = (t.cuda().clone().requires_grad_(True) for t in (x, w, b))
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            y = fn(xs, ws, bs)
+        y.backward(go.cuda().to(y.dtype))
+        return y, xs.grad, ws.grad, bs.grad
+
+    ours = run(linear)
+    ref = run(torch.nn.functional.linear)
+    dt = torch.bfloat16 if autocast else torch.float32
+    assert ours[0].dtype == ref[0].dtype
+    for a, r, what in zip(ours, ref, ("y", "dx", "dw", "db")):
+        assert a.dtype == r.dtype, what
+        assert_close(a, r.double(), dt, "linear " + what)
