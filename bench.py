@@ -197,6 +197,8 @@ def main():
     l0 = N.LIB.affb200_launch_count()
     ms = timed_loop(lambda i: run.step(dev_batch), args.steps, world, device)
     launches = (N.LIB.affb200_launch_count() - l0) // max(args.steps, 1)
+    if getattr(run, "gstep", None) is not None:
+        launches = run.gstep.kernels_per_step  # recorded once at capture, launched by every graph replay
     clocks = sampler.finish()
     imgs = B * world * args.steps
     value = imgs / (ms * 1e-3)
@@ -214,6 +216,9 @@ def main():
     ms_e2e = timed_loop(e2e_step, args.steps, world, device)
     e2e_value = imgs / (ms_e2e * 1e-3)
     h2d = sum(t.numel() * t.element_size() for t in host[0])
+
+    if getattr(run, "gstep", None) is not None:
+        run.gstep.check()  # one host read: the index plans assumed by the captured step held in every replay
 
     # ---- roofline of the dominant kernel, timed live --------------------------------------------------------
     peak, peak_src = peaks()

@@ -183,7 +183,9 @@ class AffTrain:
                 "global_batch": B * world, "parallelism": "dp%d" % world,
                 "step": "forward + cross-entropy + backward + AdamW step, bf16 autocast, drop_path as configured",
                 "l2": "activations per step (GBs) far exceed the 126 MB L2; inputs alternate between two batches",
-                "attention": os.environ.get("AFFB200_ATTN", "fused")}
+                "attention": os.environ.get("AFFB200_ATTN", "fused"),
+                "launch": "eager" if os.environ.get("AFFB200_GRAPH", "1") == "0" else
+                          "CUDA graphs (fwd+loss+bwd, optimizer); one flat NCCL all-reduce between them for dp > 1"}
 
     def build(self, B, device, world):
         return _AffRun(self, B, device, world)
@@ -217,11 +219,16 @@ class _AffRun:
         self.ops = ops
         model = build_aff(wl.model_name, ops=ops).to(device).train()
         self.model = model
-        if world > 1:
+        # default: the step replayed as CUDA graphs (affb200/graph_step.py; gradients averaged with one flat NCCL
+        # all-reduce).  AFFB200_GRAPH=0: eager launches, DistributedDataParallel for world > 1 as the reference does.
+        self.graphed = os.environ.get("AFFB200_GRAPH", "1") != "0"
+        self.gstep = None
+        if world > 1 and not self.graphed:
             from torch.nn.parallel import DistributedDataParallel as DDP
             model = DDP(model, device_ids=[device.index], broadcast_buffers=False, gradient_as_bucket_view=True)
         self.net = model
-        self.opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.05, fused=True)
+        self.opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.05, fused=True,
+                                     capturable=self.graphed)
 
     def make_host_batch(self, i):
         g = torch.Generator().manual_seed(1000 + i)
@@ -234,6 +241,12 @@ class _AffRun:
 
     def step(self, batch):
         x, y = batch
+        if self.graphed:
+            if self.gstep is None:
+                from affb200.graph_step import GraphedTrainStep
+                self.gstep = GraphedTrainStep(self.model, self.opt, torch.nn.functional.cross_entropy, x, y,
+                                              world=self.world)
+            return self.gstep(x, y)
         self.opt.zero_grad(set_to_none=True)
         with torch.autocast("cuda", dtype=torch.bfloat16):
             logits = self.net(x)

@@ -16,7 +16,7 @@ import torch
 from torch.autograd import Function
 
 from . import _native as N
-from .plan import get_plan
+from .plan import get_plan, is_static, guard_add
 
 
 class _View(ctypes.Structure):
@@ -42,7 +42,11 @@ def _packed_pe(plan, pe_idx, mask):
         bad = torch.zeros(1, dtype=torch.int32, device=dev)
         N.check(N.LIB.affb200_fused_attn_pack_pe(N.p(pe_c), N.p(mask_c), pe_c.numel(), N.p(out), N.p(bad),
                                                  N.stream_ptr(dev)), "pack_pe")
-        res = out if int(bad.item()) == 0 else None
+        if is_static():
+            guard_add(bad)   # no read-back under graph capture: an out-of-range bias index trips the guard instead
+            res = out
+        else:
+            res = out if int(bad.item()) == 0 else None
     if not hasattr(plan, "_pe"):
         plan._pe = {}
     plan._pe.clear()

@@ -1,0 +1,94 @@
+"""A training step of the off-grid model as CUDA graphs (the stages are launch-latency-bound once the
+kernels are fast; the reference's step is ~3000 eager launches plus host syncs such as `nonzero`,
+aff_transformer.py:323).
+
+    step = GraphedTrainStep(model, optimizer, loss_fn, example_x, example_y, world=1)
+    loss = step(x, y)           # device tensor; no host sync
+    step.check()                # one host read: raises if a speculated index plan did not hold since the last check
+
+Shapes are static (batch, image size, and therefore every stage's token count `int(n * ds_rate)`), so the whole
+forward + loss + backward is captured once and replayed; the optimizer step is a second graph.  Between the two, for
+world_size > 1, the gradients — all views of ONE flat fp32 buffer — are averaged with a single NCCL all-reduce over
+NVLink (the batch-sharded data parallelism of the reference's DDP, main.py:102, with one bucket).
+
+What normally needs a device->host read while the index structures are built (tile-plan statistics, the range check
+of the packed bias indices) runs in `plan.static_plans()` mode: the sizes observed in the eager warm-up passes are
+assumed, and violations are accumulated in a device-side guard that `check()` reads.
+
+The warm-up passes are real optimisation steps on the example batch (the optimizer state must exist before capture).
+"""
+import torch
+import torch.distributed as dist
+
+from . import plan as _plan
+
+
+class GraphedTrainStep:
+    def __init__(self, model, optimizer, loss_fn, example_x, example_y, world=1, autocast_dtype=torch.bfloat16,
+                 warmup=3):
+        self.model, self.opt, self.loss_fn, self.world = model, optimizer, loss_fn, world
+        self.autocast_dtype = autocast_dtype
+        dev = example_x.device
+        self.device = dev
+        self.params = [p for p in model.parameters() if p.requires_grad]
+        if any(p.dtype != torch.float32 for p in self.params):
+            raise RuntimeError("GraphedTrainStep expects fp32 master parameters (autocast training)")
+        if world > 1:
+            for p in self.params:            # same start on every rank, as DDP's constructor does
+                dist.broadcast(p.data, 0)
+            for b in model.buffers():
+                dist.broadcast(b.data, 0)
+        n = sum(p.numel() for p in self.params)
+        self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
+        off = 0
+        for p in self.params:
+            p.grad = self.flat_grad[off:off + p.numel()].view_as(p)
+            off += p.numel()
+        self.x = example_x.clone()
+        self.y = example_y.clone()
+        self.loss = None
+        _plan.guard_tensor(dev)              # allocated outside the graphs' memory pool
+
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._fwd_bwd()
+                self._reduce()
+                self.opt.step()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+
+        from . import _native as N
+        l0 = N.LIB.affb200_launch_count()
+        self.g_fb = torch.cuda.CUDAGraph()
+        with _plan.static_plans(), torch.cuda.graph(self.g_fb):
+            self.loss = self._fwd_bwd()
+        # libaffb200 kernels recorded in the graph = launched by every replay
+        self.kernels_per_step = int(N.LIB.affb200_launch_count() - l0)
+        self.g_opt = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.g_opt, pool=self.g_fb.pool()):
+            self.opt.step()
+
+    def _fwd_bwd(self):
+        self.flat_grad.zero_()
+        with torch.autocast("cuda", dtype=self.autocast_dtype):
+            out = self.model(self.x)
+        loss = self.loss_fn(out.float(), self.y)
+        loss.backward()
+        return loss.detach()
+
+    def _reduce(self):
+        if self.world > 1:
+            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.AVG)
+
+    def __call__(self, x, y):
+        self.x.copy_(x, non_blocking=True)
+        self.y.copy_(y, non_blocking=True)
+        self.g_fb.replay()
+        self._reduce()
+        self.g_opt.replay()
+        return self.loss
+
+    def check(self):
+        _plan.check_guard(self.device)

@@ -10,8 +10,14 @@ backward call that receives the same tensor object:
     backward passes (affb200_csr_build).
 
 Plans are looked up by tensor identity and die with the tensor (weakref), and are invalidated by in-place writes
-(`Tensor._version`).  Building a tile plan reads back one 16-byte counter block (tiles whose union exceeded 256
-rows): a plan with overflowed tiles is discarded and the generic kernels are used for that tensor.
+(`Tensor._version`).  Building a tile plan reads back one 32-byte counter block (tiles whose union exceeded 256
+rows, the largest union): a plan with overflowed tiles is discarded and the generic kernels are used for that tensor.
+
+Static mode (`static_plans()`), for CUDA-graph capture of a whole training step: nothing may be read back, so a plan
+is built with the tile size and row bound *observed for the same problem shape* in earlier eager passes, and what the
+read-back would have checked is accumulated on the device instead (`guard_tensor()`: non-zero = a speculation failed
+in some step since the last `check_guard()`).  Kernels skip tiles that break the assumptions, so a failed speculation
+produces wrong numbers but no out-of-bounds access, and `check_guard()` raises.
 """
 import ctypes
 import os
@@ -24,6 +30,62 @@ from . import _native as N
 
 _lock = threading.Lock()
 _plans = {}  # id(tensor) -> (weakref, version, NbhdPlan)
+_observed = {}  # (kind, B, Nq, Nk, M) -> dict(T=tile size that did not overflow, umax=largest union seen)
+_static = False
+_guards = {}  # device index -> int32[1] tensor, non-zero after a failed speculation
+
+
+class static_plans:
+    """Context manager: tile plans are built from recorded shapes' statistics without any device->host read."""
+
+    def __enter__(self):
+        global _static
+        self.prev, _static = _static, True
+        return self
+
+    def __exit__(self, *exc):
+        global _static
+        _static = self.prev
+        return False
+
+
+def is_static():
+    return _static
+
+
+def guard_tensor(dev):
+    dev = torch.device(dev)
+    g = _guards.get(dev.index)
+    if g is None:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("affb200.plan: allocate the guard (guard_tensor(device)) before graph capture")
+        g = torch.zeros(1, dtype=torch.int32, device=dev)
+        _guards[dev.index] = g
+    return g
+
+
+def guard_add(flag_tensor):
+    """Accumulate a device-side boolean/int condition into the device's guard (capturable: no host read)."""
+    guard_tensor(flag_tensor.device).add_(flag_tensor.reshape(-1).ne(0).sum().to(torch.int32))
+
+
+def check_guard(dev):
+    """One device->host read: raises if any speculated plan of the steps since the last call was wrong."""
+    g = guard_tensor(dev)
+    bad = int(g.item())
+    if bad:
+        g.zero_()
+        raise RuntimeError("affb200: %d speculated index plan(s) did not hold (a tile referenced more rows than in "
+                           "the recorded passes); rerun the step eagerly" % bad)
+
+
+def observed_umax_cap(kind, shape_key):
+    """Largest union size the buffers sized for the observed maximum can take: the fused kernels round umax+1 up
+    to a multiple of 32 rows, so any union up to that bound runs with the same launch configuration."""
+    o = _observed.get((kind,) + shape_key)
+    if o is None:
+        return None
+    return min(N.PLAN_UMAX - 1, ((o["umax"] + 1 + 31) & ~31) - 1)
 
 NUM_SMS = 148
 
@@ -86,6 +148,12 @@ class NbhdPlan:
                 B, Nq, M = self.shape
                 dev = idx.device
                 T = pick_tile(B, Nq, M)
+                skey = (B, Nq, Nk, M)
+                obs = _observed.get(("q",) + skey)
+                if _static and obs is None:
+                    raise RuntimeError("affb200.plan: static mode needs an eager pass over shape %s first" % (skey,))
+                if _static:
+                    T = obs["T"]
                 with torch.cuda.device(dev):
                     while True:
                         nt = (Nq + T - 1) // T
@@ -95,10 +163,18 @@ class NbhdPlan:
                         stats = torch.zeros(8, dtype=torch.int32, device=dev)
                         N.check(N.LIB.affb200_qplan_build(N.p(idx), B, Nq, Nk, M, T, N.p(hdr), N.p(rows), N.p(loc),
                                                           N.p(stats), N.stream_ptr(dev)), "qplan_build")
+                        if _static:
+                            cap = observed_umax_cap("q", skey)
+                            guard_add((stats[0] != 0) | (stats[4] > cap))
+                            res = (T, hdr, rows, loc)
+                            self.stats["q"] = dict(T=T, overflow=0, dup_tiles=None, tiles=B * nt, umax=cap, static=True)
+                            break
                         st = stats.tolist()
                         if st[0] == 0:
                             res = (T, hdr, rows, loc)
                             self.stats["q"] = dict(T=T, overflow=0, dup_tiles=st[1], tiles=B * nt, umax=st[4])
+                            if obs is None or obs["T"] != T or st[4] > obs["umax"]:
+                                _observed[("q",) + skey] = dict(T=T, umax=max(st[4], obs["umax"] if obs and obs["T"] == T else 0))
                             break
                         if T == 16:
                             self.stats["q"] = dict(T=T, overflow=st[0], tiles=B * nt)
@@ -117,6 +193,12 @@ class NbhdPlan:
                 B, Nq, M = self.shape
                 dev = idx.device
                 T = pick_tile(B, Nk, M)
+                skey = (B, Nq, Nk, M)
+                obs = _observed.get(("k",) + skey)
+                if _static and obs is None:
+                    raise RuntimeError("affb200.plan: static mode needs an eager pass over shape %s first" % (skey,))
+                if _static:
+                    T = obs["T"]
                 with torch.cuda.device(dev):
                     while True:
                         nt = (Nk + T - 1) // T
@@ -127,10 +209,17 @@ class NbhdPlan:
                         stats = torch.zeros(8, dtype=torch.int32, device=dev)
                         N.check(N.LIB.affb200_kplan_build(N.p(idx), B, Nq, Nk, M, T, N.p(hdr), N.p(utok), N.p(rloc),
                                                           N.p(cnt), N.p(stats), N.stream_ptr(dev)), "kplan_build")
+                        if _static:
+                            guard_add(stats[2] != 0)   # the key-tile kernels size their buffers for 256 rows
+                            res = (T, hdr, utok, rloc)
+                            self.stats["k"] = dict(T=T, overflow=0, dup_tiles=None, tiles=B * nt, umax=N.PLAN_UMAX,
+                                                   static=True)
+                            break
                         st = stats.tolist()
                         if st[2] == 0:
                             res = (T, hdr, utok, rloc)
                             self.stats["k"] = dict(T=T, overflow=0, dup_tiles=st[3], tiles=B * nt, umax=st[5])
+                            _observed[("k",) + skey] = dict(T=T, umax=st[5])
                             break
                         if T == 16:
                             self.stats["k"] = dict(T=T, overflow=st[2], tiles=B * nt)

@@ -107,7 +107,9 @@ gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const 
     const int t0 = tile * TT;
     const int ti = min(TT, Nq - t0);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int U = q_hdr[int64_t(b) * n_tiles + tile] & AFFB200_PLAN_COUNT_MASK;
+    const int hdr0 = q_hdr[int64_t(b) * n_tiles + tile];
+    if (hdr0 & AFFB200_PLAN_OVERFLOW) return;  // only reachable with a speculated plan; the caller's deferred check reports it
+    const int U = hdr0 & AFFB200_PLAN_COUNT_MASK;
     const int Upad = (U + 15) & ~15;
     const int n_ent = ti * M;
 
@@ -271,6 +273,7 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
     const int ti = min(TT, Nq - t0);
     const int tid = threadIdx.x;
     const int hdr = q_hdr[int64_t(b) * n_tiles + tile];
+    if (hdr & AFFB200_PLAN_OVERFLOW) return;  // speculated plan only (see gather_dot_dense_kernel)
     const int U = hdr & AFFB200_PLAN_COUNT_MASK;
     const bool dup = (hdr & AFFB200_PLAN_DUP) != 0;
     const int Upad = (U + 15) & ~15;
@@ -346,6 +349,7 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
     const int tid = threadIdx.x;
     const int64_t tix = int64_t(b) * n_tiles + tile;
     const int hdr = k_hdr[tix];
+    if (hdr & AFFB200_PLAN_OVERFLOW) return;  // speculated plan only (see gather_dot_dense_kernel)
     const int Uq = hdr & AFFB200_PLAN_COUNT_MASK;
     const bool dup = (hdr & AFFB200_PLAN_DUP) != 0;
     const int Upad = (Uq + 15) & ~15;

@@ -274,7 +274,7 @@ constexpr uint32_t kSlotUnused = 0x80000000u;
 
 struct TileHdr {
     int U, Upad, ti, t0;
-    bool dup;
+    bool dup, bad;  // bad: overflowed tile or more rows than the launch sized its buffers for (speculated plans only)
 };
 
 // common prologue: tile header and union rows (as element offsets row*kv_stride, -1 above U) -> shared memory
@@ -286,6 +286,10 @@ __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32
     t.ti = min(TT, N - t.t0);
     const int hdr = q_hdr[int64_t(b) * n_tiles + tile];
     t.U = hdr & AFFB200_PLAN_COUNT_MASK;
+    t.bad = (hdr & AFFB200_PLAN_OVERFLOW) != 0 || t.U + 1 > UC;
+    t.dup = false;
+    t.Upad = 0;
+    if (t.bad) return t;
     t.dup = (hdr & AFFB200_PLAN_DUP) != 0;
     t.Upad = (t.U + 1 + 15) & ~15;
     const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * AFFB200_PLAN_UMAX;
@@ -451,6 +455,7 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
 
     const int b = blockIdx.y, tid = threadIdx.x;
     const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
+    if (t.bad) return;  // uniform over the CTA; the host's deferred plan check reports the failed speculation
     const int i = tid / TPR, sub = tid % TPR;  // this thread's token row and its position in the row's group
     const bool live = i < t.ti, has_blank = live && sub == 0;
     uint32_t desc[NE - 1];
@@ -545,6 +550,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
 
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
+    if (t.bad) return;
     const int i = tid / TPR, sub = tid % TPR;
     const bool live = i < t.ti, has_blank = live && sub == 0;
     const int64_t tok = t.t0 + (live ? i : 0);
