@@ -16,10 +16,9 @@ def _tiny(ops):
                            num_heads=[2, 4, 8, 10], mlp_ratio=2., drop_path_rate=0.0, img_size=160, ops=ops)
 
 
-def test_graphed_step_matches_eager():
+def _models():
     from affb200.aff_transformer import CudaOps
     from affb200 import fused
-    from affb200.graph_step import GraphedTrainStep
     from oracle.aff_ops_ref import fill_parameters_by_name
     ops = CudaOps()
     ops.fused_attention = fused.fused_cluster_attention
@@ -27,37 +26,65 @@ def test_graphed_step_matches_eager():
     m1 = _tiny(ops)
     fill_parameters_by_name(m1, seed=1)
     m1 = m1.cuda().train()
-    m2 = copy.deepcopy(m1)
+    return m1, copy.deepcopy(m1)
+
+
+def _batches(n):
     g = torch.Generator().manual_seed(5)
-    xs = [torch.randn(8, 3, 160, 160, generator=g).cuda() for _ in range(6)]
-    ys = [torch.randint(0, 10, (8,), generator=g).cuda() for _ in range(6)]
-    lossf = torch.nn.functional.cross_entropy
+    xs = [torch.randn(8, 3, 160, 160, generator=g).cuda() for _ in range(n)]
+    ys = [torch.randint(0, 10, (8,), generator=g).cuda() for _ in range(n)]
+    return xs, ys
 
-    o1 = torch.optim.AdamW(m1.parameters(), lr=1e-3, fused=True, capturable=True)
-    step = GraphedTrainStep(m1, o1, lossf, xs[0], ys[0], warmup=2)   # two real steps on batch 0
-    o2 = torch.optim.AdamW(m2.parameters(), lr=1e-3, fused=True)
 
-    def eager(x, y):
-        o2.zero_grad(set_to_none=True)
-        with torch.autocast("cuda", dtype=torch.bfloat16):
-            out = m2(x)
-        loss = lossf(out.float(), y)
-        loss.backward()
-        o2.step()
-        return loss.detach()
+def _eager_step(model, opt, x, y):
+    opt.zero_grad(set_to_none=True)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = model(x)
+    loss = torch.nn.functional.cross_entropy(out.float(), y)
+    loss.backward()
+    opt.step()
+    return loss.detach()
 
-    for _ in range(2):
-        eager(xs[0], ys[0])
+
+def test_graphed_step_matches_eager_loss_and_gradients():
+    """With a zero learning rate both models keep identical weights, so every replay must reproduce the eager
+    step's loss and gradients on a batch the capture never saw (new token selections, new index plans)."""
+    from affb200.graph_step import GraphedTrainStep
+    m1, m2 = _models()
+    for m in (m1, m2):   # BatchNorm statistics: no momentum so that the two models see the same statistics path
+        for mod in m.modules():
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.momentum = 0.0
+    xs, ys = _batches(5)
+    o1 = torch.optim.AdamW(m1.parameters(), lr=0.0, weight_decay=0.0, fused=True, capturable=True)
+    o2 = torch.optim.AdamW(m2.parameters(), lr=0.0, weight_decay=0.0, fused=True)
+    step = GraphedTrainStep(m1, o1, torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=2)
     assert step.kernels_per_step > 10
     for x, y in zip(xs[1:], ys[1:]):
-        l1 = step(x, y).clone()
-        l2 = eager(x, y)
-        assert torch.isfinite(l1)
-        assert abs(float(l1) - float(l2)) < 2e-2 * max(1.0, abs(float(l2))), (float(l1), float(l2))
+        l1 = float(step(x, y))
+        l2 = float(_eager_step(m2, o2, x, y))
+        assert abs(l1 - l2) < 2e-3 * max(1.0, abs(l2)), (l1, l2)
+        g1 = step.flat_grad
+        g2 = torch.cat([p.grad.reshape(-1) for p in m2.parameters() if p.requires_grad])
+        rel = float((g1 - g2).norm() / g2.norm())
+        assert rel < 2e-2, rel
     step.check()
-    # parameters stay together over the 5 steps (bf16 arithmetic, atomics order in the table gradient)
-    worst = max(float((a - b).abs().max() / (b.abs().max() + 1e-6)) for a, b in zip(m1.parameters(), m2.parameters()))
-    assert worst < 5e-2, worst
+    for a, b in zip(m1.parameters(), m2.parameters()):
+        assert torch.equal(a, b)
+
+
+def test_graphed_step_trains():
+    """A few real optimisation steps through the graphs reduce the loss on a fixed batch."""
+    from affb200.graph_step import GraphedTrainStep
+    m1, _ = _models()
+    xs, ys = _batches(1)
+    opt = torch.optim.AdamW(m1.parameters(), lr=2e-3, fused=True, capturable=True)
+    step = GraphedTrainStep(m1, opt, torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1)
+    first = float(step(xs[0], ys[0]))
+    for _ in range(10):
+        last = float(step(xs[0], ys[0]))
+    step.check()
+    assert last < first, (first, last)
 
 
 def test_guard_reports_failed_speculation():
