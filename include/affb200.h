@@ -276,6 +276,15 @@ int affb200_layer_norm_bwd(const void *dy, const void *x, const float *gamma, co
 int64_t affb200_col_sum_work_floats(int64_t R, int64_t C);
 int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C, int dtype, void *stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Residual connection with stochastic depth in one pass: out[b][...] = a[b][...] + x[b][...] * s[b]  (a may be NULL:
+ * out = x * s[b], the backward of the x branch).  Reference: `feat = shortcut + drop_path(feat)`
+ * (models/aff_transformer.py:224-229).  a/x/out [B][per_sample] of `dtype` (f32/f16/bf16), s [B] fp32; per_sample a
+ * multiple of 16 bytes.  The product is rounded to `dtype` before the add, as in the reference's two operations.
+ * ---------------------------------------------------------------------------------------------------------- */
+int affb200_scale_add(const void *a, const void *x, const float *s, void *out, int64_t B, int64_t per_sample, int dtype,
+                      void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,8 +30,10 @@ class CudaOps:
         from . import attn_ops as A
         from . import norm_ops as L
         from . import linear_ops as LI
+        from . import residual_ops as RO
         self.layer_norm = L.layer_norm
         self.linear = LI.linear
+        self.residual_add = RO.residual_add
         self.attn_bias_add = A.attn_bias_add
         self.table_gather = A.table_gather
         self.qk = CLUSTENQKFunction.apply
@@ -168,11 +170,11 @@ class ClusterTransformerBlock(nn.Module):
         x = self.attn(_ln(ops, self.norm1, feat), member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops)
         if self.layer_scale:
             x = self.gamma1 * x
-        feat = feat + drop_path(x, self.drop_path_p, self.training)
+        feat = ops.residual_add(feat, x, self.drop_path_p, self.training)
         x = self.mlp(_ln(ops, self.norm2, feat), ops)
         if self.layer_scale:
             x = self.gamma2 * x
-        return feat + drop_path(x, self.drop_path_p, self.training)
+        return ops.residual_add(feat, x, self.drop_path_p, self.training)
 
 
 class ClusterMerging(nn.Module):
@@ -284,7 +286,7 @@ class PatchEmbed(nn.Module):
         self.proj2 = nn.Conv2d(embed_dim // 2, embed_dim, kernel_size=3, stride=2, padding=1)
         self.norm = nn.LayerNorm(embed_dim) if patch_norm else None
 
-    def forward(self, x):
+    def forward(self, x, ops=None):
         if x.is_cuda:
             # NHWC through the stem: cuDNN's native layout (no NCHW<->NHWC conversion kernels around the convs), the
             # per-channel BatchNorm reductions run over contiguous channel vectors, and the token matrix [b, h*w, c]
@@ -294,7 +296,7 @@ class PatchEmbed(nn.Module):
         b, c, h, w = x.shape
         x = x.flatten(2).transpose(1, 2)
         if self.norm is not None:
-            x = self.norm(x)
+            x = self.norm(x) if ops is None else _ln(ops, self.norm, x)
         ys, xs = torch.meshgrid(torch.arange(h, device=x.device), torch.arange(w, device=x.device), indexing="ij")
         pos = torch.stack([xs, ys], dim=2).reshape(1, -1, 2).expand(b, -1, -1).to(x.dtype)
         return pos, x, h, w
@@ -341,7 +343,7 @@ class AutoFocusFormer(nn.Module):
 
     def forward_features(self, x):
         ops = self.ops if self.ops is not None else default_ops()
-        pos, x, h, w = self.patch_embed(x)
+        pos, x, h, w = self.patch_embed(x, ops)
         x = self.pos_drop(x)
         for i, layer in enumerate(self.layers):
             pos, x = layer(pos, x, h, w, i == 0, 2 ** (i + 1), self.rel_pos_width, self.table_width,

@@ -68,20 +68,22 @@ col_sum_kernel(const T *__restrict__ x, float *__restrict__ part, int64_t R, int
     }
 }
 
-// out[c] = sum over slabs, 8 threads per column
-__global__ void __launch_bounds__(256)
+// out[c] = sum over slabs: a block owns 32 columns, 32 threads per column stride over the slabs (coalesced 128-byte
+// rows of partials), then a fixed-order tree over the 32 partial sums
+__global__ void __launch_bounds__(1024)
 col_sum_finish_kernel(const float *__restrict__ part, int n_slabs, int C, float *__restrict__ out) {
-    const int c = blockIdx.x * 32 + (threadIdx.x & 31), sub = threadIdx.x >> 5;
-    __shared__ float red[8][32];
+    __shared__ float red[32][33];
+    const int cl = threadIdx.x & 31, sub = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl;
     float a = 0.f;
     if (c < C)
-        for (int s = sub; s < n_slabs; s += 8) a += part[int64_t(s) * C + c];
-    red[sub][threadIdx.x & 31] = a;
+        for (int s = sub; s < n_slabs; s += 32) a += part[int64_t(s) * C + c];
+    red[sub][cl] = a;
     __syncthreads();
     if (sub == 0 && c < C) {
         float t = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x & 31];
+        for (int k = 0; k < 32; ++k) t += red[k][cl];
         out[c] = t;
     }
 }
@@ -91,7 +93,7 @@ static void col_sum_geometry(int64_t R, int64_t C, int *lpr, int *n_cblk, int *n
     *lpr = nch <= 8 ? 8 : (nch <= 16 ? 16 : 32);
     *n_cblk = (nch + *lpr - 1) / *lpr;
     const int rpc = kCT / *lpr;
-    int64_t slabs = std::max<int64_t>(1, (int64_t(kNumSMs) * 8) / *n_cblk);
+    int64_t slabs = std::max<int64_t>(1, (int64_t(kNumSMs) * 4) / *n_cblk);
     slabs = std::min<int64_t>(slabs, ceil_div64(R, int64_t(rpc) * 4));
     slabs = std::max<int64_t>(slabs, 1);
     *rows_per_slab = ceil_div64(ceil_div64(R, slabs), rpc) * rpc;
@@ -136,6 +138,6 @@ extern "C" int affb200_col_sum(const void *x, float *out, float *work, int64_t R
         }
     });
     if (e) return e;
-    col_sum_finish_kernel<<<unsigned((C + 31) / 32), 256, 0, st>>>(work, n_slabs, int(C), out);
+    col_sum_finish_kernel<<<unsigned((C + 31) / 32), 1024, 0, st>>>(work, n_slabs, int(C), out);
     return check_launch("col_sum_finish");
 }

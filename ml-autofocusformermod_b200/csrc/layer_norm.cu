@@ -180,22 +180,23 @@ ln_bwd_kernel(const TG *__restrict__ dy, const TI *__restrict__ x, const float *
     }
 }
 
-// dgamma / dbeta = sum of the CTA partials in block order, 8 threads per column
-__global__ void __launch_bounds__(256)
+// dgamma / dbeta = sum of the CTA partials: a block owns 32 columns, 32 threads per column stride over the CTAs
+__global__ void __launch_bounds__(1024)
 ln_bwd_finish_kernel(const float *__restrict__ part, int nblk, int C, float *__restrict__ dgamma,
                      float *__restrict__ dbeta) {
-    __shared__ float red[8][32];
-    const int c = blockIdx.x * 32 + (threadIdx.x & 31), sub = threadIdx.x >> 5;
+    __shared__ float red[32][33];
+    const int cl = threadIdx.x & 31, sub = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl;
     const int pass = blockIdx.y;
     float a = 0.f;
     if (c < C)
-        for (int b = sub; b < nblk; b += 8) a += part[(int64_t(b) * 2 + pass) * C + c];
-    red[sub][threadIdx.x & 31] = a;
+        for (int b = sub; b < nblk; b += 32) a += part[(int64_t(b) * 2 + pass) * C + c];
+    red[sub][cl] = a;
     __syncthreads();
     if (sub == 0 && c < C) {
         float t = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x & 31];
+        for (int k = 0; k < 32; ++k) t += red[k][cl];
         (pass == 0 ? dgamma : dbeta)[c] = t;
     }
 }
@@ -301,6 +302,6 @@ extern "C" int affb200_layer_norm_bwd(const void *dy, const void *x, const float
         });
     });
     if (e) return e;
-    ln_bwd_finish_kernel<<<dim3(unsigned((C + 31) / 32), 2), 256, 0, st>>>(work, nblk, int(C), dgamma, dbeta);
+    ln_bwd_finish_kernel<<<dim3(unsigned((C + 31) / 32), 2), 1024, 0, st>>>(work, nblk, int(C), dgamma, dbeta);
     return check_launch("layer_norm_bwd_finish");
 }

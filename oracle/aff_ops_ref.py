@@ -28,6 +28,15 @@ class OracleOps:
         return P.select_ref(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on)
 
     @staticmethod
+    def residual_add(feat, x, p, training):
+        """`shortcut + drop_path(x)` with timm's DropPath (aff_transformer.py:224-229)"""
+        if p == 0. or not training:
+            return feat + x
+        keep = 1 - p
+        mask = x.new_empty((x.shape[0],) + (1,) * (x.dim() - 1)).bernoulli_(keep)
+        return feat + x * mask.div_(keep)
+
+    @staticmethod
     def linear(x, weight, bias=None):
         """nn.Linear (aff_transformer.py:85-100,285)"""
         return torch.nn.functional.linear(x, weight, bias)
