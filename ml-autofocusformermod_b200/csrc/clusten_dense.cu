@@ -71,6 +71,44 @@ __device__ __forceinline__ void stage_rows(T *dst, const T *__restrict__ src_bas
     }
 }
 
+// The same staging with the row offsets held in registers for the whole tile and the copies of one batch issued back
+// to back (ptxas separates an LDGSTS from earlier shared-memory traffic with filler instructions, so per-chunk index
+// loads between the copies cost more than the copies): thread owns chunk `ch` of rows r0, r0+RPP, ...
+template <typename T, int C>
+struct RowStager {
+    static constexpr int CS = C + 8;
+    static constexpr int CH = C / 8;
+    static constexpr int RPP = kDT / CH;
+    static constexpr int KMAX = kUMaxDense / RPP;
+    int off[KMAX];   // element offset row*stride + ch*8, < 0: no copy (the row stays as the tile prologue left it)
+    uint32_t dst0;
+
+    __device__ __forceinline__ void init(const int *rows_s, int n_rows, int stride) {
+        const int r0 = threadIdx.x / CH, ch = threadIdx.x % CH;
+        dst0 = uint32_t(r0 * CS + ch * 8) * 2u;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            const int row = r0 + k * RPP;
+            const int r = row < n_rows ? rows_s[row] : -1;
+            off[k] = r >= 0 ? r * stride + ch * 8 : -1;
+        }
+    }
+    __device__ __forceinline__ void issue(uint32_t buf_addr, const T *slab) const {
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k)
+            if (off[k] >= 0)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(buf_addr + dst0 + uint32_t(k * RPP * CS * 2)),
+                             "l"(slab + off[k]) : "memory");
+    }
+};
+// rows [r_lo, r_hi) of a padded staging buffer <- 0
+template <typename T, int C>
+__device__ __forceinline__ void zero_rows(T *buf, int r_lo, int r_hi) {
+    constexpr int CS = C + 8, CH = C / 8;
+    for (int q = threadIdx.x; q < (r_hi - r_lo) * CH; q += kDT)
+        *reinterpret_cast<uint4 *>(buf + (r_lo + q / CH) * CS + (q % CH) * 8) = make_uint4(0u, 0u, 0u, 0u);
+}
+
 struct TileSmem {
     int *rows;        // [256]
     uint8_t *loc;     // [T*M] (padded to 16 bytes)
@@ -330,8 +368,8 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
 // =========================================================================================================
 // scatter-wsum over key tiles: dY[r0 + r, :] = sum_{u, j : rloc[u][j] == r} w[utok[u], j] * x[utok[u], :]
 // =========================================================================================================
-template <typename T, int C>
-__global__ void __launch_bounds__(kDT)
+template <typename T, int C, int GPT>
+__global__ void __launch_bounds__(kDT, GPT == 8 ? 2 : 3)
 scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, const int32_t *__restrict__ k_hdr,
                           const int32_t *__restrict__ k_utok, const uint8_t *__restrict__ k_rloc,
                           T *__restrict__ dy, int H, int Nq, int Nk, int M, int TT, StridedRows xs_, StridedRows ys_,
@@ -356,24 +394,81 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
     const int n_ent = Uq * M;
 
     const int32_t *ug = k_utok + tix * kUMaxDense;
-    for (int u = tid; u < Upad; u += kDT) tok_s[u] = ug[u];
+    for (int u = tid; u < Upad; u += kDT) tok_s[u] = u < Uq ? ug[u] : -1;
     __syncthreads();
     const uint8_t *rl = k_rloc + tix * int64_t(kUMaxDense) * M;
+    const T *xb = x + int64_t(b) * xs_.sB;
+    T *yb = dy + int64_t(b) * ys_.sB + int64_t(r0) * ys_.sN;
+    RowStager<T, C> st;
+    st.init(tok_s, Uq, int(xs_.sN));
+    zero_rows<T, C>(xs, Uq, Upad);
+    const uint32_t xs_a = smem_u32(xs);
+
+    // Fast path (GPT > 0: M <= 8*GPT, M % 8 == 0, Nq*M < 2^24, checked by the launcher): each thread keeps its GPT
+    // groups of 8 slots — the 8 positions, and source offset | operand column << 24 — in registers for all heads.
+    // rloc does not depend on the head, so neither does the set of operand entries that get written: the operand is
+    // zeroed once per tile and every head overwrites the same entries.
+    if constexpr (GPT > 0) {
+        if (!dup) {
+            uint2 lc[GPT];
+            uint32_t src[GPT];
+#pragma unroll
+            for (int g = 0; g < GPT; ++g) {
+                const int p = (tid + g * kDT) * 8;
+                lc[g] = make_uint2(0xffffffffu, 0xffffffffu);
+                src[g] = 0u;
+                if (p < n_ent) {
+                    const int u = p / M;
+                    lc[g] = __ldg(reinterpret_cast<const uint2 *>(rl + p));
+                    src[g] = uint32_t(tok_s[u] * M + (p - u * M)) | (uint32_t(u) << 24);
+                }
+            }
+            zero_operand<T>(ps, TT, Upad);
+            for (int h = 0; h < H; ++h) {
+                const T *wz = w + (int64_t(b) * H + h) * Nq * M;
+                uint4 wv[GPT];
+#pragma unroll
+                for (int g = 0; g < GPT; ++g) {
+                    wv[g] = make_uint4(0u, 0u, 0u, 0u);
+                    if ((lc[g].x & lc[g].y) != 0xffffffffu)
+                        wv[g] = __ldg(reinterpret_cast<const uint4 *>(wz + (src[g] & 0xffffffu)));
+                }
+                st.issue(xs_a, xb + int64_t(h) * xs_.sH);
+                cp_async_commit();
+                if (h == 0) __syncthreads();  // the zero fill above
+#pragma unroll
+                for (int g = 0; g < GPT; ++g) {
+                    uint16_t *pcol = reinterpret_cast<uint16_t *>(ps) + (src[g] >> 24);
+                    const uint32_t wr[4] = {wv[g].x, wv[g].y, wv[g].z, wv[g].w};
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const uint32_t l = ((k < 4 ? lc[g].x : lc[g].y) >> (8 * (k & 3))) & 0xffu;
+                        if (l != 0xffu) pcol[l * kSS] = uint16_t(wr[k >> 1] >> (16 * (k & 1)));
+                    }
+                }
+                cp_async_wait_all();
+                __syncthreads();
+                wsum_mma_store<T, C>(ps, xs, os, yb + int64_t(h) * ys_.sH, TT, Upad, ri, ys_.sN, alpha);
+                __syncthreads();
+            }
+            return;
+        }
+    }
 
     for (int h = 0; h < H; ++h) {
         const int64_t z = int64_t(b) * H + h;
-        stage_rows<T, C>(xs, x + int64_t(b) * xs_.sB + int64_t(h) * xs_.sH, Upad, [&](int i) { return tok_s[i]; }, xs_.sN);
+        st.issue(xs_a, xb + int64_t(h) * xs_.sH);
         cp_async_commit();
         zero_operand<T>(ps, TT, Upad);
         __syncthreads();
         const T *wz = w + z * Nq * M;
         if (!dup) {
             if (M % 8 == 0 && (reinterpret_cast<uintptr_t>(wz) & 15) == 0 && (reinterpret_cast<uintptr_t>(rl) & 7) == 0) {
-                for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {
+                for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {  // wide neighbourhoods (M > 64): groups do not fit registers
                     const int p = p8 * 8;
                     const int u = p / M, j = p - u * M;
                     const uint2 lc = __ldg(reinterpret_cast<const uint2 *>(rl + p));
-                    if (lc.x == 0xffffffffu && lc.y == 0xffffffffu) continue;
+                    if ((lc.x & lc.y) == 0xffffffffu) continue;
                     const uint4 wv = __ldg(reinterpret_cast<const uint4 *>(wz + int64_t(tok_s[u]) * M + j));
                     const uint16_t *e = reinterpret_cast<const uint16_t *>(&wv);
                     const uint8_t *l8 = reinterpret_cast<const uint8_t *>(&lc);
@@ -403,8 +498,7 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
         }
         cp_async_wait_all();
         __syncthreads();
-        wsum_mma_store<T, C>(ps, xs, os, dy + int64_t(b) * ys_.sB + int64_t(h) * ys_.sH + int64_t(r0) * ys_.sN, TT, Upad,
-                             ri, ys_.sN, alpha);
+        wsum_mma_store<T, C>(ps, xs, os, yb + int64_t(h) * ys_.sH, TT, Upad, ri, ys_.sN, alpha);
         __syncthreads();
     }
 }
@@ -479,17 +573,30 @@ int launch_scatter_wsum_dense_strided(const T *w, const T *x, const affb200_nbhd
                                       int64_t Nq, int64_t Nk, int64_t M, int64_t c, const int64_t *x_str,
                                       const int64_t *y_str, float alpha, cudaStream_t st) {
     const StridedRows xs_{x_str[0], x_str[1], x_str[2]}, ys_{y_str[0], y_str[1], y_str[2]};
+    if (xs_.sN <= 0 || Nq * xs_.sN >= (int64_t(1) << 31) || Nq * M >= (int64_t(1) << 31)) {
+        set_error("scatter_wsum_dense: source rows are addressed with 32-bit element offsets (Nq * row stride < 2^31)");
+        return AFFB200_E_ARG;
+    }
     const int TT = pl->tk;
     dim3 grid(unsigned((Nk + TT - 1) / TT), unsigned(B));
     const size_t smem = smem_scatter_wsum(int(c), TT);
-#define AFF_L(C_)                                                                                               \
+    // register-resident slot groups when they fit (see the kernel): 6 groups per thread cover M <= 48, 8 cover M <= 64
+    const bool regs_ok = (M % 8 == 0) && Nq * M < (int64_t(1) << 24) && aligned16(w) &&
+                         (reinterpret_cast<uintptr_t>(pl->k_rloc) & 7) == 0;
+    const int gpt = !regs_ok ? 0 : (M <= 48 ? 6 : (M <= 64 ? 8 : 0));
+#define AFF_L(C_, G_)                                                                                           \
     do {                                                                                                        \
-        auto kern = scatter_wsum_dense_kernel<T, C_>;                                                           \
+        auto kern = scatter_wsum_dense_kernel<T, C_, G_>;                                                       \
         if (int e = set_smem(kern, smem)) return e;                                                             \
         kern<<<grid, kDT, smem, st>>>(w, x, pl->k_hdr, pl->k_utok, pl->k_rloc, dy, int(H), int(Nq), int(Nk),    \
                                       int(M), TT, xs_, ys_, alpha);                                             \
     } while (0)
-    if (c == 32) AFF_L(32); else AFF_L(16);
+#define AFF_LG(C_)                                                          \
+    do {                                                                    \
+        if (gpt == 6) AFF_L(C_, 6); else if (gpt == 8) AFF_L(C_, 8); else AFF_L(C_, 0); \
+    } while (0)
+    if (c == 32) AFF_LG(32); else AFF_LG(16);
+#undef AFF_LG
 #undef AFF_L
     return check_launch("scatter_wsum_dense");
 }

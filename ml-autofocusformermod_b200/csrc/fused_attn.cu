@@ -437,7 +437,7 @@ __device__ __forceinline__ void f_put_blank(T *buf, int U, const float *__restri
 // has left the staging buffers, V of head h+1 as soon as O = P·V of head h has; every wait is "all but the newest
 // group" (cp.async groups retire in order: ... QK_h, V_h, QK_h+1, V_h+1 ...).
 template <typename T, int C, int TT, int NE>
-__global__ void __launch_bounds__(kFT)
+__global__ void __launch_bounds__(kFT, NE <= 7 ? 3 : 2)
 fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float *__restrict__ table,
                       const float *__restrict__ blank_k, const float *__restrict__ blank_v,
                       const int32_t *__restrict__ q_hdr, const int32_t *__restrict__ q_rows,
@@ -522,7 +522,7 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
 // after the two contractions of head h, Q/dO/O of head h+1 right after its row phase.
 // ---------------------------------------------------------------------------------------------------------
 template <typename T, int C, int TT, int NE>
-__global__ void __launch_bounds__(kFT)
+__global__ void __launch_bounds__(kFT, 2)
 fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout, ViewW<T> dq,
                       const float *__restrict__ table, const float *__restrict__ blank_k,
                       const float *__restrict__ blank_v, const int32_t *__restrict__ q_hdr,

@@ -16,6 +16,8 @@ def main():
         if r.get("Metric Name") != "gpu__time_duration.sum":
             continue
         v = float(r["Metric Value"].replace(",", ""))
+        if v != v:
+            continue  # ncu reports nan for a few graph nodes (memset nodes)
         unit = r.get("Metric Unit", "ns")
         scale = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "nsecond": 1e-3, "usecond": 1.0, "msecond": 1e3}.get(unit, 1e-3)
         rows.append((int(r["ID"]), r["Kernel Name"], v * scale))
