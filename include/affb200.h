@@ -219,6 +219,10 @@ int affb200_gather_rows_i64(const int64_t *src, const int64_t *idx, int64_t B, i
  * ---------------------------------------------------------------------------------------------------------- */
 int affb200_attn_bias_add(void *attn, const float *table, const int64_t *pe_idx, const int64_t *mask,
                           int64_t B, int64_t H, int64_t N, int64_t M, int dtype, void *stream);
+/* out[t][0..IC) = table[idx[t]][0..IC): the PointConv weight lookup of ClusterMerging (reference
+ * aff_transformer.py:347-349); rows of IC elements of elem_bytes (2, 4 or 8) bytes each, idx not range-checked. */
+int affb200_table_gather(const void *table, const int64_t *idx, void *out, int64_t total, int64_t IC, int elem_bytes,
+                         void *stream);
 int affb200_attn_bias_bwd(const void *d_vals, const int64_t *pe_idx, int64_t B, int64_t H, int64_t N, int64_t M,
                           int64_t P, int channel_last, float *d_table, int dtype, void *stream);
 

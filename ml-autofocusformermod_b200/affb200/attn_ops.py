@@ -58,9 +58,18 @@ class AttnBiasAddFunction(Function):
 class TableGatherFunction(Function):
     @staticmethod
     def forward(ctx, table, pe_idx):
+        if not table.is_cuda:
+            raise RuntimeError("table must be a CUDA tensor")
         ctx.save_for_backward(pe_idx)
         ctx.table_meta = (table.shape[0], table.dtype)
-        return table[pe_idx.reshape(-1)].reshape(*pe_idx.shape, table.shape[1])
+        tab = table.detach().contiguous()
+        idx = pe_idx.contiguous()
+        dev = table.device
+        with torch.cuda.device(dev):
+            out = torch.empty((*pe_idx.shape, table.shape[1]), dtype=table.dtype, device=dev)
+            N.check(N.LIB.affb200_table_gather(N.p(tab), N.p(idx), N.p(out), idx.numel(), table.shape[1],
+                                               table.element_size(), N.stream_ptr(dev)), "table_gather")
+        return out
 
     @staticmethod
     def backward(ctx, d_out):

@@ -129,6 +129,25 @@ table_grad_u16_kernel(const T *__restrict__ d_vals, const uint16_t *__restrict__
     }
 }
 
+// out[t][:] = table[idx[t]][:] for rows of ROWB bytes (4, 8 or 16): one thread per gathered row.  The PointConv weights
+// of ClusterMerging are rows of 4 floats (reference aff_transformer.py:347-349); the stock indexing kernel spends a
+// whole CTA on each 16-byte row.
+template <typename V>
+__global__ void __launch_bounds__(256)
+table_gather_kernel(const V *__restrict__ table, const int64_t *__restrict__ idx, V *__restrict__ out, int64_t total) {
+    const int64_t t = int64_t(blockIdx.x) * 256 + threadIdx.x;
+    if (t < total) out[t] = __ldg(table + __ldg(idx + t));
+}
+template <typename T>
+__global__ void __launch_bounds__(256)
+table_gather_generic_kernel(const T *__restrict__ table, const int64_t *__restrict__ idx, T *__restrict__ out,
+                            int64_t total, int IC) {
+    const int64_t e = int64_t(blockIdx.x) * 256 + threadIdx.x;
+    if (e >= total * IC) return;
+    const int64_t t = e / IC;
+    out[e] = __ldg(table + __ldg(idx + t) * IC + (e - t * IC));
+}
+
 int launch_table_grad_u16(const void *d_vals, const uint16_t *pe, int64_t B, int64_t H, int64_t NM, int64_t P,
                           float *d_table, int dtype, cudaStream_t st) {
     if (cudaMemsetAsync(d_table, 0, size_t(P * H) * 4, st) != cudaSuccess) return check_launch("table_grad memset", 0);
@@ -196,4 +215,34 @@ extern "C" int affb200_attn_bias_bwd(const void *d_attn, const int64_t *pe_idx, 
         }
         return check_launch("attn_bias_bwd");
     });
+}
+
+extern "C" int affb200_table_gather(const void *table, const int64_t *idx, void *out, int64_t total, int64_t IC,
+                                    int elem_bytes, void *stream) {
+    if (total < 0 || IC <= 0 || (elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8)) {
+        set_error("table_gather: bad dimensions");
+        return AFFB200_E_ARG;
+    }
+    if (total == 0) return AFFB200_OK;
+    if (!table || !idx || !out) { set_error("table_gather: null pointer"); return AFFB200_E_ARG; }
+    auto st = (cudaStream_t)stream;
+    const int64_t rowb = IC * elem_bytes;
+    const unsigned grid = unsigned((total + 255) / 256);
+    const uintptr_t al = reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(out);
+    if (rowb == 16 && (al & 15) == 0)
+        table_gather_kernel<uint4><<<grid, 256, 0, st>>>((const uint4 *)table, idx, (uint4 *)out, total);
+    else if (rowb == 8 && (al & 7) == 0)
+        table_gather_kernel<uint2><<<grid, 256, 0, st>>>((const uint2 *)table, idx, (uint2 *)out, total);
+    else if (rowb == 4 && (al & 3) == 0)
+        table_gather_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t *)table, idx, (uint32_t *)out, total);
+    else {
+        const unsigned g2 = unsigned((total * IC + 255) / 256);
+        if (elem_bytes == 2)
+            table_gather_generic_kernel<uint16_t><<<g2, 256, 0, st>>>((const uint16_t *)table, idx, (uint16_t *)out, total, int(IC));
+        else if (elem_bytes == 4)
+            table_gather_generic_kernel<uint32_t><<<g2, 256, 0, st>>>((const uint32_t *)table, idx, (uint32_t *)out, total, int(IC));
+        else
+            table_gather_generic_kernel<uint64_t><<<g2, 256, 0, st>>>((const uint64_t *)table, idx, (uint64_t *)out, total, int(IC));
+    }
+    return check_launch("table_gather");
 }
