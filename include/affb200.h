@@ -289,6 +289,24 @@ int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C
 int affb200_scale_add(const void *a, const void *x, const float *s, void *out, int64_t B, int64_t per_sample, int dtype,
                       void *stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Merge half of ClusterMerging without materialising the PointConv weights (reference
+ * models/aff_transformer.py:343-361):  W[b,i,j,:] = table[pe_idx[b,i,j]][0..4) * lp[b, nbhd[b,i,j]] * mask[b,i,j];
+ * out[b,i,q,:] = sum_j W[b,i,j,q] * feat[b, nbhd[b,i,j], :].
+ * table [P][4] fp32; pe_idx / nbhd / mask [B][Nq][M] int64 (mask may be NULL); lp [B][Nk] of lp_dtype or NULL (= 1);
+ * feat [B][Nk][C] of feat_dtype; out [B][Nq][4][C] fp32; C in {32, 64, 128, 256, 512}.
+ * Backward: d_out [B][Nq][4][C] fp32 -> d_wt [B][Nq][M][4] fp32 (the operand of the table gradient: feed it to
+ * affb200_attn_bias_bwd with channel_last = 1), d_lp [B][Nk] fp32 (NULL to skip), d_feat [B][Nk][C] of feat_dtype
+ * (NULL to skip; needs the transposed index csr_off [B][Nk+1] / csr_ent [B][Nq*M] of affb200_csr_build on nbhd).
+ * ---------------------------------------------------------------------------------------------------------- */
+int affb200_merge_fwd(const float *table, const int64_t *pe_idx, const int64_t *nbhd, const int64_t *mask,
+                      const void *lp, const void *feat, float *out, int64_t B, int64_t Nq, int64_t Nk, int64_t M,
+                      int64_t C, int lp_dtype, int feat_dtype, void *stream);
+int affb200_merge_bwd(const float *d_out, const float *table, const int64_t *pe_idx, const int64_t *nbhd,
+                      const int64_t *mask, const void *lp, const void *feat, const int32_t *csr_off,
+                      const int32_t *csr_ent, float *d_wt, float *d_lp, void *d_feat, int64_t B, int64_t Nq, int64_t Nk,
+                      int64_t M, int64_t C, int lp_dtype, int feat_dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

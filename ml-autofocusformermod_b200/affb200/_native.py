@@ -59,6 +59,8 @@ SIGNATURES = {
                                + [ctypes.c_float, _int, _ptr]),
     "affb200_fused_attn_bwd": (_int, [_ptr] * 8 + [_ptr] * 3 + [_plan_p, _ptr, ctypes.c_int32, _ptr] + [_ptr] * 4
                                + [_i64] * 6 + [ctypes.c_float, _int, _ptr]),
+    "affb200_merge_fwd": (_int, [_ptr] * 7 + [_i64] * 5 + [_int, _int, _ptr]),
+    "affb200_merge_bwd": (_int, [_ptr] * 12 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_table_gather": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),
     "affb200_scale_add": (_int, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),
     "affb200_col_sum_work_floats": (_i64, [_i64, _i64]),

@@ -34,6 +34,8 @@ class CudaOps:
         self.layer_norm = L.layer_norm
         self.linear = LI.linear
         self.residual_add = RO.residual_add
+        from . import merge_ops as MO
+        self.merge_wf = MO.merge_wf
         self.attn_bias_add = A.attn_bias_add
         self.table_gather = A.table_gather
         self.qk = CLUSTENQKFunction.apply
@@ -202,6 +204,11 @@ class ClusterMerging(nn.Module):
             cluster_mask = ops.gather_rows(cluster_mask, idx)
         m = member_idx.shape[-1]
         weights_table = self.weight_net(pre_table)                                       # T*T x ic
+        fused = getattr(ops, "merge_wf", None)
+        if fused is not None:    # weights formed inside the kernels from table[pe_idx], lp[member_idx] and the mask
+            out = fused(weights_table, pe_idx, learned_prob, cluster_mask, feat, member_idx)
+            if out is not None:
+                return pos, _lin(ops, self.linear, _ln(ops, self.norm, out))
         weights = ops.table_gather(weights_table, pe_idx)                                # b x n' x m x ic
         if learned_prob is not None:
             lp = learned_prob.gather(1, member_idx.reshape(b, -1, 1)).reshape(b, n_new, m, 1)
