@@ -295,8 +295,16 @@ class _AffRun:
             return unfused
         fmt = lambda r: {"kernel": r["kernel"], "ms": round(r["ms"], 4), "GBps": round(r["GBps"], 1),
                          "frac": round(r["GBps"] / peak, 3), "calls_per_step": r["calls_per_step"]}
+        # measured DRAM bytes of the same launch group from the committed ncu pass (profiles/r01_ncu_traffic.json)
+        traffic = None
+        try:
+            import json
+            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_ncu_traffic.json")))
+            traffic = tj["per_launch_group"].get(top["kernel"], {}).get("dram_bytes")
+        except Exception:
+            traffic = None
         return {"bound": "hbm", "kernel": top["kernel"], "achieved": top["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": top["GBps"] / peak, "traffic": None, "peak_source": peak_src,
+                "frac": top["GBps"] / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": top["bytes"], "avg_launch_ms": top["ms"],
                 "all": [fmt(r) for r in rows], "unfused_clusten_ops": unfused["all"]}
 
