@@ -128,12 +128,15 @@ template <int C> __host__ __device__ constexpr int os_floats() { return 8 * 16 *
 // =========================================================================================================
 // gather-dot
 // =========================================================================================================
-template <typename T, int C>
+// FAST (decided by the launcher: M % 8 == 0, M <= 64, 16-byte aligned operands): the tile's 1-byte positions live in
+// registers as groups of 8 slots (at most 2 groups per thread) for all heads instead of in shared memory.
+template <typename T, int C, bool FAST>
 __global__ void __launch_bounds__(kDT)
 gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const int32_t *__restrict__ q_hdr,
                         const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc, T *__restrict__ out,
                         int H, int Nq, int Nk, int M, int TT) {
     constexpr int CS = C + 8;
+    constexpr int CH = C / 8;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     int *rows_s = reinterpret_cast<int *>(smem_raw);
     T *ys = reinterpret_cast<T *>(smem_raw + 1024);
@@ -152,27 +155,54 @@ gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const 
     const int n_ent = ti * M;
 
     const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * kUMaxDense;
-    for (int u = tid; u < Upad; u += kDT) rows_s[u] = rg[u];
+    for (int u = tid; u < Upad; u += kDT) rows_s[u] = u < U ? rg[u] : -1;
     const uint8_t *lg = q_loc + (int64_t(b) * Nq + t0) * M;
-    if ((reinterpret_cast<uintptr_t>(lg) & 15) == 0) {
-        for (int p = tid; p < (n_ent + 15) / 16; p += kDT)
-            reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(reinterpret_cast<const uint4 *>(lg) + p);  // tail over-read stays inside the [B][Nq][M] array + 16-byte slack kept by the host
+    uint2 lc[2];
+    int srow[2];
+    if constexpr (FAST) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int p = (tid + k * kDT) * 8;
+            lc[k] = make_uint2(0u, 0u);
+            srow[k] = -1;
+            if (p < n_ent) {
+                lc[k] = __ldg(reinterpret_cast<const uint2 *>(lg + p));
+                srow[k] = (p / M) * kSS;
+            }
+        }
     } else {
-        for (int p = tid; p < n_ent; p += kDT) loc_s[p] = lg[p];
+        if ((reinterpret_cast<uintptr_t>(lg) & 15) == 0) {
+            for (int p = tid; p < (n_ent + 15) / 16; p += kDT)
+                reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(reinterpret_cast<const uint4 *>(lg) + p);  // tail over-read stays inside the [B][Nq][M] array + 16-byte slack kept by the host
+        } else {
+            for (int p = tid; p < n_ent; p += kDT) loc_s[p] = lg[p];
+        }
     }
+    zero_rows<T, C>(ys, U, Upad);
+    zero_rows<T, C>(xs, ti, TT);
     __syncthreads();
+    RowStager<T, C> st;
+    st.init(rows_s, U, C);
+    const uint32_t ys_a = smem_u32(ys), xs_a = smem_u32(xs);
+    const int xrow = tid / CH, xch = tid % CH;
+    const bool xok = tid < TT * CH && xrow < ti;
+    auto issue = [&](int h) {
+        const int64_t z = int64_t(b) * H + h;
+        if (xok)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(xs_a + uint32_t(xrow * CS + xch * 8) * 2u),
+                         "l"(x + (z * Nq + t0 + xrow) * C + xch * 8) : "memory");
+        st.issue(ys_a, y + z * Nk * C);
+        cp_async_commit();
+    };
+    issue(0);
 
     const int MT = TT >> 4;
     const int mt = warp % MT;
     const int nstep = 8 / MT;  // warps sharing one m-tile
     const int g = lane >> 2, q4 = lane & 3;
-    const bool vec_out = (M % 8 == 0);
 
     for (int h = 0; h < H; ++h) {
         const int64_t z = int64_t(b) * H + h;
-        stage_rows<T, C>(xs, x + (z * Nq + t0) * C, TT, [&](int i) { return i < ti ? i : -1; });
-        stage_rows<T, C>(ys, y + z * Nk * C, Upad, [&](int i) { return rows_s[i]; });
-        cp_async_commit();
         cp_async_wait_all();
         __syncthreads();
 
@@ -207,25 +237,26 @@ gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const 
             }
         }
         __syncthreads();
+        if (h + 1 < H) issue(h + 1);  // the staging buffers are free: the next head loads while this one is written out
 
         T *og = out + (z * Nq + t0) * M;
-        if (vec_out && (reinterpret_cast<uintptr_t>(og) & 15) == 0) {
-            for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {
-                const int p = p8 * 8;
-                const int t = p / M;
-                const uint2 lc = *reinterpret_cast<const uint2 *>(loc_s + p);
-                const T *srow = ss + t * kSS;
-                const uint8_t *l8 = reinterpret_cast<const uint8_t *>(&lc);
-                uint4 v;
-                uint16_t *e = reinterpret_cast<uint16_t *>(&v);
+        if constexpr (FAST) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) e[k] = *reinterpret_cast<const uint16_t *>(srow + l8[k]);
-                st_cs_u4(og + p, v);
+            for (int k = 0; k < 2; ++k) {
+                if (srow[k] < 0) continue;
+                const uint16_t *sr = reinterpret_cast<const uint16_t *>(ss + srow[k]);
+                uint32_t w4[4];
+#pragma unroll
+                for (int e = 0; e < 8; e += 2) {
+                    const uint32_t l0 = ((e < 4 ? lc[k].x : lc[k].y) >> (8 * (e & 3))) & 0xffu;
+                    const uint32_t l1 = ((e < 4 ? lc[k].x : lc[k].y) >> (8 * ((e + 1) & 3))) & 0xffu;
+                    w4[e >> 1] = uint32_t(sr[l0]) | (uint32_t(sr[l1]) << 16);
+                }
+                st_cs_u4(og + (tid + k * kDT) * 8, make_uint4(w4[0], w4[1], w4[2], w4[3]));
             }
         } else {
             for (int p = tid; p < n_ent; p += kDT) og[p] = ss[(p / M) * kSS + loc_s[p]];
         }
-        __syncthreads();
     }
 }
 
@@ -293,7 +324,7 @@ __device__ __forceinline__ void zero_operand(T *ps, int n_rows, int Kpad) {
 // =========================================================================================================
 // gather-wsum
 // =========================================================================================================
-template <typename T, int C>
+template <typename T, int C, bool FAST>
 __global__ void __launch_bounds__(kDT)
 gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const int32_t *__restrict__ q_hdr,
                          const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc, T *__restrict__ out,
@@ -318,44 +349,87 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
     const int n_ent = ti * M;
 
     const int32_t *rg = q_rows + (int64_t(b) * n_tiles + tile) * kUMaxDense;
-    for (int u = tid; u < Upad; u += kDT) rows_s[u] = rg[u];
+    for (int u = tid; u < Upad; u += kDT) rows_s[u] = u < U ? rg[u] : -1;
     const uint8_t *lg = q_loc + (int64_t(b) * Nq + t0) * M;
-    if ((reinterpret_cast<uintptr_t>(lg) & 15) == 0) {
-        for (int p = tid; p < (n_ent + 15) / 16; p += kDT)
-            reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(reinterpret_cast<const uint4 *>(lg) + p);
+    const bool regs = FAST && !dup;  // slot groups in registers, operand zeroed once (every head writes the same entries)
+    uint2 lc[2];
+    int prow[2];
+    if (regs) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int p = (tid + k * kDT) * 8;
+            lc[k] = make_uint2(0u, 0u);
+            prow[k] = -1;
+            if (p < n_ent) {
+                lc[k] = __ldg(reinterpret_cast<const uint2 *>(lg + p));
+                prow[k] = (p / M) * kSS;
+            }
+        }
+        zero_operand<T>(ps, TT, Upad);
     } else {
-        for (int p = tid; p < n_ent; p += kDT) loc_s[p] = lg[p];
+        if ((reinterpret_cast<uintptr_t>(lg) & 15) == 0) {
+            for (int p = tid; p < (n_ent + 15) / 16; p += kDT)
+                reinterpret_cast<uint4 *>(loc_s)[p] = __ldg(reinterpret_cast<const uint4 *>(lg) + p);
+        } else {
+            for (int p = tid; p < n_ent; p += kDT) loc_s[p] = lg[p];
+        }
     }
+    zero_rows<T, C>(ys, U, Upad);
     __syncthreads();
+    RowStager<T, C> st;
+    st.init(rows_s, U, C);
+    const uint32_t ys_a = smem_u32(ys);
 
     for (int h = 0; h < H; ++h) {
         const int64_t z = int64_t(b) * H + h;
-        stage_rows<T, C>(ys, y + z * Nk * C, Upad, [&](int i) { return rows_s[i]; });
-        cp_async_commit();
-        zero_operand<T>(ps, TT, Upad);
-        __syncthreads();
         const T *wg = w + (z * Nq + t0) * M;
-        if (!dup) {
-            if (M % 8 == 0 && (reinterpret_cast<uintptr_t>(wg) & 15) == 0) {
-                for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {
-                    const int p = p8 * 8;
-                    const uint4 wv = __ldg(reinterpret_cast<const uint4 *>(wg + p));
-                    const uint2 lc = *reinterpret_cast<const uint2 *>(loc_s + p);
-                    const uint16_t *e = reinterpret_cast<const uint16_t *>(&wv);
-                    const uint8_t *l8 = reinterpret_cast<const uint8_t *>(&lc);
-                    uint16_t *prow = reinterpret_cast<uint16_t *>(ps + (p / M) * kSS);
+        uint4 wv[2];
+        if (regs) {
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) prow[l8[k]] = e[k];
-                }
-            } else {
-                for (int p = tid; p < n_ent; p += kDT) ps[(p / M) * kSS + loc_s[p]] = wg[p];
+            for (int k = 0; k < 2; ++k) {
+                wv[k] = make_uint4(0u, 0u, 0u, 0u);
+                if (prow[k] >= 0) wv[k] = __ldg(reinterpret_cast<const uint4 *>(wg) + tid + k * kDT);
             }
-        } else if (tid < ti) {
-            // a token lists a row more than once: accumulate that token's operand row in slot order
-            T *prow = ps + tid * kSS;
-            for (int j = 0; j < M; ++j) {
-                const int l = loc_s[tid * M + j];
-                prow[l] = Elem<T>::from_acc(Elem<T>::to_acc(prow[l]) + Elem<T>::to_acc(wg[tid * M + j]));
+        }
+        st.issue(ys_a, y + z * Nk * C);
+        cp_async_commit();
+        if (regs) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                if (prow[k] < 0) continue;
+                uint16_t *pr = reinterpret_cast<uint16_t *>(ps + prow[k]);
+                const uint32_t wr[4] = {wv[k].x, wv[k].y, wv[k].z, wv[k].w};
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const uint32_t l = ((e < 4 ? lc[k].x : lc[k].y) >> (8 * (e & 3))) & 0xffu;
+                    pr[l] = uint16_t(wr[e >> 1] >> (16 * (e & 1)));
+                }
+            }
+        } else {
+            zero_operand<T>(ps, TT, Upad);
+            __syncthreads();
+            if (!dup) {
+                if (M % 8 == 0 && (reinterpret_cast<uintptr_t>(wg) & 15) == 0) {
+                    for (int p8 = tid; p8 < n_ent / 8; p8 += kDT) {
+                        const int p = p8 * 8;
+                        const uint4 wv8 = __ldg(reinterpret_cast<const uint4 *>(wg + p));
+                        const uint2 l2 = *reinterpret_cast<const uint2 *>(loc_s + p);
+                        const uint16_t *e = reinterpret_cast<const uint16_t *>(&wv8);
+                        const uint8_t *l8 = reinterpret_cast<const uint8_t *>(&l2);
+                        uint16_t *pr = reinterpret_cast<uint16_t *>(ps + (p / M) * kSS);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) pr[l8[k]] = e[k];
+                    }
+                } else {
+                    for (int p = tid; p < n_ent; p += kDT) ps[(p / M) * kSS + loc_s[p]] = wg[p];
+                }
+            } else if (tid < ti) {
+                // a token lists a row more than once: accumulate that token's operand row in slot order
+                T *pr = ps + tid * kSS;
+                for (int j = 0; j < M; ++j) {
+                    const int l = loc_s[tid * M + j];
+                    pr[l] = Elem<T>::from_acc(Elem<T>::to_acc(pr[l]) + Elem<T>::to_acc(wg[tid * M + j]));
+                }
             }
         }
         cp_async_wait_all();
@@ -531,14 +605,17 @@ int launch_gather_dot_dense(const T *x, const T *y, const affb200_nbhd_plan *pl,
     const int TT = pl->tq;
     dim3 grid(unsigned((Nq + TT - 1) / TT), unsigned(B));
     const size_t smem = smem_gather_dot(int(c), TT, int(M));
-#define AFF_L(C_)                                                                                               \
+    const bool fast = (M % 8 == 0) && M <= 64 && int64_t(TT) * M <= 4096 && aligned16(out) &&
+                      (reinterpret_cast<uintptr_t>(pl->q_loc) & 7) == 0;
+#define AFF_L(C_, F_)                                                                                           \
     do {                                                                                                        \
-        auto kern = gather_dot_dense_kernel<T, C_>;                                                             \
+        auto kern = gather_dot_dense_kernel<T, C_, F_>;                                                         \
         if (int e = set_smem(kern, smem)) return e;                                                             \
         kern<<<grid, kDT, smem, st>>>(x, y, pl->q_hdr, pl->q_rows, pl->q_loc, out, int(H), int(Nq), int(Nk),    \
                                       int(M), TT);                                                              \
     } while (0)
-    if (c == 32) AFF_L(32); else AFF_L(16);
+    if (c == 32) { if (fast) AFF_L(32, true); else AFF_L(32, false); }
+    else { if (fast) AFF_L(16, true); else AFF_L(16, false); }
 #undef AFF_L
     return check_launch("gather_dot_dense");
 }
@@ -549,14 +626,17 @@ int launch_gather_wsum_dense(const T *w, const T *y, const affb200_nbhd_plan *pl
     const int TT = pl->tq;
     dim3 grid(unsigned((Nq + TT - 1) / TT), unsigned(B));
     const size_t smem = smem_gather_wsum(int(c), TT, int(M));
-#define AFF_L(C_)                                                                                               \
+    const bool fast = (M % 8 == 0) && M <= 64 && int64_t(TT) * M <= 4096 && aligned16(w) &&
+                      (reinterpret_cast<uintptr_t>(pl->q_loc) & 7) == 0;
+#define AFF_L(C_, F_)                                                                                           \
     do {                                                                                                        \
-        auto kern = gather_wsum_dense_kernel<T, C_>;                                                            \
+        auto kern = gather_wsum_dense_kernel<T, C_, F_>;                                                        \
         if (int e = set_smem(kern, smem)) return e;                                                             \
         kern<<<grid, kDT, smem, st>>>(w, y, pl->q_hdr, pl->q_rows, pl->q_loc, out, int(H), int(Nq), int(Nk),    \
                                       int(M), TT);                                                              \
     } while (0)
-    if (c == 32) AFF_L(32); else AFF_L(16);
+    if (c == 32) { if (fast) AFF_L(32, true); else AFF_L(32, false); }
+    else { if (fast) AFF_L(16, true); else AFF_L(16, false); }
 #undef AFF_L
     return check_launch("gather_wsum_dense");
 }

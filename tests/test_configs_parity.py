@@ -1,0 +1,61 @@
+"""GPU: the reference's own model configurations (BASELINE.json configs 2 and 4: AFF-Mini 224x224 and AFF-Base
+384x384 inference) through the CUDA operator set against the same host glue with the CPU oracle's operators, fp32,
+same deterministic weights.  Index tensors of every stage bit-exact, logits within 1e-4 relative (the chain is tens of
+blocks deep; per-operator fp32 parity at 1e-5 is asserted in test_clusten_parity.py)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return float((a.double().cpu() - b.double().cpu()).norm() / b.double().cpu().norm())
+
+
+def _capture(model):
+    cap = {}
+    hooks = []
+    for si, layer in enumerate(model.layers):
+        def hook(m, args, si=si):
+            cap["stage%d" % si] = (args[1], args[2], args[3])   # member_idx, cluster_mask, pe_idx of the first block
+        if len(layer.blocks):
+            hooks.append(layer.blocks[0].register_forward_pre_hook(hook))
+    return cap, hooks
+
+
+@pytest.mark.parametrize("name,batch", [("aff_mini", 2), ("aff_base_22kto1k_384", 1)])
+def test_reference_config_inference_matches_oracle_ops(name, batch):
+    from affb200.aff_transformer import build_aff, CudaOps, CONFIGS
+    from affb200 import fused
+    from oracle.aff_ops_ref import OracleOps, fill_parameters_by_name
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    img = CONFIGS[name]["img_size"]
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(batch, 3, img, img, generator=g)
+
+    ops = CudaOps()
+    ops.fused_attention = fused.fused_cluster_attention   # declines in fp32; the unfused CLUSTEN operators run
+    m_gpu = build_aff(name, ops=ops)
+    fill_parameters_by_name(m_gpu, seed=3)
+    m_gpu = m_gpu.cuda().eval()
+    m_cpu = build_aff(name, ops=OracleOps())
+    fill_parameters_by_name(m_cpu, seed=3)
+    m_cpu.eval()
+
+    cap_g, h1 = _capture(m_gpu)
+    cap_c, h2 = _capture(m_cpu)
+    with torch.no_grad():
+        y_gpu = m_gpu(x.cuda())
+        y_cpu = m_cpu(x)
+    for h in h1 + h2:
+        h.remove()
+    assert set(cap_g) == set(cap_c)
+    for k in cap_c:
+        for a, b, what in zip(cap_g[k], cap_c[k], ("member_idx", "cluster_mask", "pe_idx")):
+            if b is None:
+                assert a is None, (k, what)
+            else:
+                assert torch.equal(a.cpu(), b), (k, what)
+    assert torch.isfinite(y_gpu).all()
+    assert rel(y_gpu, y_cpu) < 1e-4, rel(y_gpu, y_cpu)
