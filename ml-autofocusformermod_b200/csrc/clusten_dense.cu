@@ -456,6 +456,8 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
     float *os = reinterpret_cast<float *>(ps + TT * kSS);
 
     const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x;
+    const int HS = (H + int(gridDim.z) - 1) / int(gridDim.z);   // heads [h_lo, h_hi) of this CTA
+    const int h_lo = int(blockIdx.z) * HS, h_hi = min(H, h_lo + HS);
     const int r0 = tile * TT;
     const int ri = min(TT, Nk - r0);
     const int tid = threadIdx.x;
@@ -498,7 +500,7 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
                 }
             }
             zero_operand<T>(ps, TT, Upad);
-            for (int h = 0; h < H; ++h) {
+            for (int h = h_lo; h < h_hi; ++h) {
                 const T *wz = w + (int64_t(b) * H + h) * Nq * M;
                 uint4 wv[GPT];
 #pragma unroll
@@ -509,7 +511,7 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
                 }
                 st.issue(xs_a, xb + int64_t(h) * xs_.sH);
                 cp_async_commit();
-                if (h == 0) __syncthreads();  // the zero fill above
+                if (h == h_lo) __syncthreads();  // the zero fill above
 #pragma unroll
                 for (int g = 0; g < GPT; ++g) {
                     uint16_t *pcol = reinterpret_cast<uint16_t *>(ps) + (src[g] >> 24);
@@ -529,7 +531,7 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
         }
     }
 
-    for (int h = 0; h < H; ++h) {
+    for (int h = h_lo; h < h_hi; ++h) {
         const int64_t z = int64_t(b) * H + h;
         st.issue(xs_a, xb + int64_t(h) * xs_.sH);
         cp_async_commit();
@@ -659,6 +661,10 @@ int launch_scatter_wsum_dense_strided(const T *w, const T *x, const affb200_nbhd
     }
     const int TT = pl->tk;
     dim3 grid(unsigned((Nk + TT - 1) / TT), unsigned(B));
+    // few key tiles: split the heads over gridDim.z (power-of-two divisor of H) up to about four waves
+    while (int64_t(grid.z) * 2 <= H && H % (int64_t(grid.z) * 2) == 0 &&
+           int64_t(grid.x) * grid.y * grid.z < int64_t(4) * kNumSMs * 3)
+        grid.z *= 2;
     const size_t smem = smem_scatter_wsum(int(c), TT);
     // register-resident slot groups when they fit (see the kernel): 6 groups per thread cover M <= 48, 8 cover M <= 64
     const bool regs_ok = (M % 8 == 0) && Nq * M < (int64_t(1) << 24) && aligned16(w) &&

@@ -473,23 +473,26 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
 
     GatherStager<T, C> st;
     st.init(rows_s, t.U);
-    const T *qb = q.row(b, t.t0, 0), *kb = k.row(b, 0, 0), *vb = v.row(b, 0, 0);
+    // heads [h_lo, h_hi) of this CTA: small problems split the heads over gridDim.z to fill the machine
+    const int HS = (H + int(gridDim.z) - 1) / int(gridDim.z);
+    const int h_lo = int(blockIdx.z) * HS, h_hi = min(H, h_lo + HS);
+    const T *qb = q.row(b, t.t0, h_lo), *kb = k.row(b, 0, h_lo), *vb = v.row(b, 0, h_lo);
     f_stage_tile<T, C, TT>(xs_a, qb, int(q.sN), t.ti);
     st.issue(ks_a, kb);
     f_cp_async_commit();
     st.issue(vs_a, vb);
     f_cp_async_commit();
-    f_put_blank<T, C>(ks, t.U, blank_k, 0);
-    f_put_blank<T, C>(vs, t.U, blank_v, 0);
+    f_put_blank<T, C>(ks, t.U, blank_k, h_lo);
+    f_put_blank<T, C>(vs, t.U, blank_v, h_lo);
 
-    for (int h = 0; h < H; ++h) {
+    for (int h = h_lo; h < h_hi; ++h) {
         f_cp_async_wait<1>();  // Q_h, K_h
         __syncthreads();
         f_mma_xyT<T, C>(xs, ks, sp, L.RS, TT, t.Upad, scale);
         __syncthreads();
-        if (h + 1 < H) {
-            f_stage_tile<T, C, TT>(xs_a, qb + (h + 1) * q.sH, int(q.sN), t.ti);
-            st.issue(ks_a, kb + (h + 1) * k.sH);
+        if (h + 1 < h_hi) {
+            f_stage_tile<T, C, TT>(xs_a, qb + (h + 1 - h_lo) * q.sH, int(q.sN), t.ti);
+            st.issue(ks_a, kb + (h + 1 - h_lo) * k.sH);
             f_put_blank<T, C>(ks, t.U, blank_k, h + 1);
         }
         f_cp_async_commit();
@@ -505,8 +508,8 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
         __syncthreads();
         f_mma_pv_store<T, C>(sp, L.RS, vs, os, TT, t.Upad, t.ti, 1.f, out.row(b, t.t0, h), out.sN);
         __syncthreads();
-        if (h + 1 < H) {
-            st.issue(vs_a, vb + (h + 1) * v.sH);
+        if (h + 1 < h_hi) {
+            st.issue(vs_a, vb + (h + 1 - h_lo) * v.sH);
             f_put_blank<T, C>(vs, t.U, blank_v, h + 1);
         }
         f_cp_async_commit();
@@ -574,29 +577,31 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
 
     GatherStager<T, C> st;
     st.init(rows_s, t.U);
-    const T *qb = q.row(b, t.t0, 0), *dob = dout.row(b, t.t0, 0), *ob = out.row(b, t.t0, 0);
-    const T *kb = k.row(b, 0, 0), *vb = v.row(b, 0, 0);
+    const int HS = (H + int(gridDim.z) - 1) / int(gridDim.z);
+    const int h_lo = int(blockIdx.z) * HS, h_hi = min(H, h_lo + HS);
+    const T *qb = q.row(b, t.t0, h_lo), *dob = dout.row(b, t.t0, h_lo), *ob = out.row(b, t.t0, h_lo);
+    const T *kb = k.row(b, 0, h_lo), *vb = v.row(b, 0, h_lo);
     f_stage_tile<T, C, TT>(xs_a, qb, int(q.sN), t.ti);
     f_stage_tile<T, C, TT>(dos_a, dob, int(dout.sN), t.ti);
     f_stage_tile<T, C, TT>(outs_a, ob, int(out.sN), t.ti);
     st.issue(f_smem_u32(ks0), kb);
     st.issue(vs_a, vb);
     f_cp_async_commit();
-    f_put_blank<T, C>(ks0, t.U, blank_k, 0);
-    f_put_blank<T, C>(vs, t.U, blank_v, 0);
+    f_put_blank<T, C>(ks0, t.U, blank_k, h_lo);
+    f_put_blank<T, C>(vs, t.U, blank_v, h_lo);
     const bool pair_ok = (PER % 2 == 0) && (M % 2 == 0);
 
-    for (int h = 0; h < H; ++h) {
-        T *kcur = (h & 1) ? ks1 : ks0, *knext = (h & 1) ? ks0 : ks1;
+    for (int h = h_lo; h < h_hi; ++h) {
+        T *kcur = ((h - h_lo) & 1) ? ks1 : ks0, *knext = ((h - h_lo) & 1) ? ks0 : ks1;
         f_cp_async_wait<0>();
         __syncthreads();
         f_mma_xyT<T, C>(xs, kcur, sp, L.RS, TT, t.Upad, scale);  // S
         f_mma_xyT<T, C>(dos, vs, dp, L.RS, TT, t.Upad, 1.f);     // dP = dO · V_U^T
         if (sub == 0) const_cast<float *>(dprow)[L.UC] = 0.f;
         __syncthreads();
-        if (h + 1 < H) {
-            st.issue(f_smem_u32(knext), kb + (h + 1) * k.sH);
-            st.issue(vs_a, vb + (h + 1) * v.sH);
+        if (h + 1 < h_hi) {
+            st.issue(f_smem_u32(knext), kb + (h + 1 - h_lo) * k.sH);
+            st.issue(vs_a, vb + (h + 1 - h_lo) * v.sH);
             f_put_blank<T, C>(knext, t.U, blank_k, h + 1);
             f_put_blank<T, C>(vs, t.U, blank_v, h + 1);
         }
@@ -675,10 +680,10 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
             }
         }
         __syncthreads();
-        if (h + 1 < H) {
-            f_stage_tile<T, C, TT>(xs_a, qb + (h + 1) * q.sH, int(q.sN), t.ti);
-            f_stage_tile<T, C, TT>(dos_a, dob + (h + 1) * dout.sH, int(dout.sN), t.ti);
-            f_stage_tile<T, C, TT>(outs_a, ob + (h + 1) * out.sH, int(out.sN), t.ti);
+        if (h + 1 < h_hi) {
+            f_stage_tile<T, C, TT>(xs_a, qb + (h + 1 - h_lo) * q.sH, int(q.sN), t.ti);
+            f_stage_tile<T, C, TT>(dos_a, dob + (h + 1 - h_lo) * dout.sH, int(dout.sN), t.ti);
+            f_stage_tile<T, C, TT>(outs_a, ob + (h + 1 - h_lo) * out.sH, int(out.sN), t.ti);
         }
         f_cp_async_commit();
         if (tid < 2 * C) {
@@ -702,6 +707,15 @@ using namespace affb200;
 
 template <typename T> static View<T> mk_view(const affb200_view *v) { return View<T>{(const T *)v->p, v->sB, v->sN, v->sH}; }
 template <typename T> static ViewW<T> mk_vieww(const affb200_view *v) { return ViewW<T>{(T *)v->p, v->sB, v->sN, v->sH}; }
+
+
+// heads per CTA: problems with few tiles split the heads over gridDim.z (a power-of-two divisor of H) until the grid
+// holds about four waves of the CTAs that fit the machine
+static unsigned head_split(int64_t n_cta, int64_t H, int ctas_per_sm) {
+    unsigned z = 1;
+    while (int64_t(z) * 2 <= H && H % (int64_t(z) * 2) == 0 && n_cta * z < int64_t(4) * kNumSMs * ctas_per_sm) z *= 2;
+    return z;
+}
 
 static bool kv_ok(const affb200_view *k, const affb200_view *v, int64_t N) {
     // the kernels index gathered rows with 32-bit element offsets row * sN shared by k and v
@@ -759,6 +773,7 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
     const FusedSmem L = fused_smem(UC, TT, int(c), false);
     if (L.total > 227 * 1024) { set_error("fused_attn_fwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
     dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
+    grid.z = head_split(int64_t(grid.x) * grid.y, H, 3);
     auto st = (cudaStream_t)stream;
     return dispatch_dtype(dtype, [&](auto tag) -> int {
         using T0 = decltype(tag);
@@ -819,6 +834,7 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
     const FusedSmem L = fused_smem(UC, TT, int(c), true);
     if (L.total > 227 * 1024) { set_error("fused_attn_bwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
     dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
+    grid.z = head_split(int64_t(grid.x) * grid.y, H, 2);
     auto st = (cudaStream_t)stream;
     return dispatch_dtype(dtype, [&](auto tag) -> int {
         using T0 = decltype(tag);
