@@ -34,29 +34,57 @@ def _work(nbytes, dev):
 
 
 def space_filling_cluster(pos, m, h, w, no_reorder=False, sf_type='', use_anchor=True):
-    """Balanced clustering along a space-filling scan of an anchor grid.  Returns, like the reference,
-    (pos_sorted b×n×2 fp32, cluster_mean_pos b×k×2 fp32, member_idx b×k×m int64, cluster_mask b×k×m int64 | None,
-    pos_ranking b×n×1 int64)."""
-    if no_reorder or sf_type != '' or not use_anchor:
-        raise NotImplementedError("only the variant the models call is implemented: no_reorder=False, sf_type='', "
-                                  "use_anchor=True (reference aff_transformer.py:463,470; mixres_neighbour.py:512)")
+    """Balanced clustering along a space-filling scan (reference models/point_utils.py:61-208).  Returns, like the
+    reference, (pos_sorted b×n×2 fp32, cluster_mean_pos b×k×2 fp32, member_idx b×k×m int64,
+    cluster_mask b×k×m int64 | None, pos_ranking b×n×1 int64), or with no_reorder=True
+    (cluster_mean_pos, member_idx = the ranking cut into clusters, cluster_mask).
+
+    use_anchor=True (what every model calls): anchor grid + distance-ratio key, one fused kernel chain
+    (`affb200_sfc_cluster`).  use_anchor=False: the tokens' own row-scan order with alternating direction
+    (point_utils.py:166-179), ranked by the same stable rank sort (`affb200_argsort_f32`).  The Peano / Hilbert curve
+    orders (`sf_type`, point_utils.py:211-349) are not built: no model reaches them."""
+    if sf_type != '':
+        raise NotImplementedError("sf_type=%r: only the default scan order is implemented (no model in the reference "
+                                  "passes sf_type; aff_transformer.py:463,470; mixres_neighbour.py:512)" % (sf_type,))
     pos = _f32_pos(pos)
-    b, n, _ = pos.shape
+    b, n, d = pos.shape
     dev = pos.device
     k = int(math.ceil(n / m))
     with torch.cuda.device(dev):
-        ranking = torch.empty((b, n), dtype=torch.int64, device=dev)
-        pos_sorted = torch.empty_like(pos)
-        mean = torch.empty((b, k, 2), dtype=torch.float32, device=dev)
-        work = _work(N.LIB.affb200_sfc_work_bytes(b, n), dev)
-        N.check(N.LIB.affb200_sfc_cluster(N.p(pos), b, n, m, h, w, N.p(ranking), N.p(pos_sorted), N.p(mean),
-                                          N.p(work), N.stream_ptr(dev)), "space_filling_cluster")
-        member_idx = torch.arange(k * m, device=dev)
+        if use_anchor:
+            ranking = torch.empty((b, n), dtype=torch.int64, device=dev)
+            pos_sorted = torch.empty_like(pos)
+            mean = torch.empty((b, k, 2), dtype=torch.float32, device=dev)
+            work = _work(N.LIB.affb200_sfc_work_bytes(b, n), dev)
+            N.check(N.LIB.affb200_sfc_cluster(N.p(pos), b, n, m, h, w, N.p(ranking), N.p(pos_sorted), N.p(mean),
+                                              N.p(work), N.stream_ptr(dev)), "space_filling_cluster")
+        else:
+            x, y = pos[..., 0].long(), pos[..., 1].long()
+            key = torch.where(y % 2 == 1, (w - 1 - x) + y * w, x + y * w)
+            if h * w >= 2 ** 24:
+                raise RuntimeError("space_filling_cluster(use_anchor=False): canvas too large for an exact fp32 key")
+            ranking = argsort_stable(key.to(torch.float32))
+            pos_sorted = pos.gather(1, ranking.unsqueeze(2).expand(-1, -1, d))
+            if k * m == n:
+                mean = pos_sorted.reshape(b, k, m, d).mean(2)
+            else:
+                pad = torch.zeros(b, k * m, d, dtype=torch.float32, device=dev)
+                pad[:, :n] = pos_sorted
+                cnt = (torch.arange(k * m, device=dev) < n).reshape(1, k, m).sum(2, keepdim=True)
+                mean = pad.reshape(b, k, m, d).sum(2) / cnt
         if k * m == n:
             cluster_mask = None
         else:
-            member_idx[n:] = 0
             cluster_mask = (torch.arange(k * m, device=dev) < n).long().reshape(1, k, m).expand(b, -1, -1)
+        if no_reorder:
+            member_idx = torch.zeros(b, k * m, dtype=torch.int64, device=dev)
+            member_idx[:, :n] = ranking
+            if cluster_mask is not None:
+                cluster_mask = cluster_mask.contiguous()
+            return mean, member_idx.reshape(b, k, m), cluster_mask
+        member_idx = torch.arange(k * m, device=dev)
+        if k * m != n:
+            member_idx[n:] = 0
         member_idx = member_idx.reshape(1, k, m).expand(b, -1, -1)
     return pos_sorted, mean, member_idx, cluster_mask, ranking.unsqueeze(2)
 

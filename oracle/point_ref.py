@@ -102,6 +102,44 @@ def sfc_ref(pos, m, h, w):
     return pos_s, mean, member, mask, ranking.unsqueeze(2)
 
 
+def scan_key_ref(pos, w):
+    """Row-scan order with alternating direction of the token positions themselves (`use_anchor=False`, default curve;
+    reference point_utils.py:166-179): key = x + y*w on even rows, (w-1-x) + y*w on odd rows (integer positions)."""
+    p = pos.detach().to(F32)
+    x, y = p[..., 0].long(), p[..., 1].long()
+    return torch.where(y % 2 == 1, (w - 1 - x) + y * w, x + y * w)
+
+
+def sfc_variant_ref(pos, m, h, w, no_reorder=False, use_anchor=True):
+    """The other call forms of space_filling_cluster with the default curve (reference point_utils.py:161-201):
+    use_anchor=False ranks the tokens by `scan_key_ref`; no_reorder=True returns (cluster_mean_pos, member_idx,
+    cluster_mask) with member_idx = the ranking cut into clusters (padding -> 0) instead of reordered positions."""
+    pos = pos.detach().to(F32)
+    b, n, d = pos.shape
+    k = int(math.ceil(n / m))
+    key = sfc_key_ref(pos, m, h, w)[0] if use_anchor else scan_key_ref(pos, w)
+    ranking = key.sort(dim=1, stable=True)[1]
+    pos_s = pos.gather(1, ranking.unsqueeze(2).expand(-1, -1, d))
+    if k * m == n:
+        mask = None
+        mean = pos_s.reshape(b, k, m, d).mean(2)
+    else:
+        pad = torch.zeros(b, k * m, d, dtype=F32)
+        pad[:, :n] = pos_s
+        mask = torch.zeros(b, k * m, dtype=torch.int64)
+        mask[:, :n] = 1
+        mask = mask.reshape(b, k, m)
+        mean = pad.reshape(b, k, m, d).sum(2) / mask.sum(2, keepdim=True)
+    if no_reorder:
+        member = torch.zeros(b, k * m, dtype=torch.int64)
+        member[:, :n] = ranking
+        return mean, member.reshape(b, k, m), mask
+    member = torch.arange(k * m)
+    member[n:] = 0
+    member = member.unsqueeze(0).expand(b, -1).reshape(b, k, m)
+    return pos_s, mean, member, mask, ranking.unsqueeze(2)
+
+
 def knn_ref(query, database, k, return_dist=False):
     """idx b×nq×k int64 (and dist fp32): k smallest fp32 sqrt(dx²+dy²+…), ascending, ties -> lowest index."""
     q = query.detach().to(F32)

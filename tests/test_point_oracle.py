@@ -61,3 +61,22 @@ def test_topk_order_rule_and_selection():
     res = idx[0, -4:].tolist()
     assert res == sorted(res) and all(int(pos[0, i, 0]) % 4 == 0 and int(pos[0, i, 1]) % 4 == 0 for i in res)
     assert len(set(idx[0].tolist())) == 16
+
+
+def test_sfc_variant_oracle_matches_reference_golden():
+    """use_anchor=False / no_reorder=True call forms (SURVEY §8 a4'): the oracle restatement against outputs of the
+    reference's own space_filling_cluster (tests/golden/make_point_variants_golden.py)."""
+    import os
+    import torch
+    from oracle import point_ref as O
+    g = torch.load(os.path.join(os.path.dirname(__file__), "golden", "point_sfc_variants.pt"))
+    assert len(g) == 9
+    for name, c in g.items():
+        mine = O.sfc_variant_ref(c["pos"].float(), c["m"], c["h"], c["w"], no_reorder=c["no_reorder"],
+                                 use_anchor=c["use_anchor"])
+        assert len(mine) == len(c["out"]) == (3 if c["no_reorder"] else 5)
+        for a, b in zip(mine, c["out"]):
+            if b is None:
+                assert a is None, name
+            else:
+                assert torch.equal(a.to(b.dtype), b), name

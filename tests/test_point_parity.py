@@ -173,3 +173,32 @@ def test_argsort_and_gather_rows():
     src = torch.randint(0, 1000, (3, 50, 48), generator=g)
     idx = torch.randint(0, 50, (3, 20), generator=g)
     assert torch.equal(gather_rows(src.cuda(), idx.cuda()).cpu(), src.gather(1, idx.unsqueeze(2).expand(-1, -1, 48)))
+
+
+@pytest.mark.gpu
+def test_sfc_variants_match_reference_golden():
+    """use_anchor=False / no_reorder=True call forms through the CUDA path against outputs of the reference itself;
+    integer outputs bit-exact, cluster means within 1e-5."""
+    import os
+    from affb200.point_utils import space_filling_cluster
+    g = torch.load(os.path.join(os.path.dirname(__file__), "golden", "point_sfc_variants.pt"))
+    for name, c in g.items():
+        out = space_filling_cluster(c["pos"].float().cuda(), c["m"], c["h"], c["w"], no_reorder=c["no_reorder"],
+                                    use_anchor=c["use_anchor"])
+        assert len(out) == len(c["out"]), name
+        for a, b in zip(out, c["out"]):
+            if b is None:
+                assert a is None, name
+            elif b.dtype == torch.float32:
+                assert torch.allclose(a.cpu(), b, rtol=1e-5, atol=0), name
+            else:
+                assert torch.equal(a.cpu().to(b.dtype), b), name
+
+
+@pytest.mark.gpu
+def test_sfc_curve_variants_are_declined_loudly():
+    from affb200.point_utils import space_filling_cluster
+    pos = torch.zeros(1, 16, 2, device="cuda")
+    for sf in ("peano", "hilbert"):
+        with pytest.raises(NotImplementedError, match="sf_type"):
+            space_filling_cluster(pos, 8, 4, 4, sf_type=sf)
