@@ -191,6 +191,10 @@ int affb200_knn2d(const float *query, const float *database, int64_t B, int64_t 
 /* Replaces the neighbourhood build of BasicLayer.forward (reference models/aff_transformer.py:478-487;
  * models/mixres_neighbour.py:521-528 with clamp=1): nearest [B][N][nnc] int64 cluster ids ->
  *   nbhd_idx [B][N][nnc*m] int64, mask [B][N][nnc*m] int64 (NULL when N % m == 0), pe_idx [B][N][nnc*m] int64. */
+/* idx[b][i] = argmin_j |q_x - d_x| + |q_y - d_y| (fp32, first index on ties): torch.argmin(torch.cdist(query, db, p=1), 2),
+ * the reference's find_pos_org_order (models/maskfiner_up_down.py:150-154) without the Nq x Nd distance matrix. */
+int affb200_nearest_l1(const float *query, const float *db, int64_t B, int64_t Nq, int64_t Nd, int64_t *idx,
+                       void *stream);
 int affb200_nbhd_build(const float *pos, const int64_t *nearest, int64_t B, int64_t N, int64_t m, int64_t nnc,
                        int64_t rel_pos_width, int64_t table_width, int clamp,
                        int64_t *nbhd_idx, int64_t *mask, int64_t *pe_idx, void *stream);

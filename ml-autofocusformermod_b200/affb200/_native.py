@@ -47,6 +47,7 @@ SIGNATURES = {
     "affb200_sfc_cluster": (_int, [_ptr] + [_i64] * 5 + [_ptr] * 5),
     "affb200_argsort_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
     "affb200_argsort_f32": (_int, [_ptr, _i64, _i64, _int, _ptr, _ptr, _ptr]),
+    "affb200_nearest_l1": (_int, [_ptr, _ptr] + [_i64] * 3 + [_ptr, _ptr]),
     "affb200_knn2d": (_int, [_ptr, _ptr] + [_i64] * 4 + [_ptr] * 3),
     "affb200_nbhd_build": (_int, [_ptr, _ptr] + [_i64] * 6 + [_int] + [_ptr] * 4),
     "affb200_merge_select_work_bytes": (ctypes.c_size_t, [_i64, _i64]),

@@ -10,6 +10,7 @@ sm_100a kernels of libaffb200.so on the current CUDA stream (C ABI: include/affb
   select_merge_centers(pos, learned_prob, stride, alpha, ds_rate, reserve_num, reserve_on=True)
                                                              reference aff_transformer.py:289-326
   gather_rows(src, idx)                                      reference aff_transformer.py:335-338
+  find_pos_org_order(pos_org, pos_shuffled)                  reference maskfiner_up_down.py:150-154
 """
 import math
 
@@ -103,6 +104,19 @@ def knn_keops(query, database, k, return_dist=False):
                 "knn")
     if return_dist:
         return idx, dist
+    return idx
+
+
+def find_pos_org_order(pos_org, pos_shuffled):
+    """Index in pos_shuffled of the L1-nearest point of every pos_org point, first index on ties: the reference's
+    `argmin(cdist(pos_org, pos_shuffled, p=1), dim=2)` (maskfiner_up_down.py:150-154) without the distance matrix."""
+    q = _f32_pos(pos_org, "pos_org")
+    d = _f32_pos(pos_shuffled, "pos_shuffled")
+    b, nq, _ = q.shape
+    dev = q.device
+    with torch.cuda.device(dev):
+        idx = torch.empty((b, nq), dtype=torch.int64, device=dev)
+        N.check(N.LIB.affb200_nearest_l1(N.p(q), N.p(d), b, nq, d.shape[1], N.p(idx), N.stream_ptr(dev)), "nearest_l1")
     return idx
 
 

@@ -233,6 +233,37 @@ knn2d_kernel(const float *__restrict__ query, const float *__restrict__ db, int 
     }
 }
 
+// Nearest database point in L1 distance, first index on ties: `argmin(cdist(query, db, p=1), dim=2)` — the reference's
+// find_pos_org_order (maskfiner_up_down.py:150-154), which materialises the Nq x Nd distance matrix (N up to 16 384).
+// Same shared-memory tiling of the database as knn2d; the scan stops improving only on a strictly smaller distance,
+// so the lowest index wins ties as torch.argmin does.
+__global__ void __launch_bounds__(kIT)
+nearest_l1_kernel(const float *__restrict__ query, const float *__restrict__ db, int Nq, int Nd,
+                  int64_t *__restrict__ idx_out) {
+    __shared__ float2 tile[kKnnTile];
+    const int b = blockIdx.y;
+    const int i = blockIdx.x * kIT + threadIdx.x;
+    const bool live = i < Nq;
+    float2 q = make_float2(0.f, 0.f);
+    if (live) q = __ldg(reinterpret_cast<const float2 *>(query) + int64_t(b) * Nq + i);
+    float best = __int_as_float(0x7f800000);
+    int bi = 0;
+    const float2 *dbb = reinterpret_cast<const float2 *>(db) + int64_t(b) * Nd;
+    for (int base = 0; base < Nd; base += kKnnTile) {
+        const int nt = min(kKnnTile, Nd - base);
+        __syncthreads();
+        for (int t = threadIdx.x; t < nt; t += kIT) tile[t] = __ldg(dbb + base + t);
+        __syncthreads();
+        if (!live) continue;
+        for (int t = 0; t < nt; ++t) {
+            const float2 x = tile[t];
+            const float d = __fadd_rn(fabsf(__fsub_rn(q.x, x.x)), fabsf(__fsub_rn(q.y, x.y)));
+            if (d < best) { best = d; bi = base + t; }
+        }
+    }
+    if (live) idx_out[int64_t(b) * Nq + i] = bi;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Neighbourhood build (aff_transformer.py:478-487): for token i and its nnc nearest clusters,
 //   nbhd_idx[i, q*m + r] = member(nearest[i,q]*m + r),  member(t) = t < N ? t : 0          (point_utils.py:203-206)
@@ -516,6 +547,19 @@ extern "C" int affb200_knn2d(const float *query, const float *db, int64_t B, int
     else AFF_KNN(32);
 #undef AFF_KNN
     return check_launch("knn2d");
+}
+
+extern "C" int affb200_nearest_l1(const float *query, const float *db, int64_t B, int64_t Nq, int64_t Nd, int64_t *idx,
+                                  void *stream) {
+    if (!idx_dims_ok("nearest_l1", B, Nq) || Nd <= 0 || Nd >= (int64_t(1) << 31)) {
+        if (Nd <= 0 || Nd >= (int64_t(1) << 31)) set_error("nearest_l1: the database must hold 1..2^31-1 points");
+        return AFFB200_E_ARG;
+    }
+    if (B * Nq == 0) return AFFB200_OK;
+    if (!query || !db || !idx) { set_error("nearest_l1: null pointer"); return AFFB200_E_ARG; }
+    dim3 grid(unsigned((Nq + kIT - 1) / kIT), unsigned(B));
+    nearest_l1_kernel<<<grid, kIT, 0, (cudaStream_t)stream>>>(query, db, int(Nq), int(Nd), idx);
+    return check_launch("nearest_l1");
 }
 
 extern "C" int affb200_nbhd_build(const float *pos, const int64_t *nearest, int64_t B, int64_t N, int64_t m,

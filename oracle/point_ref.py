@@ -140,6 +140,12 @@ def sfc_variant_ref(pos, m, h, w, no_reorder=False, use_anchor=True):
     return pos_s, mean, member, mask, ranking.unsqueeze(2)
 
 
+def find_pos_org_order_ref(pos_org, pos_shuffled):
+    """reference maskfiner_up_down.py:150-154 (torch.argmin returns the first minimal index)"""
+    dists = torch.cdist(pos_org.float(), pos_shuffled.float(), p=1)
+    return torch.argmin(dists, dim=2)
+
+
 def knn_ref(query, database, k, return_dist=False):
     """idx b×nq×k int64 (and dist fp32): k smallest fp32 sqrt(dx²+dy²+…), ascending, ties -> lowest index."""
     q = query.detach().to(F32)

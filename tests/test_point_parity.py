@@ -202,3 +202,25 @@ def test_sfc_curve_variants_are_declined_loudly():
     for sf in ("peano", "hilbert"):
         with pytest.raises(NotImplementedError, match="sf_type"):
             space_filling_cluster(pos, 8, 4, 4, sf_type=sf)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [(2, 2048, 64, 32), (1, 16384, 256, 128), (3, 500, 30, 40), (1, 1, 4, 4)])
+def test_find_pos_org_order_matches_reference_expression(case):
+    """argmin(cdist(p=1)) of maskfiner_up_down.py:150-154: a shuffled copy (exact matches), and a database with
+    duplicates and missing points (ties -> first index)."""
+    from affb200.point_utils import find_pos_org_order
+    from oracle import point_ref as O
+    B, n, w, h = case
+    g = torch.Generator().manual_seed(n)
+    ys, xs = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
+    allp = torch.stack([xs, ys], 2).reshape(-1, 2).float()
+    org = torch.stack([allp[torch.randperm(h * w, generator=g)[:n]] for _ in range(B)])
+    shuf = torch.stack([org[b][torch.randperm(n, generator=g)] for b in range(B)])
+    out = find_pos_org_order(org.cuda(), shuf.cuda())
+    assert out.dtype == torch.int64 and torch.equal(out.cpu(), O.find_pos_org_order_ref(org, shuf))
+    assert torch.equal(shuf.gather(1, out.cpu().unsqueeze(2).expand(-1, -1, 2)), org)
+    if n > 8:
+        db = torch.cat([shuf[:, : n // 2], shuf[:, : n // 4]], 1)    # duplicates, and half of the points missing
+        out = find_pos_org_order(org.cuda(), db.cuda())
+        assert torch.equal(out.cpu(), O.find_pos_org_order_ref(org, db))
