@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define AFFB200_ABI_VERSION 4
+#define AFFB200_ABI_VERSION 5
 
 typedef enum {
     AFFB200_F32 = 0,
@@ -275,6 +275,23 @@ int64_t affb200_layer_norm_bwd_work_floats(int64_t R, int64_t C);
 int affb200_layer_norm_bwd(const void *dy, const void *x, const float *gamma, const float *mean, const float *rstd,
                            void *dx, float *dgamma, float *dbeta, float *work, int64_t R, int64_t C, int x_dtype,
                            int dy_dtype, void *stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Training-mode BatchNorm over the rows of a channels-last activation [R = B*H*W][C], optionally followed by the exact
+ * (erf) GELU: the `bn` + `act1` pair of the stem (reference models/aff_transformer.py:524-527,541 = nn.BatchNorm2d,
+ * nn.GELU).  x/y/dy/dx of `dtype` (f32/f16/bf16), everything per channel fp32; C in {8,16,32,64,128}.
+ * fwd: batch statistics (biased variance for the normalisation) -> mean/rstd [C]; running_mean/running_var (may be
+ * NULL) are updated in place with `momentum` and the unbiased variance; y = act(gamma*(x-mean)*rstd + beta).
+ * bwd: dx, dgamma, dbeta [C] (overwritten; may be NULL) from dy, x and the saved statistics; the GELU derivative is
+ * recomputed from x.  work = affb200_batch_norm_work_floats(R, C) floats of scratch (either direction).
+ * ---------------------------------------------------------------------------------------------------------- */
+int64_t affb200_batch_norm_work_floats(int64_t R, int64_t C);
+int affb200_batch_norm_fwd(const void *x, const float *gamma, const float *beta, float *running_mean,
+                           float *running_var, float momentum, float eps, int gelu, void *y, float *mean, float *rstd,
+                           float *work, int64_t R, int64_t C, int dtype, void *stream);
+int affb200_batch_norm_bwd(const void *dy, const void *x, const float *gamma, const float *beta, const float *mean,
+                           const float *rstd, int gelu, void *dx, float *dgamma, float *dbeta, float *work, int64_t R,
+                           int64_t C, int dtype, void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Column sums out[c] = sum_r x[r][c] in fp32 of a row-major [R][C] matrix (f32/f16/bf16, C multiple of 8): the bias

@@ -64,6 +64,10 @@ SIGNATURES = {
     "affb200_merge_bwd": (_int, [_ptr] * 12 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_table_gather": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),
     "affb200_scale_add": (_int, [_ptr, _ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),
+    "affb200_batch_norm_work_floats": (_i64, [_i64, _i64]),
+    "affb200_batch_norm_fwd": (_int, [_ptr] * 5 + [ctypes.c_float, ctypes.c_float, _int] + [_ptr] * 4
+                               + [_i64, _i64, _int, _ptr]),
+    "affb200_batch_norm_bwd": (_int, [_ptr] * 6 + [_int] + [_ptr] * 4 + [_i64, _i64, _int, _ptr]),
     "affb200_col_sum_work_floats": (_i64, [_i64, _i64]),
     "affb200_col_sum": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),
     "affb200_layer_norm_fwd": (_int, [_ptr] * 6 + [_i64, _i64, ctypes.c_float, _int, _int, _ptr]),
@@ -94,7 +98,7 @@ def _load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.affb200_abi_version() != 4:
+    if lib.affb200_abi_version() != 5:
         raise RuntimeError("libaffb200.so ABI version mismatch")
     return lib
 

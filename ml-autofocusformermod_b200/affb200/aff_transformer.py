@@ -32,6 +32,7 @@ class CudaOps:
         from . import linear_ops as LI
         from . import residual_ops as RO
         self.layer_norm = L.layer_norm
+        self.batch_norm_act = L.batch_norm_act
         self.linear = LI.linear
         self.residual_add = RO.residual_add
         from . import merge_ops as MO
@@ -299,7 +300,9 @@ class PatchEmbed(nn.Module):
             # per-channel BatchNorm reductions run over contiguous channel vectors, and the token matrix [b, h*w, c]
             # below is then a view instead of a transpose copy
             x = x.contiguous(memory_format=torch.channels_last)
-        x = self.proj2(self.act1(self.bn(self.proj1(x))))
+        x = self.proj1(x)
+        x = self.act1(self.bn(x)) if ops is None else ops.batch_norm_act(x, self.bn)
+        x = self.proj2(x)
         b, c, h, w = x.shape
         x = x.flatten(2).transpose(1, 2)
         if self.norm is not None:

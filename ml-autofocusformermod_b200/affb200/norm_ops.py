@@ -1,6 +1,8 @@
-"""LayerNorm over the channel dim of token rows (csrc/layer_norm.cu).
+"""LayerNorm over the channel dim of token rows (csrc/layer_norm.cu) and the stem's BatchNorm + GELU
+(csrc/batch_norm.cu).
 
   layer_norm(x, weight, bias, eps, out_dtype=None) -> LayerNorm(x) in `out_dtype`
+  batch_norm_act(x, bn, gelu=True)                 -> GELU(bn(x)) for a training-mode nn.BatchNorm2d `bn`
 
 The reference uses nn.LayerNorm (models/aff_transformer.py:199-200,284), which autocast evaluates in fp32: the bf16
 residual stream is copied to fp32, normalised, and copied back to bf16 by the next Linear.  This operator reads x in
@@ -74,3 +76,66 @@ def layer_norm(x, weight, bias, eps=1e-5, out_dtype=None):
         # shapes the kernel does not cover (C not a multiple of 8, C > 1024, no affine): stock CUDA LayerNorm
         return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)
     return LayerNormFunction.apply(x, weight, bias, eps, out_dtype)
+
+
+class BatchNormActFunction(Function):
+    """y = act(BatchNorm(x)) with batch statistics over a channels-last [B, C, H, W] tensor; updates the running
+    statistics in place (reference aff_transformer.py:524-527,541: nn.BatchNorm2d then nn.GELU)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, gelu):
+        B, C, H, W = x.shape
+        R = B * H * W
+        dev = x.device
+        g = weight.detach().float().contiguous()
+        b = bias.detach().float().contiguous()
+        with torch.cuda.device(dev):
+            y = torch.empty_like(x)   # keeps the channels-last strides
+            mean = torch.empty(C, dtype=torch.float32, device=dev)
+            rstd = torch.empty(C, dtype=torch.float32, device=dev)
+            work = torch.empty(max(1, N.LIB.affb200_batch_norm_work_floats(R, C)), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_batch_norm_fwd(N.p(x), N.p(g), N.p(b), N.p(running_mean), N.p(running_var),
+                                                 float(momentum), float(eps), 1 if gelu else 0, N.p(y), N.p(mean),
+                                                 N.p(rstd), N.p(work), R, C, N.dtype_enum(x), N.stream_ptr(dev)),
+                    "batch_norm_fwd")
+        ctx.save_for_backward(x, g, b, mean, rstd)
+        ctx.meta = (gelu, weight.dtype, bias.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, g, b, mean, rstd = ctx.saved_tensors
+        gelu, wdt, bdt = ctx.meta
+        B, C, H, W = x.shape
+        R = B * H * W
+        dev = x.device
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dy = dy.contiguous(memory_format=torch.channels_last)
+        with torch.cuda.device(dev):
+            dx = torch.empty_like(x)
+            dg = torch.empty(C, dtype=torch.float32, device=dev)
+            db = torch.empty(C, dtype=torch.float32, device=dev)
+            work = torch.empty(max(1, N.LIB.affb200_batch_norm_work_floats(R, C)), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_batch_norm_bwd(N.p(dy), N.p(x), N.p(g), N.p(b), N.p(mean), N.p(rstd), 1 if gelu else 0,
+                                                 N.p(dx), N.p(dg), N.p(db), N.p(work), R, C, N.dtype_enum(x),
+                                                 N.stream_ptr(dev)), "batch_norm_bwd")
+        return dx, dg.to(wdt), db.to(bdt), None, None, None, None, None
+
+
+def batch_norm_act(x, bn, gelu=True):
+    """GELU(bn(x)) (or bn(x)) for an nn.BatchNorm2d module `bn` and a channels-last CUDA tensor.  Training mode with
+    a fixed momentum runs the fused kernels; evaluation mode (running statistics: a per-channel affine map) and the
+    layouts / channel counts the kernels do not cover use the stock CUDA operators."""
+    if not x.is_cuda:
+        raise RuntimeError("x must be a CUDA tensor")
+    C = x.shape[1]
+    ok = (bn.training and bn.affine and bn.track_running_stats and bn.momentum is not None and x.dim() == 4
+          and x.dtype in _OK and C in (8, 16, 32, 64, 128) and x.numel() > 0
+          and x.is_contiguous(memory_format=torch.channels_last))
+    if not ok:
+        y = bn(x)
+        return torch.nn.functional.gelu(y) if gelu else y
+    with torch.no_grad():
+        bn.num_batches_tracked.add_(1)
+    return BatchNormActFunction.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.momentum, bn.eps, gelu)

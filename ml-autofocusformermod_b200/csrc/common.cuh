@@ -79,6 +79,31 @@ __device__ __forceinline__ void store_vec(T *__restrict__ p, const typename Elem
     }
 }
 
+// 8 consecutive elements (16-byte aligned for 2-byte types, 32-byte for fp32) <-> fp32 registers
+template <typename T> __device__ __forceinline__ void load8f(const T *p, float (&o)[8]) {
+    if constexpr (sizeof(T) == 4) {
+        const float4 a = __ldg(reinterpret_cast<const float4 *>(p)), b = __ldg(reinterpret_cast<const float4 *>(p) + 1);
+        o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+    } else {
+        const uint4 r = __ldg(reinterpret_cast<const uint4 *>(p));
+        const T *e = reinterpret_cast<const T *>(&r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = Elem<T>::to_acc(e[k]);
+    }
+}
+template <typename T> __device__ __forceinline__ void store8f(T *p, const float (&v)[8]) {
+    if constexpr (sizeof(T) == 4) {
+        reinterpret_cast<float4 *>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+        reinterpret_cast<float4 *>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+    } else {
+        uint4 r;
+        T *e = reinterpret_cast<T *>(&r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) e[k] = Elem<T>::from_acc(v[k]);
+        *reinterpret_cast<uint4 *>(p) = r;
+    }
+}
+
 // streaming (evict-first) 128-bit store for write-once outputs
 __device__ __forceinline__ void st_cs_u4(void *p, uint4 v) {
     asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");

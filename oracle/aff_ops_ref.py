@@ -42,6 +42,11 @@ class OracleOps:
         return torch.nn.functional.linear(x, weight, bias)
 
     @staticmethod
+    def batch_norm_act(x, bn):
+        """nn.BatchNorm2d then nn.GELU (aff_transformer.py:524-527,541)"""
+        return torch.nn.functional.gelu(bn(x))
+
+    @staticmethod
     def layer_norm(x, weight, bias, eps=1e-5):
         """nn.LayerNorm as the reference applies it (aff_transformer.py:199-200,284)"""
         return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)

@@ -1,0 +1,102 @@
+"""GPU parity of the fused BatchNorm + GELU of the stem (csrc/batch_norm.cu) against nn.BatchNorm2d -> nn.GELU as the
+reference applies them (aff_transformer.py:524-527,541), evaluated in float64 on the same inputs.
+Tolerances (BASELINE.json): 1e-5 relative for fp32, 1e-2 for bf16/fp16."""
+import pytest
+import torch
+
+from tests.util import assert_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(shape, dtype, seed, offset=0.5):
+    g = torch.Generator().manual_seed(seed)
+    B, C, H, W = shape
+    x = (torch.randn(shape, generator=g) * 1.5 + offset).to(dtype)
+    go = torch.randn(shape, generator=g).to(dtype)
+    w = 1 + 0.2 * torch.randn(C, generator=g)
+    b = 0.2 * torch.randn(C, generator=g)
+    return x, go, w, b
+
+
+def _bn(C, w, b, dev, dtype=torch.float32):
+    bn = torch.nn.BatchNorm2d(C).to(dev).to(dtype)
+    with torch.no_grad():
+        bn.weight.copy_(w)
+        bn.bias.copy_(b)
+        bn.running_mean.normal_(0, 0.3)
+        bn.running_var.uniform_(0.5, 1.5)
+    return bn
+
+
+@pytest.mark.parametrize("gelu", [True, False])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(4, 32, 28, 28), (3, 16, 17, 9), (2, 8, 5, 7), (2, 64, 12, 12), (1, 128, 6, 6),
+                                   (64, 32, 56, 56), (1, 32, 1, 2)])
+def test_batch_norm_act_fwd_bwd(shape, dtype, gelu):
+    from affb200.norm_ops import batch_norm_act
+    B, C, H, W = shape
+    x, go, w, b = _case(shape, dtype, C + H)
+    bn1 = _bn(C, w, b, "cuda")
+    bn2 = _bn(C, w, b, "cpu", torch.float64)
+    bn2.running_mean.copy_(bn1.running_mean.double().cpu())
+    bn2.running_var.copy_(bn1.running_var.double().cpu())
+    x1 = x.cuda().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = batch_norm_act(x1, bn1, gelu=gelu)
+    assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
+    y.backward(go.cuda())
+    x2 = x.double().requires_grad_(True)
+    z = bn2(x2)
+    ref = torch.nn.functional.gelu(z) if gelu else z
+    ref.backward(go.double())
+    assert_close(y, ref, dtype, "bn fwd")
+    if B * H * W > 2:
+        # dx is a difference of O(1) terms scaled by gamma/std; with 2-byte storage g is rounded before the reduction
+        assert_close(x1.grad, x2.grad, dtype, "bn dx")
+        assert_close(bn1.weight.grad, bn2.weight.grad, torch.float32 if dtype == torch.float32 else dtype, "bn dgamma")
+        assert_close(bn1.bias.grad, bn2.bias.grad, torch.float32 if dtype == torch.float32 else dtype, "bn dbeta")
+    assert_close(bn1.running_mean, bn2.running_mean, torch.float32, "running_mean")
+    assert_close(bn1.running_var, bn2.running_var, torch.float32, "running_var")
+    assert int(bn1.num_batches_tracked) == 1
+
+
+def test_batch_norm_statistics_survive_a_large_mean():
+    """mean >> std: the shifted sums keep the variance (a plain E[x^2] - E[x]^2 in fp32 would lose it)."""
+    from affb200.norm_ops import batch_norm_act
+    shape = (8, 32, 40, 40)
+    x, go, w, b = _case(shape, torch.float32, 5, offset=3000.0)
+    bn1 = _bn(32, w, b, "cuda")
+    x1 = x.cuda().contiguous(memory_format=torch.channels_last)
+    y = batch_norm_act(x1, bn1, gelu=False)
+    bn2 = _bn(32, w, b, "cpu", torch.float64)
+    ref = bn2(x.double())
+    assert (y.cpu().double() - ref).abs().max() < 2e-3   # x itself carries 2.4e-4 of fp32 spacing at 3000
+
+
+def test_batch_norm_act_matches_the_stock_bf16_chain():
+    """bf16 in / bf16 out, against the stock CUDA operators run one after the other in bf16 (what autocast runs):
+    same rounding points, so the results agree to an ulp of bf16 on almost every element."""
+    from affb200.norm_ops import batch_norm_act
+    shape = (16, 32, 112, 112)
+    x, go, w, b = _case(shape, torch.bfloat16, 11)
+    bn1, bn2 = _bn(32, w, b, "cuda"), _bn(32, w, b, "cuda")
+    x1 = x.cuda().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    x2 = x.cuda().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y1 = batch_norm_act(x1, bn1)
+    y2 = torch.nn.functional.gelu(bn2(x2))
+    y1.backward(go.cuda().contiguous(memory_format=torch.channels_last))
+    y2.backward(go.cuda().contiguous(memory_format=torch.channels_last))
+    d = (y1.detach().float() - y2.detach().float()).abs()
+    assert float((d > 0).float().mean()) < 0.01 and float(d.max()) <= 0.03125
+    dg = (x1.grad.float() - x2.grad.float()).abs()
+    assert float(dg.max()) <= 0.02 * float(x2.grad.float().abs().max())
+    assert_close(bn1.weight.grad, bn2.weight.grad, torch.bfloat16, "dgamma")
+
+
+def test_batch_norm_act_eval_mode_uses_running_statistics():
+    from affb200.norm_ops import batch_norm_act
+    x, go, w, b = _case((2, 32, 8, 8), torch.float32, 2)
+    bn = _bn(32, w, b, "cuda").eval()
+    x1 = x.cuda().contiguous(memory_format=torch.channels_last)
+    assert torch.equal(batch_norm_act(x1, bn), torch.nn.functional.gelu(bn(x1)))
+    assert int(bn.num_batches_tracked) == 0
