@@ -262,6 +262,29 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
                            void *ds_work, void *p_work, float *blank_part, float *d_table, int64_t P,
                            int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype, void *stream);
 
+/* Same operator for small token sets (N <= AFFB200_FUSED_IMG_MAX_N, M <= 96): one CTA per (image, head) keeps the
+ * image's K and V resident in shared memory, walks 32-row query tiles, and in the backward accumulates dK and dV on
+ * chip (no tile plans, no scatter launches, no P scratch).  affb200_fused_attn_img_prepare derives, once per
+ * (nbhd_idx, mask) pair: col [B][N][M] uint8 = nbhd_idx narrowed to a byte (the column of S is the key row itself) and
+ * dupf [B][ceil(N/32)] uint8 = a token of the tile repeats a key row among its unmasked slots.  Masked slots are
+ * left out of P and dS (their probability is below exp(-100)).  blank_part [B][H][2][c] fp32 (sum over the first axis
+ * -> d blank_k, d blank_v); everything else as above. */
+#define AFFB200_FUSED_IMG_MAX_N 255
+int affb200_fused_attn_img_prepare(const int64_t *nbhd_idx, const uint16_t *q_pe, int64_t B, int64_t N, int64_t M,
+                                   uint8_t *col, uint8_t *dupf, void *stream);
+int affb200_fused_attn_img_fwd(const affb200_view *q, const affb200_view *k, const affb200_view *v,
+                               const affb200_view *out, const float *table, const float *blank_k, const float *blank_v,
+                               const uint8_t *dupf, const uint8_t *col, const uint16_t *q_pe, float *lse,
+                               int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype,
+                               void *stream);
+int affb200_fused_attn_img_bwd(const affb200_view *q, const affb200_view *k, const affb200_view *v,
+                               const affb200_view *out, const affb200_view *dout, const affb200_view *dq,
+                               const affb200_view *dk, const affb200_view *dv, const float *table, const float *blank_k,
+                               const float *blank_v, const uint8_t *dupf, const uint8_t *col,
+                               const uint16_t *q_pe, const float *lse, void *ds_work, float *blank_part, float *d_table,
+                               int64_t P, int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype,
+                               void *stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * LayerNorm over the channel dim of token rows [R][C] (the norm on either side of the attention and in
  * ClusterMerging; reference models/aff_transformer.py:199-200,223-229,284,362 = nn.LayerNorm, which autocast runs in

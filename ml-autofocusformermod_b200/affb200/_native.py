@@ -29,6 +29,7 @@ _plan_p = ctypes.POINTER(NbhdPlanStruct)
 PLAN_UMAX = 256
 PLAN_MAX_NK = 131072
 PLAN_MAX_M = 192
+FUSED_IMG_MAX_N = 255
 
 # name -> (restype, argtypes); kept in one table so tests can check it against include/affb200.h
 SIGNATURES = {
@@ -60,6 +61,11 @@ SIGNATURES = {
                                + [ctypes.c_float, _int, _ptr]),
     "affb200_fused_attn_bwd": (_int, [_ptr] * 8 + [_ptr] * 3 + [_plan_p, _ptr, ctypes.c_int32, _ptr] + [_ptr] * 4
                                + [_i64] * 6 + [ctypes.c_float, _int, _ptr]),
+    "affb200_fused_attn_img_prepare": (_int, [_ptr, _ptr] + [_i64] * 3 + [_ptr, _ptr, _ptr]),
+    "affb200_fused_attn_img_fwd": (_int, [_ptr] * 4 + [_ptr] * 3 + [_ptr, _ptr, _ptr, _ptr] + [_i64] * 5
+                                   + [ctypes.c_float, _int, _ptr]),
+    "affb200_fused_attn_img_bwd": (_int, [_ptr] * 8 + [_ptr] * 3 + [_ptr, _ptr, _ptr, _ptr] + [_ptr] * 3
+                                   + [_i64] * 6 + [ctypes.c_float, _int, _ptr]),
     "affb200_merge_fwd": (_int, [_ptr] * 7 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_merge_bwd": (_int, [_ptr] * 12 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_table_gather": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),

@@ -9,7 +9,12 @@ q_lin [B,N,H*c] and kv_lin [B,N,2*H*c] are the Linear outputs themselves (kv lai
 f16/bf16 activations, head dim 16 or 32, bias table of at most 32768 rows, neighbourhoods whose tiles reference at
 most 255 distinct rows (any clustered index tensor).  Everything else returns None and the caller uses the unfused
 operators.
+
+Two kernel families sit behind the call: the per-query-tile kernels (csrc/fused_attn.cu) and, for at most 255 tokens
+per image and M <= 96, the per-(image, head) kernels that keep the image's K/V in shared memory and need no scatter
+pass in the backward (csrc/fused_attn_img.cu).  AFFB200_FUSED_IMG=0 forces the first family.
 """
+import os
 import ctypes
 
 import torch
@@ -52,6 +57,84 @@ def _packed_pe(plan, pe_idx, mask):
     plan._pe.clear()
     plan._pe[key] = (weakref.ref(pe_idx), res)
     return res
+
+
+def _img_prep(plan, nbhd_idx, q_pe):
+    """(col, dupf) of affb200_fused_attn_img_prepare for this (nbhd_idx, packed bias/mask) pair, cached on the plan."""
+    hit = getattr(plan, "_img", None)
+    if hit is not None and hit[0] == nbhd_idx._version and hit[1] is q_pe:
+        return hit[2], hit[3]
+    B, n, M = nbhd_idx.shape
+    dev = nbhd_idx.device
+    idx = nbhd_idx.contiguous()
+    with torch.cuda.device(dev):
+        col = torch.empty((B, n, M), dtype=torch.uint8, device=dev)
+        dupf = torch.empty((B, (n + 31) // 32), dtype=torch.uint8, device=dev)
+        N.check(N.LIB.affb200_fused_attn_img_prepare(N.p(idx), N.p(q_pe), B, n, M, N.p(col), N.p(dupf),
+                                                     N.stream_ptr(dev)), "fused_attn_img_prepare")
+    plan._img = (nbhd_idx._version, q_pe, col, dupf)
+    return col, dupf
+
+
+def _use_img(n, M):
+    return n <= N.FUSED_IMG_MAX_N and M <= 96 and os.environ.get("AFFB200_FUSED_IMG", "1") != "0"
+
+
+class FusedClusterAttentionImg(Function):
+    """Small token sets: one CTA per (image, head), K/V resident, dK/dV accumulated on chip (fused_attn_img.cu)."""
+
+    @staticmethod
+    def forward(ctx, q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe, col, dupf, meta):
+        H, scale = meta
+        B, n, hc = q_lin.shape
+        c = hc // H
+        M = nbhd_idx.shape[2]
+        dev = q_lin.device
+        q_lin = q_lin.contiguous()
+        kv_lin = kv_lin.contiguous()
+        table = pe_table.detach().float().contiguous()
+        bk = blank_k.detach().float().contiguous()
+        bv = blank_v.detach().float().contiguous()
+        with torch.cuda.device(dev):
+            out = torch.empty_like(q_lin)
+            lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_fused_attn_img_fwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), N.p(table), N.p(bk), N.p(bv),
+                N.p(dupf), N.p(col), N.p(q_pe), N.p(lse), B, H, n, M, c, float(scale), N.dtype_enum(q_lin),
+                N.stream_ptr(dev)), "fused_attn_img_fwd")
+        ctx.save_for_backward(q_lin, kv_lin, out, lse, table, bk, bv, q_pe, col, dupf)
+        ctx.M = M
+        ctx.meta = (H, scale, pe_table.dtype, blank_k.dtype, pe_table.shape[0])
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        q_lin, kv_lin, out, lse, table, bk, bv, q_pe, col, dupf = ctx.saved_tensors
+        H, scale, table_dt, blank_dt, P = ctx.meta
+        B, n, hc = q_lin.shape
+        c = hc // H
+        M = ctx.M
+        dev = q_lin.device
+        d_out = d_out.contiguous()
+        if d_out.dtype != q_lin.dtype:
+            d_out = d_out.to(q_lin.dtype)
+        with torch.cuda.device(dev):
+            dq = torch.empty_like(q_lin)
+            dkv = torch.empty_like(kv_lin)
+            ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+            blank_part = torch.empty((B, H, 2, c), dtype=torch.float32, device=dev)
+            d_table = torch.empty((P, H), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_fused_attn_img_bwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
+                _view(dq, n * hc, hc, c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c, c),
+                N.p(table), N.p(bk), N.p(bv), N.p(dupf), N.p(col), N.p(q_pe), N.p(lse), N.p(ds), N.p(blank_part),
+                N.p(d_table), P, B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)),
+                "fused_attn_img_bwd")
+            db = blank_part.sum(dim=0)  # [H, 2, c]
+        return (dq, dkv, d_table.to(table_dt), db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt),
+                None, None, None, None, None)
 
 
 class FusedClusterAttention(Function):
@@ -127,6 +210,13 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
     if c not in (16, 32) or pe_table.shape[0] > 32768 or nbhd_idx.shape[2] > N.PLAN_MAX_M:
         return None
     plan = get_plan(nbhd_idx)
+    if _use_img(n, nbhd_idx.shape[2]):
+        q_pe = _packed_pe(plan, pe_idx, cluster_mask)
+        if q_pe is None:
+            return None
+        col, dupf = _img_prep(plan, nbhd_idx, q_pe)
+        return FusedClusterAttentionImg.apply(q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe, col, dupf,
+                                              (num_heads, scale))
     if plan.qplan(nbhd_idx, n) is None or plan.kplan(nbhd_idx, n) is None:
         return None
     umax = plan.stats["q"]["umax"]
@@ -148,6 +238,8 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
     M = nbhd_idx.shape[2]
     dev = q_lin.device
     plan = get_plan(nbhd_idx)
+    if _use_img(n, M):
+        return _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v)
     if plan.qplan(nbhd_idx, n) is None or plan.kplan(nbhd_idx, n) is None:
         return None
     umax = plan.stats["q"]["umax"]
@@ -179,6 +271,43 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
                                              V(dkv, 0, True), V(dkv, c, True), N.p(table), N.p(bk), N.p(bv), st_b,
                                              N.p(q_pe), umax, N.p(lse), N.p(ds), N.p(pw), N.p(blank_part), N.p(d_table),
                                              table.shape[0], B, H, n, M, c, float(scale), de, sp), "fused_attn_bwd")
+
+    fwd._keep = keep
+    return fwd, bwd
+
+
+def _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v):
+    B, n, hc = q_lin.shape
+    c = hc // H
+    M = nbhd_idx.shape[2]
+    dev = q_lin.device
+    plan = get_plan(nbhd_idx)
+    q_pe = _packed_pe(plan, pe_idx, cluster_mask)
+    if q_pe is None:
+        return None
+    col, dupf = _img_prep(plan, nbhd_idx, q_pe)
+    table = pe_table.detach().float().contiguous()
+    bk, bv = blank_k.detach().float().contiguous(), blank_v.detach().float().contiguous()
+    out, dq, dkv, dout = torch.empty_like(q_lin), torch.empty_like(q_lin), torch.empty_like(kv_lin), torch.randn_like(q_lin)
+    lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+    ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+    blank_part = torch.empty((B, H, 2, c), dtype=torch.float32, device=dev)
+    d_table = torch.empty((table.shape[0], H), dtype=torch.float32, device=dev)
+    de, sp = N.dtype_enum(q_lin), N.stream_ptr(dev)
+    keep = (plan, q_pe, col, dupf, table, bk, bv, out, dq, dkv, dout, lse, ds, blank_part, d_table)
+    V = lambda t, off=0, kv=False: _view(t, n * (2 * hc if kv else hc), 2 * hc if kv else hc, 2 * c if kv else c, off)
+
+    def fwd():
+        N.check(N.LIB.affb200_fused_attn_img_fwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), N.p(table),
+                                                 N.p(bk), N.p(bv), N.p(dupf), N.p(col), N.p(q_pe), N.p(lse), B, H, n, M,
+                                                 c, float(scale), de, sp), "fused_attn_img_fwd")
+
+    def bwd():
+        N.check(N.LIB.affb200_fused_attn_img_bwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), V(dout),
+                                                 V(dq), V(dkv, 0, True), V(dkv, c, True), N.p(table), N.p(bk), N.p(bv),
+                                                 N.p(dupf), N.p(col), N.p(q_pe), N.p(lse), N.p(ds), N.p(blank_part),
+                                                 N.p(d_table), table.shape[0], B, H, n, M, c, float(scale), de, sp),
+                "fused_attn_img_bwd")
 
     fwd._keep = keep
     return fwd, bwd

@@ -45,15 +45,28 @@ CASES = [  # (h, w, n, B, H, c, m, nbhd, img)
     (56, 56, 784, 2, 4, 16, 8, 48, 224),      # head dim 16
     (40, 40, 70, 2, 8, 16, 8, 48, 160),
     (96, 96, 2304, 1, 8, 32, 24, 144, 384),   # AFF-Base geometry (nbhd 144); table 191^2 > 32768 -> must decline
+    # small token sets: the per-(image, head) kernels (fused_attn_img.cu); each also run through the tile kernels
+    (56, 56, 196, 3, 8, 32, 8, 48, 224),      # 13 sixteen-row slices of dK/dV: two per warp
+    (56, 56, 255, 2, 4, 16, 8, 48, 224),      # the largest image the resident kernels take
+    (56, 56, 250, 2, 2, 32, 16, 96, 224),     # M = 96: 12 slots per thread
+    (56, 56, 33, 4, 8, 32, 8, 48, 224),       # M = 40 > tokens of a tile's last rows; two tiles, second nearly empty
+    (28, 28, 32, 3, 4, 32, 8, 48, 224),       # exactly one full tile, no padding
 ]
 
 
+def _families(case):
+    return ["tile", "img"] if case[2] <= 255 else ["tile"]
+
+
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("case", CASES)
-def test_fused_attention_matches_reference_chain(case, dtype):
+@pytest.mark.parametrize("case,family", [(c, f) for c in CASES for f in _families(c)])
+def test_fused_attention_matches_reference_chain(case, family, dtype, monkeypatch):
     from affb200.point_utils import space_filling_cluster, build_nbhd
+    from affb200 import fused
     from affb200.fused import fused_cluster_attention
+    monkeypatch.setenv("AFFB200_FUSED_IMG", "1" if family == "img" else "0")
     h, w, n, B, H, c, m, nbhd_size, img = case
+    assert fused._use_img(n, m * min(round(nbhd_size / m), -(-n // m))) == (family == "img")
     rpw = img // 4 - 1
     P = (2 * rpw + 1) ** 2
     pos = _positions(h, w, n, B, seed=n).cuda()
@@ -104,3 +117,31 @@ def test_fused_attention_is_deterministic():
         outs.append((o.detach(), a[0].grad, a[1].grad))
     for x, y in zip(*outs):
         assert torch.equal(x, y)
+
+
+@pytest.mark.parametrize("family", ["tile", "img"])
+def test_fused_attention_with_repeated_unmasked_neighbours(family, monkeypatch):
+    """An index tensor drawn with replacement: tokens list the same key row several times with different bias rows,
+    some of the repeats masked.  Both kernel families must accumulate the repeats (sequential operand build)."""
+    from affb200.fused import fused_cluster_attention
+    monkeypatch.setenv("AFFB200_FUSED_IMG", "1" if family == "img" else "0")
+    B, n, H, c, M, P = 3, 100, 4, 32, 48, 6241
+    g = torch.Generator().manual_seed(41)
+    nbhd = torch.randint(0, n, (B, n, M), generator=g).cuda()
+    nbhd[0, :40] = torch.sort(torch.randperm(n, generator=g)[:M])[0].cuda()     # rows without repeats: one clean tile
+    pe_idx = torch.randint(0, P, (B, n, M), generator=g).cuda()
+    mask = (torch.rand(B, n, M, generator=g) > 0.2).long().cuda()
+    hc = H * c
+    q_lin = torch.randn(B, n, hc, generator=g).bfloat16().cuda().requires_grad_(True)
+    kv_lin = torch.randn(B, n, 2 * hc, generator=g).bfloat16().cuda().requires_grad_(True)
+    table = (0.5 * torch.randn(P, H, generator=g)).bfloat16().cuda().requires_grad_(True)
+    bk = torch.randn(hc, generator=g).cuda().requires_grad_(True)
+    bv = torch.randn(hc, generator=g).cuda().requires_grad_(True)
+    go = torch.randn(B, n, hc, generator=g).bfloat16().cuda()
+    out = fused_cluster_attention(q_lin, kv_lin, H, c ** -0.5, nbhd, pe_idx, mask, table, bk, bv)
+    assert out is not None
+    out.backward(go)
+    ref = _reference(q_lin, kv_lin, H, c ** -0.5, nbhd, pe_idx, mask, table, bk.bfloat16(), bv.bfloat16(), go)
+    for nm, a, r in zip(["out", "d_q", "d_kv", "d_table", "d_blank_k", "d_blank_v"],
+                        [out, q_lin.grad, kv_lin.grad, table.grad, bk.grad, bv.grad], ref):
+        assert rel_err(a, r) < 1e-2, (nm, rel_err(a, r))
