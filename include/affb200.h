@@ -320,9 +320,11 @@ int affb200_batch_norm_bwd(const void *dy, const void *x, const float *gamma, co
  * Column sums out[c] = sum_r x[r][c] in fp32 of a row-major [R][C] matrix (f32/f16/bf16, C multiple of 8): the bias
  * gradient of the Linears around the attention (reference aff_transformer.py:85-88,96-100,285 via autograd).
  * work = affb200_col_sum_work_floats(R, C) floats of scratch.  Fixed summation order (bit-reproducible).
+ * accumulate != 0: out[c] += the sums (gradient accumulation into an existing fp32 buffer).
  * ---------------------------------------------------------------------------------------------------------- */
 int64_t affb200_col_sum_work_floats(int64_t R, int64_t C);
-int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C, int dtype, void *stream);
+int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C, int dtype, int accumulate,
+                    void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Residual connection with stochastic depth in one pass: out[b][...] = a[b][...] + x[b][...] * s[b]  (a may be NULL:

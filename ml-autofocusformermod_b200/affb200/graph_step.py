@@ -38,12 +38,24 @@ class GraphedTrainStep:
                 dist.broadcast(p.data, 0)
             for b in model.buffers():
                 dist.broadcast(b.data, 0)
-        n = sum(p.numel() for p in self.params)
-        self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
-        off = 0
+        # parameters, gradients and the low-precision shadow each live in ONE flat buffer (32-byte aligned slices):
+        # one all-reduce, one cast kernel per step instead of one per use of every weight, and gradient GEMMs that
+        # accumulate in place (linear_ops: `_affb200_lp`, `_affb200_sink`)
+        offs, n = [], 0
         for p in self.params:
-            p.grad = self.flat_grad[off:off + p.numel()].view_as(p)
-            off += p.numel()
+            offs.append(n)
+            n += (p.numel() + 7) // 8 * 8
+        self.flat_param = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.flat_lp = torch.zeros(n, dtype=autocast_dtype, device=dev)
+        for p, off in zip(self.params, offs):
+            sl = slice(off, off + p.numel())
+            self.flat_param[sl].copy_(p.data.reshape(-1))
+            p.data = self.flat_param[sl].view_as(p)
+            p.grad = self.flat_grad[sl].view_as(p)
+            p._affb200_lp = self.flat_lp[sl].view_as(p)
+            p._affb200_sink = True
+        self.sync_params()
         self.x = example_x.clone()
         self.y = example_y.clone()
         self.loss = None
@@ -56,6 +68,7 @@ class GraphedTrainStep:
                 self._fwd_bwd()
                 self._reduce()
                 self.opt.step()
+                self.sync_params()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
 
@@ -69,6 +82,12 @@ class GraphedTrainStep:
         self.g_opt = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.g_opt, pool=self.g_fb.pool()):
             self.opt.step()
+            self.sync_params()
+
+    def sync_params(self):
+        """Refresh the low-precision shadow from the fp32 parameters (call after changing parameters by hand, e.g.
+        load_state_dict; the optimizer graph does it after every step)."""
+        self.flat_lp.copy_(self.flat_param)
 
     def _fwd_bwd(self):
         self.flat_grad.zero_()

@@ -5,6 +5,15 @@
 The two GEMMs of the backward and the forward addmm are the stock cuBLAS calls nn.Linear makes (same dtypes under
 autocast); only `grad_out.sum(0)`, which autograd runs as a generic strided reduction, is replaced — by fp32 column
 sums accumulated in a fixed order.  `col_sum(x2d)` is exported for tests.
+
+Two optional per-parameter attributes, set by `graph_step.GraphedTrainStep`, remove the per-call copies around the
+GEMMs (under autocast the reference casts every weight to bf16 on every use and rounds every weight gradient to bf16
+before adding it to the fp32 .grad):
+  `_affb200_lp`    a low-precision shadow of the parameter, refreshed after each optimizer step, used instead of
+                   `param.to(autocast dtype)`;
+  `_affb200_sink`  True: the gradient GEMM accumulates straight into the existing fp32 `.grad` (cuBLAS beta = 1, fp32
+                   output from bf16 operands: no bf16 rounding of dW, no separate add), the bias column sums likewise;
+                   autograd then receives None for that parameter.
 """
 import torch
 from torch.autograd import Function
@@ -14,20 +23,38 @@ from . import _native as N
 _OK = (torch.float32, torch.float16, torch.bfloat16)
 
 
-def col_sum(x2d):
-    """fp32 column sums of a contiguous CUDA matrix [R, C] (C a multiple of 8)."""
+def col_sum(x2d, into=None):
+    """fp32 column sums of a contiguous CUDA matrix [R, C] (C a multiple of 8); `into` (fp32 [C], contiguous): the sums
+    are added to it in place and it is returned."""
     if not x2d.is_cuda:
         raise RuntimeError("x must be a CUDA tensor")
     R, C = x2d.shape
     if x2d.dtype not in _OK or C % 8 != 0:
-        return x2d.sum(0, dtype=torch.float32)   # stock CUDA reduction for widths the kernel does not cover
+        s = x2d.sum(0, dtype=torch.float32)   # stock CUDA reduction for widths the kernel does not cover
+        return s if into is None else into.add_(s)
     x2d = x2d.contiguous()
     dev = x2d.device
     with torch.cuda.device(dev):
-        out = torch.empty(C, dtype=torch.float32, device=dev)
+        out = torch.empty(C, dtype=torch.float32, device=dev) if into is None else into
         work = torch.empty(max(1, N.LIB.affb200_col_sum_work_floats(R, C)), dtype=torch.float32, device=dev)
-        N.check(N.LIB.affb200_col_sum(N.p(x2d), N.p(out), N.p(work), R, C, N.dtype_enum(x2d), N.stream_ptr(dev)), "col_sum")
+        N.check(N.LIB.affb200_col_sum(N.p(x2d), N.p(out), N.p(work), R, C, N.dtype_enum(x2d),
+                                      0 if into is None else 1, N.stream_ptr(dev)), "col_sum")
     return out
+
+
+def low_precision(p, dt):
+    """The parameter in the compute dtype: its registered shadow when there is one, else a cast."""
+    s = getattr(p, "_affb200_lp", None)
+    return s if s is not None and s.dtype == dt else p.to(dt)
+
+
+def _sink(p):
+    """The fp32 .grad to accumulate into directly, or None."""
+    if getattr(p, "_affb200_sink", False):
+        g = p.grad
+        if g is not None and g.dtype == torch.float32 and g.is_contiguous():
+            return g
+    return None
 
 
 class LinearFunction(Function):
@@ -37,11 +64,12 @@ class LinearFunction(Function):
             raise RuntimeError("x must be a CUDA tensor")
         dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
         x2 = x.reshape(-1, x.shape[-1]).to(dt)
-        wb = weight.to(dt)
+        wb = low_precision(weight, dt)
         with torch.autocast("cuda", enabled=False):
-            y = torch.addmm(bias.to(dt), x2, wb.t())
+            y = torch.addmm(low_precision(bias, dt), x2, wb.t())
         ctx.save_for_backward(x2, wb)
         ctx.meta = (x.shape, x.dtype, weight.dtype, bias.dtype)
+        ctx.params = (weight, bias)
         return y.reshape(*x.shape[:-1], weight.shape[0])
 
     @staticmethod
@@ -53,10 +81,19 @@ class LinearFunction(Function):
         with torch.cuda.device(dy2.device):   # autograd's worker thread may not have a current device yet
             if ctx.needs_input_grad[0]:
                 dx = (dy2 @ wb).reshape(xshape).to(xdt)
+            weight, bias = ctx.params
             if ctx.needs_input_grad[1]:
-                dw = (dy2.t() @ x2).to(wdt)
+                g = _sink(weight) if dy2.dtype != torch.float32 else None
+                if g is not None:
+                    torch.ops.aten.addmm.dtype_out(g, dy2.t(), x2, torch.float32, out=g)   # g += dy^T x, fp32 out
+                else:
+                    dw = (dy2.t() @ x2).to(wdt)
             if ctx.needs_input_grad[2]:
-                db = col_sum(dy2).to(bdt)
+                g = _sink(bias)
+                if g is not None and dy2.dtype in _OK and dy2.shape[1] % 8 == 0 and g.data_ptr() % 16 == 0:
+                    col_sum(dy2, into=g)
+                else:
+                    db = col_sum(dy2).to(bdt)
         return dx, dw, db
 
 

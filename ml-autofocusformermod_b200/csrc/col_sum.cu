@@ -71,7 +71,7 @@ col_sum_kernel(const T *__restrict__ x, float *__restrict__ part, int64_t R, int
 // out[c] = sum over slabs: a block owns 32 columns, 32 threads per column stride over the slabs (coalesced 128-byte
 // rows of partials), then a fixed-order tree over the 32 partial sums
 __global__ void __launch_bounds__(1024)
-col_sum_finish_kernel(const float *__restrict__ part, int n_slabs, int C, float *__restrict__ out) {
+col_sum_finish_kernel(const float *__restrict__ part, int n_slabs, int C, float *__restrict__ out, int accumulate) {
     __shared__ float red[32][33];
     const int cl = threadIdx.x & 31, sub = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
@@ -84,7 +84,7 @@ col_sum_finish_kernel(const float *__restrict__ part, int n_slabs, int C, float 
         float t = 0.f;
 #pragma unroll
         for (int k = 0; k < 32; ++k) t += red[k][cl];
-        out[c] = t;
+        out[c] = accumulate ? out[c] + t : t;
     }
 }
 
@@ -112,11 +112,13 @@ extern "C" int64_t affb200_col_sum_work_floats(int64_t R, int64_t C) {
     return int64_t(n_slabs) * C;
 }
 
-extern "C" int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C, int dtype, void *stream) {
+extern "C" int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C, int dtype, int accumulate,
+                               void *stream) {
     if (R < 0 || C <= 0 || C % 8 != 0 || C >= (int64_t(1) << 24)) { set_error("col_sum: C must be a positive multiple of 8"); return AFFB200_E_ARG; }
     auto st = (cudaStream_t)stream;
     if (!out) { set_error("col_sum: null pointer"); return AFFB200_E_ARG; }
     if (R == 0) {
+        if (accumulate) return AFFB200_OK;
         cudaMemsetAsync(out, 0, size_t(C) * 4, st);
         return check_launch("col_sum memset", 0);
     }
@@ -138,6 +140,6 @@ extern "C" int affb200_col_sum(const void *x, float *out, float *work, int64_t R
         }
     });
     if (e) return e;
-    col_sum_finish_kernel<<<unsigned((C + 31) / 32), 1024, 0, st>>>(work, n_slabs, int(C), out);
+    col_sum_finish_kernel<<<unsigned((C + 31) / 32), 1024, 0, st>>>(work, n_slabs, int(C), out, accumulate);
     return check_launch("col_sum_finish");
 }

@@ -64,13 +64,38 @@ def test_graphed_step_matches_eager_loss_and_gradients():
         l1 = float(step(x, y))
         l2 = float(_eager_step(m2, o2, x, y))
         assert abs(l1 - l2) < 2e-3 * max(1.0, abs(l2)), (l1, l2)
-        g1 = step.flat_grad
+        g1 = torch.cat([p.grad.reshape(-1) for p in m1.parameters() if p.requires_grad])   # views of step.flat_grad
         g2 = torch.cat([p.grad.reshape(-1) for p in m2.parameters() if p.requires_grad])
         rel = float((g1 - g2).norm() / g2.norm())
         assert rel < 2e-2, rel
     step.check()
     for a, b in zip(m1.parameters(), m2.parameters()):
         assert torch.equal(a, b)
+        assert a.grad.data_ptr() >= step.flat_grad.data_ptr() and a.data_ptr() >= step.flat_param.data_ptr()
+        assert torch.equal(a._affb200_lp, a.detach().bfloat16())     # the shadow the Linears read
+
+
+def test_linear_gradient_sink_accumulates_in_place():
+    """`_affb200_sink`: the weight-gradient GEMM and the bias column sums add into the existing fp32 .grad (fp32 output
+    from bf16 operands) and autograd gets None; the result matches the stock Linear backward."""
+    from affb200.linear_ops import linear
+    torch.manual_seed(5)
+    lin = torch.nn.Linear(64, 128).cuda()
+    ref = torch.nn.Linear(64, 128).cuda()
+    ref.load_state_dict(lin.state_dict())
+    x = torch.randn(300, 64, device="cuda")
+    go = torch.randn(300, 128, device="cuda").bfloat16()
+    for p in lin.parameters():
+        p.grad = torch.full_like(p, 0.25)
+        p._affb200_sink = True
+        p._affb200_lp = p.detach().bfloat16()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        linear(x, lin.weight, lin.bias).backward(go)
+        ref(x).backward(go)
+    for a, b in zip(lin.parameters(), ref.parameters()):
+        assert a.grad.dtype == torch.float32
+        err = float((a.grad - 0.25 - b.grad).abs().max() / b.grad.abs().max())
+        assert err < 1e-2, err
 
 
 def test_graphed_step_trains():
