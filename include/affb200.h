@@ -327,6 +327,21 @@ int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C
                     void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * Exact (erf) GELU of the Mlp (reference models/aff_transformer.py:35-51, nn.GELU) for f16/bf16 as table lookups:
+ * a 2-byte input has 65 536 values.  affb200_gelu_tables fills, for `dtype`, fwd_tab (65 536 entries of dtype:
+ * GELU(x) by the stock fp32 formula, rounded once — lookups are bit-identical to the element-wise operator) and bwd_tab
+ * (32 768 fp32 entries of GELU'(x), x >= 0; GELU'(-x) = 1 - GELU'(x)); both 128 KB, 16-byte aligned, caller-owned.
+ * fwd: y = F[x] over n elements (n % 8 == 0).  bwd: dx = dy * G(x) over [R][C] (C % 8 == 0, C <= 8192); col_sums != NULL
+ * also gives the fp32 column sums of dx (the bias gradient of fc1; added to col_sums when accumulate != 0) using
+ * work = affb200_gelu_bwd_work_floats(C) floats.
+ * ---------------------------------------------------------------------------------------------------------- */
+int affb200_gelu_tables(int dtype, void *fwd_tab, float *bwd_tab, void *stream);
+int affb200_gelu_fwd(const void *x, void *y, int64_t n, int dtype, const void *fwd_tab, void *stream);
+int64_t affb200_gelu_bwd_work_floats(int64_t C);
+int affb200_gelu_bwd(const void *dy, const void *x, void *dx, int64_t R, int64_t C, int dtype, const float *bwd_tab,
+                     float *col_sums, int accumulate, float *work, void *stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Residual connection with stochastic depth in one pass: out[b][...] = a[b][...] + x[b][...] * s[b]  (a may be NULL:
  * out = x * s[b], the backward of the x branch).  Reference: `feat = shortcut + drop_path(feat)`
  * (models/aff_transformer.py:224-229).  a/x/out [B][per_sample] of `dtype` (f32/f16/bf16), s [B] fp32; per_sample a

@@ -34,6 +34,7 @@ class CudaOps:
         self.layer_norm = L.layer_norm
         self.batch_norm_act = L.batch_norm_act
         self.linear = LI.linear
+        self.linear_gelu = LI.linear_gelu
         self.residual_add = RO.residual_add
         from . import merge_ops as MO
         self.merge_wf = MO.merge_wf
@@ -100,7 +101,8 @@ class Mlp(nn.Module):
         self.drop = nn.Dropout(drop)
 
     def forward(self, x, ops):
-        return self.drop(_lin(ops, self.fc2, self.drop(self.act(_lin(ops, self.fc1, x)))))
+        h = ops.linear_gelu(x, self.fc1.weight, self.fc1.bias)    # act(fc1(x))
+        return self.drop(_lin(ops, self.fc2, self.drop(h)))
 
 
 class ClusterAttention(nn.Module):

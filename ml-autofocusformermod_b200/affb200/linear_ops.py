@@ -1,6 +1,8 @@
 """nn.Linear with the bias gradient as one column-sum pass (csrc/col_sum.cu).
 
   linear(x, weight, bias) -> x @ weight.T + bias      (reference: the nn.Linear layers of aff_transformer.py:85-100,285)
+  linear_gelu(x, weight, bias) -> GELU(linear(...))    (fc1 + act of the Mlp, aff_transformer.py:35-51)
+  gelu(x)                                              (exact GELU; table lookups for f16/bf16, csrc/gelu.cu)
 
 The two GEMMs of the backward and the forward addmm are the stock cuBLAS calls nn.Linear makes (same dtypes under
 autocast); only `grad_out.sum(0)`, which autograd runs as a generic strided reduction, is replaced — by fp32 column
@@ -15,6 +17,8 @@ before adding it to the fp32 .grad):
                    output from bf16 operands: no bf16 rounding of dW, no separate add), the bias column sums likewise;
                    autograd then receives None for that parameter.
 """
+import os
+
 import torch
 from torch.autograd import Function
 
@@ -55,6 +59,81 @@ def _sink(p):
         if g is not None and g.dtype == torch.float32 and g.is_contiguous():
             return g
     return None
+
+
+_gelu_tabs = {}   # (device index, dtype) -> (fwd_tab, bwd_tab)
+
+
+def gelu_tables(dev, dtype):
+    """The two 128 KB lookup tables of csrc/gelu.cu for this device and 2-byte dtype (built on first use; under CUDA
+    graph capture they must already exist: the eager warm-up passes of GraphedTrainStep build them)."""
+    key = (dev.index, dtype)
+    t = _gelu_tabs.get(key)
+    if t is None:
+        with torch.cuda.device(dev):
+            fwd = torch.empty(65536, dtype=torch.int16, device=dev)
+            bwd = torch.empty(32768, dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_gelu_tables(N.DTYPE_ENUM[dtype], N.p(fwd), N.p(bwd), N.stream_ptr(dev)), "gelu_tables")
+        t = _gelu_tabs[key] = (fwd, bwd)
+    return t
+
+
+def _gelu_ok(x):
+    return x.is_cuda and x.dtype in (torch.float16, torch.bfloat16) and x.shape[-1] % 8 == 0 and x.shape[-1] <= 8192
+
+
+def _gelu_fwd(h):
+    """h contiguous f16/bf16 -> GELU(h)"""
+    dev = h.device
+    fwd, _ = gelu_tables(dev, h.dtype)
+    with torch.cuda.device(dev):
+        y = torch.empty_like(h)
+        N.check(N.LIB.affb200_gelu_fwd(N.p(h), N.p(y), h.numel(), N.dtype_enum(h), N.p(fwd), N.stream_ptr(dev)), "gelu_fwd")
+    return y
+
+
+def _gelu_bwd(dy2, h2, col_into=None, want_cols=False):
+    """dy2, h2 contiguous [R, C] -> (dh, column sums of dh or None); col_into: fp32 [C] the sums are added to."""
+    dev = h2.device
+    R, C = h2.shape
+    _, bwd = gelu_tables(dev, h2.dtype)
+    with torch.cuda.device(dev):
+        dh = torch.empty_like(h2)
+        cols = col_into
+        if cols is None and want_cols:
+            cols = torch.empty(C, dtype=torch.float32, device=dev)
+        work = None
+        if cols is not None:
+            work = torch.empty(max(1, N.LIB.affb200_gelu_bwd_work_floats(C)), dtype=torch.float32, device=dev)
+        N.check(N.LIB.affb200_gelu_bwd(N.p(dy2), N.p(h2), N.p(dh), R, C, N.dtype_enum(h2), N.p(bwd), N.p(cols),
+                                       1 if col_into is not None else 0, N.p(work), N.stream_ptr(dev)), "gelu_bwd")
+    return dh, cols
+
+
+class GeluFunction(Function):
+    @staticmethod
+    def forward(ctx, x):
+        xc = x.contiguous()
+        ctx.save_for_backward(xc)
+        return _gelu_fwd(xc)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xc,) = ctx.saved_tensors
+        C = xc.shape[-1]
+        dy2 = dy.to(xc.dtype).contiguous().reshape(-1, C)
+        dh, _ = _gelu_bwd(dy2, xc.reshape(-1, C))
+        return dh.reshape(xc.shape)
+
+
+def gelu(x):
+    """Exact GELU.  f16/bf16 CUDA tensors whose last dim is a multiple of 8 take the lookup kernels; everything else
+    (fp32 activations) the stock CUDA operator."""
+    if not x.is_cuda:
+        raise RuntimeError("x must be a CUDA tensor")
+    if not _gelu_ok(x) or x.numel() == 0:
+        return torch.nn.functional.gelu(x)
+    return GeluFunction.apply(x)
 
 
 class LinearFunction(Function):
@@ -101,3 +180,54 @@ def linear(x, weight, bias=None):
     if bias is None:
         return torch.nn.functional.linear(x, weight)
     return LinearFunction.apply(x, weight, bias)
+
+
+class LinearGeluFunction(Function):
+    """GELU(x @ W^T + b): the addmm, then the lookup GELU; the backward produces d(pre-activation) and its column sums
+    (the bias gradient) in one pass."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+        x2 = x.reshape(-1, x.shape[-1]).to(dt)
+        wb = low_precision(weight, dt)
+        with torch.autocast("cuda", enabled=False):
+            h = torch.addmm(low_precision(bias, dt), x2, wb.t())
+        y = _gelu_fwd(h)
+        ctx.save_for_backward(x2, wb, h)
+        ctx.meta = (x.shape, x.dtype, weight.dtype, bias.dtype)
+        ctx.params = (weight, bias)
+        return y.reshape(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wb, h = ctx.saved_tensors
+        xshape, xdt, wdt, bdt = ctx.meta
+        weight, bias = ctx.params
+        dy2 = dy.reshape(-1, dy.shape[-1]).to(h.dtype).contiguous()
+        dx = dw = db = None
+        with torch.cuda.device(dy2.device):
+            g = _sink(bias) if ctx.needs_input_grad[2] else None
+            if g is not None and g.data_ptr() % 16 != 0:
+                g = None
+            dh, cols = _gelu_bwd(dy2, h, col_into=g, want_cols=ctx.needs_input_grad[2])
+            if ctx.needs_input_grad[2] and g is None:
+                db = cols.to(bdt)
+            if ctx.needs_input_grad[0]:
+                dx = (dh @ wb).reshape(xshape).to(xdt)
+            if ctx.needs_input_grad[1]:
+                g = _sink(weight)
+                if g is not None:
+                    torch.ops.aten.addmm.dtype_out(g, dh.t(), x2, torch.float32, out=g)
+                else:
+                    dw = (dh.t() @ x2).to(wdt)
+        return dx, dw, db
+
+
+def linear_gelu(x, weight, bias):
+    """GELU(nn.Linear(x)) as the Mlp computes it (fc1 -> act)."""
+    dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+    if bias is None or dt not in (torch.float16, torch.bfloat16) or weight.shape[0] % 8 != 0 or weight.shape[0] > 8192 \
+            or x.numel() == 0 or os.environ.get("AFFB200_GELU_LUT", "1") == "0":
+        return torch.nn.functional.gelu(linear(x, weight, bias))
+    return LinearGeluFunction.apply(x, weight, bias)

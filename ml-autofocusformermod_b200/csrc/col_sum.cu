@@ -88,6 +88,11 @@ col_sum_finish_kernel(const float *__restrict__ part, int n_slabs, int C, float 
     }
 }
 
+int launch_col_sum_finish(const float *part, int n_slabs, int C, float *out, int accumulate, cudaStream_t st) {
+    col_sum_finish_kernel<<<unsigned((C + 31) / 32), 1024, 0, st>>>(part, n_slabs, C, out, accumulate);
+    return check_launch("col_sum_finish");
+}
+
 static void col_sum_geometry(int64_t R, int64_t C, int *lpr, int *n_cblk, int *n_slabs, int64_t *rows_per_slab) {
     const int nch = int(C / 8);
     *lpr = nch <= 8 ? 8 : (nch <= 16 ? 16 : 32);
@@ -140,6 +145,5 @@ extern "C" int affb200_col_sum(const void *x, float *out, float *work, int64_t R
         }
     });
     if (e) return e;
-    col_sum_finish_kernel<<<unsigned((C + 31) / 32), 1024, 0, st>>>(work, n_slabs, int(C), out, accumulate);
-    return check_launch("col_sum_finish");
+    return launch_col_sum_finish(work, n_slabs, int(C), out, accumulate, st);
 }

@@ -47,6 +47,11 @@ class OracleOps:
         return torch.nn.functional.gelu(bn(x))
 
     @staticmethod
+    def linear_gelu(x, weight, bias=None):
+        """fc1 then nn.GELU of the Mlp (aff_transformer.py:35-51)"""
+        return torch.nn.functional.gelu(torch.nn.functional.linear(x, weight, bias))
+
+    @staticmethod
     def layer_norm(x, weight, bias, eps=1e-5):
         """nn.LayerNorm as the reference applies it (aff_transformer.py:199-200,284)"""
         return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)
