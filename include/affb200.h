@@ -290,14 +290,16 @@ int affb200_fused_attn_img_bwd(const affb200_view *q, const affb200_view *k, con
  * ClusterMerging; reference models/aff_transformer.py:199-200,223-229,284,362 = nn.LayerNorm, which autocast runs in
  * fp32 between two dtype copies).  x in `in_dtype`, y in `out_dtype` (f32/f16/bf16 each), gamma/beta/mean/rstd fp32,
  * statistics in fp32.  C multiple of 8; forward C <= 2048, backward C <= 1024.  Backward: dx in x's dtype, dgamma /
- * dbeta fp32 [C] (overwritten), work = affb200_layer_norm_bwd_work_floats(R, C) floats of scratch.
+ * dbeta fp32 [C] (overwritten, or added to when accumulate != 0), work = affb200_layer_norm_bwd_work_floats(R, C)
+ * floats of scratch.  dres (may be NULL, x's dtype): a gradient that reaches x over another branch — the residual
+ * connection that forks off before the norm (aff_transformer.py:223-229) — added to dx in the same pass.
  * ---------------------------------------------------------------------------------------------------------- */
 int affb200_layer_norm_fwd(const void *x, const float *gamma, const float *beta, void *y, float *mean, float *rstd,
                            int64_t R, int64_t C, float eps, int in_dtype, int out_dtype, void *stream);
 int64_t affb200_layer_norm_bwd_work_floats(int64_t R, int64_t C);
 int affb200_layer_norm_bwd(const void *dy, const void *x, const float *gamma, const float *mean, const float *rstd,
-                           void *dx, float *dgamma, float *dbeta, float *work, int64_t R, int64_t C, int x_dtype,
-                           int dy_dtype, void *stream);
+                           const void *dres, void *dx, float *dgamma, float *dbeta, float *work, int64_t R, int64_t C,
+                           int x_dtype, int dy_dtype, int accumulate, void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Training-mode BatchNorm over the rows of a channels-last activation [R = B*H*W][C], optionally followed by the exact

@@ -82,7 +82,7 @@ SIGNATURES = {
     "affb200_col_sum": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _int, _ptr]),
     "affb200_layer_norm_fwd": (_int, [_ptr] * 6 + [_i64, _i64, ctypes.c_float, _int, _int, _ptr]),
     "affb200_layer_norm_bwd_work_floats": (_i64, [_i64, _i64]),
-    "affb200_layer_norm_bwd": (_int, [_ptr] * 9 + [_i64, _i64, _int, _int, _ptr]),
+    "affb200_layer_norm_bwd": (_int, [_ptr] * 10 + [_i64, _i64, _int, _int, _int, _ptr]),
     "affb200_qk_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),
     "affb200_qk_bwd": (_int, [_ptr] * 4 + [_plan_p] + [_ptr] * 2 + [_i64] * 6 + [_int, _ptr]),
     "affb200_av_fwd": (_int, [_ptr, _ptr, _ptr, _plan_p, _ptr] + [_i64] * 6 + [_int, _ptr]),

@@ -32,6 +32,7 @@ class CudaOps:
         from . import linear_ops as LI
         from . import residual_ops as RO
         self.layer_norm = L.layer_norm
+        self.layer_norm_fork = L.layer_norm_fork
         self.batch_norm_act = L.batch_norm_act
         self.linear = LI.linear
         self.linear_gelu = LI.linear_gelu
@@ -172,11 +173,14 @@ class ClusterTransformerBlock(nn.Module):
             self.gamma2 = nn.Parameter(layer_scale * torch.ones(dim))
 
     def forward(self, feat, member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops):
-        x = self.attn(_ln(ops, self.norm1, feat), member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops)
+        # (shortcut, norm(shortcut)) leave one autograd node: the two gradients meet inside the LayerNorm backward
+        feat, y = ops.layer_norm_fork(feat, self.norm1.weight, self.norm1.bias, self.norm1.eps)
+        x = self.attn(y, member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops)
         if self.layer_scale:
             x = self.gamma1 * x
         feat = ops.residual_add(feat, x, self.drop_path_p, self.training)
-        x = self.mlp(_ln(ops, self.norm2, feat), ops)
+        feat, y = ops.layer_norm_fork(feat, self.norm2.weight, self.norm2.bias, self.norm2.eps)
+        x = self.mlp(y, ops)
         if self.layer_scale:
             x = self.gamma2 * x
         return ops.residual_add(feat, x, self.drop_path_p, self.training)

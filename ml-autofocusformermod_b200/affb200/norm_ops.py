@@ -24,47 +24,92 @@ def supported(x, weight, bias, out_dtype):
             and C % 8 == 0 and C <= 1024 and x.numel() > 0)
 
 
+def _ln_forward(x, weight, bias, eps, out_dtype):
+    C = x.shape[-1]
+    xc = x.contiguous()
+    R = xc.numel() // C
+    dev = x.device
+    g = weight.detach().float().contiguous()
+    b = bias.detach().float().contiguous()
+    with torch.cuda.device(dev):
+        y = torch.empty(x.shape, dtype=out_dtype, device=dev)
+        mean = torch.empty(R, dtype=torch.float32, device=dev)
+        rstd = torch.empty(R, dtype=torch.float32, device=dev)
+        N.check(N.LIB.affb200_layer_norm_fwd(N.p(xc), N.p(g), N.p(b), N.p(y), N.p(mean), N.p(rstd), R, C, float(eps),
+                                             N.dtype_enum(xc), N.DTYPE_ENUM[out_dtype], N.stream_ptr(dev)),
+                "layer_norm_fwd")
+    return xc, g, y, mean, rstd
+
+
+def _sink(p):
+    """fp32 .grad of a parameter registered for in-place accumulation (graph_step.GraphedTrainStep), or None."""
+    if getattr(p, "_affb200_sink", False):
+        g = p.grad
+        if g is not None and g.dtype == torch.float32 and g.is_contiguous() and g.data_ptr() % 16 == 0:
+            return g
+    return None
+
+
+def _ln_backward(ctx, dy, dres):
+    xc, g, mean, rstd = ctx.saved_tensors
+    weight, bias = ctx.params
+    C = xc.shape[-1]
+    R = xc.numel() // C
+    dev = xc.device
+    dy = dy.contiguous()
+    if dy.dtype not in _OK:
+        dy = dy.float()
+    if dres is not None:
+        dres = dres.to(xc.dtype).contiguous()
+    with torch.cuda.device(dev):
+        dx = torch.empty_like(xc)
+        sg, sb = _sink(weight), _sink(bias)
+        acc = sg is not None and sb is not None
+        dg = sg if acc else torch.empty(C, dtype=torch.float32, device=dev)
+        db = sb if acc else torch.empty(C, dtype=torch.float32, device=dev)
+        work = torch.empty(max(1, N.LIB.affb200_layer_norm_bwd_work_floats(R, C)), dtype=torch.float32, device=dev)
+        N.check(N.LIB.affb200_layer_norm_bwd(N.p(dy), N.p(xc), N.p(g), N.p(mean), N.p(rstd), N.p(dres), N.p(dx), N.p(dg),
+                                             N.p(db), N.p(work), R, C, N.dtype_enum(xc), N.dtype_enum(dy),
+                                             1 if acc else 0, N.stream_ptr(dev)), "layer_norm_bwd")
+    if acc:
+        return dx, None, None
+    return dx, dg.to(weight.dtype), db.to(bias.dtype)
+
+
 class LayerNormFunction(Function):
     @staticmethod
     def forward(ctx, x, weight, bias, eps, out_dtype):
         if not x.is_cuda:
             raise RuntimeError("x must be a CUDA tensor")
-        C = x.shape[-1]
-        xc = x.contiguous()
-        R = xc.numel() // C
-        dev = x.device
-        g = weight.detach().float().contiguous()
-        b = bias.detach().float().contiguous()
-        with torch.cuda.device(dev):
-            y = torch.empty(x.shape, dtype=out_dtype, device=dev)
-            mean = torch.empty(R, dtype=torch.float32, device=dev)
-            rstd = torch.empty(R, dtype=torch.float32, device=dev)
-            N.check(N.LIB.affb200_layer_norm_fwd(N.p(xc), N.p(g), N.p(b), N.p(y), N.p(mean), N.p(rstd), R, C, float(eps),
-                                                 N.dtype_enum(xc), N.DTYPE_ENUM[out_dtype], N.stream_ptr(dev)),
-                    "layer_norm_fwd")
+        xc, g, y, mean, rstd = _ln_forward(x, weight, bias, eps, out_dtype)
         ctx.save_for_backward(xc, g, mean, rstd)
-        ctx.meta = (weight.dtype, bias.dtype)
+        ctx.params = (weight, bias)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        xc, g, mean, rstd = ctx.saved_tensors
-        wdt, bdt = ctx.meta
-        C = xc.shape[-1]
-        R = xc.numel() // C
-        dev = xc.device
-        dy = dy.contiguous()
-        if dy.dtype not in _OK:
-            dy = dy.float()
-        with torch.cuda.device(dev):
-            dx = torch.empty_like(xc)
-            dg = torch.empty(C, dtype=torch.float32, device=dev)
-            db = torch.empty(C, dtype=torch.float32, device=dev)
-            work = torch.empty(max(1, N.LIB.affb200_layer_norm_bwd_work_floats(R, C)), dtype=torch.float32, device=dev)
-            N.check(N.LIB.affb200_layer_norm_bwd(N.p(dy), N.p(xc), N.p(g), N.p(mean), N.p(rstd), N.p(dx), N.p(dg), N.p(db),
-                                                 N.p(work), R, C, N.dtype_enum(xc), N.dtype_enum(dy), N.stream_ptr(dev)),
-                    "layer_norm_bwd")
-        return dx, dg.to(wdt), db.to(bdt), None, None
+        return _ln_backward(ctx, dy, None) + (None, None)
+
+
+class LayerNormForkFunction(Function):
+    """(x, LayerNorm(x)): the residual stream and its normalised copy leave one node, so the two gradients that come
+    back — over the shortcut and through the norm — are added inside the LayerNorm backward kernel instead of by a
+    separate pass of autograd's accumulation."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps, out_dtype):
+        if not x.is_cuda:
+            raise RuntimeError("x must be a CUDA tensor")
+        xc, g, y, mean, rstd = _ln_forward(x, weight, bias, eps, out_dtype)
+        ctx.save_for_backward(xc, g, mean, rstd)
+        ctx.params = (weight, bias)
+        return xc.view_as(xc), y
+
+    @staticmethod
+    def backward(ctx, dres, dy):
+        if dy is None:
+            return dres, None, None, None, None
+        return _ln_backward(ctx, dy, dres) + (None, None)
 
 
 def layer_norm(x, weight, bias, eps=1e-5, out_dtype=None):
@@ -139,3 +184,15 @@ def batch_norm_act(x, bn, gelu=True):
     with torch.no_grad():
         bn.num_batches_tracked.add_(1)
     return BatchNormActFunction.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.momentum, bn.eps, gelu)
+
+
+def layer_norm_fork(x, weight, bias, eps=1e-5, out_dtype=None):
+    """(x, layer_norm(x)) for a block's `shortcut = x; y = norm(x)` pair (reference aff_transformer.py:223-229); use
+    the returned x as the shortcut so that its gradient is folded into the LayerNorm backward pass."""
+    if not x.is_cuda:
+        raise RuntimeError("x must be a CUDA tensor")
+    if out_dtype is None:
+        out_dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+    if not supported(x, weight, bias, out_dtype) or not x.requires_grad:
+        return x, layer_norm(x, weight, bias, eps, out_dtype)
+    return LayerNormForkFunction.apply(x, weight, bias, eps, out_dtype)

@@ -99,8 +99,8 @@ ln_fwd_kernel(const TI *__restrict__ x, const float *__restrict__ gamma, const f
 template <typename TI, typename TG, int LPR, int NCH>
 __global__ void __launch_bounds__(kLT)
 ln_bwd_kernel(const TG *__restrict__ dy, const TI *__restrict__ x, const float *__restrict__ gamma,
-              const float *__restrict__ mean, const float *__restrict__ rstd, TI *__restrict__ dx,
-              float *__restrict__ part, int64_t R, int C) {
+              const float *__restrict__ mean, const float *__restrict__ rstd, const TI *__restrict__ dres,
+              TI *__restrict__ dx, float *__restrict__ part, int64_t R, int C) {
     constexpr int RPC = kLT / LPR;
     extern __shared__ float red[];  // [8 warps][C]
     const int l = threadIdx.x % LPR, rl = threadIdx.x / LPR, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -150,6 +150,12 @@ ln_bwd_kernel(const TG *__restrict__ dy, const TI *__restrict__ x, const float *
                     float o[8];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) o[e] = rs * (g[k][e] - s1 - xh[k][e] * s2);
+                    if (dres) {  // gradient arriving over the residual branch that forked off x
+                        float rv[8];
+                        ln_load8<TI>(dres + r * C + ch * 8, rv);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) o[e] += rv[e];
+                    }
                     ln_store8<TI>(dx + r * C + ch * 8, o);
                 }
             }
@@ -183,7 +189,7 @@ ln_bwd_kernel(const TG *__restrict__ dy, const TI *__restrict__ x, const float *
 // dgamma / dbeta = sum of the CTA partials: a block owns 32 columns, 32 threads per column stride over the CTAs
 __global__ void __launch_bounds__(1024)
 ln_bwd_finish_kernel(const float *__restrict__ part, int nblk, int C, float *__restrict__ dgamma,
-                     float *__restrict__ dbeta) {
+                     float *__restrict__ dbeta, int accumulate) {
     __shared__ float red[32][33];
     const int cl = threadIdx.x & 31, sub = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
@@ -197,7 +203,8 @@ ln_bwd_finish_kernel(const float *__restrict__ part, int nblk, int C, float *__r
         float t = 0.f;
 #pragma unroll
         for (int k = 0; k < 32; ++k) t += red[k][cl];
-        (pass == 0 ? dgamma : dbeta)[c] = t;
+        float *o = (pass == 0 ? dgamma : dbeta) + c;
+        *o = accumulate ? *o + t : t;
     }
 }
 
@@ -224,12 +231,12 @@ static int ln_fwd_launch(const void *x, const float *gamma, const float *beta, v
 
 template <typename TI, typename TG>
 static int ln_bwd_launch(const void *dy, const void *x, const float *gamma, const float *mean, const float *rstd,
-                         void *dx, float *part, int nblk, int64_t R, int C, cudaStream_t st) {
+                         const void *dres, void *dx, float *part, int nblk, int64_t R, int C, cudaStream_t st) {
     const int nch = C / 8;
     const size_t smem = size_t(kLT / 32) * C * 4;
 #define AFF_LNB(LPR_, NCH_)                                                                                      \
     ln_bwd_kernel<TI, TG, LPR_, NCH_><<<nblk, kLT, smem, st>>>((const TG *)dy, (const TI *)x, gamma, mean, rstd,  \
-                                                               (TI *)dx, part, R, C)
+                                                               (const TI *)dres, (TI *)dx, part, R, C)
     if (nch <= 8) AFF_LNB(8, 1);
     else if (nch <= 16) AFF_LNB(16, 1);
     else if (nch <= 32) AFF_LNB(32, 1);
@@ -277,17 +284,20 @@ extern "C" int64_t affb200_layer_norm_bwd_work_floats(int64_t R, int64_t C) {
 }
 
 extern "C" int affb200_layer_norm_bwd(const void *dy, const void *x, const float *gamma, const float *mean,
-                                      const float *rstd, void *dx, float *dgamma, float *dbeta, float *work, int64_t R,
-                                      int64_t C, int x_dtype, int dy_dtype, void *stream) {
+                                      const float *rstd, const void *dres, void *dx, float *dgamma, float *dbeta,
+                                      float *work, int64_t R, int64_t C, int x_dtype, int dy_dtype, int accumulate,
+                                      void *stream) {
     if (R < 0 || C <= 0 || C % 8 != 0 || C > 1024) { set_error("layer_norm_bwd: C must be a multiple of 8, <= 1024"); return AFFB200_E_ARG; }
     auto st = (cudaStream_t)stream;
     if (!dgamma || !dbeta) { set_error("layer_norm_bwd: null pointer"); return AFFB200_E_ARG; }
     if (R == 0) {
+        if (accumulate) return AFFB200_OK;
         cudaMemsetAsync(dgamma, 0, size_t(C) * 4, st);
         cudaMemsetAsync(dbeta, 0, size_t(C) * 4, st);
         return check_launch("layer_norm_bwd memset", 0);
     }
-    if (!dy || !x || !gamma || !mean || !rstd || !dx || !work || !aligned16(dy) || !aligned16(x) || !aligned16(dx) || !aligned16(gamma)) {
+    if (!dy || !x || !gamma || !mean || !rstd || !dx || !work || !aligned16(dy) || !aligned16(x) || !aligned16(dx) ||
+        !aligned16(gamma) || !aligned16(dres)) {
         set_error("layer_norm_bwd: null or misaligned pointer");
         return AFFB200_E_ARG;
     }
@@ -298,10 +308,10 @@ extern "C" int affb200_layer_norm_bwd(const void *dy, const void *x, const float
         using TI = decltype(ti);
         return ln_dispatch3(dy_dtype, [&](auto tg) {
             using TG = decltype(tg);
-            return ln_bwd_launch<TI, TG>(dy, x, gamma, mean, rstd, dx, work, nblk, R, int(C), st);
+            return ln_bwd_launch<TI, TG>(dy, x, gamma, mean, rstd, dres, dx, work, nblk, R, int(C), st);
         });
     });
     if (e) return e;
-    ln_bwd_finish_kernel<<<dim3(unsigned((C + 31) / 32), 2), 1024, 0, st>>>(work, nblk, int(C), dgamma, dbeta);
+    ln_bwd_finish_kernel<<<dim3(unsigned((C + 31) / 32), 2), 1024, 0, st>>>(work, nblk, int(C), dgamma, dbeta, accumulate);
     return check_launch("layer_norm_bwd_finish");
 }

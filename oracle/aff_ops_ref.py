@@ -57,6 +57,11 @@ class OracleOps:
         return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)
 
     @staticmethod
+    def layer_norm_fork(x, weight, bias, eps=1e-5):
+        """`shortcut = feat; feat = norm(feat)` (aff_transformer.py:223-229)"""
+        return x, torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)
+
+    @staticmethod
     def attn_bias_add(attn, pe_table, pe_idx, mask=None):
         """reference aff_transformer.py:131-137"""
         h = attn.shape[1]

@@ -78,3 +78,44 @@ def test_layer_norm_empty_and_unsupported_widths_use_stock_cuda():
     assert torch.allclose(layer_norm(x, w, b), torch.nn.functional.layer_norm(x, (50,), w, b))
     e = torch.randn(0, 64, device="cuda")
     assert layer_norm(e, torch.ones(64, device="cuda"), torch.zeros(64, device="cuda")).shape == (0, 64)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_layer_norm_fork_adds_the_shortcut_gradient_in_the_backward_pass(dtype):
+    """(x, LN(x)) from one node: d_x = d_shortcut + LN'(d_y), against the two-branch expression in fp64; with
+    `_affb200_sink` the parameter gradients are added into the existing fp32 .grad."""
+    from affb200.norm_ops import layer_norm_fork
+    from oracle.aff_ops_ref import OracleOps
+    g = torch.Generator().manual_seed(9)
+    shape = (3, 125, 256)
+    x = torch.randn(shape, generator=g).to(dtype)
+    w = 1 + 0.1 * torch.randn(256, generator=g)
+    b = 0.1 * torch.randn(256, generator=g)
+    g1 = torch.randn(shape, generator=g).to(dtype)
+    g2 = torch.randn(shape, generator=g).to(dtype)
+    for sink in (False, True):
+        x1 = x.cuda().requires_grad_(True)
+        w1 = w.cuda().requires_grad_(True)
+        b1 = b.cuda().requires_grad_(True)
+        if sink:
+            for p in (w1, b1):
+                p.grad = torch.full_like(p, 2.0)
+                p._affb200_sink = True
+        s, y = layer_norm_fork(x1, w1, b1, 1e-5, out_dtype=dtype)
+        assert s.data_ptr() == x1.data_ptr() and y.dtype == dtype
+        (s * g1.cuda() + y * g2.cuda()).sum().backward()
+        x2 = x.double().requires_grad_(True)
+        w2 = w.double().requires_grad_(True)
+        b2 = b.double().requires_grad_(True)
+        s2, y2 = OracleOps.layer_norm_fork(x2, w2, b2, 1e-5)
+        (s2 * g1.double() + y2 * g2.double()).sum().backward()
+        off = 2.0 if sink else 0.0
+        assert_close(y, y2, dtype, "fork y")
+        assert_close(x1.grad, x2.grad, dtype, "fork dx")
+        assert_close(w1.grad - off, w2.grad, torch.float32 if dtype == torch.float32 else dtype, "fork dgamma")
+        assert_close(b1.grad - off, b2.grad, torch.float32 if dtype == torch.float32 else dtype, "fork dbeta")
+    # only the shortcut is used downstream: the gradient passes through untouched
+    x1 = x.cuda().requires_grad_(True)
+    s, y = layer_norm_fork(x1, w.cuda().requires_grad_(True), b.cuda().requires_grad_(True), 1e-5, out_dtype=dtype)
+    (s * g1.cuda()).sum().backward()
+    assert torch.equal(x1.grad, g1.cuda())
