@@ -217,8 +217,11 @@ def main():
     e2e_value = imgs / (ms_e2e * 1e-3)
     h2d = sum(t.numel() * t.element_size() for t in host[0])
 
+    graph_fallbacks = None
     if getattr(run, "gstep", None) is not None:
-        run.gstep.check()  # one host read: the index plans assumed by the captured step held in every replay
+        # every replay is verified between the two graphs (4-byte read); a replay whose speculated index plans did not
+        # hold is redone eagerly inside the timed region.  Reported so that a slow run can be told from a clean one.
+        graph_fallbacks = run.gstep.fallbacks
 
     # ---- roofline of the dominant kernel, timed live --------------------------------------------------------
     peak, peak_src = peaks()
@@ -250,6 +253,8 @@ def main():
                 "e2e": {"value": e2e_value, "unit": wl.unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                         "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_base}
+        if graph_fallbacks is not None:
+            line["config"]["graph_fallbacks"] = graph_fallbacks
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

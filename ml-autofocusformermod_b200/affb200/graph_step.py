@@ -3,8 +3,8 @@ kernels are fast; the reference's step is ~3000 eager launches plus host syncs s
 aff_transformer.py:323).
 
     step = GraphedTrainStep(model, optimizer, loss_fn, example_x, example_y, world=1)
-    loss = step(x, y)           # device tensor; no host sync
-    step.check()                # one host read: raises if a speculated index plan did not hold since the last check
+    loss = step(x, y)           # device tensor
+    step.fallbacks              # how many steps had to be redone eagerly (a speculated index plan did not hold)
 
 Shapes are static (batch, image size, and therefore every stage's token count `int(n * ds_rate)`), so the whole
 forward + loss + backward is captured once and replayed; the optimizer step is a second graph.  Between the two, for
@@ -13,7 +13,9 @@ NVLink (the batch-sharded data parallelism of the reference's DDP, main.py:102, 
 
 What normally needs a device->host read while the index structures are built (tile-plan statistics, the range check
 of the packed bias indices) runs in `plan.static_plans()` mode: the sizes observed in the eager warm-up passes are
-assumed, and violations are accumulated in a device-side guard that `check()` reads.
+assumed, and violations are accumulated in a device-side guard.  The guard (4 bytes) is read once per step between
+the two graphs; a step whose speculation failed is redone eagerly with exact plans before the optimizer runs, so a
+failed speculation costs time, never correctness.
 
 The warm-up passes are real optimisation steps on the example batch (the optimizer state must exist before capture).
 """
@@ -72,6 +74,12 @@ class GraphedTrainStep:
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
 
+        self.fallbacks = 0        # steps whose speculated index plans did not hold and were redone eagerly
+        self.recaptures = 0
+        self.max_recaptures = 8
+        self._capture()
+
+    def _capture(self):
         from . import _native as N
         l0 = N.LIB.affb200_launch_count()
         self.g_fb = torch.cuda.CUDAGraph()
@@ -105,9 +113,28 @@ class GraphedTrainStep:
         self.x.copy_(x, non_blocking=True)
         self.y.copy_(y, non_blocking=True)
         self.g_fb.replay()
+        # One 4-byte read between the two graphs: did every speculated index plan of this replay hold?  If not, the
+        # replay skipped tiles (zeros, see csrc): the gradients are discarded and the step is redone eagerly with exact
+        # plans before the optimizer sees anything; the graphs are then re-captured with the larger sizes now on record.
+        guard = _plan.guard_tensor(self.device)
+        if int(guard.item()) != 0:
+            guard.zero_()
+            self.fallbacks += 1
+            loss = self._fwd_bwd()
+            self._reduce()
+            self.opt.step()
+            self.sync_params()
+            if self.recaptures < self.max_recaptures:
+                self.recaptures += 1
+                torch.cuda.synchronize(self.device)
+                self._capture()              # allocates a new self.loss
+            self.loss.copy_(loss)
+            return self.loss
         self._reduce()
         self.g_opt.replay()
         return self.loss
 
     def check(self):
+        """Kept for callers of the earlier interface: every replay is now verified (and redone if needed) inside
+        __call__, so this only reports a guard raised by kernels run outside the step."""
         _plan.check_guard(self.device)

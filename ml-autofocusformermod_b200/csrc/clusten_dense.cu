@@ -130,6 +130,13 @@ template <int C> __host__ __device__ constexpr int os_floats() { return 8 * 16 *
 // =========================================================================================================
 // FAST (decided by the launcher: M % 8 == 0, M <= 64, 16-byte aligned operands): the tile's 1-byte positions live in
 // registers as groups of 8 slots (at most 2 groups per thread) for all heads instead of in shared memory.
+// A tile that a speculated plan could not describe (see plan.py, static mode) is skipped; its outputs are written as
+// zeros so that the rest of the step computes on defined values until the host's deferred check redoes the step.
+template <typename T>
+__device__ __forceinline__ void zero_span(T *p, int64_t n) {
+    for (int64_t e = threadIdx.x; e < n; e += blockDim.x) p[e] = Elem<T>::from_acc(0.f);
+}
+
 template <typename T, int C, bool FAST>
 __global__ void __launch_bounds__(kDT)
 gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const int32_t *__restrict__ q_hdr,
@@ -149,7 +156,10 @@ gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const 
     const int ti = min(TT, Nq - t0);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int hdr0 = q_hdr[int64_t(b) * n_tiles + tile];
-    if (hdr0 & AFFB200_PLAN_OVERFLOW) return;  // only reachable with a speculated plan; the caller's deferred check reports it
+    if (hdr0 & AFFB200_PLAN_OVERFLOW) {  // only reachable with a speculated plan; the caller's deferred check reports it
+        for (int h = 0; h < H; ++h) zero_span<T>(out + ((int64_t(b) * H + h) * Nq + t0) * M, int64_t(ti) * M);
+        return;
+    }
     const int U = hdr0 & AFFB200_PLAN_COUNT_MASK;
     const int Upad = (U + 15) & ~15;
     const int n_ent = ti * M;
@@ -342,7 +352,10 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
     const int ti = min(TT, Nq - t0);
     const int tid = threadIdx.x;
     const int hdr = q_hdr[int64_t(b) * n_tiles + tile];
-    if (hdr & AFFB200_PLAN_OVERFLOW) return;  // speculated plan only (see gather_dot_dense_kernel)
+    if (hdr & AFFB200_PLAN_OVERFLOW) {  // speculated plan only (see gather_dot_dense_kernel)
+        for (int h = 0; h < H; ++h) zero_span<T>(out + ((int64_t(b) * H + h) * Nq + t0) * C, int64_t(ti) * C);
+        return;
+    }
     const int U = hdr & AFFB200_PLAN_COUNT_MASK;
     const bool dup = (hdr & AFFB200_PLAN_DUP) != 0;
     const int Upad = (U + 15) & ~15;
@@ -463,7 +476,12 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
     const int tid = threadIdx.x;
     const int64_t tix = int64_t(b) * n_tiles + tile;
     const int hdr = k_hdr[tix];
-    if (hdr & AFFB200_PLAN_OVERFLOW) return;  // speculated plan only (see gather_dot_dense_kernel)
+    if (hdr & AFFB200_PLAN_OVERFLOW) {  // speculated plan only (see gather_dot_dense_kernel)
+        for (int h = h_lo; h < h_hi; ++h)
+            for (int e = tid; e < ri * C; e += kDT)
+                dy[int64_t(b) * ys_.sB + int64_t(h) * ys_.sH + int64_t(r0 + e / C) * ys_.sN + e % C] = Elem<T>::from_acc(0.f);
+        return;
+    }
     const int Uq = hdr & AFFB200_PLAN_COUNT_MASK;
     const bool dup = (hdr & AFFB200_PLAN_DUP) != 0;
     const int Upad = (Uq + 15) & ~15;

@@ -54,7 +54,15 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
 
     const int b = blockIdx.y, tid = threadIdx.x;
     const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
-    if (t.bad) return;  // uniform over the CTA; the host's deferred plan check reports the failed speculation
+    if (t.bad) {  // uniform over the CTA; the host's deferred plan check reports the failed speculation and redoes
+                  // the step; until then the tile's outputs are zeros, not uninitialised memory
+        const int HS0 = (H + int(gridDim.z) - 1) / int(gridDim.z);
+        for (int h = int(blockIdx.z) * HS0; h < min(H, (int(blockIdx.z) + 1) * HS0); ++h) {
+            for (int e = tid; e < t.ti * C; e += kFT) out.row(b, t.t0 + e / C, h)[e % C] = Elem<T>::from_acc(0.f);
+            for (int e = tid; e < t.ti; e += kFT) lse[(int64_t(b) * H + h) * N + t.t0 + e] = 0.f;
+        }
+        return;
+    }
     const int i = tid / TPR, sub = tid % TPR;  // this thread's token row and its position in the row's group
     const bool live = i < t.ti, has_blank = live && sub == 0;
     uint32_t desc[NE - 1];
@@ -152,7 +160,16 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
 
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
-    if (t.bad) return;
+    if (t.bad) {  // failed speculation (see the forward kernel): zeros for everything this tile would have written
+        const int HS0 = (H + int(gridDim.z) - 1) / int(gridDim.z);
+        for (int h = int(blockIdx.z) * HS0; h < min(H, (int(blockIdx.z) + 1) * HS0); ++h) {
+            for (int e = tid; e < t.ti * C; e += kFT) dq.row(b, t.t0 + e / C, h)[e % C] = Elem<T>::from_acc(0.f);
+            const int64_t o = ((int64_t(b) * H + h) * N + t.t0) * M;
+            for (int e = tid; e < t.ti * M; e += kFT) { ds_out[o + e] = Elem<T>::from_acc(0.f); p_out[o + e] = Elem<T>::from_acc(0.f); }
+            if (tid < 2 * C) blank_part[((int64_t(b) * gridDim.x + blockIdx.x) * H + h) * 2 * C + tid] = 0.f;
+        }
+        return;
+    }
     const int i = tid / TPR, sub = tid % TPR;
     const bool live = i < t.ti, has_blank = live && sub == 0;
     const int64_t tok = t.t0 + (live ? i : 0);

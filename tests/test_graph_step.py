@@ -112,6 +112,41 @@ def test_graphed_step_trains():
     assert last < first, (first, last)
 
 
+def test_failed_speculation_is_redone_eagerly(monkeypatch):
+    """Capture with a row bound far below what the batches need (every stage-2 tile breaks it): each replay trips the
+    device guard, the step is redone eagerly before the optimizer runs, and losses / gradients still match eager."""
+    from affb200 import plan
+    from affb200.graph_step import GraphedTrainStep
+    m1, m2 = _models()
+    for m in (m1, m2):
+        for mod in m.modules():
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.momentum = 0.0
+    xs, ys = _batches(4)
+    o1 = torch.optim.AdamW(m1.parameters(), lr=0.0, weight_decay=0.0, fused=True, capturable=True)
+    o2 = torch.optim.AdamW(m2.parameters(), lr=0.0, weight_decay=0.0, fused=True)
+    real_cap = plan.observed_umax_cap
+    monkeypatch.setattr(plan, "observed_umax_cap", lambda kind, key: min(real_cap(kind, key) or 31, 31))
+    step = GraphedTrainStep(m1, o1, torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1)
+    step.max_recaptures = 1
+    for i, (x, y) in enumerate(zip(xs[1:], ys[1:])):
+        l1 = float(step(x, y))
+        l2 = float(_eager_step(m2, o2, x, y))
+        assert step.fallbacks == i + 1
+        assert abs(l1 - l2) < 2e-3 * max(1.0, abs(l2)), (l1, l2)
+        g1 = torch.cat([p.grad.reshape(-1) for p in m1.parameters() if p.requires_grad])
+        g2 = torch.cat([p.grad.reshape(-1) for p in m2.parameters() if p.requires_grad])
+        assert float((g1 - g2).norm() / g2.norm()) < 2e-2
+        assert all(bool(torch.isfinite(p).all()) for p in m1.parameters())
+    assert step.recaptures == 1
+    monkeypatch.setattr(plan, "observed_umax_cap", real_cap)
+    step.max_recaptures = 2
+    step(xs[0], ys[0])                    # falls back once more, re-captures with the real bounds ...
+    n = step.fallbacks
+    step(xs[1], ys[1])                    # ... and replays cleanly from then on
+    assert step.fallbacks == n
+
+
 def test_guard_reports_failed_speculation():
     from affb200 import plan
     dev = torch.device("cuda", 0)
