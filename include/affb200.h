@@ -262,7 +262,7 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
                            void *ds_work, void *p_work, float *blank_part, float *d_table, int64_t P,
                            int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype, void *stream);
 
-/* Same operator for small token sets (N <= AFFB200_FUSED_IMG_MAX_N, M <= 96): one CTA per (image, head) keeps the
+/* Same operator for small token sets (N <= AFFB200_FUSED_IMG_MAX_N, M even and <= 96): one CTA per (image, head) keeps the
  * image's K and V resident in shared memory, walks 32-row query tiles, and in the backward accumulates dK and dV on
  * chip (no tile plans, no scatter launches, no P scratch).  affb200_fused_attn_img_prepare derives, once per
  * (nbhd_idx, mask) pair: col [B][N][M] uint8 = nbhd_idx narrowed to a byte (the column of S is the key row itself) and

@@ -77,7 +77,7 @@ def _img_prep(plan, nbhd_idx, q_pe):
 
 
 def _use_img(n, M):
-    return n <= N.FUSED_IMG_MAX_N and M <= 96 and os.environ.get("AFFB200_FUSED_IMG", "1") != "0"
+    return n <= N.FUSED_IMG_MAX_N and M <= 96 and M % 2 == 0 and os.environ.get("AFFB200_FUSED_IMG", "1") != "0"
 
 
 class FusedClusterAttentionImg(Function):

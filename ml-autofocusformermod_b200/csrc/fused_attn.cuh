@@ -296,6 +296,57 @@ __device__ __forceinline__ void f_load_desc(const uint8_t *__restrict__ loc_r, c
     }
 }
 
+// The same in two steps, so that the global loads of tile t+1 can be issued while tile t is still being computed:
+// raw words now (PER % 2 == 0, M % 2 == 0: aligned pairs), descriptors when the tile starts.
+template <int PER> struct DescRaw {
+    uint32_t loc[PER / 2];  // two 1-byte columns
+    uint32_t pe[PER / 2];   // two packed bias indices
+};
+template <int PER>
+__device__ __forceinline__ void f_load_desc_raw(const uint8_t *__restrict__ loc_r, const uint16_t *__restrict__ pe_r, int M,
+                                                int sub, bool live, DescRaw<PER> &r) {
+    const int j0 = sub * PER;
+#pragma unroll
+    for (int e = 0; e < PER; e += 2) {
+        r.loc[e / 2] = 0xffffffffu;   // marks an unused pair
+        r.pe[e / 2] = 0u;
+        if (live && j0 + e < M) {
+            r.loc[e / 2] = __ldg(reinterpret_cast<const uint16_t *>(loc_r + j0 + e));
+            r.pe[e / 2] = __ldg(reinterpret_cast<const uint32_t *>(pe_r + j0 + e));
+        }
+    }
+}
+template <int PER>
+__device__ __forceinline__ void f_make_desc(const DescRaw<PER> &r, int UC, uint32_t (&desc)[PER]) {
+    auto mk = [](uint32_t loc, uint32_t pe) { return loc | ((pe & 0x7fffu) << 9) | ((pe >> 15) << 24); };
+#pragma unroll
+    for (int e = 0; e < PER; e += 2) {
+        if (r.loc[e / 2] == 0xffffffffu) {
+            desc[e] = desc[e + 1] = kSlotUnused | uint32_t(UC);
+        } else {
+            desc[e] = mk(r.loc[e / 2] & 0xffu, r.pe[e / 2] & 0xffffu);
+            desc[e + 1] = mk(r.loc[e / 2] >> 8, r.pe[e / 2] >> 16);
+        }
+    }
+}
+// bias-table entries of the slots, requested ahead of the contraction that produces S
+template <int PER>
+__device__ __forceinline__ void f_load_bias(const uint32_t (&desc)[PER], const float *__restrict__ table_h, int H,
+                                            float (&bias)[PER]) {
+#pragma unroll
+    for (int e = 0; e < PER; ++e) bias[e] = __ldg(table_h + ((desc[e] >> 9) & 0x7fffu) * H);
+}
+template <int NE>
+__device__ __forceinline__ void f_row_logits_b(const float *srow, const uint32_t (&desc)[NE - 1],
+                                               const float (&bias)[NE - 1], int U, bool has_blank, float (&pv)[NE]) {
+#pragma unroll
+    for (int e = 0; e < NE - 1; ++e) {
+        const uint32_t d = desc[e];
+        pv[e] = srow[d & 511u] + bias[e] + ((d & (1u << 24)) ? -100.f : 0.f);
+    }
+    pv[NE - 1] = has_blank ? srow[U] : -INFINITY;
+}
+
 __device__ __forceinline__ float f_ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

@@ -113,7 +113,7 @@ __device__ __forceinline__ void img_mma_atb(const unsigned char *ap, int RS, con
 }
 
 template <typename T, int C, int TT, int NE>
-__global__ void __launch_bounds__(kFT, 2)
+__global__ void __launch_bounds__(kFT, NE <= 7 ? 3 : 2)
 fused_attn_img_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float *__restrict__ table,
                           const float *__restrict__ blank_k, const float *__restrict__ blank_v,
                           const uint8_t *__restrict__ dupf, const uint8_t *__restrict__ col,
@@ -150,14 +150,25 @@ fused_attn_img_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const f
     const float *srow = reinterpret_cast<const float *>(prow);
     if (sub == 0) reinterpret_cast<float *>(prow)[L.UC] = -INFINITY;  // what unused slots read
 
+    // slot words of tile t+1 are requested during tile t (M even and NE-1 even: checked by the launcher)
+    DescRaw<NE - 1> raw;
+    {
+        const bool live0 = i < min(TT, N);
+        const int64_t r = (int64_t(b) * N + (live0 ? i : 0)) * M;
+        f_load_desc_raw<NE - 1>(col + r, q_pe + r, M, sub, live0, raw);
+    }
     for (int t = 0; t < n_tiles; ++t) {
         const int t0 = t * TT, ti = min(TT, N - t0);
         const bool live = i < ti, has_blank = live && sub == 0;
         const bool dup = dupf[int64_t(b) * n_tiles + t] != 0;
         uint32_t desc[NE - 1];
-        {
-            const int64_t r = (int64_t(b) * N + t0 + (live ? i : 0)) * M;
-            f_load_desc<NE - 1>(col + r, q_pe + r, M, sub, live, L.UC, desc);
+        float bias[NE - 1];
+        f_make_desc<NE - 1>(raw, L.UC, desc);
+        f_load_bias<NE - 1>(desc, table + h, H, bias);
+        if (t + 1 < n_tiles) {
+            const bool live1 = i < min(TT, N - t0 - TT);
+            const int64_t r = (int64_t(b) * N + t0 + TT + (live1 ? i : 0)) * M;
+            f_load_desc_raw<NE - 1>(col + r, q_pe + r, M, sub, live1, raw);
         }
         const T *xc = xs + (t & 1) * TT * CS;
         f_cp_async_wait<0>();
@@ -170,7 +181,7 @@ fused_attn_img_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const f
         __syncthreads();
         {
             float pv[NE];
-            f_row_logits<NE>(srow, desc, table + h, H, N, has_blank, pv);
+            f_row_logits_b<NE>(srow, desc, bias, N, has_blank, pv);
             const float l = f_row_softmax<TPR, NE>(live, pv);
             if (has_blank) lse[(int64_t(b) * H + h) * N + t0 + i] = l;
             __syncwarp();
@@ -248,17 +259,32 @@ fused_attn_img_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> 
             for (int e = 0; e < 4; ++e) acc_k[w][n][e] = acc_v[w][n][e] = 0.f;
     const bool pair_ok = (PER % 2 == 0) && (M % 2 == 0);
 
+    DescRaw<PER> raw;
+    float lse_next;
+    {
+        const bool live0 = i < min(TT, N);
+        const int64_t tok0 = live0 ? i : 0;
+        const int64_t r = (int64_t(b) * N + tok0) * M;
+        f_load_desc_raw<PER>(col + r, q_pe + r, M, sub, live0, raw);
+        lse_next = live0 ? __ldg(lse + (int64_t(b) * H + h) * N + tok0) : 0.f;
+    }
     for (int t = 0; t < n_tiles; ++t) {
         const int t0 = t * TT, ti = min(TT, N - t0);
         const bool live = i < ti, has_blank = live && sub == 0;
         const bool dup = dupf[int64_t(b) * n_tiles + t] != 0;
         const int64_t tok = t0 + (live ? i : 0);
         uint32_t desc[PER];
-        {
-            const int64_t r = (int64_t(b) * N + tok) * M;
-            f_load_desc<PER>(col + r, q_pe + r, M, sub, live, L.UC, desc);
+        float bias[PER];
+        f_make_desc<PER>(raw, L.UC, desc);
+        f_load_bias<PER>(desc, table + h, H, bias);
+        const float lse_cur = lse_next;
+        if (t + 1 < n_tiles) {
+            const bool live1 = i < min(TT, N - t0 - TT);
+            const int64_t tok1 = t0 + TT + (live1 ? i : 0);
+            const int64_t r = (int64_t(b) * N + tok1) * M;
+            f_load_desc_raw<PER>(col + r, q_pe + r, M, sub, live1, raw);
+            lse_next = live1 ? __ldg(lse + (int64_t(b) * H + h) * N + tok1) : 0.f;
         }
-        const float nl = live ? -__ldg(lse + (int64_t(b) * H + h) * N + tok) * kLog2e : 0.f;
         const int cur = (t & 1) * TT * CS, nxt = ((t + 1) & 1) * TT * CS;
         f_cp_async_wait<0>();
         __syncthreads();
@@ -283,8 +309,9 @@ fused_attn_img_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> 
 #pragma unroll
             for (int cc = 0; cc < CPT; ++cc) dl += dov[cc] * ov[cc];
             dl = f_group_sum<TPR>(dl);
+            const float nl = -lse_cur * kLog2e;   // 0 for rows past the end of the tile
             float pv[NE], dsv[NE];
-            f_row_logits<NE>(srow, desc, table + h, H, N, has_blank, pv);
+            f_row_logits_b<NE>(srow, desc, bias, N, has_blank, pv);
             T *dg = ds_out + ((int64_t(b) * H + h) * N + tok) * M + sub * PER;
 #pragma unroll
             for (int e = 0; e < PER; ++e) {
@@ -359,8 +386,8 @@ static bool img_view_ok(const affb200_view *v, int64_t N) {
 
 static int img_common_check(const char *what, const uint8_t *dupf, const void *col, const void *q_pe, int64_t B,
                             int64_t H, int64_t N, int64_t M, int64_t c, int dtype) {
-    if (B <= 0 || H <= 0 || N <= 0 || M <= 0 || B > 65535 || H > 65535 || N > AFFB200_FUSED_IMG_MAX_N || M > 96) {
-        set_error("%s: needs 1 <= N <= %d tokens per image and M <= 96 (got N=%lld M=%lld)", what,
+    if (B <= 0 || H <= 0 || N <= 0 || M <= 0 || B > 65535 || H > 65535 || N > AFFB200_FUSED_IMG_MAX_N || M > 96 || M % 2) {
+        set_error("%s: needs 1 <= N <= %d tokens per image and an even M <= 96 (got N=%lld M=%lld)", what,
                   AFFB200_FUSED_IMG_MAX_N, (long long)N, (long long)M);
         return AFFB200_E_ARG;
     }
