@@ -279,7 +279,8 @@ class _AffRun:
                 q = torch.randn(B, n, hc, device=self.device).bfloat16()
                 kv = torch.randn(B, n, 2 * hc, device=self.device).bfloat16()
                 table = torch.randn(self.model.pre_table.shape[0], H, device=self.device).bfloat16()
-                calls = fused.raw_calls(q, kv, H, attn.scale, nbhd, pe_idx, mask, table, attn.blank_k, attn.blank_v)
+                calls = fused.raw_calls(q, kv, H, attn.scale, nbhd, pe_idx, mask, table, attn.blank_k, attn.blank_v,
+                                        pre_table=self.model.pre_table)
                 if calls is None:
                     continue
                 nidx = 8 * B * n * M * (3 if mask is not None else 2)

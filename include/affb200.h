@@ -262,6 +262,16 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
                            void *ds_work, void *p_work, float *blank_part, float *d_table, int64_t P,
                            int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype, void *stream);
 
+/* Gradient of the bias table's generator.  In ClusterAttention the table is pos_embed(pre_table) = feat·W^T + b
+ * (reference aff_transformer.py:78,125) and only W and b receive its gradient, so the [P][H] histogram can be skipped:
+ * pass d_table = NULL to the backward entry points and call this on their ds_work [B][H][N*M]:
+ *   out[h][f] = sum over slots of ds[slot][h] * feat8[pe(slot)][f], f < 6 (out is [H][8] fp32)
+ * feat8 [P][8] fp32 = the feature table padded to 8 columns with a column of ones (dW = out[:, :5], db = out[:, 5]).
+ * N*M must be a multiple of 8; work = affb200_pe_feat_grad_work_floats(B, H, N*M) floats.  Fixed summation order. */
+int64_t affb200_pe_feat_grad_work_floats(int64_t B, int64_t H, int64_t NM);
+int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, const float *feat8, int64_t B, int64_t H, int64_t NM,
+                         float *out, float *work, int dtype, void *stream);
+
 /* Same operator for small token sets (N <= AFFB200_FUSED_IMG_MAX_N, M even and <= 96): one CTA per (image, head) keeps the
  * image's K and V resident in shared memory, walks 32-row query tiles, and in the backward accumulates dK and dV on
  * chip (no tile plans, no scatter launches, no P scratch).  affb200_fused_attn_img_prepare derives, once per

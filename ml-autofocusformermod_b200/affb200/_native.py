@@ -66,6 +66,8 @@ SIGNATURES = {
                                    + [ctypes.c_float, _int, _ptr]),
     "affb200_fused_attn_img_bwd": (_int, [_ptr] * 8 + [_ptr] * 3 + [_ptr, _ptr, _ptr, _ptr] + [_ptr] * 3
                                    + [_i64] * 6 + [ctypes.c_float, _int, _ptr]),
+    "affb200_pe_feat_grad_work_floats": (_i64, [_i64, _i64, _i64]),
+    "affb200_pe_feat_grad": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr, _int, _ptr]),
     "affb200_merge_fwd": (_int, [_ptr] * 7 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_merge_bwd": (_int, [_ptr] * 12 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_table_gather": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),

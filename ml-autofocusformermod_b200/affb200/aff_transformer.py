@@ -129,12 +129,14 @@ class ClusterAttention(nn.Module):
         c_ = c // h
         q_lin = _lin(ops, self.q, feat)
         kv = _lin(ops, self.kv, feat)
-        pe_table = self.pos_embed(pre_table)                       # T*T x h
         if not global_attn and ops.fused_attention is not None and self.attn_drop.p == 0.:
-            out = ops.fused_attention(q_lin, kv, h, self.scale, member_idx, pe_idx, cluster_mask, pe_table,
-                                      self.blank_k, self.blank_v)   # b n c, or None when unsupported
-            if out is not None:
+            # the bias table pos_embed(pre_table) is evaluated inside; its gradient goes straight to weight / bias
+            out = ops.fused_attention(q_lin, kv, h, self.scale, member_idx, pe_idx, cluster_mask, None,
+                                      self.blank_k, self.blank_v,
+                                      pos_embed=(pre_table, self.pos_embed.weight, self.pos_embed.bias))
+            if out is not None:                                     # b n c; None when unsupported
                 return self.proj_drop(_lin(ops, self.proj, out))
+        pe_table = self.pos_embed(pre_table)                       # T*T x h
         q = (q_lin * self.scale).reshape(b, n, h, c_).permute(0, 2, 1, 3)   # b h n c_
         kv = kv.view(b, n, h, 2, c_).permute(3, 0, 2, 1, 4)        # 2 b h n c_
         key, v = kv[0], kv[1]

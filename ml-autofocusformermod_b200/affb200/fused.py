@@ -76,6 +76,50 @@ def _img_prep(plan, nbhd_idx, q_pe):
     return col, dupf
 
 
+_feat_cache = {}
+
+
+def _pe_features(pre_table, dt):
+    """(feature table in the compute dtype, feat8 [P, 8] fp32 = those values padded with a column of ones) for the
+    Linear that generates the bias table (reference aff_transformer.py:78,125: pos_embed(pre_table)); cached."""
+    key = (pre_table.data_ptr(), pre_table._version, dt)
+    hit = _feat_cache.get(key)
+    if hit is None:
+        src = pre_table.detach()
+        lp = src.to(dt) if dt is not None else src.float()
+        P, F = lp.shape
+        feat8 = torch.zeros((P, 8), dtype=torch.float32, device=src.device)
+        feat8[:, :F] = lp.float()
+        feat8[:, F] = 1.0
+        if len(_feat_cache) > 16:
+            _feat_cache.clear()
+        hit = _feat_cache[key] = (lp.contiguous(), feat8)
+    return hit
+
+
+def _table_of(pe_table, pe_w, pe_b, pe_feat):
+    """fp32 [P, H] bias table: given, or pos_embed evaluated the way autocast evaluates the nn.Linear."""
+    if pe_w is None:
+        return pe_table.detach().float().contiguous()
+    from .linear_ops import low_precision
+    lp, _ = pe_feat
+    dt = lp.dtype
+    with torch.autocast("cuda", enabled=False):
+        return torch.nn.functional.linear(lp, low_precision(pe_w, dt).detach(), low_precision(pe_b, dt).detach()
+                                          ).float().contiguous()
+
+
+def _pe_grad(ds, q_pe, pe_feat, B, H, NM, F, w_dt, b_dt):
+    """(dW [H, F], db [H]) of the table-generating Linear from dS [B, H, N*M] (affb200_pe_feat_grad)."""
+    dev = ds.device
+    _, feat8 = pe_feat
+    out = torch.empty((H, 8), dtype=torch.float32, device=dev)
+    work = torch.empty(max(1, N.LIB.affb200_pe_feat_grad_work_floats(B, H, NM)), dtype=torch.float32, device=dev)
+    N.check(N.LIB.affb200_pe_feat_grad(N.p(ds), N.p(q_pe), N.p(feat8), B, H, NM, N.p(out), N.p(work), N.dtype_enum(ds),
+                                       N.stream_ptr(dev)), "pe_feat_grad")
+    return out[:, :F].to(w_dt), out[:, F].to(b_dt)
+
+
 def _use_img(n, M):
     return n <= N.FUSED_IMG_MAX_N and M <= 96 and M % 2 == 0 and os.environ.get("AFFB200_FUSED_IMG", "1") != "0"
 
@@ -84,7 +128,7 @@ class FusedClusterAttentionImg(Function):
     """Small token sets: one CTA per (image, head), K/V resident, dK/dV accumulated on chip (fused_attn_img.cu)."""
 
     @staticmethod
-    def forward(ctx, q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe, col, dupf, meta):
+    def forward(ctx, q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, q_pe, col, dupf, pe_feat, meta):
         H, scale = meta
         B, n, hc = q_lin.shape
         c = hc // H
@@ -92,7 +136,7 @@ class FusedClusterAttentionImg(Function):
         dev = q_lin.device
         q_lin = q_lin.contiguous()
         kv_lin = kv_lin.contiguous()
-        table = pe_table.detach().float().contiguous()
+        table = _table_of(pe_table, pe_w, pe_b, pe_feat)
         bk = blank_k.detach().float().contiguous()
         bv = blank_v.detach().float().contiguous()
         with torch.cuda.device(dev):
@@ -105,7 +149,8 @@ class FusedClusterAttentionImg(Function):
                 N.stream_ptr(dev)), "fused_attn_img_fwd")
         ctx.save_for_backward(q_lin, kv_lin, out, lse, table, bk, bv, q_pe, col, dupf)
         ctx.M = M
-        ctx.meta = (H, scale, pe_table.dtype, blank_k.dtype, pe_table.shape[0])
+        ctx.meta = (H, scale, None if pe_table is None else pe_table.dtype, blank_k.dtype, table.shape[0])
+        ctx.pe_lin = None if pe_w is None else (pe_feat, pe_w.shape[1], pe_w.dtype, pe_b.dtype)
         return out
 
     @staticmethod
@@ -124,7 +169,7 @@ class FusedClusterAttentionImg(Function):
             dkv = torch.empty_like(kv_lin)
             ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
             blank_part = torch.empty((B, H, 2, c), dtype=torch.float32, device=dev)
-            d_table = torch.empty((P, H), dtype=torch.float32, device=dev)
+            d_table = torch.empty((P, H), dtype=torch.float32, device=dev) if ctx.pe_lin is None else None
             N.check(N.LIB.affb200_fused_attn_img_bwd(
                 _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
                 _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
@@ -133,13 +178,17 @@ class FusedClusterAttentionImg(Function):
                 N.p(d_table), P, B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)),
                 "fused_attn_img_bwd")
             db = blank_part.sum(dim=0)  # [H, 2, c]
-        return (dq, dkv, d_table.to(table_dt), db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt),
-                None, None, None, None, None)
+            dw = dpb = None
+            if ctx.pe_lin is not None:
+                pe_feat, F, w_dt, b_dt = ctx.pe_lin
+                dw, dpb = _pe_grad(ds, q_pe, pe_feat, B, H, n * M, F, w_dt, b_dt)
+        return (dq, dkv, None if d_table is None else d_table.to(table_dt), dw, dpb,
+                db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt), None, None, None, None, None, None)
 
 
 class FusedClusterAttention(Function):
     @staticmethod
-    def forward(ctx, q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe, meta):
+    def forward(ctx, q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, q_pe, pe_feat, meta):
         H, scale, umax = meta
         B, n, hc = q_lin.shape
         c = hc // H
@@ -147,7 +196,7 @@ class FusedClusterAttention(Function):
         dev = q_lin.device
         q_lin = q_lin.contiguous()
         kv_lin = kv_lin.contiguous()
-        table = pe_table.detach().float().contiguous()
+        table = _table_of(pe_table, pe_w, pe_b, pe_feat)
         bk = blank_k.detach().float().contiguous()
         bv = blank_v.detach().float().contiguous()
         plan = get_plan(nbhd_idx)
@@ -161,7 +210,8 @@ class FusedClusterAttention(Function):
                 N.p(q_pe), umax, N.p(lse), B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)),
                 "fused_attn_fwd")
         ctx.save_for_backward(q_lin, kv_lin, out, lse, table, bk, bv, nbhd_idx, q_pe)
-        ctx.meta = (H, scale, umax, pe_table.dtype, blank_k.dtype, pe_table.shape[0])
+        ctx.meta = (H, scale, umax, None if pe_table is None else pe_table.dtype, blank_k.dtype, table.shape[0])
+        ctx.pe_lin = None if pe_w is None else (pe_feat, pe_w.shape[1], pe_w.dtype, pe_b.dtype)
         return out
 
     @staticmethod
@@ -185,7 +235,7 @@ class FusedClusterAttention(Function):
             ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
             pw = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
             blank_part = torch.empty((B, nt, H, 2, c), dtype=torch.float32, device=dev)
-            d_table = torch.empty((P, H), dtype=torch.float32, device=dev)
+            d_table = torch.empty((P, H), dtype=torch.float32, device=dev) if ctx.pe_lin is None else None
             N.check(N.LIB.affb200_fused_attn_bwd(
                 _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
                 _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
@@ -193,21 +243,43 @@ class FusedClusterAttention(Function):
                 N.p(table), N.p(bk), N.p(bv), st, N.p(q_pe), umax, N.p(lse), N.p(ds), N.p(pw), N.p(blank_part),
                 N.p(d_table), P, B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)), "fused_attn_bwd")
             db = blank_part.sum(dim=(0, 1))  # [H, 2, c]
-        return (dq, dkv, d_table.to(table_dt), db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt),
-                None, None, None)
+            dw = dpb = None
+            if ctx.pe_lin is not None:
+                pe_feat, F, w_dt, b_dt = ctx.pe_lin
+                dw, dpb = _pe_grad(ds, q_pe, pe_feat, B, H, n * M, F, w_dt, b_dt)
+        return (dq, dkv, None if d_table is None else d_table.to(table_dt), dw, dpb,
+                db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt), None, None, None, None)
 
 
 _ctypes_sigs_done = False
 
 
 def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k,
-                            blank_v):
-    """Returns out [B, N, H*c], or None when this case must take the unfused operators."""
+                            blank_v, pos_embed=None):
+    """Returns out [B, N, H*c], or None when this case must take the unfused operators.
+
+    pos_embed = (pre_table [P, F<=5], weight [H, F], bias [H]) may be given instead of pe_table (pass None): the table
+    is then pos_embed evaluated inside (as autocast evaluates the nn.Linear) and the backward produces d weight /
+    d bias directly from dS, without the [P, H] table gradient."""
     if not q_lin.is_cuda or q_lin.dtype not in (torch.float16, torch.bfloat16) or kv_lin.dtype != q_lin.dtype:
         return None
     B, n, hc = q_lin.shape
     c = hc // num_heads
-    if c not in (16, 32) or pe_table.shape[0] > 32768 or nbhd_idx.shape[2] > N.PLAN_MAX_M:
+    pe_w = pe_b = pe_feat = None
+    if pos_embed is not None:
+        pre_table, pe_w, pe_b = pos_embed
+        P = pre_table.shape[0]
+        if pre_table.shape[1] > 5 or pe_b is None or (n * nbhd_idx.shape[2]) % 8 != 0 \
+                or os.environ.get("AFFB200_PE_LINEAR", "1") == "0":
+            pe_table = torch.nn.functional.linear(pre_table, pe_w, pe_b)   # the stock path: table through autograd
+            pe_w = pe_b = None
+        else:
+            dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else None
+            pe_feat = _pe_features(pre_table, dt)
+            pe_table = None
+    else:
+        P = pe_table.shape[0]
+    if c not in (16, 32) or P > 32768 or nbhd_idx.shape[2] > N.PLAN_MAX_M:
         return None
     plan = get_plan(nbhd_idx)
     if _use_img(n, nbhd_idx.shape[2]):
@@ -215,8 +287,8 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
         if q_pe is None:
             return None
         col, dupf = _img_prep(plan, nbhd_idx, q_pe)
-        return FusedClusterAttentionImg.apply(q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe, col, dupf,
-                                              (num_heads, scale))
+        return FusedClusterAttentionImg.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, q_pe, col,
+                                              dupf, pe_feat, (num_heads, scale))
     if plan.qplan(nbhd_idx, n) is None or plan.kplan(nbhd_idx, n) is None:
         return None
     umax = plan.stats["q"]["umax"]
@@ -225,13 +297,30 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
     q_pe = _packed_pe(plan, pe_idx, cluster_mask)
     if q_pe is None:
         return None
-    return FusedClusterAttention.apply(q_lin, kv_lin, pe_table, blank_k, blank_v, nbhd_idx, q_pe,
+    return FusedClusterAttention.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, q_pe, pe_feat,
                                        (num_heads, scale, umax))
 
 
-def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v):
+def _raw_pe_grad(pre_table, ds, q_pe, B, H, NM, keep):
+    """Closure enqueueing affb200_pe_feat_grad on preallocated buffers (None when the table gradient is wanted)."""
+    if pre_table is None or pre_table.shape[1] > 5 or NM % 8 != 0:
+        return None
+    _, feat8 = _pe_features(pre_table, ds.dtype)
+    dev = ds.device
+    out = torch.empty((H, 8), dtype=torch.float32, device=dev)
+    work = torch.empty(max(1, N.LIB.affb200_pe_feat_grad_work_floats(B, H, NM)), dtype=torch.float32, device=dev)
+    keep += (feat8, out, work)
+    de, sp = N.dtype_enum(ds), N.stream_ptr(dev)
+    return lambda: N.check(N.LIB.affb200_pe_feat_grad(N.p(ds), N.p(q_pe), N.p(feat8), B, H, NM, N.p(out), N.p(work), de,
+                                                      sp), "pe_feat_grad")
+
+
+def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v,
+              pre_table=None):
     """(fwd, bwd) closures that enqueue the forward kernel / the backward kernel group through the C ABI on
-    preallocated buffers (no autograd, no allocation) — what bench.py times for the roofline entries."""
+    preallocated buffers (no autograd, no allocation) — what bench.py times for the roofline entries.  With
+    pre_table (the model's call form) the backward group ends with affb200_pe_feat_grad instead of the [P, H] table
+    histogram."""
     B, n, hc = q_lin.shape
     H = num_heads
     c = hc // H
@@ -239,7 +328,8 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
     dev = q_lin.device
     plan = get_plan(nbhd_idx)
     if _use_img(n, M):
-        return _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v)
+        return _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v,
+                              pre_table)
     if plan.qplan(nbhd_idx, n) is None or plan.kplan(nbhd_idx, n) is None:
         return None
     umax = plan.stats["q"]["umax"]
@@ -258,7 +348,9 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
     blank_part = torch.empty((B, (n + T - 1) // T, H, 2, c), dtype=torch.float32, device=dev)
     d_table = torch.empty((table.shape[0], H), dtype=torch.float32, device=dev)
     de, sp = N.dtype_enum(q_lin), N.stream_ptr(dev)
-    keep = (plan, q_pe, table, bk, bv, out, dq, dkv, dout, lse, ds, pw, blank_part, d_table)
+    keep = [plan, q_pe, table, bk, bv, out, dq, dkv, dout, lse, ds, pw, blank_part, d_table]
+    pe_grad = _raw_pe_grad(pre_table, ds, q_pe, B, H, n * M, keep)
+    dtp = None if pe_grad is not None else N.p(d_table)
     V = lambda t, off=0, kv=False: _view(t, n * (2 * hc if kv else hc), 2 * hc if kv else hc, 2 * c if kv else c, off)
 
     def fwd():
@@ -269,14 +361,16 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
     def bwd():
         N.check(N.LIB.affb200_fused_attn_bwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), V(dout), V(dq),
                                              V(dkv, 0, True), V(dkv, c, True), N.p(table), N.p(bk), N.p(bv), st_b,
-                                             N.p(q_pe), umax, N.p(lse), N.p(ds), N.p(pw), N.p(blank_part), N.p(d_table),
+                                             N.p(q_pe), umax, N.p(lse), N.p(ds), N.p(pw), N.p(blank_part), dtp,
                                              table.shape[0], B, H, n, M, c, float(scale), de, sp), "fused_attn_bwd")
+        if pe_grad is not None:
+            pe_grad()
 
     fwd._keep = keep
     return fwd, bwd
 
 
-def _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v):
+def _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v, pre_table=None):
     B, n, hc = q_lin.shape
     c = hc // H
     M = nbhd_idx.shape[2]
@@ -294,7 +388,9 @@ def _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_t
     blank_part = torch.empty((B, H, 2, c), dtype=torch.float32, device=dev)
     d_table = torch.empty((table.shape[0], H), dtype=torch.float32, device=dev)
     de, sp = N.dtype_enum(q_lin), N.stream_ptr(dev)
-    keep = (plan, q_pe, col, dupf, table, bk, bv, out, dq, dkv, dout, lse, ds, blank_part, d_table)
+    keep = [plan, q_pe, col, dupf, table, bk, bv, out, dq, dkv, dout, lse, ds, blank_part, d_table]
+    pe_grad = _raw_pe_grad(pre_table, ds, q_pe, B, H, n * M, keep)
+    dtp = None if pe_grad is not None else N.p(d_table)
     V = lambda t, off=0, kv=False: _view(t, n * (2 * hc if kv else hc), 2 * hc if kv else hc, 2 * c if kv else c, off)
 
     def fwd():
@@ -306,8 +402,10 @@ def _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_t
         N.check(N.LIB.affb200_fused_attn_img_bwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), V(dout),
                                                  V(dq), V(dkv, 0, True), V(dkv, c, True), N.p(table), N.p(bk), N.p(bv),
                                                  N.p(dupf), N.p(col), N.p(q_pe), N.p(lse), N.p(ds), N.p(blank_part),
-                                                 N.p(d_table), table.shape[0], B, H, n, M, c, float(scale), de, sp),
+                                                 dtp, table.shape[0], B, H, n, M, c, float(scale), de, sp),
                 "fused_attn_img_bwd")
+        if pe_grad is not None:
+            pe_grad()
 
     fwd._keep = keep
     return fwd, bwd

@@ -129,6 +129,81 @@ table_grad_u16_kernel(const T *__restrict__ d_vals, const uint16_t *__restrict__
     }
 }
 
+// The bias table of ClusterAttention is itself a Linear of a fixed feature table, table = feat·W^T + b
+// (reference aff_transformer.py:78,125: pos_embed(pre_table), 5 features per relative offset), and nothing but W and
+// b receive its gradient.  So instead of the [P][H] histogram d_table (one shared-memory atomic per slot and head),
+// the gradient goes straight to the 6 numbers per head
+//     G[h][f] = sum over slots of d_vals[slot][h] · feat8[pe[slot]][f]         f < 8
+// (feat8 rows padded to 8 floats, a column of ones gives db), accumulated in registers: dW = G[:, :F], db = G[:, F].
+// grid (chunks, head groups of HG); part[chunk][H][8]; a second kernel adds the chunks in a fixed order.
+template <typename T, int HG>
+__global__ void __launch_bounds__(256)
+pe_feat_grad_kernel(const T *__restrict__ d_vals, const uint16_t *__restrict__ pe, const float *__restrict__ feat8, int H,
+                    int64_t NM, int64_t total, float *__restrict__ part) {
+    __shared__ float red[8][HG][8];
+    const int h0 = blockIdx.y * HG, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float acc[HG][6];
+#pragma unroll
+    for (int hh = 0; hh < HG; ++hh)
+#pragma unroll
+        for (int f = 0; f < 6; ++f) acc[hh][f] = 0.f;
+    const int64_t groups = total / 8;   // NM % 8 == 0 (checked by the launcher)
+    const int64_t per = (groups + gridDim.x - 1) / gridDim.x;
+    const int64_t g0 = int64_t(blockIdx.x) * per, g1 = min(groups, g0 + per);
+    for (int64_t g = g0 + threadIdx.x; g < g1; g += 256) {
+        const int64_t t = g * 8;
+        const int64_t b = t / NM, r = t - b * NM;
+        const uint4 pv = __ldg(reinterpret_cast<const uint4 *>(pe + t));
+        uint4 dv[HG];
+#pragma unroll
+        for (int hh = 0; hh < HG; ++hh) {
+            dv[hh] = make_uint4(0u, 0u, 0u, 0u);
+            if (h0 + hh < H) dv[hh] = __ldg(reinterpret_cast<const uint4 *>(d_vals + (b * H + h0 + hh) * NM + r));
+        }
+        const uint16_t *p8 = reinterpret_cast<const uint16_t *>(&pv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float *fr = feat8 + size_t(p8[k] & 0x7fffu) * 8;
+            const float4 fa = __ldg(reinterpret_cast<const float4 *>(fr));
+            const float2 fb = __ldg(reinterpret_cast<const float2 *>(fr + 4));
+#pragma unroll
+            for (int hh = 0; hh < HG; ++hh) {
+                const float d = Elem<T>::to_acc(reinterpret_cast<const T *>(&dv[hh])[k]);
+                acc[hh][0] = fmaf(d, fa.x, acc[hh][0]); acc[hh][1] = fmaf(d, fa.y, acc[hh][1]);
+                acc[hh][2] = fmaf(d, fa.z, acc[hh][2]); acc[hh][3] = fmaf(d, fa.w, acc[hh][3]);
+                acc[hh][4] = fmaf(d, fb.x, acc[hh][4]); acc[hh][5] = fmaf(d, fb.y, acc[hh][5]);
+            }
+        }
+    }
+#pragma unroll
+    for (int hh = 0; hh < HG; ++hh)
+#pragma unroll
+        for (int f = 0; f < 6; ++f) {
+            float a = acc[hh][f];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            if (lane == 0) red[warp][hh][f] = a;
+        }
+    __syncthreads();
+    if (threadIdx.x < HG * 8) {
+        const int hh = threadIdx.x / 8, f = threadIdx.x % 8;
+        float a = 0.f;
+        if (f < 6)
+#pragma unroll
+            for (int w = 0; w < 8; ++w) a += red[w][hh][f];
+        if (h0 + hh < H) part[(int64_t(blockIdx.x) * H + h0 + hh) * 8 + f] = a;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+pe_feat_grad_finish_kernel(const float *__restrict__ part, int n_chunks, int H8, float *__restrict__ out) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e >= H8) return;
+    float a = 0.f;
+    for (int c = 0; c < n_chunks; ++c) a += part[int64_t(c) * H8 + e];
+    out[e] = a;
+}
+
 // out[t][:] = table[idx[t]][:] for rows of ROWB bytes (4, 8 or 16): one thread per gathered row.  The PointConv weights
 // of ClusterMerging are rows of 4 floats (reference aff_transformer.py:347-349); the stock indexing kernel spends a
 // whole CTA on each 16-byte row.
@@ -245,4 +320,43 @@ extern "C" int affb200_table_gather(const void *table, const int64_t *idx, void 
             table_gather_generic_kernel<uint64_t><<<g2, 256, 0, st>>>((const uint64_t *)table, idx, (uint64_t *)out, total, int(IC));
     }
     return check_launch("table_gather");
+}
+
+static int pe_feat_chunks(int64_t total) {
+    return int(std::max<int64_t>(1, std::min<int64_t>(int64_t(kNumSMs) * 4, total / (8 * 256 * 2))));
+}
+
+extern "C" int64_t affb200_pe_feat_grad_work_floats(int64_t B, int64_t H, int64_t NM) {
+    if (B <= 0 || H <= 0 || NM <= 0) return 0;
+    return int64_t(pe_feat_chunks(B * NM)) * H * 8;
+}
+
+extern "C" int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, const float *feat8, int64_t B, int64_t H,
+                                    int64_t NM, float *out, float *work, int dtype, void *stream) {
+    if (B <= 0 || H <= 0 || NM <= 0 || NM % 8 != 0 || H > 65535) {
+        set_error("pe_feat_grad: needs B, H > 0 and N*M a positive multiple of 8");
+        return AFFB200_E_ARG;
+    }
+    if (!d_vals || !q_pe || !feat8 || !out || !work || !aligned16(d_vals) || !aligned16(q_pe) || !aligned16(feat8)) {
+        set_error("pe_feat_grad: null or misaligned pointer");
+        return AFFB200_E_ARG;
+    }
+    auto st = (cudaStream_t)stream;
+    const int64_t total = B * NM;
+    const int chunks = pe_feat_chunks(total);
+    constexpr int HG = 4;
+    const dim3 grid{unsigned(chunks), unsigned((H + HG - 1) / HG)};
+    int e = dispatch_dtype(dtype, [&](auto tag) -> int {
+        using T = decltype(tag);
+        if constexpr (sizeof(T) != 2) {
+            set_error("pe_feat_grad: f16 / bf16 only");
+            return AFFB200_E_ARG;
+        } else {
+            pe_feat_grad_kernel<T, HG><<<grid, 256, 0, st>>>((const T *)d_vals, q_pe, feat8, int(H), NM, total, work);
+            return check_launch("pe_feat_grad");
+        }
+    });
+    if (e) return e;
+    pe_feat_grad_finish_kernel<<<unsigned((H * 8 + 255) / 256), 256, 0, st>>>(work, chunks, int(H * 8), out);
+    return check_launch("pe_feat_grad_finish");
 }

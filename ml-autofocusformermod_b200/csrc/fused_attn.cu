@@ -435,7 +435,7 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
     if (int e = fused_common_check("fused_attn_bwd", plan, q_pe, B, H, N, M, c, umax, dtype)) return e;
     if (!view_ok(q, c) || !view_ok(k, c) || !view_ok(v, c) || !view_ok(out, c) || !view_ok(dout, c) || !view_ok(dq, c) ||
         !view_ok(dk, c) || !view_ok(dv, c) || !table || !blank_k || !blank_v || !lse || !ds_work || !p_work ||
-        !blank_part || !d_table) {
+        !blank_part) {
         set_error("fused_attn_bwd: null or misaligned operand");
         return AFFB200_E_ARG;
     }
@@ -490,6 +490,7 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
             if (int e = launch_scatter_wsum_dense_strided<T>((const T *)p_work, (const T *)dout->p, plan, (T *)dv->p, B, H,
                                                              N, N, M, c, dos_, dvs, 1.f, st))
                 return e;
+            if (!d_table) return AFFB200_OK;   // the caller takes the bias gradient from ds_work (affb200_pe_feat_grad)
             return launch_table_grad_u16(ds_work, q_pe, B, H, N * M, P, d_table, dtype, st);
         } else {
             return AFFB200_E_ARG;

@@ -462,7 +462,7 @@ extern "C" int affb200_fused_attn_img_bwd(const affb200_view *q, const affb200_v
     if (int e = img_common_check("fused_attn_img_bwd", dupf, col, q_pe, B, H, N, M, c, dtype)) return e;
     if (!img_view_ok(q, N) || !img_view_ok(k, N) || !img_view_ok(v, N) || !img_view_ok(out, N) || !img_view_ok(dout, N) ||
         !img_view_ok(dq, N) || !img_view_ok(dk, N) || !img_view_ok(dv, N) || !table || !blank_k || !blank_v || !lse ||
-        !ds_work || !blank_part || !d_table) {
+        !ds_work || !blank_part) {
         set_error("fused_attn_img_bwd: null or misaligned operand");
         return AFFB200_E_ARG;
     }
@@ -496,6 +496,7 @@ extern "C" int affb200_fused_attn_img_bwd(const affb200_view *q, const affb200_v
 #undef AFF_IBC
 #undef AFF_IB
             if (int e = check_launch("fused_attn_img_bwd")) return e;
+            if (!d_table) return AFFB200_OK;   // the caller takes the bias gradient from ds_work (affb200_pe_feat_grad)
             return launch_table_grad_u16(ds_work, q_pe, B, H, N * M, P, d_table, dtype, st);
         } else {
             return AFFB200_E_ARG;

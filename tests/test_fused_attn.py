@@ -145,3 +145,59 @@ def test_fused_attention_with_repeated_unmasked_neighbours(family, monkeypatch):
     for nm, a, r in zip(["out", "d_q", "d_kv", "d_table", "d_blank_k", "d_blank_v"],
                         [out, q_lin.grad, kv_lin.grad, table.grad, bk.grad, bv.grad], ref):
         assert rel_err(a, r) < 1e-2, (nm, rel_err(a, r))
+
+
+@pytest.mark.parametrize("autocast", [False, True])
+@pytest.mark.parametrize("case,family", [(CASES[1], "tile"), (CASES[2], "img"), (CASES[2], "tile"), (CASES[0], "tile")])
+def test_fused_attention_pos_embed_form(case, family, autocast, monkeypatch):
+    """pos_embed=(pre_table, W, b) instead of a table (what ClusterAttention passes, reference aff_transformer.py:78,125):
+    same output and d_q / d_kv as with the table handed in, and dW / db equal to the chain rule through the [P, H] table
+    gradient of the table form (d_table^T · [feat | 1]), which the kernel never materialises."""
+    from affb200.point_utils import space_filling_cluster, build_nbhd
+    from affb200.fused import fused_cluster_attention
+    from affb200.aff_transformer import build_pe_lookup
+    monkeypatch.setenv("AFFB200_FUSED_IMG", "1" if family == "img" else "0")
+    h, w, n, B, H, c, m, nbhd_size, img = case
+    rpw = img // 4 - 1
+    pos = _positions(h, w, n, B, seed=n).cuda()
+    p_s, mean, _, _, _ = space_filling_cluster(pos, m, h, w)
+    nbhd, mask, pe_idx, _ = build_nbhd(p_s, mean, m, nbhd_size, rpw)
+    pre_table = build_pe_lookup(img)[2].cuda()
+    g = torch.Generator().manual_seed(11 + n)
+    hc = H * c
+    dt = torch.bfloat16
+    q0 = torch.randn(B, n, hc, generator=g).to(dt).cuda()
+    kv0 = torch.randn(B, n, 2 * hc, generator=g).to(dt).cuda()
+    W = (0.2 * torch.randn(H, 5, generator=g)).cuda().requires_grad_(True)
+    b = (0.2 * torch.randn(H, generator=g)).cuda().requires_grad_(True)
+    bk, bv = torch.randn(hc, generator=g).cuda(), torch.randn(hc, generator=g).cuda()
+    go = torch.randn(B, n, hc, generator=g).to(dt).cuda()
+    scale = c ** -0.5
+
+    def run(form):
+        q, kv = q0.clone().requires_grad_(True), kv0.clone().requires_grad_(True)
+        with torch.autocast("cuda", dtype=dt, enabled=autocast):
+            if form == "linear":
+                out = fused_cluster_attention(q, kv, H, scale, nbhd, pe_idx, mask, None, bk, bv,
+                                              pos_embed=(pre_table, W, b))
+                tab = None
+            else:
+                # the stock module's table (bf16 under autocast), as an fp32 leaf so that its gradient is not
+                # rounded to bf16 before the chain rule below
+                tab = torch.nn.functional.linear(pre_table, W, b).detach().float().requires_grad_(True)
+                out = fused_cluster_attention(q, kv, H, scale, nbhd, pe_idx, mask, tab, bk, bv)
+        out.backward(go)
+        if tab is not None:
+            return out.detach(), q.grad, kv.grad, None, None, tab.grad
+        res = (out.detach(), q.grad, kv.grad, W.grad.clone(), b.grad.clone(), None)
+        W.grad = b.grad = None
+        return res
+
+    lin, tab = run("linear"), run("table")
+    assert torch.equal(lin[0], tab[0]) and torch.equal(lin[1], tab[1]) and torch.equal(lin[2], tab[2])
+    # chain rule in fp64 from the table form's own table gradient
+    feat = (pre_table.to(dt) if autocast else pre_table).double()
+    dT = tab[5].double()
+    tol = 1e-4
+    assert rel_err(lin[3], dT.t() @ feat) < tol, rel_err(lin[3], dT.t() @ feat)
+    assert rel_err(lin[4], dT.sum(0)) < tol, rel_err(lin[4], dT.sum(0))
