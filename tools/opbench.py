@@ -63,6 +63,7 @@ def make_idx(B, Nq, Nk, M, mode, dev, m=8):
 
 _flush = None
 NO_DENSE = False
+REF = False
 WARM = 5
 
 
@@ -120,6 +121,16 @@ def bench_qkav(name, S, dtype, mode, iters):
                                                          N.p(o_attn), N.p(d_k), *A), "avb"),
                    s * (2 * B * H * Nn * M + 4 * B * H * Nn * c) + 8 * B * Nn * M),
     }
+    if REF and dtype in (torch.float32, torch.float16):
+        # the reference's own CUDA kernels (oracle/_ref) on the same tensors, called as clusten/clusten.py calls them
+        from oracle import ref_cuda as RC
+        nb = {k_: v_[1] for k_, v_ in ops.items()}
+        ops.update({
+            "ref_qk_fwd": (lambda: RC.forward("qk", q, k, idx), nb["qk_fwd"]),
+            "ref_qk_bwd": (lambda: RC.backward("qk", attn, q, k, idx), nb["qk_bwd"]),
+            "ref_av_fwd": (lambda: RC.forward("av", attn, k, idx), nb["av_fwd"]),
+            "ref_av_bwd": (lambda: RC.backward("av", q, attn, k, idx), nb["av_bwd"]),
+        })
     return run_ops(name, ops, dtype, mode, iters, S)
 
 
@@ -143,6 +154,13 @@ def bench_wf(name, S, dtype, mode, iters):
                                                          N.p(d_w), N.p(d_f), *A), "wfb"),
                    s * (B * Nq * IC * C + 2 * B * Nq * M * IC + 2 * B * Nk * C) + 8 * B * Nq * M),
     }
+    if REF and dtype in (torch.float32, torch.float16):
+        from oracle import ref_cuda as RC
+        nb = {k_: v_[1] for k_, v_ in ops.items()}
+        ops.update({
+            "ref_wf_fwd": (lambda: RC.forward("wf", w, f, idx), nb["wf_fwd"]),
+            "ref_wf_bwd": (lambda: RC.backward("wf", go, w, f, idx), nb["wf_bwd"]),
+        })
     return run_ops(name, ops, dtype, mode, iters, S)
 
 
@@ -170,9 +188,12 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--warm", type=int, default=5)
     ap.add_argument("--no-dense", action="store_true", help="force the generic (row-gather) kernels")
+    ap.add_argument("--ref", action="store_true",
+                    help="also time the reference's own CUDA kernels from oracle/_ref (f32/f16 only)")
     a = ap.parse_args()
-    global NO_DENSE, WARM
+    global NO_DENSE, WARM, REF
     NO_DENSE = a.no_dense
+    REF = a.ref
     WARM = a.warm
     rows = []
     for dt in a.dtype.split(","):
