@@ -72,6 +72,92 @@ gather_dot_kernel(const T *__restrict__ x, const T *__restrict__ y, const int64_
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// gather-dot, lane-group form (c a compile-time multiple of the 16-byte vector width W, LPR = c/W <= 16 lanes).
+// The kernel above gives a thread a whole neighbour row: one warp load then touches 32 different 128-byte lines and
+// the L1 tag stage (one line per clock) is the bound (fp32 c=32: 8 loads x 32 lines per 32 outputs — measured 2.3 ms
+// at the AFF-Tiny stage-1 shape, the same as the reference kernel).  Here LPR lanes share a row, so a warp load
+// covers 32/LPR whole rows (4 lines for fp32 c=32); a group walks LPR consecutive (token, slot) pairs, keeps the LPR
+// partial dot products in registers and reduces them with a transposing butterfly (LPR-1 shuffles for LPR sums,
+// lane l ends up with pair l), so the 32 results of a warp leave as one coalesced store.
+// SAME: M % LPR == 0, all pairs of a group belong to one token -> its x chunk is read once per head.
+// ---------------------------------------------------------------------------------------------------------
+template <typename Acc, int N>
+__device__ __forceinline__ Acc transpose_reduce(Acc (&v)[N], int l) {
+#pragma unroll
+    for (int s = N / 2; s >= 1; s >>= 1) {
+        const bool up = (l & s) != 0;
+#pragma unroll
+        for (int i = 0; i < s; ++i) {
+            const Acc keep = up ? v[i + s] : v[i];
+            const Acc send = up ? v[i] : v[i + s];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+        }
+    }
+    return v[0];
+}
+
+template <typename T, int CT, bool SAME>
+__global__ void __launch_bounds__(kThreads)
+gather_dot_group_kernel(const T *__restrict__ x, const T *__restrict__ y, const int64_t *__restrict__ idx,
+                        T *__restrict__ out, int H, int Nq, int Nk, int M, int TI) {
+    using Acc = typename Elem<T>::Acc;
+    constexpr int W = Elem<T>::VEC;
+    constexpr int LPR = CT / W;
+    static_assert(LPR >= 1 && LPR <= 16 && (LPR & (LPR - 1)) == 0 && CT % W == 0, "lane-group shape");
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Acc *x_s = reinterpret_cast<Acc *>(smem_raw);  // [H][TI][CT]
+
+    const int b = blockIdx.y;
+    const int i0 = blockIdx.x * TI;
+    const int ti = min(TI, Nq - i0);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int l = lane % LPR, g0 = lane - l;  // lane in group, first lane of the group
+
+    for (int h = 0; h < H; ++h) {
+        const T *xg = x + ((int64_t(b) * H + h) * Nq + i0) * CT;
+        Acc *xs = x_s + int64_t(h) * TI * CT;
+        for (int t = tid; t < ti * CT; t += kThreads) xs[t] = Elem<T>::to_acc(xg[t]);
+    }
+    __syncthreads();
+
+    const int P = ti * M;
+    const int64_t *idx_g = idx + (int64_t(b) * Nq + i0) * M;
+    for (int base = warp * 32; base < P; base += (kThreads / 32) * 32) {
+        const int p = base + lane;
+        const int rl = p < P ? int(idx_g[p]) : 0;
+        const int p0 = base + g0;                  // first pair of this group
+        const int il0 = min(p0, P - 1) / M;
+        for (int h = 0; h < H; ++h) {
+            const T *yz = y + (int64_t(b) * H + h) * Nk * CT + l * W;
+            const Acc *xz = x_s + int64_t(h) * TI * CT + l * W;
+            Acc xv[W];
+            if constexpr (SAME) {
+#pragma unroll
+                for (int t = 0; t < W; ++t) xv[t] = xz[il0 * CT + t];
+            }
+            Acc part[LPR];
+#pragma unroll
+            for (int r = 0; r < LPR; ++r) {
+                const int row = __shfl_sync(0xffffffffu, rl, g0 + r);
+                Acc yv[W];
+                load_vec<T, W>(yz + int64_t(row) * CT, yv);
+                if constexpr (!SAME) {
+                    const int il = min(p0 + r, P - 1) / M;
+#pragma unroll
+                    for (int t = 0; t < W; ++t) xv[t] = xz[il * CT + t];
+                }
+                Acc a = Acc(0);
+#pragma unroll
+                for (int t = 0; t < W; ++t) a += xv[t] * yv[t];
+                part[r] = a;
+            }
+            const Acc sum = transpose_reduce<Acc, LPR>(part, l);
+            if (p < P) out[((int64_t(b) * H + h) * Nq + i0) * M + p] = Elem<T>::from_acc(sum);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // gather-wsum.  grid (ceil(Nq/TI), B); LPR = c/W lanes cooperate on one output row, each owning W channels.
 // nbhd_idx of the tile is narrowed to int32 in shared memory once and reused by all heads.
 // WW = vector width of the weight loads (W when M % W == 0 and rows are 16-byte aligned, else 1).
@@ -353,6 +439,25 @@ static int pick_tile(int64_t per_token_bytes, int64_t Nq, int budget = 40 * 1024
     return int(ti);
 }
 
+template <typename T, int CT>
+static int launch_gather_dot_group(const T *x, const T *y, const int64_t *idx, T *out, int64_t B, int64_t H,
+                                   int64_t Nq, int64_t Nk, int64_t M, int TI, size_t smem, dim3 grid,
+                                   cudaStream_t st) {
+    constexpr int LPR = CT / Elem<T>::VEC;
+    if constexpr (LPR > 16) {
+        return 1;
+    } else {
+        auto go = [&](auto kern) {
+            if (smem > 48 * 1024)
+                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+            kern<<<grid, kThreads, smem, st>>>(x, y, idx, out, int(H), int(Nq), int(Nk), int(M), TI);
+        };
+        if (M % LPR == 0) go(gather_dot_group_kernel<T, CT, true>);
+        else go(gather_dot_group_kernel<T, CT, false>);
+        return check_launch("gather_dot_group");
+    }
+}
+
 template <typename T>
 int launch_gather_dot(const T *x, const T *y, const int64_t *idx, T *out, int64_t B, int64_t H, int64_t Nq,
                       int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
@@ -365,6 +470,13 @@ int launch_gather_dot(const T *x, const T *y, const int64_t *idx, T *out, int64_
     const size_t smem = size_t(H) * TI * c * sizeof(Acc);
     dim3 grid(unsigned(ceil_div64(Nq, TI)), unsigned(B));
     const bool vec = (c % W == 0) && aligned16(y);
+    if (vec) {
+        int e = 1;  // 1: shape not covered by the lane-group kernel
+        if (c == 32) e = launch_gather_dot_group<T, 32>(x, y, idx, out, B, H, Nq, Nk, M, TI, smem, grid, st);
+        else if (c == 16) e = launch_gather_dot_group<T, 16>(x, y, idx, out, B, H, Nq, Nk, M, TI, smem, grid, st);
+        else if (c == 64) e = launch_gather_dot_group<T, 64>(x, y, idx, out, B, H, Nq, Nk, M, TI, smem, grid, st);
+        if (e <= 0) return e;
+    }
 #define AFF_GD(WW_, CT_)                                                                                       \
     do {                                                                                                       \
         auto kern = gather_dot_kernel<T, WW_, CT_>;                                                            \
