@@ -126,8 +126,13 @@ def cuda_ordering_rules():
         idx = topk_unsorted_cuda_order(self.detach().float(), k)
         return self.gather(1, idx), idx
 
-    torch.Tensor.sort, torch.Tensor.topk = sort, topk
+    o_fsort = torch.sort
+
+    def fsort(t, *a, **kw):     # torch.sort(x, dim=..., descending=...) as mixres_neighbour.py:735 calls it
+        return sort(t, *a, **kw)
+
+    torch.Tensor.sort, torch.Tensor.topk, torch.sort = sort, topk, fsort
     try:
         yield
     finally:
-        torch.Tensor.sort, torch.Tensor.topk = o_sort, o_topk
+        torch.Tensor.sort, torch.Tensor.topk, torch.sort = o_sort, o_topk, o_fsort
