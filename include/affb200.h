@@ -176,6 +176,21 @@ size_t affb200_sfc_work_bytes(int64_t B, int64_t N);
 int affb200_sfc_cluster(const float *pos, int64_t B, int64_t N, int64_t m, int64_t h, int64_t w,
                         int64_t *ranking, float *pos_sorted, float *mean, void *work, void *stream);
 
+/* Curve keys of calculate_peano_order / calculate_hilbert_order (reference models/point_utils.py:211-282, :285-349):
+ * key[b][i] = the fp32 `final_order` of token i; the curve order is the stable ascending argsort of the key
+ * (affb200_argsort_f32).  curve: 1 = Peano, 2 = Hilbert.  Replaces the key computation of
+ * space_filling_cluster(..., sf_type='peano'|'hilbert') (:108-122 on the anchor grid, :163-166 on the tokens). */
+int affb200_curve_key(const float *pos, int64_t B, int64_t N, int64_t h, int64_t w, int curve, float *key,
+                      void *stream);
+
+/* affb200_sfc_cluster with the anchor order supplied as tables (Peano / Hilbert anchors, point_utils.py:104-122,
+ * 135-159): grid_rank [nump] int32 = rank of anchor cell x + y*npw along the curve, prev / next [nump][2] fp32 =
+ * centres of the previous / next anchor per rank, (plw, plh) = anchor patch size.  Same outputs and work size as
+ * affb200_sfc_cluster. */
+int affb200_sfc_cluster_tables(const float *pos, int64_t B, int64_t N, int64_t m, int64_t npw, int64_t nump,
+                               float plw, float plh, const int32_t *grid_rank, const float *prev, const float *next,
+                               int64_t *ranking, float *pos_sorted, float *mean, void *work, void *stream);
+
 /* Stable argsort of fp32 rows: order[b][r] = index of the r-th element; replaces torch.sort(...)[1] on CUDA
  * (reference models/mixres_neighbour.py:735, models/point_utils.py:159). */
 size_t affb200_argsort_work_bytes(int64_t B, int64_t N);

@@ -2,7 +2,8 @@
 code inlined in models/aff_transformer.py / models/mixres_neighbour.py).  Every function enqueues hand-written
 sm_100a kernels of libaffb200.so on the current CUDA stream (C ABI: include/affb200.h); there is no CPU path.
 
-  space_filling_cluster(pos, m, h, w, no_reorder=False)      reference point_utils.py:61-208 (default variant)
+  space_filling_cluster(pos, m, h, w, no_reorder, sf_type, use_anchor)   reference point_utils.py:61-208
+  calculate_peano_order / calculate_hilbert_order(h, w, pos)               reference point_utils.py:211-349
   knn_keops(query, database, k, return_dist=False)           reference point_utils.py:27-58
   argsort_stable(x, descending=False)                        torch.sort(...)[1] on CUDA (mixres_neighbour.py:735)
   build_nbhd(pos, cluster_mean_pos, m, nbhd_size, rel_pos_width, clamp=False)
@@ -42,11 +43,11 @@ def space_filling_cluster(pos, m, h, w, no_reorder=False, sf_type='', use_anchor
 
     use_anchor=True (what every model calls): anchor grid + distance-ratio key, one fused kernel chain
     (`affb200_sfc_cluster`).  use_anchor=False: the tokens' own row-scan order with alternating direction
-    (point_utils.py:166-179), ranked by the same stable rank sort (`affb200_argsort_f32`).  The Peano / Hilbert curve
-    orders (`sf_type`, point_utils.py:211-349) are not built: no model reaches them."""
-    if sf_type != '':
-        raise NotImplementedError("sf_type=%r: only the default scan order is implemented (no model in the reference "
-                                  "passes sf_type; aff_transformer.py:463,470; mixres_neighbour.py:512)" % (sf_type,))
+    (point_utils.py:166-179), ranked by the same stable rank sort (`affb200_argsort_f32`).  sf_type 'peano' /
+    'hilbert' (point_utils.py:98-122,162-165): curve keys from `affb200_curve_key`; with anchors the anchor grid is
+    ordered along the curve and the token kernels take the order as tables (`affb200_sfc_cluster_tables`).  Any other
+    sf_type means the default scan, as in the reference."""
+    curve = {'peano': 1, 'hilbert': 2}.get(sf_type, 0)
     pos = _f32_pos(pos)
     b, n, d = pos.shape
     dev = pos.device
@@ -57,13 +58,23 @@ def space_filling_cluster(pos, m, h, w, no_reorder=False, sf_type='', use_anchor
             pos_sorted = torch.empty_like(pos)
             mean = torch.empty((b, k, 2), dtype=torch.float32, device=dev)
             work = _work(N.LIB.affb200_sfc_work_bytes(b, n), dev)
-            N.check(N.LIB.affb200_sfc_cluster(N.p(pos), b, n, m, h, w, N.p(ranking), N.p(pos_sorted), N.p(mean),
-                                              N.p(work), N.stream_ptr(dev)), "space_filling_cluster")
+            if curve:
+                npw, nump, plw, plh, grid_rank, prev, nxt = _curve_anchor_tables(curve, k, h, w, dev)
+                N.check(N.LIB.affb200_sfc_cluster_tables(N.p(pos), b, n, m, npw, nump, plw, plh, N.p(grid_rank),
+                                                         N.p(prev), N.p(nxt), N.p(ranking), N.p(pos_sorted),
+                                                         N.p(mean), N.p(work), N.stream_ptr(dev)),
+                        "space_filling_cluster")
+            else:
+                N.check(N.LIB.affb200_sfc_cluster(N.p(pos), b, n, m, h, w, N.p(ranking), N.p(pos_sorted), N.p(mean),
+                                                  N.p(work), N.stream_ptr(dev)), "space_filling_cluster")
         else:
-            x, y = pos[..., 0].long(), pos[..., 1].long()
-            key = torch.where(y % 2 == 1, (w - 1 - x) + y * w, x + y * w)
-            if h * w >= 2 ** 24:
-                raise RuntimeError("space_filling_cluster(use_anchor=False): canvas too large for an exact fp32 key")
+            if curve:
+                key = curve_key(pos, h, w, curve)
+            else:
+                x, y = pos[..., 0].long(), pos[..., 1].long()
+                key = torch.where(y % 2 == 1, (w - 1 - x) + y * w, x + y * w)
+                if h * w >= 2 ** 24:
+                    raise RuntimeError("space_filling_cluster(use_anchor=False): canvas too large for an exact fp32 key")
             ranking = argsort_stable(key.to(torch.float32))
             pos_sorted = pos.gather(1, ranking.unsqueeze(2).expand(-1, -1, d))
             if k * m == n:
@@ -88,6 +99,64 @@ def space_filling_cluster(pos, m, h, w, no_reorder=False, sf_type='', use_anchor
             member_idx[n:] = 0
         member_idx = member_idx.reshape(1, k, m).expand(b, -1, -1)
     return pos_sorted, mean, member_idx, cluster_mask, ranking.unsqueeze(2)
+
+
+def curve_key(pos, h, w, curve):
+    """fp32 `final_order` of calculate_peano_order (curve=1) / calculate_hilbert_order (curve=2) per token
+    (reference point_utils.py:211-282, :285-349)."""
+    pos = _f32_pos(pos)
+    b, n, _ = pos.shape
+    dev = pos.device
+    with torch.cuda.device(dev):
+        key = torch.empty((b, n), dtype=torch.float32, device=dev)
+        N.check(N.LIB.affb200_curve_key(N.p(pos), b, n, h, w, curve, N.p(key), N.stream_ptr(dev)), "curve_key")
+    return key
+
+
+def calculate_peano_order(h, w, pos):
+    """(rank of every token b x n, tokens in curve order b x n), reference point_utils.py:211-282."""
+    return _curve_order(h, w, pos, 1)
+
+
+def calculate_hilbert_order(h, w, pos):
+    """reference point_utils.py:285-349."""
+    return _curve_order(h, w, pos, 2)
+
+
+def _curve_order(h, w, pos, curve):
+    order_index = argsort_stable(curve_key(pos, h, w, curve))
+    src = torch.arange(order_index.shape[1], device=order_index.device).unsqueeze(0).expand_as(order_index)
+    return torch.zeros_like(order_index).scatter_(1, order_index, src), order_index
+
+
+def _curve_anchor_tables(curve, k, h, w, dev):
+    """Anchor grid of a Peano / Hilbert clustering (reference point_utils.py:93-146): grid size snapped to a power of
+    the curve's base, anchors ordered along the curve, centres of the previous / next anchor per rank.  The tables are a
+    few hundred entries; they are formed with the reference's own fp32 tensor expressions on the device."""
+    base = 3 if curve == 1 else 2
+    patch_len = (h * w / k) ** 0.5
+    nph = int(round(h / patch_len))
+    nph = max(base, int(base ** round(math.log(nph, base))))
+    plh = h / nph
+    npw = int(round(w / h * base) * (nph / base))
+    plw = w / npw
+    ys, xs = torch.meshgrid(torch.arange(nph, device=dev), torch.arange(npw, device=dev), indexing="ij")
+    grid_pos = torch.stack([xs, ys], dim=2).reshape(-1, 2)
+    grid_rank, order_idx = _curve_order(nph, npw, grid_pos.unsqueeze(0).float(), curve)
+    ordered_grid = grid_pos[order_idx[0]]
+    patch_len_hw = torch.tensor([plw, plh], dtype=torch.float32, device=dev)
+    init = ordered_grid * patch_len_hw + patch_len_hw / 2 - 0.5
+    nump = init.shape[0]
+    if nump < 3:
+        raise RuntimeError("space_filling_cluster: anchor grid too small")
+    prev = torch.zeros_like(init)
+    prev[1:] = init[:nump - 1]
+    prev[0] = prev[1] - (prev[2] - prev[1])
+    nxt = torch.zeros_like(init)
+    nxt[:nump - 1] = init[1:]
+    nxt[-1] = nxt[-2] + (nxt[-2] - nxt[-3])
+    return npw, nump, float(patch_len_hw[0].item()), float(patch_len_hw[1].item()), \
+        grid_rank[0].to(torch.int32).contiguous(), prev.contiguous(), nxt.contiguous()
 
 
 def knn_keops(query, database, k, return_dist=False):

@@ -101,6 +101,107 @@ sfc_key_kernel(const int32_t *__restrict__ rank, const float *__restrict__ ratio
     comp[t] = (uint64_t(f32_sortable(key)) << 32) | uint32_t(t % N);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Peano / Hilbert curve keys (point_utils.py:211-282 / :285-349): per level the cell of the token inside the
+// current square (floor(rem / cur_h), then rem %= cur_h, fp32 like the reference's tensor ops), mapped through the
+// curve's digit table under the orientation accumulated from the coarser levels; the key is the fp32 sum
+// orders[L-1] + sum_i orders[i] * base^(L-i-1) in the reference's order of additions.
+// Peano (:236-268): digit table [[2,3,8],[1,4,7],[0,5,6]] indexed x + 3y; a level flips x of the finer levels
+// when its y is 1 and flips y when its x is 1 (x parity for the widened first level, :229-233).
+// Hilbert (:303-340): rotation state r; digit = rot_res[r mod 4][x + 2y]; r += rotate_dict[r mod 3][x + 2y].
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kCurveMaxLevels = 16;
+struct CurveGeom {
+    int type;      // 1 peano, 2 hilbert
+    int levels;
+    int first_w;   // widened first level (peano, h != w), 0 when absent
+    float cur_h[kCurveMaxLevels];
+    float weight[kCurveMaxLevels];   // base^(L-i-1) as fp32
+};
+
+__device__ __forceinline__ int pymod(int a, int n) { const int r = a % n; return r < 0 ? r + n : r; }
+
+__global__ void __launch_bounds__(kIT)
+curve_key_kernel(const float *__restrict__ pos, int64_t total, CurveGeom g, float *__restrict__ key) {
+    const int64_t t = int64_t(blockIdx.x) * kIT + threadIdx.x;
+    if (t >= total) return;
+    const float2 p = __ldg(reinterpret_cast<const float2 *>(pos) + t);
+    float rx = p.x, ry = p.y;
+    float ord[kCurveMaxLevels];
+    int invx = 1, invy = 1, rot = 0;
+    const int pe_tab[9] = {2, 3, 8, 1, 4, 7, 0, 5, 6};
+    const int hil_rot[12] = {-1, 1, 0, 0, 0, -1, 0, 1, 1, 0, -1, 0};
+    const int hil_res[16] = {0, 3, 1, 2, 2, 3, 1, 0, 2, 1, 3, 0, 0, 1, 3, 2};
+#pragma unroll
+    for (int i = 0; i < kCurveMaxLevels; ++i) {
+        if (i < g.levels) {
+            const float ch = g.cur_h[i];
+            const int lx = int(floorf(__fdiv_rn(rx, ch))), ly = int(floorf(__fdiv_rn(ry, ch)));
+            rx = fmodf(rx, ch);
+            ry = fmodf(ry, ch);
+            if (g.type == 1) {
+                const int ix = invx > 0 ? lx : 2 - lx, iy = invy > 0 ? ly : 2 - ly;
+                int o;
+                if (i == 0 && g.first_w) {
+                    const int c6 = ix % 6;
+                    const int base = c6 < 3 ? pe_tab[min(max(iy, 0), 2) * 3 + c6] : pe_tab[(2 - min(max(iy, 0), 2)) * 3 + c6 - 3];
+                    o = base + (ix / 3) * 9;
+                    invy *= (lx & 1) ? -1 : 1;
+                } else {
+                    o = pe_tab[min(max(iy, 0), 2) * 3 + min(max(ix, 0), 2)];
+                    invy *= lx == 1 ? -1 : 1;
+                }
+                invx *= ly == 1 ? -1 : 1;
+                ord[i] = float(o);
+            } else {
+                const int cell = min(max(lx + ly * 2, 0), 3);
+                ord[i] = float(hil_res[pymod(rot, 4) * 4 + cell]);
+                rot += hil_rot[pymod(rot, 3) * 4 + cell];
+            }
+        } else {
+            ord[i] = 0.f;
+        }
+    }
+    float k = 0.f;
+#pragma unroll
+    for (int i = 0; i < kCurveMaxLevels; ++i)
+        if (i == g.levels - 1) k = ord[i];
+#pragma unroll
+    for (int i = 0; i < kCurveMaxLevels; ++i)
+        if (i < g.levels - 1) k = __fadd_rn(k, __fmul_rn(ord[i], g.weight[i]));
+    key[t] = k;
+}
+
+// Clustering key with the anchor order given as tables (Peano / Hilbert anchors, point_utils.py:104-122,135-156):
+// grid_rank[cell] = position of the anchor cell in the curve, prev/next[rank] = centres of the neighbouring anchors.
+__global__ void __launch_bounds__(kIT)
+sfc_ratio_table_kernel(const float *__restrict__ pos, int64_t total, int npw, int nump, float plw, float plh,
+                       const int32_t *__restrict__ grid_rank, const float2 *__restrict__ prev,
+                       const float2 *__restrict__ next, int32_t *__restrict__ rank, float *__restrict__ ratio,
+                       uint32_t *__restrict__ max_bits) {
+    const int64_t t = int64_t(blockIdx.x) * kIT + threadIdx.x;
+    float r = 0.f;
+    if (t < total) {
+        const float2 p = __ldg(reinterpret_cast<const float2 *>(pos) + t);
+        const float cx = floorf(__fdiv_rn(p.x, plw)), cy = floorf(__fdiv_rn(p.y, plh));
+        long long cell = (long long)__fadd_rn(cx, __fmul_rn(cy, float(npw)));
+        cell = cell < 0 ? 0 : (cell >= nump ? nump - 1 : cell);
+        const int rk = __ldg(grid_rank + cell);
+        const float2 pv = __ldg(prev + rk), nx = __ldg(next + rk);
+        const float dxp = __fsub_rn(p.x, pv.x), dyp = __fsub_rn(p.y, pv.y);
+        const float dxn = __fsub_rn(p.x, nx.x), dyn = __fsub_rn(p.y, nx.y);
+        const float dp = __fadd_rn(__fmul_rn(dxp, dxp), __fmul_rn(dyp, dyp));
+        const float dn = __fadd_rn(__fmul_rn(dxn, dxn), __fmul_rn(dyn, dyn));
+        r = __fdiv_rn(dp, __fadd_rn(dn, 1e-5f));
+        rank[t] = rk;
+        ratio[t] = r;
+    }
+    uint32_t m = __float_as_uint(r);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(max_bits, m);
+}
+
 __global__ void __launch_bounds__(kIT)
 f32_key_kernel(const float *__restrict__ x, int64_t total, int N, int descending, uint64_t *__restrict__ comp) {
     const int64_t t = int64_t(blockIdx.x) * kIT + threadIdx.x;
@@ -506,6 +607,81 @@ extern "C" int affb200_sfc_cluster(const float *pos, int64_t B, int64_t N, int64
     int32_t *prank = reinterpret_cast<int32_t *>(wp);
     if (cudaMemsetAsync(max_bits, 0, 16, st) != cudaSuccess) return check_launch("sfc memset", 0);
     sfc_ratio_kernel<<<blocks_for(B * N), kIT, 0, st>>>(pos, B * N, g, rank, ratio, max_bits);
+    sfc_key_kernel<<<blocks_for(B * N), kIT, 0, st>>>(rank, ratio, max_bits, B * N, int(N), comp);
+    if (int e = check_launch("sfc_key", 2)) return e;
+    if (int e = rank_sort(comp, prank, B, N, ranking, pos, pos_sorted, st)) return e;
+    cluster_mean_kernel<<<blocks_for(B * K), kIT, 0, st>>>(pos_sorted, B * K, int(N), int(K), int(m), mean);
+    return check_launch("cluster_mean");
+}
+
+// Python's math.log(x, base) is log(x)/log(base) in doubles, round() is half-to-even like nearbyint
+static int curve_geom(int64_t h, int64_t w, int curve, CurveGeom &g) {
+    const double base = curve == 1 ? 3.0 : 2.0;
+    g.type = curve;
+    g.levels = int(std::ceil(std::log(double(h)) / std::log(base)));
+    if (g.levels < 1) { set_error("curve_key: h too short"); return AFFB200_E_ARG; }
+    if (g.levels > kCurveMaxLevels) { set_error("curve_key: more than %d levels", kCurveMaxLevels); return AFFB200_E_ARG; }
+    g.first_w = 0;
+    if (h != w) {
+        const int fw = int(std::nearbyint(base * (double(w) / double(h))));
+        if (fw != int(base)) g.first_w = fw;
+    }
+    if (curve == 2 && g.first_w) {
+        set_error("curve_key: the Hilbert order needs round(2*w/h) == 2 (the reference indexes a 4-entry table with "
+                  "x + y*first_w, point_utils.py:322-338)");
+        return AFFB200_E_ARG;
+    }
+    if (curve == 1 && g.first_w < 0) { set_error("curve_key: bad aspect ratio"); return AFFB200_E_ARG; }
+    double last = double(h);
+    for (int i = 0; i < kCurveMaxLevels; ++i) { g.cur_h[i] = 1.f; g.weight[i] = 0.f; }
+    for (int i = 0; i < g.levels; ++i) {
+        last = last / base;
+        g.cur_h[i] = float(last);
+        g.weight[i] = float(std::pow(base * base, double(g.levels - i - 1)));
+    }
+    return AFFB200_OK;
+}
+
+extern "C" int affb200_curve_key(const float *pos, int64_t B, int64_t N, int64_t h, int64_t w, int curve, float *key,
+                                 void *stream) {
+    if (!idx_dims_ok("curve_key", B, N)) return AFFB200_E_ARG;
+    if (curve != 1 && curve != 2) { set_error("curve_key: curve must be 1 (peano) or 2 (hilbert)"); return AFFB200_E_ARG; }
+    if (h <= 0 || w <= 0) { set_error("curve_key: h, w must be positive"); return AFFB200_E_ARG; }
+    if (B * N == 0) return AFFB200_OK;
+    if (!pos || !key) { set_error("curve_key: null pointer"); return AFFB200_E_ARG; }
+    CurveGeom g;
+    if (int e = curve_geom(h, w, curve, g)) return e;
+    curve_key_kernel<<<blocks_for(B * N), kIT, 0, (cudaStream_t)stream>>>(pos, B * N, g, key);
+    return check_launch("curve_key");
+}
+
+extern "C" int affb200_sfc_cluster_tables(const float *pos, int64_t B, int64_t N, int64_t m, int64_t npw, int64_t nump,
+                                          float plw, float plh, const int32_t *grid_rank, const float *prev,
+                                          const float *next, int64_t *ranking, float *pos_sorted, float *mean,
+                                          void *work, void *stream) {
+    if (!idx_dims_ok("sfc_cluster_tables", B, N)) return AFFB200_E_ARG;
+    if (m <= 0 || npw <= 0 || nump <= 0 || nump >= (int64_t(1) << 31)) {
+        set_error("sfc_cluster_tables: m, npw, nump must be positive");
+        return AFFB200_E_ARG;
+    }
+    if (B * N == 0) return AFFB200_OK;
+    if (!pos || !ranking || !pos_sorted || !mean || !work || !grid_rank || !prev || !next) {
+        set_error("sfc_cluster_tables: null pointer");
+        return AFFB200_E_ARG;
+    }
+    const int64_t K = (N + m - 1) / m;
+    auto st = (cudaStream_t)stream;
+    char *wp = reinterpret_cast<char *>(work);
+    int32_t *rank = reinterpret_cast<int32_t *>(wp); wp += al16(size_t(B * N) * 4);
+    float *ratio = reinterpret_cast<float *>(wp);    wp += al16(size_t(B * N) * 4);
+    uint32_t *max_bits = reinterpret_cast<uint32_t *>(wp); wp += 16;
+    uint64_t *comp = reinterpret_cast<uint64_t *>(wp); wp += al16(size_t(B * N) * 8);
+    int32_t *prank = reinterpret_cast<int32_t *>(wp);
+    if (cudaMemsetAsync(max_bits, 0, 16, st) != cudaSuccess) return check_launch("sfc memset", 0);
+    sfc_ratio_table_kernel<<<blocks_for(B * N), kIT, 0, st>>>(pos, B * N, int(npw), int(nump), plw, plh, grid_rank,
+                                                              reinterpret_cast<const float2 *>(prev),
+                                                              reinterpret_cast<const float2 *>(next), rank, ratio,
+                                                              max_bits);
     sfc_key_kernel<<<blocks_for(B * N), kIT, 0, st>>>(rank, ratio, max_bits, B * N, int(N), comp);
     if (int e = check_launch("sfc_key", 2)) return e;
     if (int e = rank_sort(comp, prank, B, N, ranking, pos, pos_sorted, st)) return e;

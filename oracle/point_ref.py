@@ -140,6 +140,117 @@ def sfc_variant_ref(pos, m, h, w, no_reorder=False, use_anchor=True):
     return pos_s, mean, member, mask, ranking.unsqueeze(2)
 
 
+# ---- Peano / Hilbert curve orders (reference models/point_utils.py:211-349) --------------------------------------
+_PEANO = torch.tensor([2, 3, 8, 1, 4, 7, 0, 5, 6])                    # digit of cell x + 3y (:224)
+_HIL_ROT = torch.tensor([[-1, 1, 0, 0], [0, -1, 0, 1], [1, 0, -1, 0]])  # rotation step by state%3, cell x + 2y (:303)
+_HIL_RES = torch.tensor([[0, 3, 1, 2], [2, 3, 1, 0], [2, 1, 3, 0], [0, 1, 3, 2]])  # digit by state%4, cell (:308)
+
+
+def curve_key_ref(pos, h, w, curve):
+    """fp32 `final_order` of calculate_peano_order (curve='peano', :211-277) / calculate_hilbert_order ('hilbert',
+    :285-344), restated level by level with the orientation carried as running state instead of the reference's
+    re-multiplied products: per level cell = floor(rem / cur_h), rem %= cur_h (fp32 tensor / Python scalar, :237-242);
+    Peano: a level whose y is 1 mirrors x of all finer levels, whose x is 1 (x odd on a widened first level) mirrors
+    y (:225,233,247-254); Hilbert: digit = RES[state%4][cell], state += ROT[state%3][cell] (:318-338)."""
+    base = 3 if curve == 'peano' else 2
+    p = pos.detach().to(F32)
+    levels = math.ceil(math.log(h, base))
+    assert levels >= 1, "h too short"
+    first_w = None
+    if h != w:
+        first_w = round(base * (w / h))
+        if first_w == base:
+            first_w = None
+    if curve == 'hilbert' and first_w is not None:
+        raise IndexError("hilbert with round(2*w/h) != 2 indexes a 4-entry table out of range in the reference")
+    rem, last = p, h
+    cells = []
+    for _ in range(levels):
+        cur = last / base
+        cells.append((rem / cur).floor().long())
+        rem = rem % cur
+        last = cur
+    orders = []
+    if curve == 'peano':
+        sx = torch.ones(p.shape[:2], dtype=torch.long)
+        sy = torch.ones(p.shape[:2], dtype=torch.long)
+        for i, c in enumerate(cells):
+            x = torch.where(sx > 0, c[..., 0], 2 - c[..., 0])
+            y = torch.where(sy > 0, c[..., 1], 2 - c[..., 1])
+            if i == 0 and first_w is not None:
+                c6 = x % 6
+                d = torch.where(c6 < 3, _PEANO[(y * 3 + c6.clamp(max=2))], _PEANO[((2 - y) * 3 + (c6 - 3).clamp(min=0))])
+                orders.append((d + (x // 3) * 9).to(F32))
+                sy = sy * torch.where(c[..., 0] % 2 == 1, -1, 1)
+            else:
+                orders.append(_PEANO[y * 3 + x].to(F32))
+                sy = sy * torch.where(c[..., 0] == 1, -1, 1)
+            sx = sx * torch.where(c[..., 1] == 1, -1, 1)
+    else:
+        state = torch.zeros(p.shape[:2], dtype=torch.long)
+        for c in cells:
+            cell = c[..., 0] + 2 * c[..., 1]
+            orders.append(_HIL_RES[state % 4, cell].to(F32))
+            state = state + _HIL_ROT[state % 3, cell]
+    key = orders[-1]
+    for i in range(levels - 1):
+        key = key + orders[i] * float(base * base) ** (levels - i - 1)
+    return key
+
+
+def curve_order_ref(h, w, pos, curve):
+    """(rank of each token, tokens in curve order) = calculate_*_order's two returns (:278-282)."""
+    idx = curve_key_ref(pos, h, w, curve).sort(dim=1, stable=True)[1]
+    src = torch.arange(idx.shape[1]).unsqueeze(0).expand_as(idx)
+    return torch.zeros_like(idx).scatter_(1, idx, src), idx
+
+
+def sfc_curve_ref(pos, m, h, w, sf_type, no_reorder=False, use_anchor=True):
+    """space_filling_cluster with sf_type 'peano' / 'hilbert' (reference point_utils.py:98-122,135-166)."""
+    pos = pos.detach().to(F32)
+    b, n, d = pos.shape
+    k = int(math.ceil(n / m))
+    base = 3 if sf_type == 'peano' else 2
+    if use_anchor:
+        patch_len = (h * w / k) ** 0.5
+        nph = int(round(h / patch_len))
+        nph = max(base, int(base ** round(math.log(nph, base))))
+        plh = h / nph
+        npw = int(round(w / h * base) * (nph / base))
+        plw = w / npw
+        ys, xs = torch.meshgrid(torch.arange(nph), torch.arange(npw), indexing="ij")
+        grid = torch.stack([xs, ys], 2).reshape(-1, 2)
+        rank_of_cell, order = curve_order_ref(nph, npw, grid.unsqueeze(0), sf_type)
+        pl = torch.tensor([plw, plh], dtype=F32)
+        centre = grid[order[0]] * pl + pl / 2 - 0.5
+        prev = torch.cat([(centre[0] - (centre[1] - centre[0]))[None], centre[:-1]])
+        nxt = torch.cat([centre[1:], (centre[-1] + (centre[-1] - centre[-2]))[None]])
+        cell = (pos / pl).floor()
+        rank = rank_of_cell[0][(cell[..., 0] + cell[..., 1] * npw).long()]
+        ratio = (pos - prev[rank]).pow(2).sum(-1) / ((pos - nxt[rank]).pow(2).sum(-1) + 1e-5)
+        key = (rank.unsqueeze(2) * (ratio.max() + 1) + ratio.unsqueeze(2)).squeeze(2)
+    else:
+        key = curve_key_ref(pos, h, w, sf_type)
+    ranking = key.sort(dim=1, stable=True)[1]
+    pos_s = pos.gather(1, ranking.unsqueeze(2).expand(-1, -1, d))
+    if k * m == n:
+        mask, mean = None, pos_s.reshape(b, k, m, d).mean(2)
+    else:
+        pad = torch.zeros(b, k * m, d, dtype=F32)
+        pad[:, :n] = pos_s
+        mask = torch.zeros(b, k * m, dtype=torch.int64)
+        mask[:, :n] = 1
+        mask = mask.reshape(b, k, m)
+        mean = pad.reshape(b, k, m, d).sum(2) / mask.sum(2, keepdim=True)
+    if no_reorder:
+        member = torch.zeros(b, k * m, dtype=torch.int64)
+        member[:, :n] = ranking
+        return mean, member.reshape(b, k, m), mask
+    member = torch.arange(k * m)
+    member[n:] = 0
+    return pos_s, mean, member.unsqueeze(0).expand(b, -1).reshape(b, k, m), mask, ranking.unsqueeze(2)
+
+
 def find_pos_org_order_ref(pos_org, pos_shuffled):
     """reference maskfiner_up_down.py:150-154 (torch.argmin returns the first minimal index)"""
     dists = torch.cdist(pos_org.float(), pos_shuffled.float(), p=1)

@@ -80,3 +80,25 @@ def test_sfc_variant_oracle_matches_reference_golden():
                 assert a is None, name
             else:
                 assert torch.equal(a.to(b.dtype), b), name
+
+
+def test_curve_oracle_matches_reference_golden():
+    """Peano / Hilbert restatement (oracle/point_ref.py::curve_order_ref, sfc_curve_ref) against outputs of the
+    reference's own calculate_*_order and space_filling_cluster(sf_type=...) (tests/golden/make_point_curves_golden.py)."""
+    import os
+    import torch
+    from oracle import point_ref as O
+    g = torch.load(os.path.join(os.path.dirname(__file__), "golden", "point_sfc_curves.pt"))
+    assert len(g["orders"]) == 9 and len(g["clusters"]) == 19
+    for name, c in g["orders"].items():
+        rank, order = O.curve_order_ref(c["h"], c["w"], c["pos"], c["curve"])
+        assert torch.equal(rank.to(torch.int32), c["rank"]) and torch.equal(order.to(torch.int32), c["order"]), name
+    for name, c in g["clusters"].items():
+        mine = O.sfc_curve_ref(c["pos"].float(), c["m"], c["h"], c["w"], c["sf_type"], no_reorder=c["no_reorder"],
+                               use_anchor=c["use_anchor"])
+        assert len(mine) == len(c["out"])
+        for a, b in zip(mine, c["out"]):
+            if b is None:
+                assert a is None, name
+            else:
+                assert torch.equal(a.to(b.dtype), b), name

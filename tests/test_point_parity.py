@@ -196,12 +196,48 @@ def test_sfc_variants_match_reference_golden():
 
 
 @pytest.mark.gpu
-def test_sfc_curve_variants_are_declined_loudly():
+def test_curve_orders_match_reference_golden():
+    """calculate_peano_order / calculate_hilbert_order through affb200_curve_key + the stable rank sort against the
+    reference's own outputs (square, widened-first-level, non-power and fractional-position cases): bit-exact."""
+    import os
+    from affb200.point_utils import calculate_peano_order, calculate_hilbert_order
+    g = torch.load(os.path.join(os.path.dirname(__file__), "golden", "point_sfc_curves.pt"))["orders"]
+    assert len(g) == 9
+    for name, c in g.items():
+        fn = calculate_peano_order if c["curve"] == "peano" else calculate_hilbert_order
+        rank, order = fn(c["h"], c["w"], c["pos"].cuda())
+        assert rank.dtype == torch.int64 and order.dtype == torch.int64
+        assert torch.equal(order.cpu().to(torch.int32), c["order"]), name
+        assert torch.equal(rank.cpu().to(torch.int32), c["rank"]), name
+
+
+@pytest.mark.gpu
+def test_sfc_curve_variants_match_reference_golden():
+    """space_filling_cluster(sf_type='peano'|'hilbert') with and without anchors / reordering against outputs of the
+    reference itself; integer outputs bit-exact, cluster means within 1e-5."""
+    import os
     from affb200.point_utils import space_filling_cluster
-    pos = torch.zeros(1, 16, 2, device="cuda")
-    for sf in ("peano", "hilbert"):
-        with pytest.raises(NotImplementedError, match="sf_type"):
-            space_filling_cluster(pos, 8, 4, 4, sf_type=sf)
+    g = torch.load(os.path.join(os.path.dirname(__file__), "golden", "point_sfc_curves.pt"))["clusters"]
+    assert len(g) == 19
+    for name, c in g.items():
+        out = space_filling_cluster(c["pos"].float().cuda(), c["m"], c["h"], c["w"], no_reorder=c["no_reorder"],
+                                    sf_type=c["sf_type"], use_anchor=c["use_anchor"])
+        assert len(out) == len(c["out"]), name
+        for a, b in zip(out, c["out"]):
+            if b is None:
+                assert a is None, name
+            elif b.dtype == torch.float32:
+                assert torch.allclose(a.cpu(), b, rtol=1e-5, atol=0), name
+            else:
+                assert torch.equal(a.cpu().to(b.dtype), b), name
+
+
+@pytest.mark.gpu
+def test_hilbert_on_a_wide_canvas_is_refused():
+    """round(2*w/h) != 2: the reference indexes its 4-entry digit table out of range (point_utils.py:322-338)."""
+    from affb200.point_utils import calculate_hilbert_order
+    with pytest.raises(RuntimeError, match="Hilbert"):
+        calculate_hilbert_order(16, 48, torch.zeros(1, 8, 2, device="cuda"))
 
 
 @pytest.mark.gpu
