@@ -74,6 +74,18 @@ def build_pe_lookup(img_size):
     return rel_pos_width, table_width, table.reshape(-1, 5)
 
 
+def compact_table(pe_idx, table):
+    """Rows of `table` that pe_idx references, and pe_idx re-expressed in them: table[pe_idx] == table_c[pe_idx_c].
+    Neighbourhoods are local, so a stage touches a few thousand of the (2w+1)^2 relative offsets; evaluating
+    pos_embed / weight_net on those rows only is SURVEY §8 f2, and it brings the 191 x 191 table of the 384-pixel
+    configs (and the 1023 x 1023 one of MixRes) under the fused attention kernel's 32 768-row limit."""
+    uniq, inv = torch.unique(pe_idx, return_inverse=True)
+    return inv.reshape(pe_idx.shape), table.index_select(0, uniq)
+
+
+COMPACT_ROWS_ABOVE = 32768   # tables larger than this are compacted per stage (0 = always)
+
+
 def _ln(ops, mod, x):
     """nn.LayerNorm `mod` applied through the operator set (one fused pass on the product path)."""
     return ops.layer_norm(x, mod.weight, mod.bias, mod.eps)
@@ -247,8 +259,9 @@ class BasicLayer(nn.Module):
             self.prob_net = nn.Linear(dim, 1)
         self._grid_cache = {}
 
-    def _index(self, pos, h, w, rel_pos_width, ops):
-        """-> (pos_sorted, reorder | None, nbhd_idx, mask, pe_idx) for local attention."""
+    def _index(self, pos, h, w, rel_pos_width, ops, pre_table):
+        """-> (pos_sorted, reorder | None, nbhd_idx, mask, pe_idx, table) for local attention; `table` is pre_table
+        or, for large tables, its rows referenced by this stage (pe_idx then indexes those)."""
         b, n, _ = pos.shape
         m = self.cluster_size
         k = int(math.ceil(n / float(m)))
@@ -257,7 +270,9 @@ class BasicLayer(nn.Module):
         else:
             pos, mean, _, _, reorder = ops.space_filling_cluster(pos, m, h, w, no_reorder=False)
         nbhd, mask, pe_idx, _ = ops.build_nbhd(pos, mean, m, self.nbhd_size, rel_pos_width)
-        return pos, reorder, nbhd, mask, pe_idx
+        if pre_table.shape[0] > COMPACT_ROWS_ABOVE and not (pe_idx.is_cuda and torch.cuda.is_current_stream_capturing()):
+            pe_idx, pre_table = compact_table(pe_idx, pre_table)
+        return pos, reorder, nbhd, mask, pe_idx, pre_table
 
     def forward(self, pos, feat, h, w, on_grid, stride, rel_pos_width, table_width, pre_table, ops):
         b, n, d = pos.shape
@@ -269,13 +284,14 @@ class BasicLayer(nn.Module):
             pe_idx = (rel_pos[..., 1] * table_width + rel_pos[..., 0]).long()
         else:
             if on_grid:
-                key = (b, n, h, w, str(pos.device), id(ops))
+                key = (b, n, h, w, str(pos.device), id(ops), COMPACT_ROWS_ABOVE)
                 if key not in self._grid_cache:
                     self._grid_cache.clear()
-                    self._grid_cache[key] = self._index(pos, h, w, rel_pos_width, ops)
-                pos, reorder, member_idx, cluster_mask, pe_idx = self._grid_cache[key]
+                    self._grid_cache[key] = self._index(pos, h, w, rel_pos_width, ops, pre_table)
+                pos, reorder, member_idx, cluster_mask, pe_idx, pre_table = self._grid_cache[key]
             else:
-                pos, reorder, member_idx, cluster_mask, pe_idx = self._index(pos, h, w, rel_pos_width, ops)
+                pos, reorder, member_idx, cluster_mask, pe_idx, pre_table = self._index(pos, h, w, rel_pos_width, ops,
+                                                                                        pre_table)
             if reorder is not None:  # store tokens of a cluster together
                 feat = feat.gather(1, reorder.expand(-1, -1, c))
         for blk in self.blocks:

@@ -18,7 +18,7 @@ import math
 import torch
 import torch.nn as nn
 
-from .aff_transformer import ClusterTransformerBlock, build_pe_lookup, default_ops
+from .aff_transformer import ClusterTransformerBlock, build_pe_lookup, compact_table, default_ops
 
 # assumes largest input resolution is 2048 x 2048 (reference mixres_neighbour.py:13-15)
 REL_POS_WIDTH = 2048 // 4 - 1
@@ -35,12 +35,6 @@ def pre_table(device):
         assert w == REL_POS_WIDTH and tw == TABLE_WIDTH
         _tables[key] = table.to(device)
     return _tables[key]
-
-
-def compact_table(pe_idx, table):
-    """Rows of `table` that pe_idx references and pe_idx re-expressed in them: table[pe_idx] == table_c[pe_idx_c]."""
-    uniq, inv = torch.unique(pe_idx, return_inverse=True)
-    return inv.reshape(pe_idx.shape), table.index_select(0, uniq)
 
 
 class BasicLayer(nn.Module):
