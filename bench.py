@@ -195,7 +195,12 @@ def main():
     sampler = ClockSampler(physical_gpu_index(local_rank))
     sampler.start()
     l0 = N.LIB.affb200_launch_count()
+    cuprof = os.environ.get("AFFB200_CUPROF") == "1"   # `ncu --profile-from-start off`: only the timed steps are captured
+    if cuprof:
+        torch.cuda.profiler.start()
     ms = timed_loop(lambda i: run.step(dev_batch), args.steps, world, device)
+    if cuprof:
+        torch.cuda.profiler.stop()
     launches = (N.LIB.affb200_launch_count() - l0) // max(args.steps, 1)
     if getattr(run, "gstep", None) is not None:
         launches = run.gstep.kernels_per_step  # recorded once at capture, launched by every graph replay

@@ -20,6 +20,7 @@ import ctypes
 import torch
 from torch.autograd import Function
 
+from .linear_ops import col_sum as _col_sum
 from . import _native as N
 from .plan import get_plan, is_static, guard_add
 
@@ -177,7 +178,7 @@ class FusedClusterAttentionImg(Function):
                 N.p(table), N.p(bk), N.p(bv), N.p(dupf), N.p(col), N.p(q_pe), N.p(lse), N.p(ds), N.p(blank_part),
                 N.p(d_table), P, B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)),
                 "fused_attn_img_bwd")
-            db = blank_part.sum(dim=0)  # [H, 2, c]
+            db = _col_sum(blank_part.view(B, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
             dw = dpb = None
             if ctx.pe_lin is not None:
                 pe_feat, F, w_dt, b_dt = ctx.pe_lin
@@ -242,7 +243,7 @@ class FusedClusterAttention(Function):
                 _view(dq, n * hc, hc, c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c, c),
                 N.p(table), N.p(bk), N.p(bv), st, N.p(q_pe), umax, N.p(lse), N.p(ds), N.p(pw), N.p(blank_part),
                 N.p(d_table), P, B, H, n, M, c, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)), "fused_attn_bwd")
-            db = blank_part.sum(dim=(0, 1))  # [H, 2, c]
+            db = _col_sum(blank_part.view(B * nt, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
             dw = dpb = None
             if ctx.pe_lin is not None:
                 pe_feat, F, w_dt, b_dt = ctx.pe_lin

@@ -195,13 +195,24 @@ pe_feat_grad_kernel(const T *__restrict__ d_vals, const uint16_t *__restrict__ p
     }
 }
 
-__global__ void __launch_bounds__(256)
+// out[e] = sum over chunks, in a fixed order: a block owns 32 outputs, 32 threads per output stride over the chunks
+// (a single thread walking the ~600 chunks is a 27 us chain of dependent loads), then a fixed-order sum of the 32
+__global__ void __launch_bounds__(1024)
 pe_feat_grad_finish_kernel(const float *__restrict__ part, int n_chunks, int H8, float *__restrict__ out) {
-    const int e = blockIdx.x * 256 + threadIdx.x;
-    if (e >= H8) return;
+    __shared__ float red[32][33];
+    const int el = threadIdx.x & 31, sub = threadIdx.x >> 5;
+    const int e = blockIdx.x * 32 + el;
     float a = 0.f;
-    for (int c = 0; c < n_chunks; ++c) a += part[int64_t(c) * H8 + e];
-    out[e] = a;
+    if (e < H8)
+        for (int c = sub; c < n_chunks; c += 32) a += part[int64_t(c) * H8 + e];
+    red[sub][el] = a;
+    __syncthreads();
+    if (sub == 0 && e < H8) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) t += red[k][el];
+        out[e] = t;
+    }
 }
 
 // out[t][:] = table[idx[t]][:] for rows of ROWB bytes (4, 8 or 16): one thread per gathered row.  The PointConv weights
@@ -357,6 +368,6 @@ extern "C" int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, co
         }
     });
     if (e) return e;
-    pe_feat_grad_finish_kernel<<<unsigned((H * 8 + 255) / 256), 256, 0, st>>>(work, chunks, int(H * 8), out);
+    pe_feat_grad_finish_kernel<<<unsigned((H * 8 + 31) / 32), 1024, 0, st>>>(work, chunks, int(H * 8), out);
     return check_launch("pe_feat_grad_finish");
 }
