@@ -173,7 +173,9 @@ def main():
     torch.cuda.set_device(device)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: the contract is ONE JSON line
+        # the contract is ONE JSON line on stdout: NCCL prints its version banner (and any NCCL_DEBUG output) to stdout
+        # unless told otherwise, so whatever debug level the caller chose goes to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group(backend="nccl", device_id=device)
 
     import bench_workloads as W

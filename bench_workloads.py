@@ -217,18 +217,20 @@ class _AffRun:
             except ImportError:
                 pass
         self.ops = ops
-        model = build_aff(wl.model_name, ops=ops).to(device).train()
+        self.infer = bool(getattr(wl, "infer", False))
+        model = build_aff(wl.model_name, ops=ops).to(device)
+        model = model.eval() if self.infer else model.train()
         self.model = model
         # default: the step replayed as CUDA graphs (affb200/graph_step.py; gradients averaged with one flat NCCL
         # all-reduce).  AFFB200_GRAPH=0: eager launches, DistributedDataParallel for world > 1 as the reference does.
         self.graphed = os.environ.get("AFFB200_GRAPH", "1") != "0"
         self.gstep = None
-        if world > 1 and not self.graphed:
+        if world > 1 and not self.graphed and not self.infer:
             from torch.nn.parallel import DistributedDataParallel as DDP
             model = DDP(model, device_ids=[device.index], broadcast_buffers=False, gradient_as_bucket_view=True)
         self.net = model
-        self.opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.05, fused=True,
-                                     capturable=self.graphed)
+        self.opt = None if self.infer else torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.05,
+                                                             fused=True, capturable=self.graphed)
 
     def make_host_batch(self, i):
         g = torch.Generator().manual_seed(1000 + i)
@@ -241,6 +243,14 @@ class _AffRun:
 
     def step(self, batch):
         x, y = batch
+        if self.infer:       # replicas only: no collective on the inference path
+            if self.graphed:
+                if self.gstep is None:
+                    from affb200.graph_step import GraphedForward
+                    self.gstep = GraphedForward(self.model, x)
+                return self.gstep(x)[0, 0]
+            with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+                return self.model(x)[0, 0]
         if self.graphed:
             if self.gstep is None:
                 from affb200.graph_step import GraphedTrainStep
@@ -262,7 +272,7 @@ class _AffRun:
         operands once: fwd q + kv + out at s bytes, nbhd_idx + pe_idx (+ mask) at 8 B; bwd q, kv, out, d_out read and
         d_q, d_kv written, plus the same index tensors."""
         cap = []
-        hooks = [layer.blocks[0].register_forward_pre_hook(lambda m, a: cap.append((a[1], a[2], a[3])))
+        hooks = [layer.blocks[0].register_forward_pre_hook(lambda m, a: cap.append((a[1], a[2], a[3], a[5])))
                  for layer in self.model.layers[:3]]
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
             self.model(torch.randn(self.B, 3, self.wl.img, self.wl.img, device=self.device))
@@ -271,16 +281,16 @@ class _AffRun:
         rows = []
         if self.ops.fused_attention is not None:
             from affb200 import fused
-            for st, (nbhd, mask, pe_idx) in enumerate(cap):
+            for st, (nbhd, mask, pe_idx, stage_table) in enumerate(cap):   # stage_table: the (compacted) rows pe_idx indexes
                 layer = self.model.layers[st]
                 attn = layer.blocks[0].attn
                 B, n, M = nbhd.shape
                 H, hc = attn.num_heads, attn.dim
                 q = torch.randn(B, n, hc, device=self.device).bfloat16()
                 kv = torch.randn(B, n, 2 * hc, device=self.device).bfloat16()
-                table = torch.randn(self.model.pre_table.shape[0], H, device=self.device).bfloat16()
+                table = torch.randn(stage_table.shape[0], H, device=self.device).bfloat16()
                 calls = fused.raw_calls(q, kv, H, attn.scale, nbhd, pe_idx, mask, table, attn.blank_k, attn.blank_v,
-                                        pre_table=self.model.pre_table)
+                                        pre_table=stage_table)
                 if calls is None:
                     continue
                 nidx = 8 * B * n * M * (3 if mask is not None else 2)
@@ -315,5 +325,47 @@ class AffTinyTrain(AffTrain):
     metric = "AFF-Tiny 224x224 fwd+bwd img/s"
 
 
-WORKLOADS.update({"aff_tiny_1_5th": AffTrain, "aff_tiny": AffTinyTrain})
+class AffInfer(AffTrain):
+    """Inference throughput as the reference's own `throughput()` measures it (main.py:387-414): model.eval(), autocast
+    forward on a fixed batch.  BASELINE config 2: AFF-Mini 224x224, synthetic batch 256, one B200."""
+    model_name = "aff_mini"
+    metric = "AFF-Mini 224x224 inference img/s"
+    default_batch = 256
+    infer = True
+
+    def config(self, B, world):
+        c = super().config(B, world)
+        c.update(workload="%s_%d_inference" % (self.model_name, self.img),
+                 step="model.eval() forward, bf16 autocast (reference main.py:387-414)",
+                 launch="eager" if os.environ.get("AFFB200_GRAPH", "1") == "0" else "one CUDA graph per forward")
+        return c
+
+    def cpu_reference(self, sample_b):
+        from affb200.aff_transformer import build_aff
+        from oracle.aff_ops_ref import OracleOps  # the checker, timed here as the CPU baseline only
+        torch.manual_seed(0)
+        model = build_aff(self.model_name, ops=OracleOps()).eval()
+        x = torch.randn(sample_b, 3, self.img, self.img, generator=torch.Generator().manual_seed(1))
+
+        def go():
+            with torch.no_grad():
+                model(x)
+        return go
+
+
+class AffBase384Infer(AffInfer):
+    """BASELINE config 4: AFF-Base 384x384 (22kto1k) inference, yaml batch 16."""
+    model_name = "aff_base_22kto1k_384"
+    metric = "AFF-Base 384x384 inference img/s"
+    default_batch = 16
+    img = 384
+
+
+class AffTinyInfer(AffInfer):
+    model_name = "aff_tiny_1_5th"
+    metric = "AFF-Tiny-1/5 224x224 inference img/s"
+
+
+WORKLOADS.update({"aff_tiny_1_5th": AffTrain, "aff_tiny": AffTinyTrain, "aff_mini_infer": AffInfer,
+                  "aff_base_384_infer": AffBase384Infer, "aff_tiny_1_5th_infer": AffTinyInfer})
 DEFAULT = "aff_tiny_1_5th"

@@ -138,3 +138,59 @@ class GraphedTrainStep:
         """Kept for callers of the earlier interface: every replay is now verified (and redone if needed) inside
         __call__, so this only reports a guard raised by kernels run outside the step."""
         _plan.check_guard(self.device)
+
+
+class GraphedForward:
+    """Inference forward of the off-grid model as one CUDA graph (the reference's `throughput()` loop, main.py:387-414,
+    is `model.eval()` + autocast forward on a fixed batch shape).
+
+        fwd = GraphedForward(model, example_x)      # eval mode, autocast
+        logits = fwd(x)                             # static output tensor, overwritten by the next call
+
+    Index plans are speculated from the eager warm-up passes exactly as in GraphedTrainStep; the guard is read after the
+    replay and a failed speculation is redone eagerly (and the graph re-captured) before the result is returned."""
+
+    def __init__(self, model, example_x, autocast_dtype=torch.bfloat16, warmup=2):
+        self.model, self.autocast_dtype = model, autocast_dtype
+        self.device = example_x.device
+        self.x = example_x.clone()
+        self.out = None
+        self.fallbacks = 0
+        self.recaptures = 0
+        self.max_recaptures = 8
+        _plan.guard_tensor(self.device)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._fwd()
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        self._capture()
+
+    def _fwd(self):
+        with torch.no_grad(), torch.autocast("cuda", dtype=self.autocast_dtype):
+            return self.model(self.x)
+
+    def _capture(self):
+        from . import _native as N
+        l0 = N.LIB.affb200_launch_count()
+        self.g = torch.cuda.CUDAGraph()
+        with _plan.static_plans(), torch.cuda.graph(self.g):
+            self.out = self._fwd()
+        self.kernels_per_step = int(N.LIB.affb200_launch_count() - l0)
+
+    def __call__(self, x):
+        self.x.copy_(x, non_blocking=True)
+        self.g.replay()
+        guard = _plan.guard_tensor(self.device)
+        if int(guard.item()) != 0:
+            guard.zero_()
+            self.fallbacks += 1
+            out = self._fwd()
+            if self.recaptures < self.max_recaptures:
+                self.recaptures += 1
+                torch.cuda.synchronize(self.device)
+                self._capture()
+            self.out.copy_(out)
+        return self.out

@@ -155,7 +155,7 @@ class NbhdPlan:
                 if _static:
                     T = obs["T"]
                 with torch.cuda.device(dev):
-                    while True:
+                    while T is not None:   # T None (static mode): the eager passes found this shape not tileable
                         nt = (Nq + T - 1) // T
                         hdr = torch.empty((B, nt), dtype=torch.int32, device=dev)
                         rows = torch.empty((B, nt, N.PLAN_UMAX), dtype=torch.int32, device=dev)
@@ -176,8 +176,9 @@ class NbhdPlan:
                             if obs is None or obs["T"] != T or st[4] > obs["umax"]:
                                 _observed[("q",) + skey] = dict(T=T, umax=max(st[4], obs["umax"] if obs and obs["T"] == T else 0))
                             break
-                        if T == 16:
+                        if T == 8:    # 8-token tiles (run in 16-row kernels) keep a tile inside one cluster of 24
                             self.stats["q"] = dict(T=T, overflow=st[0], tiles=B * nt)
+                            _observed[("q",) + skey] = dict(T=None, umax=0)   # remembered: generic kernels for this shape
                             break
                         T //= 2
             self._q[Nk] = res
@@ -200,7 +201,7 @@ class NbhdPlan:
                 if _static:
                     T = obs["T"]
                 with torch.cuda.device(dev):
-                    while True:
+                    while T is not None:
                         nt = (Nk + T - 1) // T
                         hdr = torch.empty((B, nt), dtype=torch.int32, device=dev)
                         utok = torch.empty((B, nt, N.PLAN_UMAX), dtype=torch.int32, device=dev)
@@ -223,6 +224,7 @@ class NbhdPlan:
                             break
                         if T == 16:
                             self.stats["k"] = dict(T=T, overflow=st[2], tiles=B * nt)
+                            _observed[("k",) + skey] = dict(T=None, umax=0)
                             break
                         T //= 2
             self._k[Nk] = res

@@ -141,7 +141,8 @@ template <typename T, int C, bool FAST>
 __global__ void __launch_bounds__(kDT)
 gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const int32_t *__restrict__ q_hdr,
                         const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc, T *__restrict__ out,
-                        int H, int Nq, int Nk, int M, int TT) {
+                        int H, int Nq, int Nk, int M, int TT, int TS) {
+    // TS tokens per tile (the plan's tile size), TT >= TS rows of capacity (a multiple of the 16-row MMA tile)
     constexpr int CS = C + 8;
     constexpr int CH = C / 8;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -152,8 +153,8 @@ gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const 
     uint8_t *loc_s = reinterpret_cast<uint8_t *>(xs + TT * CS);
 
     const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x;
-    const int t0 = tile * TT;
-    const int ti = min(TT, Nq - t0);
+    const int t0 = tile * TS;
+    const int ti = min(TS, Nq - t0);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int hdr0 = q_hdr[int64_t(b) * n_tiles + tile];
     if (hdr0 & AFFB200_PLAN_OVERFLOW) {  // only reachable with a speculated plan; the caller's deferred check reports it
@@ -338,7 +339,7 @@ template <typename T, int C, bool FAST>
 __global__ void __launch_bounds__(kDT)
 gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const int32_t *__restrict__ q_hdr,
                          const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc, T *__restrict__ out,
-                         int H, int Nq, int Nk, int M, int TT) {
+                         int H, int Nq, int Nk, int M, int TT, int TS) {
     constexpr int CS = C + 8;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     int *rows_s = reinterpret_cast<int *>(smem_raw);
@@ -348,8 +349,8 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
     uint8_t *loc_s = reinterpret_cast<uint8_t *>(os + os_floats<C>());
 
     const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x;
-    const int t0 = tile * TT;
-    const int ti = min(TT, Nq - t0);
+    const int t0 = tile * TS;
+    const int ti = min(TS, Nq - t0);
     const int tid = threadIdx.x;
     const int hdr = q_hdr[int64_t(b) * n_tiles + tile];
     if (hdr & AFFB200_PLAN_OVERFLOW) {  // speculated plan only (see gather_dot_dense_kernel)
@@ -622,8 +623,8 @@ template <typename K> static int set_smem(K kern, size_t smem) {
 template <typename T>
 int launch_gather_dot_dense(const T *x, const T *y, const affb200_nbhd_plan *pl, T *out, int64_t B, int64_t H,
                             int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
-    const int TT = pl->tq;
-    dim3 grid(unsigned((Nq + TT - 1) / TT), unsigned(B));
+    const int TS = pl->tq, TT = (TS + 15) & ~15;
+    dim3 grid(unsigned((Nq + TS - 1) / TS), unsigned(B));
     const size_t smem = smem_gather_dot(int(c), TT, int(M));
     const bool fast = (M % 8 == 0) && M <= 64 && int64_t(TT) * M <= 4096 && aligned16(out) &&
                       (reinterpret_cast<uintptr_t>(pl->q_loc) & 7) == 0;
@@ -632,7 +633,7 @@ int launch_gather_dot_dense(const T *x, const T *y, const affb200_nbhd_plan *pl,
         auto kern = gather_dot_dense_kernel<T, C_, F_>;                                                         \
         if (int e = set_smem(kern, smem)) return e;                                                             \
         kern<<<grid, kDT, smem, st>>>(x, y, pl->q_hdr, pl->q_rows, pl->q_loc, out, int(H), int(Nq), int(Nk),    \
-                                      int(M), TT);                                                              \
+                                      int(M), TT, TS);                                                          \
     } while (0)
     if (c == 32) { if (fast) AFF_L(32, true); else AFF_L(32, false); }
     else { if (fast) AFF_L(16, true); else AFF_L(16, false); }
@@ -643,8 +644,8 @@ int launch_gather_dot_dense(const T *x, const T *y, const affb200_nbhd_plan *pl,
 template <typename T>
 int launch_gather_wsum_dense(const T *w, const T *y, const affb200_nbhd_plan *pl, T *out, int64_t B, int64_t H,
                              int64_t Nq, int64_t Nk, int64_t M, int64_t c, cudaStream_t st) {
-    const int TT = pl->tq;
-    dim3 grid(unsigned((Nq + TT - 1) / TT), unsigned(B));
+    const int TS = pl->tq, TT = (TS + 15) & ~15;
+    dim3 grid(unsigned((Nq + TS - 1) / TS), unsigned(B));
     const size_t smem = smem_gather_wsum(int(c), TT, int(M));
     const bool fast = (M % 8 == 0) && M <= 64 && int64_t(TT) * M <= 4096 && aligned16(w) &&
                       (reinterpret_cast<uintptr_t>(pl->q_loc) & 7) == 0;
@@ -653,7 +654,7 @@ int launch_gather_wsum_dense(const T *w, const T *y, const affb200_nbhd_plan *pl
         auto kern = gather_wsum_dense_kernel<T, C_, F_>;                                                        \
         if (int e = set_smem(kern, smem)) return e;                                                             \
         kern<<<grid, kDT, smem, st>>>(w, y, pl->q_hdr, pl->q_rows, pl->q_loc, out, int(H), int(Nq), int(Nk),    \
-                                      int(M), TT);                                                              \
+                                      int(M), TT, TS);                                                          \
     } while (0)
     if (c == 32) { if (fast) AFF_L(32, true); else AFF_L(32, false); }
     else { if (fast) AFF_L(16, true); else AFF_L(16, false); }

@@ -41,7 +41,7 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
                       const float *__restrict__ blank_k, const float *__restrict__ blank_v,
                       const int32_t *__restrict__ q_hdr, const int32_t *__restrict__ q_rows,
                       const uint8_t *__restrict__ q_loc, const uint16_t *__restrict__ q_pe, float *__restrict__ lse,
-                      int H, int N, int M, float scale, FusedSmem L) {
+                      int H, int N, int M, float scale, FusedSmem L, int TS) {
     constexpr int TPR = kFT / TT;
     extern __shared__ __align__(128) unsigned char smem[];
     int *rows_s = reinterpret_cast<int *>(smem + L.rows);
@@ -53,7 +53,7 @@ fused_attn_fwd_kernel(View<T> q, View<T> k, View<T> v, ViewW<T> out, const float
     const uint32_t ks_a = f_smem_u32(ks), vs_a = f_smem_u32(vs), xs_a = f_smem_u32(xs);
 
     const int b = blockIdx.y, tid = threadIdx.x;
-    const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
+    const TileHdr t = f_load_tile(q_hdr, q_rows, N, TS, L.UC, int(k.sN), rows_s);
     if (t.bad) {  // uniform over the CTA; the host's deferred plan check reports the failed speculation and redoes
                   // the step; until then the tile's outputs are zeros, not uninitialised memory
         const int HS0 = (H + int(gridDim.z) - 1) / int(gridDim.z);
@@ -139,7 +139,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
                       const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc,
                       const uint16_t *__restrict__ q_pe, const float *__restrict__ lse, T *__restrict__ ds_out,
                       T *__restrict__ p_out, float *__restrict__ blank_part, int H, int N, int M, float scale,
-                      FusedSmem L) {
+                      FusedSmem L, int TS) {
     constexpr int CS = C + 8;
     constexpr int TPR = kFT / TT;
     constexpr int PER = NE - 1;
@@ -159,7 +159,7 @@ fused_attn_bwd_kernel(View<T> q, View<T> k, View<T> v, View<T> out, View<T> dout
     const uint32_t vs_a = f_smem_u32(vs), xs_a = f_smem_u32(xs), dos_a = f_smem_u32(dos), outs_a = f_smem_u32(outs);
 
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const TileHdr t = f_load_tile(q_hdr, q_rows, N, TT, L.UC, int(k.sN), rows_s);
+    const TileHdr t = f_load_tile(q_hdr, q_rows, N, TS, L.UC, int(k.sN), rows_s);
     if (t.bad) {  // failed speculation (see the forward kernel): zeros for everything this tile would have written
         const int HS0 = (H + int(gridDim.z) - 1) / int(gridDim.z);
         for (int h = int(blockIdx.z) * HS0; h < min(H, (int(blockIdx.z) + 1) * HS0); ++h) {
@@ -384,11 +384,11 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
         return AFFB200_E_ARG;
     }
     if (!kv_ok(k, v, N) || N * q->sN >= (int64_t(1) << 31)) { set_error("fused_attn_fwd: k/v token strides must match and fit int32"); return AFFB200_E_ARG; }
-    const int TT = plan->tq;
+    const int TS = plan->tq, TT = (TS + 15) & ~15;   // tokens per tile; row capacity of the kernel
     const int UC = (umax + 1 + 31) & ~31;
     const FusedSmem L = fused_smem(UC, TT, int(c), false);
     if (L.total > 227 * 1024) { set_error("fused_attn_fwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
-    dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
+    dim3 grid(unsigned((N + TS - 1) / TS), unsigned(B));
     grid.z = head_split(int64_t(grid.x) * grid.y, H, 3);
     auto st = (cudaStream_t)stream;
     return dispatch_dtype(dtype, [&](auto tag) -> int {
@@ -403,7 +403,7 @@ extern "C" int affb200_fused_attn_fwd(const affb200_view *q, const affb200_view 
             return check_launch("cudaFuncSetAttribute", 0);                                                        \
         kern<<<grid, kFT, L.total, st>>>(mk_view<T>(q), mk_view<T>(k), mk_view<T>(v), mk_vieww<T>(out), table,     \
                                          blank_k, blank_v, plan->q_hdr, plan->q_rows, plan->q_loc, q_pe, lse,      \
-                                         int(H), int(N), int(M), scale, L);                                        \
+                                         int(H), int(N), int(M), scale, L, TS);                                        \
     } while (0)
             // (tile size, slots per thread): 256/TT threads per row, each NE-1 neighbour slots: (NE-1)*256/TT >= M
             const int need = int(M);
@@ -445,11 +445,11 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
         return AFFB200_E_ARG;
     }
     if (P <= 0 || P > 32768) { set_error("fused_attn_bwd: bias table must have 1..32768 rows"); return AFFB200_E_ARG; }
-    const int TT = plan->tq;
+    const int TS = plan->tq, TT = (TS + 15) & ~15;   // tokens per tile; row capacity of the kernel
     const int UC = (umax + 1 + 31) & ~31;
     const FusedSmem L = fused_smem(UC, TT, int(c), true);
     if (L.total > 227 * 1024) { set_error("fused_attn_bwd: tile needs %zu bytes of shared memory", L.total); return AFFB200_E_ARG; }
-    dim3 grid(unsigned((N + TT - 1) / TT), unsigned(B));
+    dim3 grid(unsigned((N + TS - 1) / TS), unsigned(B));
     grid.z = head_split(int64_t(grid.x) * grid.y, H, 2);
     auto st = (cudaStream_t)stream;
     return dispatch_dtype(dtype, [&](auto tag) -> int {
@@ -465,7 +465,7 @@ extern "C" int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view 
         kern<<<grid, kFT, L.total, st>>>(mk_view<T>(q), mk_view<T>(k), mk_view<T>(v), mk_view<T>(out),             \
                                          mk_view<T>(dout), mk_vieww<T>(dq), table, blank_k, blank_v, plan->q_hdr,  \
                                          plan->q_rows, plan->q_loc, q_pe, lse, (T *)ds_work, (T *)p_work,          \
-                                         blank_part, int(H), int(N), int(M), scale, L);                            \
+                                         blank_part, int(H), int(N), int(M), scale, L, TS);                            \
     } while (0)
             // (tile size, slots per thread): 256/TT threads per row, each NE-1 neighbour slots: (NE-1)*256/TT >= M
             const int need = int(M);

@@ -255,7 +255,7 @@ __device__ __forceinline__ TileHdr f_load_tile(const int32_t *q_hdr, const int32
                                                int kv_stride, int *rows_s) {
     TileHdr t;
     const int b = blockIdx.y, tile = blockIdx.x, n_tiles = gridDim.x, tid = threadIdx.x;
-    t.t0 = tile * TT;
+    t.t0 = tile * TT;   // TT here = tokens per tile of the plan (<= the kernel's row capacity)
     t.ti = min(TT, N - t.t0);
     const int hdr = q_hdr[int64_t(b) * n_tiles + tile];
     t.U = hdr & AFFB200_PLAN_COUNT_MASK;

@@ -253,9 +253,9 @@ kplan_finish_kernel(const int64_t *__restrict__ idx, int Nq, int Nk, int M, int 
 using namespace affb200;
 
 static bool plan_dims_ok(const char *what, int64_t B, int64_t Nq, int64_t Nk, int64_t M, int64_t T) {
-    if (B < 0 || Nq < 0 || Nk < 0 || M < 0 || (T != 16 && T != 32 && T != 64) || B > 65535 ||
+    if (B < 0 || Nq < 0 || Nk < 0 || M < 0 || (T != 8 && T != 16 && T != 32 && T != 64) || B > 65535 ||
         Nq * M >= (int64_t(1) << 31) || Nk > AFFB200_PLAN_MAX_NK || M > AFFB200_PLAN_MAX_M) {
-        set_error("%s: unsupported dimensions (T in {16,32,64}, Nk <= %d, M <= %d, B <= 65535)", what,
+        set_error("%s: unsupported dimensions (T in {8,16,32,64}, Nk <= %d, M <= %d, B <= 65535)", what,
                   AFFB200_PLAN_MAX_NK, AFFB200_PLAN_MAX_M);
         return false;
     }

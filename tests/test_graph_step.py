@@ -163,3 +163,21 @@ def test_static_mode_needs_an_eager_pass_first():
     with plan.static_plans():
         with pytest.raises(RuntimeError, match="eager pass"):
             plan.get_plan(idx).qplan(idx, 77)
+
+
+def test_graphed_forward_matches_eager_inference():
+    """GraphedForward (the reference's throughput() loop as one CUDA graph): replays on batches the capture never saw
+    reproduce the eager eval-mode forward; token selections differ per batch, so the speculated plans are exercised."""
+    from affb200.graph_step import GraphedForward
+    m1, _ = _models()
+    m1.eval()
+    xs, _ = _batches(4)
+    fwd = GraphedForward(m1, xs[0])
+    for x in xs[1:]:
+        got = fwd(x).float().clone()
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            want = m1(x).float()
+        assert torch.isfinite(got).all()
+        # bit-identical kernels on identical inputs; a fallback (eager redo) would also be exact
+        assert torch.equal(got, want), (got - want).abs().max()
+    assert fwd.kernels_per_step > 0
