@@ -24,6 +24,11 @@ __device__ __forceinline__ void cp_async16(void *dst, const void *src, bool vali
     const int sz = valid ? 16 : 0;
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
 }
+// 16-bit store to a 32-bit shared-window address: a store through a generic pointer derived from the dynamic shared
+// array makes ptxas rebuild the shared address per (predicated) store from SR_CgaCtaId
+__device__ __forceinline__ void st_shared_u16(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((unsigned short)v) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
@@ -145,7 +150,7 @@ gather_dot_dense_kernel(const T *__restrict__ x, const T *__restrict__ y, const 
     // TS tokens per tile (the plan's tile size), TT >= TS rows of capacity (a multiple of the 16-row MMA tile)
     constexpr int CS = C + 8;
     constexpr int CH = C / 8;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char *const smem_raw = affb200_dsm;
     int *rows_s = reinterpret_cast<int *>(smem_raw);
     T *ys = reinterpret_cast<T *>(smem_raw + 1024);
     T *ss = ys + kUMaxDense * CS;
@@ -341,7 +346,7 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
                          const int32_t *__restrict__ q_rows, const uint8_t *__restrict__ q_loc, T *__restrict__ out,
                          int H, int Nq, int Nk, int M, int TT, int TS) {
     constexpr int CS = C + 8;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char *const smem_raw = affb200_dsm;
     int *rows_s = reinterpret_cast<int *>(smem_raw);
     T *ys = reinterpret_cast<T *>(smem_raw + 1024);
     T *ps = ys + kUMaxDense * CS;
@@ -392,7 +397,7 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
     __syncthreads();
     RowStager<T, C> st;
     st.init(rows_s, U, C);
-    const uint32_t ys_a = smem_u32(ys);
+    const uint32_t ys_a = smem_u32(ys), ps_a = dsm_addr() + 1024u + uint32_t(kUMaxDense * CS * 2);
 
     for (int h = 0; h < H; ++h) {
         const int64_t z = int64_t(b) * H + h;
@@ -411,12 +416,12 @@ gather_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ y, const
 #pragma unroll
             for (int k = 0; k < 2; ++k) {
                 if (prow[k] < 0) continue;
-                uint16_t *pr = reinterpret_cast<uint16_t *>(ps + prow[k]);
+                const uint32_t pr = ps_a + uint32_t(prow[k]) * 2u;
                 const uint32_t wr[4] = {wv[k].x, wv[k].y, wv[k].z, wv[k].w};
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     const uint32_t l = ((e < 4 ? lc[k].x : lc[k].y) >> (8 * (e & 3))) & 0xffu;
-                    pr[l] = uint16_t(wr[e >> 1] >> (16 * (e & 1)));
+                    st_shared_u16(pr + l * 2u, wr[e >> 1] >> (16 * (e & 1)));
                 }
             }
         } else {
@@ -463,7 +468,7 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
                           T *__restrict__ dy, int H, int Nq, int Nk, int M, int TT, StridedRows xs_, StridedRows ys_,
                           float alpha) {
     constexpr int CS = C + 8;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char *const smem_raw = affb200_dsm;
     int *tok_s = reinterpret_cast<int *>(smem_raw);
     T *xs = reinterpret_cast<T *>(smem_raw + 1024);
     T *ps = xs + kUMaxDense * CS;
@@ -519,6 +524,8 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
                 }
             }
             zero_operand<T>(ps, TT, Upad);
+            // shared address of ps formed from the array symbol itself (a link-time constant plus an offset)
+            const uint32_t ps_a = dsm_addr() + 1024u + uint32_t(kUMaxDense * CS * 2);
             for (int h = h_lo; h < h_hi; ++h) {
                 const T *wz = w + (int64_t(b) * H + h) * Nq * M;
                 uint4 wv[GPT];
@@ -531,14 +538,17 @@ scatter_wsum_dense_kernel(const T *__restrict__ w, const T *__restrict__ x, cons
                 st.issue(xs_a, xb + int64_t(h) * xs_.sH);
                 cp_async_commit();
                 if (h == h_lo) __syncthreads();  // the zero fill above
+                uint32_t hz;  // an opaque zero per head: keeps ptxas from hoisting the 48 store addresses out of the
+                              // head loop into registers it does not have (248 bytes of spills otherwise)
+                asm volatile("mov.u32 %0, 0;" : "=r"(hz));
 #pragma unroll
                 for (int g = 0; g < GPT; ++g) {
-                    uint16_t *pcol = reinterpret_cast<uint16_t *>(ps) + (src[g] >> 24);
+                    const uint32_t pcol = ps_a + hz + (src[g] >> 24) * 2u;
                     const uint32_t wr[4] = {wv[g].x, wv[g].y, wv[g].z, wv[g].w};
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
                         const uint32_t l = ((k < 4 ? lc[g].x : lc[g].y) >> (8 * (k & 3))) & 0xffu;
-                        if (l != 0xffu) pcol[l * kSS] = uint16_t(wr[k >> 1] >> (16 * (k & 1)));
+                        if (l != 0xffu) st_shared_u16(pcol + l * uint32_t(kSS * 2), wr[k >> 1] >> (16 * (k & 1)));
                     }
                 }
                 cp_async_wait_all();

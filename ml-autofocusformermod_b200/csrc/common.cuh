@@ -11,7 +11,19 @@
 #error "libaffb200 targets sm_100a (B200) only"
 #endif
 
+// The dynamic shared memory of every kernel, declared at global scope so that inline PTX can name it: `mov.u32 r,
+// affb200_dsm` is the array's address in the shared window, a link-time constant.  Going through
+// __cvta_generic_to_shared(pointer) instead makes ptxas form the generic address first (S2R SR_CgaCtaId + LEA) and,
+// under register pressure, rebuild it in front of every store of an unrolled loop.
+extern __shared__ __align__(128) unsigned char affb200_dsm[];
+
 namespace affb200 {
+
+__device__ __forceinline__ uint32_t dsm_addr() {
+    uint32_t a;
+    asm("mov.u32 %0, affb200_dsm;" : "=r"(a));
+    return a;
+}
 
 void set_error(const char *fmt, ...);
 int check_launch(const char *what, int n_kernels = 1);  // also counts kernels enqueued (affb200_launch_count)
