@@ -355,7 +355,7 @@ extern "C" int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, co
     auto st = (cudaStream_t)stream;
     const int64_t total = B * NM;
     const int chunks = pe_feat_chunks(total);
-    constexpr int HG = 4;
+    const int HG = H <= 2 ? 2 : 4;   // heads per CTA: two-head stages do not pay for the FMAs of two absent heads
     const dim3 grid{unsigned(chunks), unsigned((H + HG - 1) / HG)};
     int e = dispatch_dtype(dtype, [&](auto tag) -> int {
         using T = decltype(tag);
@@ -363,7 +363,10 @@ extern "C" int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, co
             set_error("pe_feat_grad: f16 / bf16 only");
             return AFFB200_E_ARG;
         } else {
-            pe_feat_grad_kernel<T, HG><<<grid, 256, 0, st>>>((const T *)d_vals, q_pe, feat8, int(H), NM, total, work);
+            if (HG == 2)
+                pe_feat_grad_kernel<T, 2><<<grid, 256, 0, st>>>((const T *)d_vals, q_pe, feat8, int(H), NM, total, work);
+            else
+                pe_feat_grad_kernel<T, 4><<<grid, 256, 0, st>>>((const T *)d_vals, q_pe, feat8, int(H), NM, total, work);
             return check_launch("pe_feat_grad");
         }
     });
