@@ -364,6 +364,91 @@ wf_bwd_w_kernel(const T *__restrict__ d_out, const T *__restrict__ f, const int6
     }
 }
 
+// N partial sums per lane, L lanes (powers of two, N >= L): after log2(L) exchange steps lane l of the group holds the
+// complete sums [l*N/L, (l+1)*N/L) in v[0 .. N/L).  N-N/L shuffles in all, against N*log2(L) for N butterflies.
+template <typename Acc, int N, int L>
+__device__ __forceinline__ void transpose_reduce_block(Acc (&v)[N], int l) {
+    static_assert(N >= L && (N & (N - 1)) == 0 && (L & (L - 1)) == 0, "powers of two");
+#pragma unroll
+    for (int bit = L / 2, half = N / 2; bit >= 1; bit >>= 1, half >>= 1) {
+        const bool up = (l & bit) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const Acc keep = up ? v[i + half] : v[i];
+            const Acc send = up ? v[i] : v[i + half];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+        }
+    }
+}
+
+// WF backward, weights half, grouped form (IC == 4, C = G*NCH*W): G lanes own one token's d_out rows (4 x C, converted
+// once, in registers) and walk 8 of its slots; the 8 x 4 partial sums per lane meet in one transposing reduction, so
+// lane l of a group ends with the four inner-channel sums of slot l/.. and the group's 32 results leave as contiguous
+// stores.  grid (groups of the image, 1, B): no 64-bit divisions (the pair-per-lane-group kernel above spent most of
+// its 320 instructions per pair on two of them and on re-converting the d_out rows for every slot).
+template <typename T, int G, int NCH>
+__global__ void __launch_bounds__(kThreads)
+wf_bwd_w_group_kernel(const T *__restrict__ d_out, const T *__restrict__ f, const int64_t *__restrict__ idx,
+                      T *__restrict__ d_w, int Nq, int Nk, int M, FastDiv div_gpt, int gpt, int n_groups) {
+    using Acc = typename Elem<T>::Acc;
+    constexpr int W = Elem<T>::VEC, ICT = 4, PP = 8, C = G * NCH * W;
+    const int b = blockIdx.z;
+    const int gthread = blockIdx.x * kThreads + threadIdx.x;
+    const int grp = gthread / G, l = gthread % G;
+    const bool live = grp < n_groups;
+    const int gq = live ? grp : n_groups - 1;           // dead lanes of the last warp compute on a valid group
+    const int tok = int(div_gpt.div(uint32_t(gq)));
+    const int j0 = (gq - tok * gpt) * PP;
+    const int64_t bt = int64_t(b) * Nq + tok;
+    Acc dv[ICT][NCH][W];
+#pragma unroll
+    for (int q = 0; q < ICT; ++q)
+#pragma unroll
+        for (int n = 0; n < NCH; ++n) load_vec<T, W>(d_out + (bt * ICT + q) * C + (n * G + l) * W, dv[q][n]);
+    const int64_t *ir = idx + bt * M;
+    const T *fb = f + int64_t(b) * Nk * C;
+    Acc acc[PP * ICT];
+#pragma unroll
+    for (int p = 0; p < PP; ++p) {
+        const int j = min(j0 + p, M - 1);
+        const int64_t r = __ldg(ir + j);
+        Acc a[ICT] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+#pragma unroll
+        for (int n = 0; n < NCH; ++n) {
+            Acc fv[W];
+            load_vec<T, W>(fb + r * C + (n * G + l) * W, fv);
+#pragma unroll
+            for (int q = 0; q < ICT; ++q)
+#pragma unroll
+                for (int t = 0; t < W; ++t) a[q] += fv[t] * dv[q][n][t];
+        }
+#pragma unroll
+        for (int q = 0; q < ICT; ++q) acc[p * ICT + q] = a[q];
+    }
+    transpose_reduce_block<Acc, PP * ICT, G>(acc, l);
+    // lane l holds results [l*R, (l+1)*R) of the group's 32, R = 32/G; result k = slot j0 + k/4, inner channel k%4
+    constexpr int R = PP * ICT / G;
+    if (live) {
+        T *o = d_w + (bt * M + j0) * ICT;
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            const int e = l * R + k;
+            if (j0 + e / ICT < M) o[e] = Elem<T>::from_acc(acc[k]);
+        }
+    }
+}
+
+template <typename T, int G, int NCH>
+static int launch_wf_bwd_w_group(const T *d_out, const T *f, const int64_t *idx, T *d_w, int64_t B, int64_t Nq,
+                                 int64_t Nk, int64_t M, cudaStream_t st) {
+    const int gpt = int((M + 7) / 8);
+    const int64_t n_groups = Nq * gpt;
+    dim3 grid(unsigned(ceil_div64(n_groups * G, kThreads)), 1u, unsigned(B));
+    wf_bwd_w_group_kernel<T, G, NCH><<<grid, kThreads, 0, st>>>(d_out, f, idx, d_w, int(Nq), int(Nk), int(M),
+                                                               FastDiv{uint32_t(gpt)}, gpt, int(n_groups));
+    return check_launch("wf_bwd_w_group");
+}
+
 // WF backward, feature half: d_f[b,r,c] = sum_{e=(i,j)->r} sum_ic d_out[b,i,ic,c] * w[b,i,j,ic]  (CSR walk).
 template <typename T, int W, int ICT>
 __global__ void __launch_bounds__(kThreads)
@@ -570,6 +655,17 @@ int launch_wf_bwd_w(const T *d_out, const T *f, const int64_t *idx, T *d_w, int6
     int G = 1;
     while (G * 2 <= 32 && G * 2 <= lpr) G *= 2;
     const bool ic4 = (IC == 4);
+    if (vec && ic4 && B <= 65535 && Nq * ((M + 7) / 8) * 32 < (int64_t(1) << 31)) {   // grouped kernel: C = G*NCH*W
+        const int64_t lanes = C / W;
+#define AFF_WG(G_, N_) return launch_wf_bwd_w_group<T, G_, N_>(d_out, f, idx, d_w, B, Nq, Nk, M, st)
+        if (lanes == 4) AFF_WG(4, 1);
+        if (lanes == 8) AFF_WG(8, 1);
+        if (lanes == 16) AFF_WG(16, 1);
+        if (lanes == 32) AFF_WG(32, 1);
+        if (lanes == 64) AFF_WG(32, 2);
+        if (lanes == 128 && sizeof(T) <= 4) AFF_WG(32, 4);
+#undef AFF_WG
+    }
     const int64_t n_pairs = B * Nq * M;
     dim3 grid(unsigned(ceil_div64(n_pairs * G, kThreads)), ic4 ? 1u : unsigned(IC));
     const FastDiv divM{uint32_t(M)};
