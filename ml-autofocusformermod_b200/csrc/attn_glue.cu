@@ -150,9 +150,15 @@ pe_feat_grad_kernel(const T *__restrict__ d_vals, const uint16_t *__restrict__ p
     const int64_t groups = total / 8;   // NM % 8 == 0 (checked by the launcher)
     const int64_t per = (groups + gridDim.x - 1) / gridDim.x;
     const int64_t g0 = int64_t(blockIdx.x) * per, g1 = min(groups, g0 + per);
-    for (int64_t g = g0 + threadIdx.x; g < g1; g += 256) {
+    // (image, offset in the image) of this thread's group, advanced without a 64-bit division per iteration
+    int64_t b = 0, r = 0;
+    if (g0 + threadIdx.x < g1) {
+        b = ((g0 + threadIdx.x) * 8) / NM;
+        r = (g0 + threadIdx.x) * 8 - b * NM;
+    }
+    for (int64_t g = g0 + threadIdx.x; g < g1; g += 256, r += 256 * 8) {
+        while (r >= NM) { r -= NM; ++b; }
         const int64_t t = g * 8;
-        const int64_t b = t / NM, r = t - b * NM;
         const uint4 pv = __ldg(reinterpret_cast<const uint4 *>(pe + t));
         uint4 dv[HG];
 #pragma unroll

@@ -210,7 +210,8 @@ template <typename TF, typename TL, int CPL>
 __global__ void __launch_bounds__(kMT)
 merge_bwd_f_kernel(const float *__restrict__ d_out, const float *__restrict__ table, const int64_t *__restrict__ pe_idx,
                    const int64_t *__restrict__ mask, const TL *__restrict__ lp, const int32_t *__restrict__ off,
-                   const int32_t *__restrict__ ent, TF *__restrict__ d_feat, int64_t n_rows, int Nq, int Nk, int M) {
+                   const int32_t *__restrict__ ent, TF *__restrict__ d_feat, int64_t n_rows, int Nq, int Nk, int M,
+                   FastDiv divM) {
     constexpr int C = CPL * 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row = int64_t(blockIdx.x) * kMW + warp;
@@ -239,7 +240,7 @@ merge_bwd_f_kernel(const float *__restrict__ d_out, const float *__restrict__ ta
             const int eu = __shfl_sync(0xffffffffu, e, u);
             const float tx = __shfl_sync(0xffffffffu, t.x, u), ty = __shfl_sync(0xffffffffu, t.y, u);
             const float tz = __shfl_sync(0xffffffffu, t.z, u), tw = __shfl_sync(0xffffffffu, t.w, u);
-            const float *gi = gb + int64_t(eu / M) * 4 * C;
+            const float *gi = gb + int64_t(divM.div(uint32_t(eu))) * 4 * C;
             float g0[CPL], g1[CPL], g2[CPL], g3[CPL];
             mg_load<float, CPL>(gi, g0);
             mg_load<float, CPL>(gi + C, g1);
@@ -347,7 +348,8 @@ extern "C" int affb200_merge_bwd(const float *d_out, const float *table, const i
                 if (int e = check_launch("merge_bwd_w")) return e;
                 if (!d_feat) return int(AFFB200_OK);
                 merge_bwd_f_kernel<TF, TL, CPL><<<unsigned((n_rows + kMW - 1) / kMW), kMT, 0, st>>>(
-                    d_out, table, pe_idx, mask, (const TL *)lp, csr_off, csr_ent, (TF *)d_feat, n_rows, int(Nq), int(Nk), int(M));
+                    d_out, table, pe_idx, mask, (const TL *)lp, csr_off, csr_ent, (TF *)d_feat, n_rows, int(Nq), int(Nk), int(M),
+                    FastDiv{uint32_t(M)});
                 return check_launch("merge_bwd_f");
             });
         });
