@@ -191,6 +191,13 @@ int affb200_sfc_cluster_tables(const float *pos, int64_t B, int64_t N, int64_t m
                                float plw, float plh, const int32_t *grid_rank, const float *prev, const float *next,
                                int64_t *ranking, float *pos_sorted, float *mean, void *work, void *stream);
 
+/* Token reorder of a stage (reference models/aff_transformer.py:466,472 `feat[b, reorder]`; models/mixres_neighbour.py:
+ * 503-504,514-515): rows of row_bytes (multiple of 16) bytes.  scatter == 0: dst[b][i] = src[b][perm[b][i]];
+ * scatter == 1 (the adjoint, for the backward pass): dst[b][perm[b][i]] = src[b][i].  perm [B][N] int64 must be a
+ * permutation of 0..N-1 per b (pos_ranking is), which makes the scatter conflict-free and complete. */
+int affb200_permute_rows(const void *src, const int64_t *perm, void *dst, int64_t B, int64_t N, int64_t row_bytes,
+                         int scatter, void *stream);
+
 /* Stable argsort of fp32 rows: order[b][r] = index of the r-th element; replaces torch.sort(...)[1] on CUDA
  * (reference models/mixres_neighbour.py:735, models/point_utils.py:159). */
 size_t affb200_argsort_work_bytes(int64_t B, int64_t N);

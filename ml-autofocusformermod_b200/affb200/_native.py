@@ -48,6 +48,7 @@ SIGNATURES = {
     "affb200_sfc_cluster": (_int, [_ptr] + [_i64] * 5 + [_ptr] * 5),
     "affb200_curve_key": (_int, [_ptr, _i64, _i64, _i64, _i64, _int, _ptr, _ptr]),
     "affb200_sfc_cluster_tables": (_int, [_ptr] + [_i64] * 5 + [ctypes.c_float, ctypes.c_float] + [_ptr] * 8),
+    "affb200_permute_rows": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _int, _ptr]),
     "affb200_argsort_work_bytes": (ctypes.c_size_t, [_i64, _i64]),
     "affb200_argsort_f32": (_int, [_ptr, _i64, _i64, _int, _ptr, _ptr, _ptr]),
     "affb200_nearest_l1": (_int, [_ptr, _ptr] + [_i64] * 3 + [_ptr, _ptr]),

@@ -48,6 +48,7 @@ class CudaOps:
         self.build_nbhd = P.build_nbhd
         self.select_merge_centers = P.select_merge_centers
         self.gather_rows = P.gather_rows
+        self.reorder_tokens = P.reorder_tokens
         self.fused_attention = None  # set by affb200.fused when available
 
 
@@ -84,6 +85,12 @@ def compact_table(pe_idx, table):
 
 
 COMPACT_ROWS_ABOVE = 32768   # tables larger than this are compacted per stage (0 = always)
+
+
+def _gather_tokens(feat, reorder):
+    """feat[b, reorder] (reference aff_transformer.py:466,472) with stock indexing: operator sets without a
+    `reorder_tokens` entry (the CPU oracle set) use this."""
+    return feat.gather(1, reorder.expand(-1, -1, feat.shape[2]))
 
 
 def _ln(ops, mod, x):
@@ -293,7 +300,7 @@ class BasicLayer(nn.Module):
                 pos, reorder, member_idx, cluster_mask, pe_idx, pre_table = self._index(pos, h, w, rel_pos_width, ops,
                                                                                         pre_table)
             if reorder is not None:  # store tokens of a cluster together
-                feat = feat.gather(1, reorder.expand(-1, -1, c))
+                feat = getattr(ops, 'reorder_tokens', _gather_tokens)(feat, reorder)
         for blk in self.blocks:
             feat = blk(feat, member_idx, cluster_mask, pe_idx, global_attn, pre_table, ops)
         if self.downsample is not None:

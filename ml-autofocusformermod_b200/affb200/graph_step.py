@@ -159,6 +159,7 @@ class GraphedForward:
         self.recaptures = 0
         self.max_recaptures = 8
         _plan.guard_tensor(self.device)
+        self.refresh()
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):
@@ -167,6 +168,17 @@ class GraphedForward:
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
         self._capture()
+
+    def refresh(self):
+        """Low-precision shadows of the (frozen) parameters, so that the forward does not cast every weight at every
+        use (linear_ops.low_precision).  Call again after loading new weights."""
+        for p in self.model.parameters():
+            if p.dtype == torch.float32:
+                sh = getattr(p, "_affb200_lp", None)
+                if sh is not None and sh.dtype == self.autocast_dtype and sh.shape == p.shape:
+                    sh.copy_(p.detach())
+                else:
+                    p._affb200_lp = p.detach().to(self.autocast_dtype)
 
     def _fwd(self):
         with torch.no_grad(), torch.autocast("cuda", dtype=self.autocast_dtype):

@@ -18,7 +18,7 @@ import math
 import torch
 import torch.nn as nn
 
-from .aff_transformer import ClusterTransformerBlock, build_pe_lookup, compact_table, default_ops
+from .aff_transformer import ClusterTransformerBlock, _gather_tokens, build_pe_lookup, compact_table, default_ops
 
 # assumes largest input resolution is 2048 x 2048 (reference mixres_neighbour.py:13-15)
 REL_POS_WIDTH = 2048 // 4 - 1
@@ -93,7 +93,7 @@ class BasicLayer(nn.Module):
             else:
                 pos, reorder, member_idx, cluster_mask, pe_idx = self._index(pos, h, w, ops)
             if reorder is not None:
-                feat = feat.gather(1, reorder.expand(-1, -1, c))
+                feat = getattr(ops, 'reorder_tokens', _gather_tokens)(feat, reorder)
                 pos_scale = pos_scale.gather(1, reorder)
         if self.compact:
             pe_idx, table = compact_table(pe_idx, table)

@@ -12,6 +12,7 @@ sm_100a kernels of libaffb200.so on the current CUDA stream (C ABI: include/affb
                                                              reference aff_transformer.py:289-326
   gather_rows(src, idx)                                      reference aff_transformer.py:335-338
   find_pos_org_order(pos_org, pos_shuffled)                  reference maskfiner_up_down.py:150-154
+  reorder_tokens(feat, pos_ranking)                          reference aff_transformer.py:466,472
 """
 import math
 
@@ -266,3 +267,39 @@ def gather_rows(src, idx):
         N.check(N.LIB.affb200_gather_rows_i64(N.p(src), N.p(idx), b, n, K, M, N.p(out), N.stream_ptr(dev)),
                 "gather_rows")
     return out
+
+
+class PermuteRowsFunction(torch.autograd.Function):
+    """feat[b, perm[b]] with the adjoint scatter as backward (perm is a permutation per image)."""
+
+    @staticmethod
+    def forward(ctx, feat, perm):
+        ctx.save_for_backward(perm)
+        return _permute_rows(feat, perm, 0)
+
+    @staticmethod
+    def backward(ctx, d_out):
+        (perm,) = ctx.saved_tensors
+        return _permute_rows(d_out.contiguous(), perm, 1), None
+
+
+def _permute_rows(x, perm, scatter):
+    b, n, c = x.shape
+    dev = x.device
+    with torch.cuda.device(dev):
+        out = torch.empty_like(x)
+        N.check(N.LIB.affb200_permute_rows(N.p(x), N.p(perm), N.p(out), b, n, c * x.element_size(), scatter,
+                                           N.stream_ptr(dev)), "permute_rows")
+    return out
+
+
+def reorder_tokens(feat, pos_ranking):
+    """feat [B, N, C] reordered by pos_ranking [B, N, 1] (or [B, N]) as `feat[b, reorder]` does in the reference
+    (aff_transformer.py:466,472).  pos_ranking must be a permutation per image (space_filling_cluster's is)."""
+    if not feat.is_cuda:
+        raise RuntimeError("feat must be a CUDA tensor")
+    b, n, c = feat.shape
+    perm = pos_ranking.reshape(b, n)
+    if (c * feat.element_size()) % 16 != 0 or feat.numel() == 0:
+        return feat.gather(1, perm.unsqueeze(2).expand(-1, -1, c))
+    return PermuteRowsFunction.apply(feat.contiguous(), perm.contiguous())

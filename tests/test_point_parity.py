@@ -260,3 +260,23 @@ def test_find_pos_org_order_matches_reference_expression(case):
         db = torch.cat([shuf[:, : n // 2], shuf[:, : n // 4]], 1)    # duplicates, and half of the points missing
         out = find_pos_org_order(org.cuda(), db.cuda())
         assert torch.equal(out.cpu(), O.find_pos_org_order_ref(org, db))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_reorder_tokens_matches_indexing_and_its_backward(dtype):
+    """feat[b, reorder] (aff_transformer.py:466,472) through affb200_permute_rows: forward bit-equal to stock indexing,
+    backward (conflict-free scatter) bit-equal to autograd's scatter_add of the same permutation."""
+    from affb200.point_utils import reorder_tokens
+    g = torch.Generator().manual_seed(12)
+    for (B, n, c) in ((3, 627, 64), (2, 3136, 32), (1, 5, 8), (2, 125, 256)):
+        perm = torch.stack([torch.randperm(n, generator=g) for _ in range(B)]).cuda()
+        x = torch.randn(B, n, c, generator=g).to(dtype).cuda().requires_grad_(True)
+        y = reorder_tokens(x, perm.unsqueeze(2))
+        ref = x.detach().clone().requires_grad_(True)
+        yr = ref.gather(1, perm.unsqueeze(2).expand(-1, -1, c))
+        assert torch.equal(y, yr)
+        go = torch.randn(B, n, c, generator=g).to(dtype).cuda()
+        y.backward(go)
+        yr.backward(go)
+        assert torch.equal(x.grad, ref.grad)
