@@ -34,6 +34,7 @@ class CudaOps:
         self.layer_norm = L.layer_norm
         self.layer_norm_fork = L.layer_norm_fork
         self.batch_norm_act = L.batch_norm_act
+        self.conv_batch_norm_act = L.conv_batch_norm_act
         self.linear = LI.linear
         self.linear_gelu = LI.linear_gelu
         self.residual_add = RO.residual_add
@@ -331,8 +332,11 @@ class PatchEmbed(nn.Module):
             # per-channel BatchNorm reductions run over contiguous channel vectors, and the token matrix [b, h*w, c]
             # below is then a view instead of a transpose copy
             x = x.contiguous(memory_format=torch.channels_last)
-        x = self.proj1(x)
-        x = self.act1(self.bn(x)) if ops is None else ops.batch_norm_act(x, self.bn)
+        if ops is not None and hasattr(ops, 'conv_batch_norm_act'):
+            x = ops.conv_batch_norm_act(x, self.proj1, self.bn)
+        else:
+            x = self.proj1(x)
+            x = self.act1(self.bn(x)) if ops is None else ops.batch_norm_act(x, self.bn)
         x = self.proj2(x)
         b, c, h, w = x.shape
         x = x.flatten(2).transpose(1, 2)

@@ -3,6 +3,7 @@
 
   layer_norm(x, weight, bias, eps, out_dtype=None) -> LayerNorm(x) in `out_dtype`
   batch_norm_act(x, bn, gelu=True)                 -> GELU(bn(x)) for a training-mode nn.BatchNorm2d `bn`
+  conv_batch_norm_act(x, conv, bn, gelu=True)      -> GELU(bn(conv(x))) with the conv bias folded into the batch statistics
 
 The reference uses nn.LayerNorm (models/aff_transformer.py:199-200,284), which autocast evaluates in fp32: the bf16
 residual stream is copied to fp32, normalised, and copied back to bf16 by the next Linear.  This operator reads x in
@@ -184,6 +185,38 @@ def batch_norm_act(x, bn, gelu=True):
     with torch.no_grad():
         bn.num_batches_tracked.add_(1)
     return BatchNormActFunction.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.momentum, bn.eps, gelu)
+
+
+class _ZeroGradFor(torch.autograd.Function):
+    """y -> y, registering `p` as an input whose gradient is exactly zero."""
+
+    @staticmethod
+    def forward(ctx, y, p):
+        ctx.meta = (p.shape, p.dtype, p.device)
+        return y.view_as(y)
+
+    @staticmethod
+    def backward(ctx, g):
+        shape, dtype, device = ctx.meta
+        return g, torch.zeros(shape, dtype=dtype, device=device)
+
+
+def conv_batch_norm_act(x, conv, bn, gelu=True):
+    """GELU(bn(conv(x))) for the stem's conv -> BatchNorm pair (reference aff_transformer.py:541-543).  A per-channel
+    constant added before a training-mode BatchNorm cancels in (x - mean): the convolution runs without its bias (no
+    bias-add pass over the activation, no bias-gradient reduction over it in the backward), the batch mean that feeds
+    `running_mean` gets the bias back, and the bias receives the gradient it has in exact arithmetic: zero.  Evaluation
+    mode and unsupported layouts run conv (with bias) -> bn -> gelu through the stock operators."""
+    if conv.bias is None or not (x.is_cuda and bn.training and bn.affine and bn.track_running_stats
+                                 and bn.momentum is not None and conv.out_channels in (8, 16, 32, 64, 128)):
+        return batch_norm_act(conv(x), bn, gelu)
+    y = conv._conv_forward(x, conv.weight, None)
+    if not (y.dtype in _OK and y.numel() > 0 and y.is_contiguous(memory_format=torch.channels_last)):
+        return batch_norm_act(y + conv.bias.to(y.dtype).view(1, -1, 1, 1), bn, gelu)
+    out = batch_norm_act(y, bn, gelu)
+    with torch.no_grad():
+        bn.running_mean.add_(conv.bias.detach().to(bn.running_mean.dtype), alpha=bn.momentum)
+    return _ZeroGradFor.apply(out, conv.bias) if conv.bias.requires_grad else out
 
 
 def layer_norm_fork(x, weight, bias, eps=1e-5, out_dtype=None):

@@ -100,3 +100,44 @@ def test_batch_norm_act_eval_mode_uses_running_statistics():
     x1 = x.cuda().contiguous(memory_format=torch.channels_last)
     assert torch.equal(batch_norm_act(x1, bn), torch.nn.functional.gelu(bn(x1)))
     assert int(bn.num_batches_tracked) == 0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_conv_batch_norm_act_folds_the_conv_bias(dtype):
+    """conv -> BatchNorm(train) -> GELU with the conv bias dropped from the activation and put back into running_mean:
+    output, running statistics and gradients of the stock chain; the conv bias gets an exactly-zero gradient (the stock
+    chain's is rounding noise around zero); evaluation mode keeps the bias in the activation."""
+    from affb200.norm_ops import conv_batch_norm_act
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(8, 3, 32, 32, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    go = torch.randn(8, 32, 16, 16, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    mods = []
+    for _ in range(2):
+        torch.manual_seed(5)
+        conv = torch.nn.Conv2d(3, 32, 3, 2, 1).cuda()
+        with torch.no_grad():
+            conv.bias.normal_(0, 0.5)
+        _, _, w, b = _case((1, 32, 1, 1), torch.float32, 6)
+        mods.append((conv, _bn(32, w, b, "cuda")))
+    ac = dict(device_type="cuda", dtype=torch.bfloat16, enabled=dtype == torch.bfloat16)
+    (c1, b1), (c2, b2) = mods
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    with torch.autocast(**ac):
+        y1 = conv_batch_norm_act(x1, c1, b1)
+        y2 = torch.nn.functional.gelu(b2(c2(x2)))
+    assert y1.dtype == y2.dtype
+    y1.backward(go.to(y1.dtype))
+    y2.backward(go.to(y2.dtype))
+    assert_close(y1, y2.double(), dtype, "fwd")
+    assert_close(x1.grad, x2.grad.double(), dtype, "dx")
+    assert_close(c1.weight.grad, c2.weight.grad.double(), dtype, "d conv.weight")
+    assert_close(b1.weight.grad, b2.weight.grad.double(), dtype, "d gamma")
+    assert_close(b1.bias.grad, b2.bias.grad.double(), dtype, "d beta")
+    assert c1.bias.grad is not None and c1.bias.grad.abs().max().item() == 0
+    assert c2.bias.grad.abs().max().item() < (1e-3 if dtype == torch.float32 else 0.5)
+    assert_close(b1.running_mean, b2.running_mean.double(), dtype, "running_mean")
+    assert_close(b1.running_var, b2.running_var.double(), dtype, "running_var")
+    assert int(b1.num_batches_tracked) == 1
+    b1.eval()
+    with torch.no_grad():
+        assert torch.equal(conv_batch_norm_act(x, c1, b1), torch.nn.functional.gelu(b1(c1(x))))
