@@ -126,6 +126,36 @@ class Mlp(nn.Module):
         return self.drop(_lin(ops, self.fc2, self.drop(h)))
 
 
+_global_nbhd = {}
+
+
+def global_as_neighbourhood(pe_idx):
+    """Global attention (every token attends to all n tokens; reference aff_transformer.py:112-113,141-142) written as
+    neighbourhood attention so that the fused operator can run it: -> (member_idx, mask, pe_idx), each b x n x M with
+    M = n rounded up to a multiple of 8, member_idx[., ., j] = j, the padding slots masked (they get the -100 bias the
+    reference gives padded cluster slots, i.e. weight exp(-100)), or None when n is too large for the operator.
+    Cached on the pe_idx tensor (one stage's blocks share it); the index / mask tensors are static per (b, n)."""
+    hit = getattr(pe_idx, "_affb200_gnb", None)
+    if hit is not None and hit[0] == pe_idx._version:
+        return hit[1] if hit[1] is None or hit[1][2] is not None else (hit[1][0], hit[1][1], pe_idx)
+    b, n, n2 = pe_idx.shape
+    M = (n + 7) // 8 * 8
+    res = None
+    if n == n2 and M <= 96 and pe_idx.is_cuda:
+        key = (b, n, str(pe_idx.device))
+        if key not in _global_nbhd:
+            ar = torch.arange(M, device=pe_idx.device)
+            member = torch.where(ar < n, ar, torch.zeros_like(ar)).expand(b, n, M).contiguous()
+            mask = (ar < n).long().expand(b, n, M).contiguous() if M != n else None
+            if len(_global_nbhd) > 8:
+                _global_nbhd.clear()
+            _global_nbhd[key] = (member, mask)
+        member, mask = _global_nbhd[key]
+        res = (member, mask, torch.nn.functional.pad(pe_idx, (0, M - n)) if M != n else None)
+    pe_idx._affb200_gnb = (pe_idx._version, res)      # (no reference to pe_idx itself: no cycle)
+    return res if res is None or res[2] is not None else (member, mask, pe_idx)
+
+
 class ClusterAttention(nn.Module):
     """Attention of every token over the members of its nearest clusters (+ a learned blank token), with a
     relative-position bias looked up by pe_idx (reference aff_transformer.py:54-160)."""
@@ -149,13 +179,19 @@ class ClusterAttention(nn.Module):
         c_ = c // h
         q_lin = _lin(ops, self.q, feat)
         kv = _lin(ops, self.kv, feat)
-        if not global_attn and ops.fused_attention is not None and self.attn_drop.p == 0.:
-            # the bias table pos_embed(pre_table) is evaluated inside; its gradient goes straight to weight / bias
-            out = ops.fused_attention(q_lin, kv, h, self.scale, member_idx, pe_idx, cluster_mask, None,
-                                      self.blank_k, self.blank_v,
-                                      pos_embed=(pre_table, self.pos_embed.weight, self.pos_embed.bias))
-            if out is not None:                                     # b n c; None when unsupported
-                return self.proj_drop(_lin(ops, self.proj, out))
+        if ops.fused_attention is not None and self.attn_drop.p == 0.:
+            # global attention over a small token set is neighbourhood attention with member_idx = all tokens
+            if not global_attn:
+                nb = (member_idx, cluster_mask, pe_idx)
+            else:
+                nb = global_as_neighbourhood(pe_idx) if q_lin.dtype in (torch.float16, torch.bfloat16) else None
+            if nb is not None:
+                # the bias table pos_embed(pre_table) is evaluated inside; its gradient goes straight to weight / bias
+                out = ops.fused_attention(q_lin, kv, h, self.scale, nb[0], nb[2], nb[1], None,
+                                          self.blank_k, self.blank_v,
+                                          pos_embed=(pre_table, self.pos_embed.weight, self.pos_embed.bias))
+                if out is not None:                                     # b n c; None when unsupported
+                    return self.proj_drop(_lin(ops, self.proj, out))
         pe_table = self.pos_embed(pre_table)                       # T*T x h
         q = (q_lin * self.scale).reshape(b, n, h, c_).permute(0, 2, 1, 3)   # b h n c_
         kv = kv.view(b, n, h, 2, c_).permute(3, 0, 2, 1, 4)        # 2 b h n c_

@@ -16,6 +16,7 @@ pass in the backward (csrc/fused_attn_img.cu).  AFFB200_FUSED_IMG=0 forces the f
 """
 import os
 import ctypes
+import weakref
 
 import torch
 from torch.autograd import Function
@@ -85,6 +86,8 @@ def _pe_features(pre_table, dt):
     Linear that generates the bias table (reference aff_transformer.py:78,125: pos_embed(pre_table)); cached."""
     key = (pre_table.data_ptr(), pre_table._version, dt)
     hit = _feat_cache.get(key)
+    if hit is not None and hit[2]() is not pre_table:   # a freed (compacted) table's address reused by another one
+        hit = None
     if hit is None:
         src = pre_table.detach()
         lp = src.to(dt) if dt is not None else src.float()
@@ -94,8 +97,8 @@ def _pe_features(pre_table, dt):
         feat8[:, F] = 1.0
         if len(_feat_cache) > 16:
             _feat_cache.clear()
-        hit = _feat_cache[key] = (lp.contiguous(), feat8)
-    return hit
+        hit = _feat_cache[key] = (lp.contiguous(), feat8, weakref.ref(pre_table))
+    return hit[:2]
 
 
 def _table_of(pe_table, pe_w, pe_b, pe_feat):

@@ -201,3 +201,47 @@ def test_fused_attention_pos_embed_form(case, family, autocast, monkeypatch):
     tol = 1e-4
     assert rel_err(lin[3], dT.t() @ feat) < tol, rel_err(lin[3], dT.t() @ feat)
     assert rel_err(lin[4], dT.sum(0)) < tol, rel_err(lin[4], dT.sum(0))
+
+
+@pytest.mark.parametrize("n,heads,dim", [(25, 16, 512), (32, 4, 64), (7, 2, 64)])
+def test_global_attention_runs_through_the_fused_operator(n, heads, dim):
+    """A stage whose token count is below the neighbourhood size attends globally (reference aff_transformer.py:
+    112-113,141-142: q @ k^T, softmax with the blank token, attn @ v).  ClusterAttention hands that to the fused
+    operator as a neighbourhood of all tokens (padded to a multiple of 8 with masked slots); output and gradients
+    match the stock chain in bf16 (1e-2 per operator; chain of three)."""
+    from affb200.aff_transformer import ClusterAttention, CudaOps, build_pe_lookup
+    from affb200 import fused as fa
+    B = 6
+    g = torch.Generator().manual_seed(n)
+    w, tw, table = build_pe_lookup(64)
+    table = table.cuda()
+    cells = torch.stack([torch.randperm(15 * 15, generator=g)[:n] for _ in range(B)])
+    pos = torch.stack([cells % 15, cells // 15], 2).float().cuda()
+    rel = (pos[:, None, :, :] + w) - pos[:, :, None, :]
+    pe_idx = (rel[..., 1] * tw + rel[..., 0]).long()
+    feat = torch.randn(B, n, dim, generator=g).cuda()
+    go = torch.randn(B, n, dim, generator=g).cuda()
+    torch.manual_seed(1)
+    attn = ClusterAttention(dim, heads).cuda()
+    res, hits = [], []
+
+    def counting(*a, **kw):
+        out = fa.fused_cluster_attention(*a, **kw)
+        hits.append(out is not None)
+        return out
+    for fused in (False, True):
+        ops = CudaOps()
+        ops.fused_attention = counting if fused else None
+        for p in attn.parameters():
+            p.grad = None
+        x = feat.clone().requires_grad_(True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            y = attn(x, None, None, pe_idx, True, table, ops)
+        y.backward(go.to(y.dtype))
+        res.append((y.float(), x.grad, {k: p.grad.clone() for k, p in attn.named_parameters()}))
+    assert hits == [True]
+    (y0, dx0, g0), (y1, dx1, g1) = res
+    assert rel_err(y1, y0) < 2e-2, rel_err(y1, y0)
+    assert rel_err(dx1, dx0) < 3e-2, rel_err(dx1, dx0)
+    for k in g0:
+        assert rel_err(g1[k], g0[k]) < 3e-2, (k, rel_err(g1[k], g0[k]))
