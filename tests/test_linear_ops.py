@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("shape", [(1, 64), (37, 64), (5000, 64), (100003, 128), (777, 96), (4096, 256), (300, 1024),
-                                   (64, 2048), (9, 8)])
+                                   (64, 2048), (9, 8), (32000, 768), (802816, 64), (700, 4096), (300, 4104)])
 def test_col_sum(shape, dtype):
     from affb200.linear_ops import col_sum
     g = torch.Generator().manual_seed(shape[0] + shape[1])
@@ -20,6 +20,31 @@ def test_col_sum(shape, dtype):
     assert_close(out, x.double().sum(0), torch.float32, "col_sum")
     # fixed summation order: bit-reproducible
     assert torch.equal(out, col_sum(x.cuda()))
+
+
+def test_col_sum_accumulates_and_is_exact_across_calls_and_streams():
+    """`into`: sums are added in place; back-to-back calls of different shapes on one stream and calls on a second
+    stream give the same bits."""
+    from affb200.linear_ops import col_sum
+    g = torch.Generator(device="cuda").manual_seed(3)
+    xs = [torch.randn(r, c, device="cuda", generator=g).bfloat16() for r, c in
+          [(32000, 256), (32000, 768), (6400, 512), (160512, 128), (32000, 256), (1, 4096), (33, 8)]]
+    want = [x.double().sum(0) for x in xs]
+    for _ in range(3):
+        for x, w in zip(xs, want):
+            assert_close(col_sum(x), w, torch.float32, "col_sum")
+    base = torch.randn(256, device="cuda", generator=g)
+    acc = base.clone()
+    assert col_sum(xs[0], into=acc) is acc
+    assert_close(acc, base.double() + want[0], torch.float32, "col_sum into")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        outs = [col_sum(x) for x in xs]
+    mains = [col_sum(x) for x in xs]
+    torch.cuda.synchronize()
+    for a, b in zip(outs, mains):
+        assert torch.equal(a, b)
 
 
 def test_col_sum_edge_cases():
