@@ -376,13 +376,13 @@ int affb200_gelu_bwd(const void *dy, const void *x, void *dx, int64_t R, int64_t
                      float *col_sums, int accumulate, float *work, void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
- * Residual connection with stochastic depth in one pass: out[b][...] = a[b][...] + x[b][...] * s[b]  (a may be NULL:
- * out = x * s[b], the backward of the x branch).  Reference: `feat = shortcut + drop_path(feat)`
+ * Residual connection with stochastic depth in one pass: out[b][...] = a[b][...] + x[b][...] * (s[b] * s_scale)  (a may
+ * be NULL: out = x * (s[b] * s_scale), the backward of the x branch; s = the 0/1 keep draw, s_scale = 1/(1-p)).  Reference: `feat = shortcut + drop_path(feat)`
  * (models/aff_transformer.py:224-229).  a/x/out [B][per_sample] of `dtype` (f32/f16/bf16), s [B] fp32; per_sample a
  * multiple of 16 bytes.  The product is rounded to `dtype` before the add, as in the reference's two operations.
  * ---------------------------------------------------------------------------------------------------------- */
-int affb200_scale_add(const void *a, const void *x, const float *s, void *out, int64_t B, int64_t per_sample, int dtype,
-                      void *stream);
+int affb200_scale_add(const void *a, const void *x, const float *s, float s_scale, void *out, int64_t B,
+                      int64_t per_sample, int dtype, void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Merge half of ClusterMerging without materialising the PointConv weights (reference

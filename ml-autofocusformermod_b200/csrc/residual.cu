@@ -2,7 +2,7 @@
 // Reference: `feat = shortcut + self.drop_path(feat)` (models/aff_transformer.py:224-229; timm DropPath scales the
 // kept samples of the batch by 1/(1-p) and zeroes the dropped ones).  Stock PyTorch runs a broadcast multiply
 // (scalar-indexed, not vectorised) and an add; the backward another broadcast multiply.  Here the per-sample factor
-// s[b] (fp32, 0 or 1/(1-p)) is applied inside the residual add with 16-byte accesses; the backward of the x branch is
+// s[b] * s_scale (fp32: the 0/1 keep draw times 1/(1-p)) is applied inside the residual add with 16-byte accesses; the backward of the x branch is
 // the same kernel without `a`.
 #include "common.cuh"
 #include <algorithm>
@@ -11,11 +11,11 @@ namespace affb200 {
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-scale_add_kernel(const T *__restrict__ a, const T *__restrict__ x, const float *__restrict__ s, T *__restrict__ out,
-                 int64_t per_sample_vec, int64_t total_vec) {
+scale_add_kernel(const T *__restrict__ a, const T *__restrict__ x, const float *__restrict__ s, float s_scale,
+                 T *__restrict__ out, int64_t per_sample_vec, int64_t total_vec) {
     constexpr int V = 16 / sizeof(T);
     for (int64_t i = int64_t(blockIdx.x) * 256 + threadIdx.x; i < total_vec; i += int64_t(gridDim.x) * 256) {
-        const float sc = __ldg(s + i / per_sample_vec);
+        const float sc = __ldg(s + i / per_sample_vec) * s_scale;
         float xv[V], av[V];
         load_vec<T, V>(x + i * V, xv);
         if (a) {
@@ -35,7 +35,7 @@ scale_add_kernel(const T *__restrict__ a, const T *__restrict__ x, const float *
 
 using namespace affb200;
 
-extern "C" int affb200_scale_add(const void *a, const void *x, const float *s, void *out, int64_t B,
+extern "C" int affb200_scale_add(const void *a, const void *x, const float *s, float s_scale, void *out, int64_t B,
                                  int64_t per_sample, int dtype, void *stream) {
     if (B < 0 || per_sample < 0) { set_error("scale_add: negative size"); return AFFB200_E_ARG; }
     if (B * per_sample == 0) return AFFB200_OK;
@@ -53,7 +53,7 @@ extern "C" int affb200_scale_add(const void *a, const void *x, const float *s, v
             }
             const int64_t pv = per_sample / V, tv = B * pv;
             const unsigned grid = unsigned(std::min<int64_t>((tv + 255) / 256, int64_t(kNumSMs) * 16));
-            scale_add_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T *)a, (const T *)x, s, (T *)out, pv, tv);
+            scale_add_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T *)a, (const T *)x, s, s_scale, (T *)out, pv, tv);
             return check_launch("scale_add");
         }
     });
