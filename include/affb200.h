@@ -340,7 +340,9 @@ int affb200_layer_norm_bwd(const void *dy, const void *x, const float *gamma, co
  * fwd: batch statistics (biased variance for the normalisation) -> mean/rstd [C]; running_mean/running_var (may be
  * NULL) are updated in place with `momentum` and the unbiased variance; y = act(gamma*(x-mean)*rstd + beta).
  * bwd: dx, dgamma, dbeta [C] (overwritten; may be NULL) from dy, x and the saved statistics; the GELU derivative is
- * recomputed from x.  work = affb200_batch_norm_work_floats(R, C) floats of scratch (either direction).
+ * recomputed from x — per element with erf/exp, or, for f16/bf16 when gelu_bwd_tab (the bwd_tab of affb200_gelu_tables
+ * for `dtype`; may be NULL) is given, looked up in it.  work = affb200_batch_norm_work_floats(R, C) floats of scratch
+ * (either direction).
  * ---------------------------------------------------------------------------------------------------------- */
 int64_t affb200_batch_norm_work_floats(int64_t R, int64_t C);
 int affb200_batch_norm_fwd(const void *x, const float *gamma, const float *beta, float *running_mean,
@@ -348,7 +350,7 @@ int affb200_batch_norm_fwd(const void *x, const float *gamma, const float *beta,
                            float *work, int64_t R, int64_t C, int dtype, void *stream);
 int affb200_batch_norm_bwd(const void *dy, const void *x, const float *gamma, const float *beta, const float *mean,
                            const float *rstd, int gelu, void *dx, float *dgamma, float *dbeta, float *work, int64_t R,
-                           int64_t C, int dtype, void *stream);
+                           int64_t C, int dtype, const float *gelu_bwd_tab, void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Column sums out[c] = sum_r x[r][c] in fp32 of a row-major [R][C] matrix (f32/f16/bf16, C multiple of 8): the bias

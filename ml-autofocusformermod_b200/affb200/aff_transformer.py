@@ -37,6 +37,7 @@ class CudaOps:
         self.conv_batch_norm_act = L.conv_batch_norm_act
         self.linear = LI.linear
         self.linear_gelu = LI.linear_gelu
+        self.linear_pair = LI.linear_pair
         self.residual_add = RO.residual_add
         from . import merge_ops as MO
         self.merge_wf = MO.merge_wf
@@ -177,8 +178,11 @@ class ClusterAttention(nn.Module):
         b, n, c = feat.shape
         h = self.num_heads
         c_ = c // h
-        q_lin = _lin(ops, self.q, feat)
-        kv = _lin(ops, self.kv, feat)
+        if hasattr(ops, 'linear_pair'):     # one dx in the backward instead of two and their sum
+            q_lin, kv = ops.linear_pair(feat, self.q.weight, self.q.bias, self.kv.weight, self.kv.bias)
+        else:
+            q_lin = _lin(ops, self.q, feat)
+            kv = _lin(ops, self.kv, feat)
         if ops.fused_attention is not None and self.attn_drop.p == 0.:
             # global attention over a small token set is neighbourhood attention with member_idx = all tokens
             if not global_attn:
@@ -367,7 +371,9 @@ class PatchEmbed(nn.Module):
             # NHWC through the stem: cuDNN's native layout (no NCHW<->NHWC conversion kernels around the convs), the
             # per-channel BatchNorm reductions run over contiguous channel vectors, and the token matrix [b, h*w, c]
             # below is then a view instead of a transpose copy
-            x = x.contiguous(memory_format=torch.channels_last)
+            # (under autocast the cast to the compute dtype rides on the same copy: one pass over the images, not two)
+            dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+            x = x.to(dtype=dt, memory_format=torch.channels_last)
         if ops is not None and hasattr(ops, 'conv_batch_norm_act'):
             x = ops.conv_batch_norm_act(x, self.proj1, self.bn)
         else:

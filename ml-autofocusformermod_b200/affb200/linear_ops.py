@@ -182,6 +182,68 @@ def linear(x, weight, bias=None):
     return LinearFunction.apply(x, weight, bias)
 
 
+def _param_grads(dy2, x2, weight, bias, wdt, bdt, need_w, need_b):
+    """(dw, db) of y = x W^T + b for the caller to return — None where the gradient went straight into the
+    parameter's fp32 .grad (weight: GEMM accumulating into it; bias: column sums added to it)."""
+    dw = db = None
+    if need_w:
+        g = _sink(weight) if dy2.dtype != torch.float32 else None
+        if g is not None:
+            torch.ops.aten.addmm.dtype_out(g, dy2.t(), x2, torch.float32, out=g)   # g += dy^T x, fp32 out
+        else:
+            dw = (dy2.t() @ x2).to(wdt)
+    if need_b:
+        g = _sink(bias)
+        if g is not None and dy2.dtype in _OK and dy2.shape[1] % 8 == 0 and g.data_ptr() % 16 == 0:
+            col_sum(dy2, into=g)
+        else:
+            db = col_sum(dy2).to(bdt)
+    return dw, db
+
+
+class LinearPairFunction(Function):
+    """(x W1^T + b1, x W2^T + b2) for two Linears on one input (q and kv of ClusterAttention, reference
+    aff_transformer.py:85-86,96-100).  The backward forms dx = dy1 W1 + dy2 W2 by letting the second GEMM accumulate
+    onto the first one's output, where autograd would write two dx tensors and add them in another pass."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2):
+        if not x.is_cuda:
+            raise RuntimeError("x must be a CUDA tensor")
+        dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+        x2 = x.reshape(-1, x.shape[-1]).to(dt)
+        wb1, wb2 = low_precision(w1, dt), low_precision(w2, dt)
+        with torch.autocast("cuda", enabled=False):
+            y1 = torch.addmm(low_precision(b1, dt), x2, wb1.t())
+            y2 = torch.addmm(low_precision(b2, dt), x2, wb2.t())
+        ctx.save_for_backward(x2, wb1, wb2)
+        ctx.meta = (x.shape, x.dtype, w1.dtype, b1.dtype, w2.dtype, b2.dtype)
+        ctx.params = (w1, b1, w2, b2)
+        return y1.reshape(*x.shape[:-1], w1.shape[0]), y2.reshape(*x.shape[:-1], w2.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy1, dy2):
+        x2, wb1, wb2 = ctx.saved_tensors
+        xshape, xdt, w1dt, b1dt, w2dt, b2dt = ctx.meta
+        w1, b1, w2, b2 = ctx.params
+        g1 = dy1.reshape(-1, dy1.shape[-1]).to(wb1.dtype).contiguous()
+        g2 = dy2.reshape(-1, dy2.shape[-1]).to(wb2.dtype).contiguous()
+        dx = None
+        with torch.cuda.device(g1.device):   # autograd's worker thread may not have a current device yet
+            if ctx.needs_input_grad[0]:
+                dx = (g1 @ wb1).addmm_(g2, wb2).reshape(xshape).to(xdt)
+            dw1, db1 = _param_grads(g1, x2, w1, b1, w1dt, b1dt, ctx.needs_input_grad[1], ctx.needs_input_grad[2])
+            dw2, db2 = _param_grads(g2, x2, w2, b2, w2dt, b2dt, ctx.needs_input_grad[3], ctx.needs_input_grad[4])
+        return dx, dw1, db1, dw2, db2
+
+
+def linear_pair(x, w1, b1, w2, b2):
+    """(linear(x, w1, b1), linear(x, w2, b2)) with one dx in the backward."""
+    if b1 is None or b2 is None:
+        return linear(x, w1, b1), linear(x, w2, b2)
+    return LinearPairFunction.apply(x, w1, b1, w2, b2)
+
+
 class LinearGeluFunction(Function):
     """GELU(x @ W^T + b): the addmm, then the lookup GELU; the backward produces d(pre-activation) and its column sums
     (the bias gradient) in one pass."""

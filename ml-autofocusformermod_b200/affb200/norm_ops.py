@@ -163,9 +163,13 @@ class BatchNormActFunction(Function):
             dg = torch.empty(C, dtype=torch.float32, device=dev)
             db = torch.empty(C, dtype=torch.float32, device=dev)
             work = torch.empty(max(1, N.LIB.affb200_batch_norm_work_floats(R, C)), dtype=torch.float32, device=dev)
+            tab = None
+            if gelu and x.dtype in (torch.float16, torch.bfloat16):
+                from .linear_ops import gelu_tables      # GELU' as a lookup: a 2-byte BN output has 65 536 values
+                tab = gelu_tables(dev, x.dtype)[1]
             N.check(N.LIB.affb200_batch_norm_bwd(N.p(dy), N.p(x), N.p(g), N.p(b), N.p(mean), N.p(rstd), 1 if gelu else 0,
                                                  N.p(dx), N.p(dg), N.p(db), N.p(work), R, C, N.dtype_enum(x),
-                                                 N.stream_ptr(dev)), "batch_norm_bwd")
+                                                 N.p(tab), N.stream_ptr(dev)), "batch_norm_bwd")
         return dx, dg.to(wdt), db.to(bdt), None, None, None, None, None
 
 

@@ -164,20 +164,41 @@ bn_apply_kernel(const T *__restrict__ x, const float *__restrict__ gamma, const 
 }
 
 // g = dy (· GELU'(z), z = BN(x) rounded to T), rounded to T: what the stock GELU backward hands to the BatchNorm backward
-template <typename T, bool GELU>
-__device__ __forceinline__ float bn_g(float dy, float xm, float w, float inv, float b) {
-    if constexpr (GELU) return bn_round<T>(bn_gelu_grad(bn_round<T>(w * xm * inv + b), dy));
-    return dy;
+// TAB (2-byte T): GELU'(z) from the 32 768-entry fp32 half table of gelu.cu in shared memory (z has 65 536 bit patterns;
+// G(-z) = 1 - G(z)) instead of erf + exp per element, which bound both backward kernels.
+template <typename T, bool GELU, bool TAB = false>
+__device__ __forceinline__ float bn_g(float dy, float xm, float w, float inv, float b, const float *tabf = nullptr) {
+    if constexpr (!GELU) {
+        return dy;
+    } else if constexpr (TAB) {
+        const T z = Elem<T>::from_acc(w * xm * inv + b);
+        const uint32_t bits = *reinterpret_cast<const uint16_t *>(&z);
+        float g = tabf[bits & 0x7fffu];
+        if (bits & 0x8000u) g = 1.f - g;
+        return bn_round<T>(dy * g);
+    } else {
+        return bn_round<T>(bn_gelu_grad(bn_round<T>(w * xm * inv + b), dy));
+    }
+}
+
+constexpr int kBnTabBytes = 128 * 1024;
+constexpr int kBnTabThreads = 1024;
+__device__ __forceinline__ void bn_load_table(float *tabf, const float *tab_g, int nthreads) {
+    for (int i = threadIdx.x; i < kBnTabBytes / 16; i += nthreads)
+        reinterpret_cast<uint4 *>(tabf)[i] = __ldg(reinterpret_cast<const uint4 *>(tab_g) + i);
+    __syncthreads();
 }
 
 // per-CTA partial sums: part[blk][2][C] = (sum g, sum g·(x − mean))
-template <typename T, int LPR, bool GELU>
-__global__ void __launch_bounds__(kBT)
+template <typename T, int LPR, bool GELU, int BT = kBT, bool TAB = false>
+__global__ void __launch_bounds__(BT)
 bn_bwd_reduce_kernel(const T *__restrict__ dy, const T *__restrict__ x, const float *__restrict__ gamma,
                      const float *__restrict__ beta, const float *__restrict__ mean, const float *__restrict__ rstd,
-                     float *__restrict__ part, int64_t R) {
-    constexpr int RPC = kBT / LPR, C = LPR * 8;
-    __shared__ float red[8][2][C];
+                     float *__restrict__ part, int64_t R, const float *__restrict__ tab_g = nullptr) {
+    constexpr int RPC = BT / LPR, C = LPR * 8;
+    __shared__ float red[BT / 32][2][C];
+    extern __shared__ __align__(16) float bn_tabf[];
+    if constexpr (TAB) bn_load_table(bn_tabf, tab_g, BT);
     const int l = threadIdx.x % LPR, rl = threadIdx.x / LPR, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float w[8], b[8], m[8], inv[8], a1[8], a2[8];
     load8f<float>(gamma + l * 8, w);
@@ -195,7 +216,7 @@ bn_bwd_reduce_kernel(const T *__restrict__ dy, const T *__restrict__ x, const fl
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             const float xm = v[e] - m[e];
-            const float g = bn_g<T, GELU>(d[e], xm, w[e], inv[e], b[e]);
+            const float g = bn_g<T, GELU, TAB>(d[e], xm, w[e], inv[e], b[e], bn_tabf);
             a1[e] += g;
             a2[e] = fmaf(g, xm, a2[e]);
         }
@@ -220,7 +241,7 @@ bn_bwd_reduce_kernel(const T *__restrict__ dy, const T *__restrict__ x, const fl
         const int which = threadIdx.x / C, c = threadIdx.x % C;
         float acc = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc += red[k][which][c];
+        for (int k = 0; k < BT / 32; ++k) acc += red[k][which][c];
         part[(int64_t(blockIdx.x) * 2 + which) * C + c] = acc;
     }
 }
@@ -250,12 +271,14 @@ bn_bwd_finish_kernel(const float *__restrict__ part, int n_blk, int C, const flo
 }
 
 // dx = (g − mean(g) − (x − mean)·rstd²·mean(g·(x − mean)))·rstd·gamma
-template <typename T, int LPR, bool GELU>
-__global__ void __launch_bounds__(kBT)
+template <typename T, int LPR, bool GELU, int BT = kBT, bool TAB = false>
+__global__ void __launch_bounds__(BT)
 bn_bwd_elemt_kernel(const T *__restrict__ dy, const T *__restrict__ x, const float *__restrict__ gamma,
                     const float *__restrict__ beta, const float *__restrict__ mean, const float *__restrict__ rstd,
-                    const float *__restrict__ sums, T *__restrict__ dx, int64_t R) {
-    constexpr int RPC = kBT / LPR, C = LPR * 8;
+                    const float *__restrict__ sums, T *__restrict__ dx, int64_t R, const float *__restrict__ tab_g = nullptr) {
+    constexpr int RPC = BT / LPR, C = LPR * 8;
+    extern __shared__ __align__(16) float bn_tabf[];
+    if constexpr (TAB) bn_load_table(bn_tabf, tab_g, BT);
     const int l = threadIdx.x % LPR, rl = threadIdx.x / LPR;
     float w[8], b[8], m[8], inv[8], mdy[8], f1[8], f2[8];
     load8f<float>(gamma + l * 8, w);
@@ -280,7 +303,7 @@ bn_bwd_elemt_kernel(const T *__restrict__ dy, const T *__restrict__ x, const flo
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             const float xm = v[e] - m[e];
-            const float g = bn_g<T, GELU>(d[e], xm, w[e], inv[e], b[e]);
+            const float g = bn_g<T, GELU, TAB>(d[e], xm, w[e], inv[e], b[e], bn_tabf);
             v[e] = (g - mdy[e] - xm * f1[e]) * f2[e];
         }
         store8f<T>(dx + r * C + l * 8, v);
@@ -358,8 +381,10 @@ extern "C" int affb200_batch_norm_fwd(const void *x, const float *gamma, const f
 
 extern "C" int affb200_batch_norm_bwd(const void *dy, const void *x, const float *gamma, const float *beta,
                                       const float *mean, const float *rstd, int gelu, void *dx, float *dgamma,
-                                      float *dbeta, float *work, int64_t R, int64_t C, int dtype, void *stream) {
+                                      float *dbeta, float *work, int64_t R, int64_t C, int dtype,
+                                      const float *gelu_bwd_tab, void *stream) {
     if (!bn_shape_ok("batch_norm_bwd", R, C, dtype)) return AFFB200_E_ARG;
+    if (gelu_bwd_tab && !aligned16(gelu_bwd_tab)) { set_error("batch_norm_bwd: misaligned table"); return AFFB200_E_ARG; }
     if (!dy || !x || !gamma || !beta || !mean || !rstd || !dx || !work || !aligned16(dy) || !aligned16(x) ||
         !aligned16(dx) || !aligned16(gamma) || !aligned16(beta) || !aligned16(mean) || !aligned16(rstd) || !aligned16(work)) {
         set_error("batch_norm_bwd: null or misaligned pointer");
@@ -373,6 +398,26 @@ extern "C" int affb200_batch_norm_bwd(const void *dy, const void *x, const float
         if constexpr (std::is_same<T, double>::value) {
             return AFFB200_E_ARG;
         } else {
+            if constexpr (sizeof(T) == 2) {
+                if (gelu && gelu_bwd_tab) {   // one 1024-thread CTA per SM around the 128 KB derivative table
+                    const int rpc = kBnTabThreads / int(C / 8);
+                    const int tg = int(std::min<int64_t>((R + rpc - 1) / rpc, int64_t(kNumSMs)));
+#define AFF_BN_TAB(L_)                                                                                                  \
+    do {                                                                                                                \
+        auto kr = bn_bwd_reduce_kernel<T, L_, true, kBnTabThreads, true>;                                               \
+        auto ke = bn_bwd_elemt_kernel<T, L_, true, kBnTabThreads, true>;                                                \
+        if (cudaFuncSetAttribute(kr, cudaFuncAttributeMaxDynamicSharedMemorySize, kBnTabBytes) != cudaSuccess ||        \
+            cudaFuncSetAttribute(ke, cudaFuncAttributeMaxDynamicSharedMemorySize, kBnTabBytes) != cudaSuccess)          \
+            return check_launch("cudaFuncSetAttribute", 0);                                                             \
+        kr<<<tg, kBnTabThreads, kBnTabBytes, st>>>((const T *)dy, (const T *)x, gamma, beta, mean, rstd, part, R, gelu_bwd_tab); \
+        bn_bwd_finish_kernel<<<unsigned((C + 31) / 32), 1024, 0, st>>>(part, tg, int(C), rstd, sums, dgamma, dbeta);   \
+        ke<<<tg, kBnTabThreads, kBnTabBytes, st>>>((const T *)dy, (const T *)x, gamma, beta, mean, rstd, sums, (T *)dx, R, gelu_bwd_tab); \
+    } while (0)
+                    AFF_BN_LPR(AFF_BN_TAB)
+#undef AFF_BN_TAB
+                    return check_launch("batch_norm_bwd", 3);
+                }
+            }
 #define AFF_BN_RED(L_)                                                                                                  \
     do {                                                                                                                \
         if (gelu) bn_bwd_reduce_kernel<T, L_, true><<<grid, kBT, 0, st>>>((const T *)dy, (const T *)x, gamma, beta, mean, rstd, part, R); \

@@ -81,3 +81,38 @@ def test_linear_matches_nn_linear(shape, autocast):
     for a, r, what in zip(ours, ref, ("y", "dx", "dw", "db")):
         assert a.dtype == r.dtype, what
         assert_close(a, r.double(), dt, "linear " + what)
+
+
+@pytest.mark.parametrize("sink", [False, True])
+@pytest.mark.parametrize("autocast", [False, True])
+def test_linear_pair_matches_two_linears(autocast, sink):
+    """q / kv of the attention: two Linears on one input, one dx in the backward (second GEMM accumulates onto the
+    first); with fp32 gradient sinks the parameter gradients land in .grad directly."""
+    from affb200.linear_ops import linear_pair
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(3, 125, 256, generator=g)
+    ws = [torch.randn(256, 256, generator=g) / 16, torch.randn(512, 256, generator=g) / 16]
+    bs = [torch.randn(256, generator=g), torch.randn(512, generator=g)]
+    gos = [torch.randn(3, 125, 256, generator=g), torch.randn(3, 125, 512, generator=g)]
+
+    def run(pair):
+        xs = x.cuda().clone().requires_grad_(True)
+        ps = [t.cuda().clone().requires_grad_(True) for t in (ws[0], bs[0], ws[1], bs[1])]
+        if sink and pair:
+            for p_ in ps:
+                p_.grad = torch.zeros_like(p_)
+                p_._affb200_sink = True
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            if pair:
+                y1, y2 = linear_pair(xs, *ps)
+            else:
+                y1 = torch.nn.functional.linear(xs, ps[0], ps[1])
+                y2 = torch.nn.functional.linear(xs, ps[2], ps[3])
+        torch.autograd.backward([y1, y2], [gos[0].cuda().to(y1.dtype), gos[1].cuda().to(y2.dtype)])
+        return [y1, y2, xs.grad] + [p_.grad for p_ in ps]
+
+    ours, ref = run(True), run(False)
+    dt = torch.bfloat16 if autocast else torch.float32
+    for a, r, what in zip(ours, ref, ("y1", "y2", "dx", "dw1", "db1", "dw2", "db2")):
+        assert a.dtype == r.dtype and a.shape == r.shape, what
+        assert_close(a, r.double(), dt, "linear_pair " + what)
