@@ -19,6 +19,8 @@ import sys
 import threading
 import time
 
+_OUT = sys.stdout   # main() replaces it with a private duplicate of the original stdout
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.join(ROOT, "ml-autofocusformermod_b200")
 for _p in (ROOT, PKG):
@@ -142,7 +144,7 @@ def run_reference(args, rank, world):
                                        (sample_b, steps, torch.__version__, cores)},
             "e2e": {"value": v, "unit": wl.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 def main():
@@ -162,6 +164,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # the contract is ONE JSON line on stdout.  Libraries write to file descriptor 1 behind Python's back (NCCL prints
+    # its version banner there at NCCL_DEBUG=VERSION whatever NCCL_DEBUG_FILE says), so fd 1 is pointed at stderr for
+    # the whole run and the JSON line goes to a private duplicate of the original stdout.
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     if args.impl == "reference":
         run_reference(args, rank, world)
@@ -173,8 +182,6 @@ def main():
     torch.cuda.set_device(device)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # the contract is ONE JSON line on stdout: NCCL prints its version banner (and any NCCL_DEBUG output) to stdout
-        # unless told otherwise, so whatever debug level the caller chose goes to stderr
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group(backend="nccl", device_id=device)
 
@@ -282,7 +289,7 @@ def main():
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_base}
         if graph_fallbacks is not None:
             line["config"]["graph_fallbacks"] = graph_fallbacks
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
