@@ -18,6 +18,9 @@ the two graphs; a step whose speculation failed is redone eagerly with exact pla
 failed speculation costs time, never correctness.
 
 The warm-up passes are real optimisation steps on the example batch (the optimizer state must exist before capture).
+
+Parameters and gradients are views of flat fp32 buffers ordered by optimizer param group; for Adam / AdamW / SGD the
+step itself then runs on ONE tensor per group (`flat_optimizer=True`, see `_flat_optimizer`): same update, one launch.
 """
 import torch
 import torch.distributed as dist
@@ -27,7 +30,7 @@ from . import plan as _plan
 
 class GraphedTrainStep:
     def __init__(self, model, optimizer, loss_fn, example_x, example_y, world=1, autocast_dtype=torch.bfloat16,
-                 warmup=3):
+                 warmup=3, flat_optimizer=True):
         self.model, self.opt, self.loss_fn, self.world = model, optimizer, loss_fn, world
         self.autocast_dtype = autocast_dtype
         dev = example_x.device
@@ -43,6 +46,12 @@ class GraphedTrainStep:
         # parameters, gradients and the low-precision shadow each live in ONE flat buffer (32-byte aligned slices):
         # one all-reduce, one cast kernel per step instead of one per use of every weight, and gradient GEMMs that
         # accumulate in place (linear_ops: `_affb200_lp`, `_affb200_sink`)
+        # (the optimizer's param groups first, in order, so that each group is one contiguous range: see _flat_optimizer)
+        ids = {id(p) for p in self.params}
+        ordered = [p for g in optimizer.param_groups for p in g["params"] if id(p) in ids and p.requires_grad]
+        seen = {id(p) for p in ordered}
+        group_counts = [sum(1 for p in g["params"] if id(p) in ids and p.requires_grad) for g in optimizer.param_groups]
+        self.params = ordered + [p for p in self.params if id(p) not in seen]
         offs, n = [], 0
         for p in self.params:
             offs.append(n)
@@ -57,6 +66,8 @@ class GraphedTrainStep:
             p.grad = self.flat_grad[sl].view_as(p)
             p._affb200_lp = self.flat_lp[sl].view_as(p)
             p._affb200_sink = True
+        if flat_optimizer:
+            self.opt = self._flat_optimizer(optimizer, group_counts, offs, n) or optimizer
         self.sync_params()
         self.x = example_x.clone()
         self.y = example_y.clone()
@@ -78,6 +89,32 @@ class GraphedTrainStep:
         self.recaptures = 0
         self.max_recaptures = 8
         self._capture()
+
+    def _flat_optimizer(self, opt, group_counts, offs, n):
+        """Adam / AdamW / SGD update every element independently with its group's hyper-parameters, so an optimizer
+        over one flat tensor per param group (a contiguous range of the flat buffers, padding included: its gradient
+        is always zero) performs the same update as one over the ~400 parameter tensors — in one kernel launch per
+        group at streaming bandwidth instead of dozens of multi-tensor chunks.  Returns that optimizer (same class, the
+        groups' hyper-parameters), or None when the given optimizer is of another class, already has state, or owns
+        parameters outside the model.  The optimizer passed in then only supplies class and hyper-parameters; the
+        state lives in `self.opt` (one tensor per group)."""
+        import inspect
+        if type(opt) not in (torch.optim.Adam, torch.optim.AdamW, torch.optim.SGD) or len(opt.state) != 0:
+            return None
+        if sum(group_counts) != len(self.params) or any(len(g["params"]) != c for g, c in zip(opt.param_groups, group_counts)):
+            return None
+        groups, k = [], 0
+        for g, c in zip(opt.param_groups, group_counts):
+            if c == 0:
+                continue
+            lo = offs[k]
+            hi = offs[k + c] if k + c < len(offs) else n
+            k += c
+            fp = torch.nn.Parameter(self.flat_param[lo:hi])
+            fp.grad = self.flat_grad[lo:hi]
+            groups.append({**{kk: v for kk, v in g.items() if kk != "params"}, "params": [fp]})
+        accepted = set(inspect.signature(type(opt).__init__).parameters)
+        return type(opt)(groups, **{kk: v for kk, v in opt.defaults.items() if kk in accepted})
 
     def _capture(self):
         from . import _native as N

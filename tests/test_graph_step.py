@@ -181,3 +181,45 @@ def test_graphed_forward_matches_eager_inference():
         # bit-identical kernels on identical inputs; a fallback (eager redo) would also be exact
         assert torch.equal(got, want), (got - want).abs().max()
     assert fwd.kernels_per_step > 0
+
+
+def test_flat_optimizer_performs_the_per_tensor_update():
+    """AdamW over one flat tensor per param group (the default of GraphedTrainStep) and AdamW over the individual
+    parameter tensors: the same element-wise update.  On a deterministic toy network (no atomics anywhere) the
+    parameters stay bit-identical over several real steps with two param groups (weights decayed, biases / norms not,
+    as the reference's build_optimizer does); on the AFF model the two trajectories agree to gradient noise."""
+    from affb200.graph_step import GraphedTrainStep
+    xs, ys = _batches(5)
+
+    def opt_for(m, lr):
+        decay = [p for p in m.parameters() if p.dim() > 1]
+        rest = [p for p in m.parameters() if p.dim() <= 1]
+        return torch.optim.AdamW([{"params": decay, "weight_decay": 0.05}, {"params": rest, "weight_decay": 0.0}],
+                                 lr=lr, fused=True, capturable=True)
+
+    def toy():
+        torch.manual_seed(3)
+        return torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(3 * 160 * 160, 64), torch.nn.LayerNorm(64),
+                                   torch.nn.GELU(), torch.nn.Linear(64, 10)).cuda()
+    t1, t2 = toy(), toy()
+    s1 = GraphedTrainStep(t1, opt_for(t1, 1e-3), torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1)
+    s2 = GraphedTrainStep(t2, opt_for(t2, 1e-3), torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1,
+                          flat_optimizer=False)
+    assert [len(g["params"]) for g in s1.opt.param_groups] == [1, 1]
+    assert [len(g["params"]) for g in s2.opt.param_groups] == [2, 4]
+    for x, y in zip(xs[1:], ys[1:]):
+        assert float(s1(x, y)) == float(s2(x, y))
+    fresh = toy()
+    for (k, a), b, c in zip(t1.named_parameters(), t2.parameters(), fresh.parameters()):
+        assert torch.equal(a, b), k
+        assert torch.equal(a._affb200_lp, b._affb200_lp), k
+        assert not torch.equal(a, c), k          # the steps were real
+
+    m1, m2 = _models()
+    s1 = GraphedTrainStep(m1, opt_for(m1, 1e-5), torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1)
+    s2 = GraphedTrainStep(m2, opt_for(m2, 1e-5), torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1,
+                          flat_optimizer=False)
+    assert [len(g["params"]) for g in s1.opt.param_groups] == [1, 1]
+    for x, y in zip(xs[1:], ys[1:]):
+        l1, l2 = float(s1(x, y)), float(s2(x, y))
+        assert abs(l1 - l2) < 2e-2 * abs(l2), (l1, l2)
