@@ -387,6 +387,21 @@ int affb200_scale_add(const void *a, const void *x, const float *s, float s_scal
                       int64_t per_sample, int dtype, void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
+ * The PointConv weight table of ClusterMerging: out[P][4] = GELU(LayerNorm_4(Linear_{5->4}(feat[P][5]))) (reference
+ * models/aff_transformer.py:262-264,343: `self.weight_net(pre_table)`, nn.Sequential(Linear(5, 4), LayerNorm(4), GELU)).
+ * feat / w [4][5] / b [4] / gamma [4] / beta [4] / out fp32.  compute_dtype = the dtype autocast runs the Linear in
+ * (its inputs, weight, bias and result are rounded to it; AFFB200_F32 = no rounding); LayerNorm and GELU in fp32.
+ * bwd: grads[32] = d w [4][5], d b [4], d gamma [4], d beta [4] (overwritten) from d_out [P][4]; the row is recomputed;
+ * work = affb200_weight_net_work_floats(P) floats.  Fixed summation order.
+ * ---------------------------------------------------------------------------------------------------------- */
+int64_t affb200_weight_net_work_floats(int64_t P);
+int affb200_weight_net_fwd(const float *feat, const float *w, const float *b, const float *gamma, const float *beta,
+                           float eps, int64_t P, int compute_dtype, float *out, void *stream);
+int affb200_weight_net_bwd(const float *feat, const float *w, const float *b, const float *gamma, const float *beta,
+                           float eps, int64_t P, int compute_dtype, const float *d_out, float *grads, float *work,
+                           void *stream);
+
+/* ------------------------------------------------------------------------------------------------------------
  * Merge half of ClusterMerging without materialising the PointConv weights (reference
  * models/aff_transformer.py:343-361):  W[b,i,j,:] = table[pe_idx[b,i,j]][0..4) * lp[b, nbhd[b,i,j]] * mask[b,i,j];
  * out[b,i,q,:] = sum_j W[b,i,j,q] * feat[b, nbhd[b,i,j], :].

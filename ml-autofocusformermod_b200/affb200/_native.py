@@ -83,6 +83,9 @@ SIGNATURES = {
     "affb200_gelu_fwd": (_int, [_ptr, _ptr, _i64, _int, _ptr, _ptr]),
     "affb200_gelu_bwd_work_floats": (_i64, [_i64]),
     "affb200_gelu_bwd": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr, _ptr, _int, _ptr, _ptr]),
+    "affb200_weight_net_work_floats": (_i64, [_i64]),
+    "affb200_weight_net_fwd": (_int, [_ptr] * 5 + [ctypes.c_float, _i64, _int, _ptr, _ptr]),
+    "affb200_weight_net_bwd": (_int, [_ptr] * 5 + [ctypes.c_float, _i64, _int, _ptr, _ptr, _ptr, _ptr]),
     "affb200_col_sum_work_floats": (_i64, [_i64, _i64]),
     "affb200_col_sum": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _int, _ptr]),
     "affb200_layer_norm_fwd": (_int, [_ptr] * 6 + [_i64, _i64, ctypes.c_float, _int, _int, _ptr]),

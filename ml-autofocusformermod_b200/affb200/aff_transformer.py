@@ -41,6 +41,7 @@ class CudaOps:
         self.residual_add = RO.residual_add
         from . import merge_ops as MO
         self.merge_wf = MO.merge_wf
+        self.weight_net_table = MO.weight_net_table
         self.attn_bias_add = A.attn_bias_add
         self.table_gather = A.table_gather
         self.qk = CLUSTENQKFunction.apply
@@ -272,7 +273,8 @@ class ClusterMerging(nn.Module):
         if cluster_mask is not None:
             cluster_mask = ops.gather_rows(cluster_mask, idx)
         m = member_idx.shape[-1]
-        weights_table = self.weight_net(pre_table)                                       # T*T x ic
+        wn = getattr(ops, "weight_net_table", None)                                      # T*T x ic
+        weights_table = self.weight_net(pre_table) if wn is None else wn(self.weight_net, pre_table)
         fused = getattr(ops, "merge_wf", None)
         if fused is not None:    # weights formed inside the kernels from table[pe_idx], lp[member_idx] and the mask
             out = fused(weights_table, pe_idx, learned_prob, cluster_mask, feat, member_idx)

@@ -84,3 +84,52 @@ def merge_wf(weights_table, pe_idx, learned_prob, cluster_mask, feat, member_idx
             or (learned_prob is not None and learned_prob.dtype not in _OK) or member_idx.shape[2] > 1024):
         return None
     return MergeWFFunction.apply(weights_table, learned_prob, feat, pe_idx, cluster_mask, member_idx)
+
+
+class WeightNetFunction(Function):
+    """weight_net(pre_table) = GELU(LayerNorm(Linear(pre_table))) as one kernel per direction (csrc/weight_net.cu)."""
+
+    @staticmethod
+    def forward(ctx, feat, w, b, gamma, beta, eps, dt):
+        dev = feat.device
+        P = feat.shape[0]
+        args = [t.detach().float().contiguous() for t in (feat, w, b, gamma, beta)]
+        with torch.cuda.device(dev):
+            out = torch.empty((P, 4), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_weight_net_fwd(*[N.p(t) for t in args], float(eps), P, N.DTYPE_ENUM[dt], N.p(out),
+                                                 N.stream_ptr(dev)), "weight_net_fwd")
+        ctx.save_for_backward(*args)
+        ctx.meta = (float(eps), dt, w.dtype, b.dtype, gamma.dtype, beta.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        args = ctx.saved_tensors
+        eps, dt, wdt, bdt, gdt, bedt = ctx.meta
+        dev = d_out.device
+        P = args[0].shape[0]
+        d_out = d_out.float().contiguous()
+        with torch.cuda.device(dev):
+            grads = torch.empty(32, dtype=torch.float32, device=dev)
+            work = torch.empty(max(1, N.LIB.affb200_weight_net_work_floats(P)), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_weight_net_bwd(*[N.p(t) for t in args], eps, P, N.DTYPE_ENUM[dt], N.p(d_out),
+                                                 N.p(grads), N.p(work), N.stream_ptr(dev)), "weight_net_bwd")
+        return (None, grads[:20].view(4, 5).to(wdt), grads[20:24].to(bdt), grads[24:28].to(gdt), grads[28:32].to(bedt),
+                None, None)
+
+
+def weight_net_table(weight_net, pre_table):
+    """`weight_net(pre_table)` for the reference's nn.Sequential(Linear(5, 4), LayerNorm(4), GELU) (aff_transformer.py:
+    262-264) -> fp32 [P, 4]; any other module structure, or a table that needs a gradient, runs the module itself."""
+    if not pre_table.is_cuda:
+        raise RuntimeError("pre_table must be a CUDA tensor")
+    mods = list(weight_net) if isinstance(weight_net, torch.nn.Sequential) else []
+    ok = (len(mods) == 3 and isinstance(mods[0], torch.nn.Linear) and isinstance(mods[1], torch.nn.LayerNorm)
+          and isinstance(mods[2], torch.nn.GELU) and mods[2].approximate == "none" and mods[0].bias is not None
+          and tuple(mods[0].weight.shape) == (4, 5) and tuple(mods[1].normalized_shape) == (4,)
+          and mods[1].elementwise_affine and mods[1].bias is not None
+          and pre_table.dim() == 2 and pre_table.shape[1] == 5 and not pre_table.requires_grad)
+    dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else pre_table.dtype
+    if not ok or dt not in _OK:
+        return weight_net(pre_table)
+    return WeightNetFunction.apply(pre_table, mods[0].weight, mods[0].bias, mods[1].weight, mods[1].bias, mods[1].eps, dt)

@@ -72,3 +72,34 @@ def test_merge_wf_declines_unsupported_cases():
     assert merge_wf(torch.randn(50, 3, device="cuda"), pe, None, None, torch.randn(1, 5, 64, device="cuda"), nb) is None
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         merge_wf(t, pe, None, None, torch.randn(1, 5, 64), nb)
+
+
+@pytest.mark.parametrize("autocast", [False, True])
+@pytest.mark.parametrize("P", [12321, 633, 1])
+def test_weight_net_table_matches_the_module(P, autocast):
+    """weight_net = Sequential(Linear(5, 4), LayerNorm(4), GELU) on the relative-position feature table (reference
+    aff_transformer.py:262-264,343) as one kernel per direction: output and the four parameter gradients of the stock
+    modules, fp32 at 1e-5, under bf16 autocast (Linear in bf16, LayerNorm / GELU in fp32) at 1e-2."""
+    from affb200.merge_ops import weight_net_table
+    from affb200.aff_transformer import build_pe_lookup
+    g = torch.Generator().manual_seed(P)
+    _, _, table = build_pe_lookup(224)
+    table = table[torch.randperm(table.shape[0], generator=g)[:P]].cuda()
+    go = torch.randn(P, 4, generator=g).cuda()
+    res = []
+    for ours in (True, False):
+        torch.manual_seed(7)
+        net = torch.nn.Sequential(torch.nn.Linear(5, 4), torch.nn.LayerNorm(4), torch.nn.GELU()).cuda()
+        with torch.no_grad():
+            net[1].weight.normal_(1, 0.2)
+            net[1].bias.normal_(0, 0.2)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            out = weight_net_table(net, table) if ours else net(table)
+        assert out.dtype == torch.float32 and out.shape == (P, 4)
+        out.backward(go)
+        res.append([out.detach()] + [p.grad for p in net.parameters()])
+    tol = 1e-2 if autocast else 1e-5
+    for a, b, what in zip(res[0], res[1], ("out", "d_w", "d_b", "d_gamma", "d_beta")):
+        assert a.shape == b.shape and a.dtype == b.dtype, what
+        err = float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-12))
+        assert err < tol, (what, err)
