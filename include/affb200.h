@@ -385,6 +385,10 @@ int affb200_gelu_bwd(const void *dy, const void *x, void *dx, int64_t R, int64_t
  * ---------------------------------------------------------------------------------------------------------- */
 int affb200_scale_add(const void *a, const void *x, const float *s, float s_scale, void *out, int64_t B,
                       int64_t per_sample, int dtype, void *stream);
+/* y[r][c] = x[r][c] + bias[c] over channels-last rows [R][C] of `dtype` (bias fp32, rounded to `dtype` first, as
+ * autocast hands a conv bias to the stock add): the bias of the stem's second convolution (reference
+ * models/aff_transformer.py:528,544).  16-byte chunks; C * sizeof(dtype) / 16 must divide 256. */
+int affb200_bias_rows(const void *x, const float *bias, void *y, int64_t R, int64_t C, int dtype, void *stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * The PointConv weight table of ClusterMerging: out[P][4] = GELU(LayerNorm_4(Linear_{5->4}(feat[P][5]))) (reference

@@ -35,6 +35,7 @@ class CudaOps:
         self.layer_norm_fork = L.layer_norm_fork
         self.batch_norm_act = L.batch_norm_act
         self.conv_batch_norm_act = L.conv_batch_norm_act
+        self.conv_bias = L.conv_bias
         self.linear = LI.linear
         self.linear_gelu = LI.linear_gelu
         self.linear_pair = LI.linear_pair
@@ -381,7 +382,7 @@ class PatchEmbed(nn.Module):
         else:
             x = self.proj1(x)
             x = self.act1(self.bn(x)) if ops is None else ops.batch_norm_act(x, self.bn)
-        x = self.proj2(x)
+        x = ops.conv_bias(x, self.proj2) if ops is not None and hasattr(ops, 'conv_bias') and x.is_cuda else self.proj2(x)
         b, c, h, w = x.shape
         x = x.flatten(2).transpose(1, 2)
         if self.norm is not None:

@@ -4,6 +4,7 @@
   layer_norm(x, weight, bias, eps, out_dtype=None) -> LayerNorm(x) in `out_dtype`
   batch_norm_act(x, bn, gelu=True)                 -> GELU(bn(x)) for a training-mode nn.BatchNorm2d `bn`
   conv_batch_norm_act(x, conv, bn, gelu=True)      -> GELU(bn(conv(x))) with the conv bias folded into the batch statistics
+  conv_bias(x, conv)                               -> conv(x), bias added / its gradient reduced by streaming row kernels
 
 The reference uses nn.LayerNorm (models/aff_transformer.py:199-200,284), which autocast evaluates in fp32: the bf16
 residual stream is copied to fp32, normalised, and copied back to bf16 by the next Linear.  This operator reads x in
@@ -221,6 +222,55 @@ def conv_batch_norm_act(x, conv, bn, gelu=True):
     with torch.no_grad():
         bn.running_mean.add_(conv.bias.detach().to(bn.running_mean.dtype), alpha=bn.momentum)
     return _ZeroGradFor.apply(out, conv.bias) if conv.bias.requires_grad else out
+
+
+class BiasRowsFunction(Function):
+    """y = x + bias[c] on a channels-last activation; d_bias as one column-sum pass."""
+
+    @staticmethod
+    def forward(ctx, x, bias):
+        B, C, H, W = x.shape
+        dev = x.device
+        b32 = bias.detach().float().contiguous()
+        with torch.cuda.device(dev):
+            y = torch.empty_like(x)      # preserves the channels-last strides
+            N.check(N.LIB.affb200_bias_rows(N.p(x), N.p(b32), N.p(y), B * H * W, C, N.dtype_enum(x), N.stream_ptr(dev)),
+                    "bias_rows")
+        ctx.bias = bias
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        from .linear_ops import col_sum, _sink
+        bias = ctx.bias
+        db = None
+        if ctx.needs_input_grad[1]:
+            B, C, H, W = g.shape
+            rows = g.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1).reshape(B * H * W, C)
+            with torch.cuda.device(g.device):
+                sink = _sink(bias)
+                if sink is not None and sink.data_ptr() % 16 == 0:
+                    col_sum(rows, into=sink)
+                else:
+                    db = col_sum(rows).to(bias.dtype)
+        return g, db
+
+
+def conv_bias(x, conv):
+    """conv(x) for a channels-last CUDA activation with the bias added (and its gradient reduced) by this package's
+    row kernels: the stock path adds the bias with a broadcast kernel and reduces the gradient with a generic strided
+    sum, each several times slower than a streaming pass (the stem's proj2, reference aff_transformer.py:528,544)."""
+    if not x.is_cuda:
+        raise RuntimeError("x must be a CUDA tensor")
+    if conv.bias is None:
+        return conv(x)
+    y = conv._conv_forward(x, conv.weight, None)
+    C = y.shape[1]
+    chunks = C * y.element_size() // 16
+    if not (y.dim() == 4 and y.dtype in _OK and y.numel() > 0 and y.is_contiguous(memory_format=torch.channels_last)
+            and (C * y.element_size()) % 16 == 0 and chunks <= 256 and 256 % chunks == 0 and C % 8 == 0):
+        return y + conv.bias.to(y.dtype).view(1, -1, 1, 1)
+    return BiasRowsFunction.apply(y, conv.bias)
 
 
 def layer_norm_fork(x, weight, bias, eps=1e-5, out_dtype=None):

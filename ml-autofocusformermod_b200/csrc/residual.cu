@@ -31,9 +31,54 @@ scale_add_kernel(const T *__restrict__ a, const T *__restrict__ x, const float *
     }
 }
 
+// y[r][c] = x[r][c] + bias[c] over channels-last rows, the sum rounded to T (bias rounded to T first: the conv bias
+// as autocast hands it to the stock add).  C/V consecutive threads cover a row; the bias chunk stays in registers.
+template <typename T>
+__global__ void __launch_bounds__(256)
+bias_rows_kernel(const T *__restrict__ x, const float *__restrict__ bias, T *__restrict__ y, int chunks, int64_t total_vec) {
+    constexpr int V = 16 / sizeof(T);
+    const int64_t stride = int64_t(gridDim.x) * 256;     // host makes it a multiple of `chunks`
+    int64_t i = int64_t(blockIdx.x) * 256 + threadIdx.x;
+    const int ch = int(i % chunks);
+    float bv[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) bv[k] = Elem<T>::to_acc(Elem<T>::from_acc(__ldg(bias + ch * V + k)));
+    for (; i < total_vec; i += stride) {
+        float xv[V];
+        load_vec<T, V>(x + i * V, xv);
+#pragma unroll
+        for (int k = 0; k < V; ++k) xv[k] += bv[k];
+        store_vec<T, V>(y + i * V, xv);
+    }
+}
+
 }  // namespace affb200
 
 using namespace affb200;
+
+extern "C" int affb200_bias_rows(const void *x, const float *bias, void *y, int64_t R, int64_t C, int dtype, void *stream) {
+    if (R < 0 || C <= 0) { set_error("bias_rows: bad size"); return AFFB200_E_ARG; }
+    if (R == 0) return AFFB200_OK;
+    if (!x || !bias || !y || !aligned16(x) || !aligned16(y)) { set_error("bias_rows: null or misaligned pointer"); return AFFB200_E_ARG; }
+    return dispatch_dtype(dtype, [&](auto tag) -> int {
+        using T = decltype(tag);
+        if constexpr (sizeof(T) == 8) {
+            set_error("bias_rows: f32 / f16 / bf16 only");
+            return AFFB200_E_ARG;
+        } else {
+            constexpr int V = 16 / sizeof(T);
+            if (C % V != 0 || C / V > 256 || 256 % (C / V) != 0) {
+                set_error("bias_rows: C / %d must divide 256", V);
+                return AFFB200_E_ARG;
+            }
+            const int chunks = int(C / V);
+            const int64_t tv = R * chunks;
+            const unsigned grid = unsigned(std::min<int64_t>((tv + 255) / 256, int64_t(kNumSMs) * 16));
+            bias_rows_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T *)x, bias, (T *)y, chunks, tv);
+            return check_launch("bias_rows");
+        }
+    });
+}
 
 extern "C" int affb200_scale_add(const void *a, const void *x, const float *s, float s_scale, void *out, int64_t B,
                                  int64_t per_sample, int dtype, void *stream) {

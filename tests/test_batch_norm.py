@@ -141,3 +141,35 @@ def test_conv_batch_norm_act_folds_the_conv_bias(dtype):
     b1.eval()
     with torch.no_grad():
         assert torch.equal(conv_batch_norm_act(x, c1, b1), torch.nn.functional.gelu(b1(c1(x))))
+
+
+@pytest.mark.parametrize("sink", [False, True])
+@pytest.mark.parametrize("autocast", [False, True])
+def test_conv_bias_matches_the_stock_convolution(autocast, sink):
+    """proj2 of the stem: conv without bias + the row bias kernel; output bit-identical to the stock conv with bias
+    in bf16 (same rounding: conv result rounded, bias rounded, sum rounded), gradients of x / weight identical, bias
+    gradient = fp32 column sums (stock: a bf16 reduction)."""
+    from affb200.norm_ops import conv_bias
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(4, 32, 28, 28, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    go = torch.randn(4, 64, 14, 14, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+    res = []
+    for ours in (True, False):
+        torch.manual_seed(9)
+        conv = torch.nn.Conv2d(32, 64, 3, 2, 1).cuda()
+        if sink and ours:
+            conv.bias.grad = torch.zeros_like(conv.bias)
+            conv.bias._affb200_sink = True
+        xx = x.clone().requires_grad_(True)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            y = conv_bias(xx, conv) if ours else conv(xx)
+        y.backward(go.to(y.dtype))
+        res.append((y, xx.grad, conv.weight.grad, conv.bias.grad))
+    dt = torch.bfloat16 if autocast else torch.float32
+    (y1, dx1, dw1, db1), (y2, dx2, dw2, db2) = res
+    assert y1.dtype == y2.dtype and y1.is_contiguous(memory_format=torch.channels_last)
+    assert_close(y1, y2.double(), dt, "conv_bias y")
+    assert torch.equal(dx1, dx2) and torch.equal(dw1, dw2)
+    assert_close(db1, go.double().sum((0, 2, 3)) if not autocast else go.bfloat16().double().sum((0, 2, 3)), torch.float32,
+                 "conv_bias d_bias")
+    assert_close(db1, db2.double(), dt, "conv_bias d_bias vs stock")
