@@ -209,6 +209,7 @@ class _AffRun:
     def __init__(self, wl, B, device, world):
         from affb200.aff_transformer import build_aff, CudaOps
         self.wl, self.B, self.device, self.world = wl, B, device, world
+        torch.backends.cudnn.benchmark = True     # as the reference's entry point does (main.py:434): the stem convs
         ops = CudaOps()
         if os.environ.get("AFFB200_ATTN", "fused") == "fused":
             try:

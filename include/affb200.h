@@ -385,6 +385,12 @@ int affb200_gelu_bwd(const void *dy, const void *x, void *dx, int64_t R, int64_t
  * ---------------------------------------------------------------------------------------------------------- */
 int affb200_scale_add(const void *a, const void *x, const float *s, float s_scale, void *out, int64_t B,
                       int64_t per_sample, int dtype, void *stream);
+/* The first convolution of the patch embedding without its bias: y[B][H/2][W/2][Cout] = conv 3x3, stride 2, padding 1 of
+ * channels-last images x[B][H][W][3] with w[Cout][3][3][3] (fp32 master weights, rounded to `dtype` inside; reference
+ * models/aff_transformer.py:524,541 `proj1`).  x / y f16 or bf16, fp32 accumulate; H, W even, W*6 a multiple of 16,
+ * Cout a multiple of 16, (W/2)*(Cout/16) <= 256 (one thread per output column and 16 channels). */
+int affb200_conv_stem_fwd(const void *x, const float *w, void *y, int64_t B, int64_t H, int64_t W, int64_t Cout,
+                          int dtype, void *stream);
 /* y[r][c] = x[r][c] + bias[c] over channels-last rows [R][C] of `dtype` (bias fp32, rounded to `dtype` first, as
  * autocast hands a conv bias to the stock add): the bias of the stem's second convolution (reference
  * models/aff_transformer.py:528,544).  16-byte chunks; C * sizeof(dtype) / 16 must divide 256. */

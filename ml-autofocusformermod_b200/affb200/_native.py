@@ -74,6 +74,7 @@ SIGNATURES = {
     "affb200_merge_fwd": (_int, [_ptr] * 7 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_merge_bwd": (_int, [_ptr] * 12 + [_i64] * 5 + [_int, _int, _ptr]),
     "affb200_table_gather": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),
+    "affb200_conv_stem_fwd": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _i64, _int, _ptr]),
     "affb200_bias_rows": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _ptr]),
     "affb200_scale_add": (_int, [_ptr, _ptr, _ptr, ctypes.c_float, _ptr, _i64, _i64, _int, _ptr]),
     "affb200_batch_norm_work_floats": (_i64, [_i64, _i64]),

@@ -206,6 +206,53 @@ class _ZeroGradFor(torch.autograd.Function):
         return g, torch.zeros(shape, dtype=dtype, device=device)
 
 
+class ConvStemFunction(Function):
+    """conv 3x3 / stride 2 / padding 1 from 3 input channels, no bias, channels-last (csrc/conv_stem.cu); the weight
+    gradient through the library's convolution backward (the images need no gradient)."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        B, _, H, W = x.shape
+        Cout = weight.shape[0]
+        dev = x.device
+        w32 = weight.detach().float().contiguous()
+        with torch.cuda.device(dev):
+            y = torch.empty((B, Cout, H // 2, W // 2), dtype=x.dtype, device=dev, memory_format=torch.channels_last)
+            N.check(N.LIB.affb200_conv_stem_fwd(N.p(x), N.p(w32), N.p(y), B, H, W, Cout, N.dtype_enum(x),
+                                                N.stream_ptr(dev)), "conv_stem_fwd")
+        ctx.save_for_backward(x)
+        ctx.weight = weight
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        from .linear_ops import low_precision, _sink
+        (x,) = ctx.saved_tensors
+        weight = ctx.weight
+        if not ctx.needs_input_grad[1]:
+            return None, None
+        with torch.cuda.device(g.device):
+            wl = low_precision(weight, x.dtype)
+            g = g.to(x.dtype).contiguous(memory_format=torch.channels_last)
+            _, dw, _ = torch.ops.aten.convolution_backward(g, x, wl, None, [2, 2], [1, 1], [1, 1], False, [0, 0], 1,
+                                                           [False, True, False])
+            sink = _sink(weight)
+            if sink is not None:
+                sink.add_(dw)
+                return None, None
+        return None, dw.to(weight.dtype)
+
+
+def _stem_conv_ok(x, conv):
+    return (x.is_cuda and x.dim() == 4 and x.dtype in (torch.float16, torch.bfloat16) and not x.requires_grad
+            and conv.in_channels == 3 and conv.kernel_size == (3, 3) and conv.stride == (2, 2)
+            and conv.padding == (1, 1) and conv.dilation == (1, 1) and conv.groups == 1
+            and conv.padding_mode == "zeros" and conv.out_channels % 16 == 0
+            and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and (x.shape[3] * 6) % 16 == 0
+            and (x.shape[3] // 2) * (conv.out_channels // 16) <= 256 and 0 < x.shape[0] <= 65535
+            and x.is_contiguous(memory_format=torch.channels_last) and conv.weight.dtype == torch.float32)
+
+
 def conv_batch_norm_act(x, conv, bn, gelu=True):
     """GELU(bn(conv(x))) for the stem's conv -> BatchNorm pair (reference aff_transformer.py:541-543).  A per-channel
     constant added before a training-mode BatchNorm cancels in (x - mean): the convolution runs without its bias (no
@@ -215,7 +262,9 @@ def conv_batch_norm_act(x, conv, bn, gelu=True):
     if conv.bias is None or not (x.is_cuda and bn.training and bn.affine and bn.track_running_stats
                                  and bn.momentum is not None and conv.out_channels in (8, 16, 32, 64, 128)):
         return batch_norm_act(conv(x), bn, gelu)
-    y = conv._conv_forward(x, conv.weight, None)
+    # (the images arrive already in the compute dtype, see PatchEmbed.forward; the 3-channel stem convolution then
+    # runs on this package's kernel, any other convolution on the library's)
+    y = ConvStemFunction.apply(x, conv.weight) if _stem_conv_ok(x, conv) else conv._conv_forward(x, conv.weight, None)
     if not (y.dtype in _OK and y.numel() > 0 and y.is_contiguous(memory_format=torch.channels_last)):
         return batch_norm_act(y + conv.bias.to(y.dtype).view(1, -1, 1, 1), bn, gelu)
     out = batch_norm_act(y, bn, gelu)

@@ -173,3 +173,28 @@ def test_conv_bias_matches_the_stock_convolution(autocast, sink):
     assert_close(db1, go.double().sum((0, 2, 3)) if not autocast else go.bfloat16().double().sum((0, 2, 3)), torch.float32,
                  "conv_bias d_bias")
     assert_close(db1, db2.double(), dt, "conv_bias d_bias vs stock")
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape,cout", [((3, 3, 224, 224), 32), ((2, 3, 160, 160), 32), ((2, 3, 40, 24), 16),
+                                        ((1, 3, 64, 64), 64), ((2, 3, 30, 56), 48)])
+def test_stem_convolution_kernel_matches_the_library(shape, cout, dtype):
+    """proj1 (3 -> cout, 3x3, stride 2, padding 1, no bias) on channels-last images: the kernel against the stock
+    convolution evaluated in float64 on the same rounded operands (1e-2 for 2-byte outputs; the kernel accumulates in
+    fp32 and rounds once), including the zero padding at the top / left edges and a row count that is not a multiple of
+    the four rows a CTA owns; the weight gradient comes from the library."""
+    from affb200.norm_ops import ConvStemFunction, _stem_conv_ok
+    g = torch.Generator().manual_seed(sum(shape) + cout)
+    x = torch.randn(shape, generator=g).to(dtype).cuda().contiguous(memory_format=torch.channels_last)
+    conv = torch.nn.Conv2d(3, cout, 3, 2, 1).cuda()
+    assert _stem_conv_ok(x, conv)
+    y = ConvStemFunction.apply(x, conv.weight)
+    assert y.shape == (shape[0], cout, shape[2] // 2, shape[3] // 2) and y.dtype == dtype
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    want = torch.nn.functional.conv2d(x.double(), conv.weight.detach().to(dtype).double(), None, 2, 1)
+    assert_close(y, want, dtype, "stem conv")
+    go = torch.randn(y.shape, generator=g).to(dtype).cuda().contiguous(memory_format=torch.channels_last)
+    y.backward(go)
+    wantw = torch.nn.grad.conv2d_weight(x.double(), conv.weight.shape, go.double(), 2, 1)
+    assert_close(conv.weight.grad, wantw, dtype, "stem conv d_weight")
+    assert not _stem_conv_ok(x.float(), conv) and not _stem_conv_ok(x.clone().requires_grad_(True), conv)
