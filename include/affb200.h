@@ -348,6 +348,9 @@ int64_t affb200_batch_norm_work_floats(int64_t R, int64_t C);
 int affb200_batch_norm_fwd(const void *x, const float *gamma, const float *beta, float *running_mean,
                            float *running_var, float momentum, float eps, int gelu, void *y, float *mean, float *rstd,
                            float *work, int64_t R, int64_t C, int dtype, void *stream);
+/* apply only: y = act(gamma*(x-mean)*rstd + beta) with given mean / rstd [C] (evaluation mode: running statistics). */
+int affb200_batch_norm_apply(const void *x, const float *gamma, const float *beta, const float *mean, const float *rstd,
+                             int gelu, void *y, int64_t R, int64_t C, int dtype, void *stream);
 int affb200_batch_norm_bwd(const void *dy, const void *x, const float *gamma, const float *beta, const float *mean,
                            const float *rstd, int gelu, void *dx, float *dgamma, float *dbeta, float *work, int64_t R,
                            int64_t C, int dtype, const float *gelu_bwd_tab, void *stream);

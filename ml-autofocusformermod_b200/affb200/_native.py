@@ -80,6 +80,7 @@ SIGNATURES = {
     "affb200_batch_norm_work_floats": (_i64, [_i64, _i64]),
     "affb200_batch_norm_fwd": (_int, [_ptr] * 5 + [ctypes.c_float, ctypes.c_float, _int] + [_ptr] * 4
                                + [_i64, _i64, _int, _ptr]),
+    "affb200_batch_norm_apply": (_int, [_ptr] * 5 + [_int, _ptr, _i64, _i64, _int, _ptr]),
     "affb200_batch_norm_bwd": (_int, [_ptr] * 6 + [_int] + [_ptr] * 4 + [_i64, _i64, _int, _ptr, _ptr]),
     "affb200_gelu_tables": (_int, [_int, _ptr, _ptr, _ptr]),
     "affb200_gelu_fwd": (_int, [_ptr, _ptr, _i64, _int, _ptr, _ptr]),

@@ -253,12 +253,40 @@ def _stem_conv_ok(x, conv):
             and x.is_contiguous(memory_format=torch.channels_last) and conv.weight.dtype == torch.float32)
 
 
+def _conv_bn_eval(x, conv, bn, gelu):
+    """Inference: evaluation-mode BatchNorm is a per-channel affine map, so conv bias, running statistics, affine and
+    GELU run as ONE pass over the bias-free convolution output (the stock chain: bias add, normalisation, GELU — three
+    to five passes over the largest activation of the network).  None when the layout is not covered."""
+    with torch.no_grad():
+        y = ConvStemFunction.apply(x, conv.weight) if _stem_conv_ok(x, conv) else conv._conv_forward(x, conv.weight, None)
+        if not (y.dtype in _OK and y.numel() > 0 and y.is_contiguous(memory_format=torch.channels_last)):
+            return None
+        B, C, H, W = y.shape
+        dev = y.device
+        mean = bn.running_mean.float()
+        if conv.bias is not None:
+            mean = mean - conv.bias.float()
+        rstd = torch.rsqrt(bn.running_var.float() + bn.eps)
+        g, b = bn.weight.float().contiguous(), bn.bias.float().contiguous()
+        with torch.cuda.device(dev):
+            out = torch.empty_like(y)
+            N.check(N.LIB.affb200_batch_norm_apply(N.p(y), N.p(g), N.p(b), N.p(mean.contiguous()), N.p(rstd.contiguous()),
+                                                   1 if gelu else 0, N.p(out), B * H * W, C, N.dtype_enum(y),
+                                                   N.stream_ptr(dev)), "batch_norm_apply")
+    return out
+
+
 def conv_batch_norm_act(x, conv, bn, gelu=True):
     """GELU(bn(conv(x))) for the stem's conv -> BatchNorm pair (reference aff_transformer.py:541-543).  A per-channel
     constant added before a training-mode BatchNorm cancels in (x - mean): the convolution runs without its bias (no
     bias-add pass over the activation, no bias-gradient reduction over it in the backward), the batch mean that feeds
     `running_mean` gets the bias back, and the bias receives the gradient it has in exact arithmetic: zero.  Evaluation
     mode and unsupported layouts run conv (with bias) -> bn -> gelu through the stock operators."""
+    if (x.is_cuda and not bn.training and bn.affine and bn.track_running_stats and conv.out_channels in (8, 16, 32, 64, 128)
+            and not (torch.is_grad_enabled() and (x.requires_grad or conv.weight.requires_grad or bn.weight.requires_grad))):
+        out = _conv_bn_eval(x, conv, bn, gelu)
+        if out is not None:
+            return out
     if conv.bias is None or not (x.is_cuda and bn.training and bn.affine and bn.track_running_stats
                                  and bn.momentum is not None and conv.out_channels in (8, 16, 32, 64, 128)):
         return batch_norm_act(conv(x), bn, gelu)

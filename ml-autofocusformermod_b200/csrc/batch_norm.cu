@@ -379,6 +379,36 @@ extern "C" int affb200_batch_norm_fwd(const void *x, const float *gamma, const f
     });
 }
 
+// y = act(gamma * (x - mean) * rstd + beta) with GIVEN per-channel mean / rstd: evaluation-mode BatchNorm (running
+// statistics) as one pass, GELU included.
+extern "C" int affb200_batch_norm_apply(const void *x, const float *gamma, const float *beta, const float *mean,
+                                        const float *rstd, int gelu, void *y, int64_t R, int64_t C, int dtype,
+                                        void *stream) {
+    if (!bn_shape_ok("batch_norm_apply", R, C, dtype)) return AFFB200_E_ARG;
+    if (!x || !gamma || !beta || !mean || !rstd || !y || !aligned16(x) || !aligned16(y) || !aligned16(gamma) ||
+        !aligned16(beta) || !aligned16(mean) || !aligned16(rstd)) {
+        set_error("batch_norm_apply: null or misaligned pointer");
+        return AFFB200_E_ARG;
+    }
+    auto st = (cudaStream_t)stream;
+    const int grid = bn_grid(R, int(C / 8));
+    return dispatch_dtype(dtype, [&](auto tag) -> int {
+        using T = decltype(tag);
+        if constexpr (std::is_same<T, double>::value) {
+            return AFFB200_E_ARG;
+        } else {
+#define AFF_BN_APPLY2(L_)                                                                                         \
+    do {                                                                                                          \
+        if (gelu) bn_apply_kernel<T, L_, true><<<grid, kBT, 0, st>>>((const T *)x, gamma, beta, mean, rstd, (T *)y, R); \
+        else bn_apply_kernel<T, L_, false><<<grid, kBT, 0, st>>>((const T *)x, gamma, beta, mean, rstd, (T *)y, R);     \
+    } while (0)
+            AFF_BN_LPR(AFF_BN_APPLY2)
+#undef AFF_BN_APPLY2
+            return check_launch("batch_norm_apply");
+        }
+    });
+}
+
 extern "C" int affb200_batch_norm_bwd(const void *dy, const void *x, const float *gamma, const float *beta,
                                       const float *mean, const float *rstd, int gelu, void *dx, float *dgamma,
                                       float *dbeta, float *work, int64_t R, int64_t C, int dtype,

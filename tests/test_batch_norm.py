@@ -138,9 +138,21 @@ def test_conv_batch_norm_act_folds_the_conv_bias(dtype):
     assert_close(b1.running_mean, b2.running_mean.double(), dtype, "running_mean")
     assert_close(b1.running_var, b2.running_var.double(), dtype, "running_var")
     assert int(b1.num_batches_tracked) == 1
+    # evaluation mode: bias, running statistics, affine and GELU as one pass over the bias-free convolution output
     b1.eval()
     with torch.no_grad():
-        assert torch.equal(conv_batch_norm_act(x, c1, b1), torch.nn.functional.gelu(b1(c1(x))))
+        want = torch.nn.functional.gelu(b1(c1(x))).double()
+        assert_close(conv_batch_norm_act(x, c1, b1), want, torch.float32, "eval fp32")
+        xl = x.to(dtype)
+        with torch.autocast(**ac):
+            got = conv_batch_norm_act(xl, c1, b1)
+        assert got.dtype == dtype
+        assert_close(got, want, dtype, "eval")
+    # with gradients wanted in evaluation mode the stock operators run
+    xg = x.clone().requires_grad_(True)
+    y = conv_batch_norm_act(xg, c1, b1)
+    y.sum().backward()
+    assert xg.grad is not None and torch.equal(y, torch.nn.functional.gelu(b1(c1(x))))
 
 
 @pytest.mark.parametrize("sink", [False, True])
