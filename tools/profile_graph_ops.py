@@ -16,18 +16,22 @@ import bench_workloads as W  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=60)
+    ap.add_argument("--workload", default="", help="e.g. aff_tiny_1_5th_infer: profiles the eager inference forward")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
-    wl = W.get("")
+    wl = W.get(a.workload)
     run = wl.build(wl.default_batch, dev, 1)
     batch = run.to_device(run.make_host_batch(0))
     for _ in range(2):
         run.step(batch)
     torch.cuda.synchronize()
-    g = run.gstep
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU], record_shapes=True) as prof:
-        g._fwd_bwd()
+        if getattr(run, "infer", False):
+            with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+                run.model(batch[0])
+        else:
+            run.gstep._fwd_bwd()
         torch.cuda.synchronize()
     rows = []
     for e in prof.key_averages(group_by_input_shape=True):
