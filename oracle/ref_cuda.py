@@ -7,7 +7,7 @@ compiled modules can be driven without importing /root/reference at run time:
   AV  clusten/clusten.py:47-66   forward(attn, v, idx);                 backward(grad, attn, v, idx)
   WF  clusten/clusten.py:73-92   forward(weights, feat, idx);           backward(grad, weights, feat, idx)
 
-Only tests/, tools/opbench.py and bench.py's comparator leg may import this module; the product package never does
+Only tests/ (incl. the tests/opbench.py timing script) and bench.py's comparator leg may import this module; the product package never does
 (tests/test_layout.py).  `available()` is False when oracle/_ref/ holds no built modules (the build needs
 /root/reference, which exists only in the build container; the built .so files travel to the GPU box)."""
 import glob

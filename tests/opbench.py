@@ -2,7 +2,7 @@
 GB/s on the algorithmic bytes of SURVEY.md §8(d), fraction of the measured HBM peak.  Working sets are larger than
 L2 (126 MB) at the training shapes; smaller shapes get an L2 flush between iterations.
 
-  python tools/opbench.py [--shapes tiny15_s1,...] [--dtype bf16] [--idx S|U] [--iters 20]
+  python tests/opbench.py [--shapes tiny15_s1,...] [--dtype bf16] [--idx S|U] [--iters 20]
 """
 import argparse
 import json
