@@ -17,6 +17,17 @@ def test_package_does_not_import_oracle_or_reference():
     assert not bad, bad
 
 
+def test_tools_do_not_touch_the_oracle():
+    """Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline / reference leg may import oracle/."""
+    bad = []
+    for fn in os.listdir(os.path.join(ROOT, "tools")):
+        if fn.endswith(".py"):
+            src = open(os.path.join(ROOT, "tools", fn)).read()
+            if re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M):
+                bad.append(fn)
+    assert not bad, bad
+
+
 def test_oracle_says_it_is_test_infrastructure():
     for fn in os.listdir(os.path.join(ROOT, "oracle")):
         if fn.endswith((".py", ".c")):
