@@ -17,3 +17,10 @@ with torch.no_grad():
     print("cudnn %.1f us" % t(lambda: torch.nn.functional.conv2d(x, wl, None, 2, 1)))
 g = torch.randn(256, 32, 112, 112, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
 print("cudnn wgrad %.1f us" % t(lambda: torch.ops.aten.convolution_backward(g, x, wl, None, [2, 2], [1, 1], [1, 1], False, [0, 0], 1, [False, True, False])))
+for cpad in (4, 8):
+    xp = torch.zeros(256, cpad, 224, 224, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    xp[:, :3] = x
+    wp = torch.zeros(32, cpad, 3, 3, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    print("cudnn wgrad, input padded to %d channels %.1f us" % (cpad, t(lambda: torch.ops.aten.convolution_backward(
+        g, xp, wp, None, [2, 2], [1, 1], [1, 1], False, [0, 0], 1, [False, True, False]))))
+    print("   pad copy %.1f us" % t(lambda: xp[:, :3].copy_(x)))
