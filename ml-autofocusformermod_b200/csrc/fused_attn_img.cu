@@ -43,8 +43,20 @@ __host__ __device__ inline ImgSmem img_smem(int UC, int TT, int C, bool bwd) {
 template <typename T, int C>
 __device__ __forceinline__ void img_stage_rows(uint32_t buf_addr, const T *base, int stride, int n) {
     constexpr int CS = C + 8, CH = C / 8;
+    // lane -> chunk so that the 8 lanes of a 128-bit shared-memory phase write the SAME chunk of 8 consecutive rows:
+    // with the 16-byte row padding those 8 stores fall into distinct bank groups (rows of one phase in the natural
+    // order, 2 rows x 4 chunks, collide: row r chunk 0 and row r+1 chunk 3 share banks)
+    const int n8 = n & ~7;
     for (int e = threadIdx.x; e < n * CH; e += kFT) {
-        const int row = e / CH, ch = e % CH;
+        int row, ch;
+        if (e < n8 * CH) {
+            const int blk = e / (8 * CH), in = e - blk * (8 * CH);
+            row = blk * 8 + (in & 7);
+            ch = in >> 3;
+        } else {
+            row = e / CH;
+            ch = e % CH;
+        }
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(buf_addr + uint32_t(row * CS + ch * 8) * 2u),
                      "l"(base + row * stride + ch * 8) : "memory");
     }
