@@ -365,6 +365,20 @@ int64_t affb200_col_sum_work_floats(int64_t R, int64_t C);
 int affb200_col_sum(const void *x, float *out, float *work, int64_t R, int64_t C, int dtype, int accumulate,
                     void *stream);
 
+/* affb200_col_sum without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The slab partials live in a file-scope `static __device__` array of
+ * AFFB200_COL_SUM_STATIC_MAX_FLOATS floats (1 MiB; every GPU that loads the library holds it until the process
+ * exits).  Shapes whose affb200_col_sum_work_floats(R, C) exceeds that limit are rejected with AFFB200_E_WORKSPACE
+ * (the partials take at most 151 552 floats for C <= 151 552 and C floats above, for any R: only C > 262 144 is refused).  Same arithmetic and summation order as
+ * affb200_col_sum (bit-identical results).  The call makes no cudaMalloc / cudaFree / allocating library call; `stream`
+ * must belong to the current device.  All calls on a device share the one array, which keeps the last call's partials
+ * (nothing in it needs to start at zero: each call first overwrites what it later reads); two calls that overlap on
+ * the GPU (different streams without an ordering between them) RACE on it — serialise them or use affb200_col_sum. */
+#define AFFB200_COL_SUM_STATIC_MAX_FLOATS 262144
+int64_t affb200_col_sum_static_max_floats(void);
+int affb200_col_sum_static(const void *x, float *out, int64_t R, int64_t C, int dtype, int accumulate, void *stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * Exact (erf) GELU of the Mlp (reference models/aff_transformer.py:35-51, nn.GELU) for f16/bf16 as table lookups:
  * a 2-byte input has 65 536 values.  affb200_gelu_tables fills, for `dtype`, fwd_tab (65 536 entries of dtype:

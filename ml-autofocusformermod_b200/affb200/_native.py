@@ -91,6 +91,8 @@ SIGNATURES = {
     "affb200_weight_net_bwd": (_int, [_ptr] * 5 + [ctypes.c_float, _i64, _int, _ptr, _ptr, _ptr, _ptr]),
     "affb200_col_sum_work_floats": (_i64, [_i64, _i64]),
     "affb200_col_sum": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _int, _int, _ptr]),
+    "affb200_col_sum_static_max_floats": (_i64, []),
+    "affb200_col_sum_static": (_int, [_ptr, _ptr, _i64, _i64, _int, _int, _ptr]),
     "affb200_layer_norm_fwd": (_int, [_ptr] * 6 + [_i64, _i64, ctypes.c_float, _int, _int, _ptr]),
     "affb200_layer_norm_bwd_work_floats": (_i64, [_i64, _i64]),
     "affb200_layer_norm_bwd": (_int, [_ptr] * 10 + [_i64, _i64, _int, _int, _int, _ptr]),

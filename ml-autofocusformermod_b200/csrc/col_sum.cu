@@ -5,6 +5,7 @@
 // leaves fp32 partials [slab][C]; a second kernel adds the slabs in a fixed order (no atomics: bit-reproducible).
 #include "common.cuh"
 #include <algorithm>
+#include <atomic>
 
 namespace affb200 {
 
@@ -146,4 +147,84 @@ extern "C" int affb200_col_sum(const void *x, float *out, float *work, int64_t R
     });
     if (e) return e;
     return launch_col_sum_finish(work, n_slabs, int(C), out, accumulate, st);
+}
+
+// ---- allocation-free variant --------------------------------------------------------------------------------
+// affb200_col_sum_static: the same two kernels with the slab partials in a file-scope device array instead of a
+// caller-provided workspace, for callers that cannot allocate (CUDA graph capture, serving loops).  No counterpart
+// in the reference.  The array (1 MiB) is part of the module image: every GPU that loads the library holds it until
+// the process exits.  In host code `g_static_part` names a host-side stand-in, not device memory, so its device
+// address is looked up once per device with cudaGetSymbolAddress while that device is current.
+namespace affb200 {
+
+constexpr int64_t kStaticWorkFloats = AFFB200_COL_SUM_STATIC_MAX_FLOATS;
+static __device__ __align__(256) float g_static_part[kStaticWorkFloats];
+
+constexpr int kMaxDevices = 64;
+static std::atomic<float *> g_static_ptr[kMaxDevices];
+
+static float *static_part_address() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        set_error("col_sum_static: cudaGetDevice failed or device ordinal %d unsupported (%s)", dev,
+                  cudaGetErrorString(e));
+        return nullptr;
+    }
+    float *ptr = g_static_ptr[dev].load(std::memory_order_acquire);
+    if (ptr) return ptr;
+    void *sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_static_part);
+    if (e != cudaSuccess || !sym) {
+        set_error("col_sum_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        return nullptr;
+    }
+    g_static_ptr[dev].store(static_cast<float *>(sym), std::memory_order_release);
+    return static_cast<float *>(sym);
+}
+
+}  // namespace affb200
+
+extern "C" int64_t affb200_col_sum_static_max_floats(void) { return kStaticWorkFloats; }
+
+extern "C" int affb200_col_sum_static(const void *x, float *out, int64_t R, int64_t C, int dtype, int accumulate,
+                                      void *stream) {
+    if (R <= 0 || C <= 0 || C % 8 != 0 || C >= (int64_t(1) << 24)) {
+        set_error("col_sum_static: R must be positive and C a positive multiple of 8");
+        return AFFB200_E_ARG;
+    }
+    if (!x || !out || !aligned16(x)) { set_error("col_sum_static: null or misaligned pointer"); return AFFB200_E_ARG; }
+    int lpr, n_cblk, n_slabs;
+    int64_t rps;
+    col_sum_geometry(R, C, &lpr, &n_cblk, &n_slabs, &rps);
+    const int64_t need = int64_t(n_slabs) * C;
+    if (need > kStaticWorkFloats) {
+        set_error("col_sum_static: [%lld][%lld] needs %lld floats of scratch, the built-in array holds %lld; use "
+                  "affb200_col_sum with a caller workspace", (long long)R, (long long)C, (long long)need,
+                  (long long)kStaticWorkFloats);
+        return AFFB200_E_WORKSPACE;
+    }
+    if (dtype != AFFB200_F32 && dtype != AFFB200_F16 && dtype != AFFB200_BF16) {
+        set_error("col_sum_static: f32 / f16 / bf16 only");
+        return AFFB200_E_ARG;
+    }
+    float *part = static_part_address();
+    if (!part) return AFFB200_E_CUDA;
+    auto st = (cudaStream_t)stream;
+    const dim3 grid{unsigned(n_slabs), unsigned(n_cblk), 1u};
+    // every partial [slab][col] that the finish kernel reads is written by the first kernel of this call: nothing in
+    // the shared array has to start at zero, whatever an earlier call left there
+    int e = dispatch_dtype(dtype, [&](auto tag) -> int {
+        using T = decltype(tag);
+        if constexpr (sizeof(T) == 8) {
+            return AFFB200_E_ARG;
+        } else {
+            if (lpr == 8) col_sum_kernel<T, 8><<<grid, kCT, 0, st>>>((const T *)x, part, R, int(C), rps);
+            else if (lpr == 16) col_sum_kernel<T, 16><<<grid, kCT, 0, st>>>((const T *)x, part, R, int(C), rps);
+            else col_sum_kernel<T, 32><<<grid, kCT, 0, st>>>((const T *)x, part, R, int(C), rps);
+            return check_launch("col_sum_static");
+        }
+    });
+    if (e) return e;
+    return launch_col_sum_finish(part, n_slabs, int(C), out, accumulate, st);
 }
