@@ -284,6 +284,53 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
                            void *ds_work, void *p_work, float *blank_part, float *d_table, int64_t P,
                            int64_t B, int64_t H, int64_t N, int64_t M, int64_t c, float scale, int dtype, void *stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Block-structured form of the same operator (csrc/fused_cl_*.cu).  The reference builds every neighbourhood from
+ * whole clusters of consecutive rows (models/point_utils.py:203-206 member_idx = arange; models/aff_transformer.py:
+ * 476-480 nbhd = member_idx.gather(nearest_cluster)) and every bias index from a position difference (:483-487), so
+ *   nbhd_idx[b,i,8q+r] = blk[b,i,q]*8 + r  (rows >= N of the padded last cluster masked),
+ *   pe_idx[b,i,j] = (y_u - y_i + w)*tw + (x_u - x_i + w),  w = rel_pos_width, tw = table_width = 2w+1.
+ * affb200_cl_qplan_build verifies exactly that against nbhd_idx / cluster_mask / pe_idx / pos [B][N][2] (integer
+ * coordinates in 0..32767) and emits, per tile of 64 tokens, the ascending union of referenced 8-row blocks (<= 64),
+ * per token a 64-bit membership word over that union, the block ids, and positions packed (y << 16 | x) (padded to
+ * a multiple of 8 rows with 0xffffffff).  stats[8] int32 (caller-zeroed): [0] tiles whose union exceeds 64 blocks,
+ * [1] tiles that do not have the structure (AFFB200_CL_BAD in their header), [4] largest union, [2]/[5] the same for
+ * affb200_cl_kplan_build (query tokens per tile of 64 key rows: overflow count over `kumax`, largest list).  A plan
+ * with stats[0] | stats[1] | stats[2] != 0 must not be used: keep affb200_fused_attn_fwd/_bwd (any index tensor).
+ * k_utok entries are (query token << 8) | (bit r set: the token references block 8*tile + r), ascending by token.
+ *
+ * The kernels stage a union row's K|V (both heads of a group, one 256-byte bulk-async copy) once per tile, form S by
+ * blocks in tensor-core accumulators, take the bias from table[pos_u - pos_i] (a shared-memory window of `table`
+ * [P][H] fp32, P = tw*tw) and keep P in registers as the operand of P·V: no pe_idx stream, no per-slot gather.  k / v
+ * must be the two halves of one kv row ([H][2][c]: v->p == k->p + c elements, sH == 2c), q / out rows [H][c], H even.
+ * `guard` (int32, device) is incremented for every tile the kernels had to skip (header flagged or union > ucap):
+ * only plans built without reading stats back (CUDA graph capture) can trip it; the tile's outputs are then zeros.
+ * ---------------------------------------------------------------------------------------------------------- */
+#define AFFB200_CL_UMAX 64
+#define AFFB200_CL_BAD 0x10000000
+typedef struct {
+    int32_t ucap;            /* union blocks the launch sizes shared memory for: >= stats[4], <= AFFB200_CL_UMAX */
+    const int32_t *q_hdr;    /* [B][ceil(N/64)] */
+    const uint16_t *q_ucl;   /* [B][ceil(N/64)][64] */
+    const uint64_t *q_mask;  /* [B][N] */
+    const uint32_t *pos16;   /* [B][ceil(N/8)*8] */
+    const uint16_t *blk;     /* [B][N][M/8] */
+    int32_t kumax;           /* capacity of a key tile's token list (multiple of 16); 0: no key-tile plan */
+    const int32_t *k_hdr;    /* [B][ceil(N/64)] */
+    const uint32_t *k_utok;  /* [B][ceil(N/64)][kumax] */
+} affb200_cl_plan;
+
+int64_t affb200_cl_tiles(int64_t n);
+int affb200_cl_qplan_build(const int64_t *nbhd_idx, const int64_t *mask, const int64_t *pe_idx, const float *pos,
+                           int64_t B, int64_t N, int64_t M, int64_t rel_pos_width, int64_t table_width, uint16_t *blk,
+                           int32_t *hdr, uint16_t *ucl, uint64_t *qmask, uint32_t *pos16, int32_t *stats, void *stream);
+int affb200_cl_kplan_build(const uint16_t *blk, int64_t B, int64_t N, int64_t M, int64_t kumax, int32_t *hdr,
+                           uint32_t *utok, int32_t *stats, void *stream);
+int affb200_fused_cl_fwd(const affb200_view *q, const affb200_view *k, const affb200_view *v, const affb200_view *out,
+                         const float *table, const float *blank_k, const float *blank_v, const affb200_cl_plan *plan,
+                         float *lse, int32_t *guard, int64_t B, int64_t H, int64_t N, int64_t c, int64_t rel_pos_width,
+                         int64_t table_width, float scale, int dtype, void *stream);
+
 /* Gradient of the bias table's generator.  In ClusterAttention the table is pos_embed(pre_table) = feat·W^T + b
  * (reference aff_transformer.py:78,125) and only W and b receive its gradient, so the [P][H] histogram can be skipped:
  * pass d_table = NULL to the backward entry points and call this on their ds_work [B][H][N*M]:

@@ -1,0 +1,141 @@
+// fused_cl.cuh — shared pieces of the block-structured fused neighbourhood attention (fused_cl_fwd.cu,
+// fused_cl_bwd.cu) and its plan builders (fused_cl_plan.cu).
+//
+// Structure exploited (reference models/point_utils.py:203-206, models/aff_transformer.py:476-480): after
+// space_filling_cluster the tokens of a cluster are stored contiguously and a neighbourhood is the member lists of
+// the nnc nearest clusters, so nbhd_idx[b,i,8q..8q+7] are 8 CONSECUTIVE rows starting at a multiple of 8 (clusters of
+// 8, 16, 24 ... rows are 1, 2, 3 ... such blocks); only the padded tail of the last cluster is irregular (rows >= N,
+// masked).  A neighbourhood is therefore M/8 block ids, and a tile of 64 consecutive tokens references a union of
+// ~25-40 blocks (measured on the AFF pipelines).  The kernels treat a tile as DENSE MASKED attention over that union:
+//   * every union row is staged once per tile with ONE bulk-async copy (cp.async.bulk -> UBLKCP, completion on an
+//     mbarrier -> SYNCS) of the row's K and V for a group of heads (256 B), instead of 16-byte cp.async pieces;
+//   * S = Q·K_U^T is produced block by block in mma.sync accumulator registers (an n-tile of 8 columns IS one block),
+//     masked by the row's 64-bit membership word over the tile's union, biased with table[pos_u - pos_i] from a
+//     shared-memory window of the relative-position table (no pe_idx stream), exponentiated in registers and fed
+//     straight back as the A operand of P·V_U — no S/P round trip through shared memory, no per-slot gather;
+//   * a warp (16 tokens) visits only the union blocks its own rows reference (~12 of the tile's ~30).
+#pragma once
+#include "fused_attn.cuh"
+
+namespace affb200 {
+
+constexpr int kClT = 64;        // tokens per query tile / key rows per key tile
+constexpr int kClThreads = 128; // 4 warps x 16 rows
+constexpr int kClUMax = AFFB200_CL_UMAX;   // union blocks per tile (membership is a 64-bit word)
+constexpr int kClWin = 32;      // side of the shared-memory window of the relative-position table
+constexpr int kClWinHalf = 16;  // offsets -16 .. 15 are served from the window, the rest from the global table
+constexpr uint32_t kClPosBias = (uint32_t(kClWinHalf) << 16) | uint32_t(kClWinHalf);
+constexpr uint32_t kClPosInvalid = 0xffffffffu;   // packed position of a padded row (>= N)
+
+// ---- mbarrier + bulk async copy (PTX ISA 8.x; SASS: SYNCS.*, UBLKCP) --------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+// global -> shared, `bytes` a multiple of 16, both addresses 16-byte aligned; completes `bytes` on the mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void cl_ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void cl_ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void cl_ldsm_x2(uint32_t (&r)[2], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint2 lds_u64(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float2 lds_f2(uint32_t addr) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float lds_f1(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+
+// Relative-position bias of (token i, union row u) for a group of HG heads.
+//   d = pos_u - (pos_i - (16,16)) as packed (y << 16 | x) integers; when both offsets lie in [-16, 16) the two fields of
+//   d are the window coordinates and the entry comes from shared memory ([32*32][HG] floats); otherwise (rare: far
+//   neighbours of sparse stages, padded rows) the offsets are rebuilt and the global table [P][H] is read.
+// All values are pre-multiplied by log2(e).  A padded row (pos_u == kClPosInvalid) yields -inf.
+struct ClBiasCtx {
+    uint32_t win;          // shared-memory address of the window
+    const float *table;    // [P][H] fp32
+    int H, h0, w, tw;      // heads, first head of the group, rel_pos_width, table_width
+};
+
+template <int HG>
+__device__ __noinline__ void cl_bias_far(const ClBiasCtx &cx, uint32_t pu, uint32_t pi_biased, float (&out)[HG]) {
+    if (pu == kClPosInvalid) {
+#pragma unroll
+        for (int hh = 0; hh < HG; ++hh) out[hh] = -INFINITY;
+        return;
+    }
+    const uint32_t pi = pi_biased + kClPosBias;
+    const int dx = int(pu & 0xffffu) - int(pi & 0xffffu), dy = int(pu >> 16) - int(pi >> 16);
+    const int pe = (dy + cx.w) * cx.tw + dx + cx.w;
+#pragma unroll
+    for (int hh = 0; hh < HG; ++hh) out[hh] = __ldg(cx.table + int64_t(pe) * cx.H + cx.h0 + hh) * kLog2e;
+}
+
+template <int HG>
+__device__ __forceinline__ void cl_bias(const ClBiasCtx &cx, uint32_t pu, uint32_t pi_biased, bool member,
+                                        float (&out)[HG]) {
+    const uint32_t d = pu - pi_biased;
+    if (member && (d & 0xffe0ffe0u) != 0u) {
+        cl_bias_far<HG>(cx, pu, pi_biased, out);
+        return;
+    }
+    const uint32_t idx = ((d >> 11) | (d & 31u)) & 1023u;   // the mask only matters for non-members (value unused)
+    if constexpr (HG == 2) {
+        const float2 v = lds_f2(cx.win + idx * 8u);
+        out[0] = v.x; out[1] = v.y;
+    } else {
+#pragma unroll
+        for (int hh = 0; hh < HG; ++hh) out[hh] = lds_f1(cx.win + (idx * HG + hh) * 4u);
+    }
+}
+
+// fill the window for head group h0..h0+HG-1 (all threads of the CTA; caller synchronises)
+template <int HG>
+__device__ __forceinline__ void cl_fill_window(float *win, const float *__restrict__ table, int H, int h0, int w, int tw) {
+    for (int e = threadIdx.x; e < kClWin * kClWin; e += blockDim.x) {
+        const int dy = (e >> 5) - kClWinHalf, dx = (e & 31) - kClWinHalf;
+        const bool ok = dy >= -w && dy <= w && dx >= -w && dx <= w;
+        const int64_t pe = int64_t(dy + w) * tw + dx + w;
+#pragma unroll
+        for (int hh = 0; hh < HG; ++hh) win[e * HG + hh] = ok ? __ldg(table + pe * H + h0 + hh) * kLog2e : 0.f;
+    }
+}
+
+}  // namespace affb200
