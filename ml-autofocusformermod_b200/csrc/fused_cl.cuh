@@ -13,14 +13,17 @@
 //     masked by the row's 64-bit membership word over the tile's union, biased with table[pos_u - pos_i] from a
 //     shared-memory window of the relative-position table (no pe_idx stream), exponentiated in registers and fed
 //     straight back as the A operand of P·V_U — no S/P round trip through shared memory, no per-slot gather;
-//   * a warp (16 tokens) visits only the union blocks its own rows reference (~12 of the tile's ~30).
+//   * a warp owns 8 tokens (one cluster of the space-filling order) and BOTH heads of a head group: rows 0-7 of its
+//     m16 tiles are head 0, rows 8-15 head 1 of the same tokens (the operand halves of the other head are zero), so
+//     membership and the bias index are computed once per (token, row) for both heads, and a warp visits only the
+//     union blocks its 8 tokens reference (~9 of the tile's ~30; each token uses 6).
 #pragma once
 #include "fused_attn.cuh"
 
 namespace affb200 {
 
 constexpr int kClT = 64;        // tokens per query tile / key rows per key tile
-constexpr int kClThreads = 128; // 4 warps x 16 rows
+constexpr int kClThreads = 256; // 8 warps x (8 tokens x 2 heads)
 constexpr int kClUMax = AFFB200_CL_UMAX;   // union blocks per tile (membership is a 64-bit word)
 constexpr int kClWin = 32;      // side of the shared-memory window of the relative-position table
 constexpr int kClWinHalf = 16;  // offsets -16 .. 15 are served from the window, the rest from the global table
@@ -67,6 +70,11 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
+    uint16_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ uint2 lds_u64(uint32_t addr) {
     uint2 v;
     asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
@@ -85,45 +93,30 @@ __device__ __forceinline__ float lds_f1(uint32_t addr) {
 
 // Relative-position bias of (token i, union row u) for a group of HG heads.
 //   d = pos_u - (pos_i - (16,16)) as packed (y << 16 | x) integers; when both offsets lie in [-16, 16) the two fields of
-//   d are the window coordinates and the entry comes from shared memory ([32*32][HG] floats); otherwise (rare: far
-//   neighbours of sparse stages, padded rows) the offsets are rebuilt and the global table [P][H] is read.
-// All values are pre-multiplied by log2(e).  A padded row (pos_u == kClPosInvalid) yields -inf.
+//   d are the window coordinates and the entry comes from shared memory ([32*32 + 1][HG] floats, the last entry -inf:
+//   where non-members are pointed); otherwise (rare: far neighbours of sparse stages, padded rows) cl_bias_far
+//   rebuilds the offsets and reads the global table [P][H].  Values are pre-multiplied by log2(e).
 struct ClBiasCtx {
     uint32_t win;          // shared-memory address of the window
     const float *table;    // [P][H] fp32
     int H, h0, w, tw;      // heads, first head of the group, rel_pos_width, table_width
 };
+constexpr uint32_t kClWinSentinel = kClWin * kClWin;   // index of the -inf entry
 
-template <int HG>
-__device__ __noinline__ void cl_bias_far(const ClBiasCtx &cx, uint32_t pu, uint32_t pi_biased, float (&out)[HG]) {
-    if (pu == kClPosInvalid) {
-#pragma unroll
-        for (int hh = 0; hh < HG; ++hh) out[hh] = -INFINITY;
-        return;
-    }
-    const uint32_t pi = pi_biased + kClPosBias;
-    const int dx = int(pu & 0xffffu) - int(pi & 0xffffu), dy = int(pu >> 16) - int(pi >> 16);
-    const int pe = (dy + cx.w) * cx.tw + dx + cx.w;
-#pragma unroll
-    for (int hh = 0; hh < HG; ++hh) out[hh] = __ldg(cx.table + int64_t(pe) * cx.H + cx.h0 + hh) * kLog2e;
+__device__ __forceinline__ uint32_t cl_win_index(uint32_t pu, uint32_t pi_biased, bool member, bool &far) {
+    const uint32_t d = pu - pi_biased;
+    far = member && (d & 0xffe0ffe0u) != 0u;
+    return member ? (((d >> 11) | (d & 31u)) & 1023u) : kClWinSentinel;
 }
 
-template <int HG>
-__device__ __forceinline__ void cl_bias(const ClBiasCtx &cx, uint32_t pu, uint32_t pi_biased, bool member,
-                                        float (&out)[HG]) {
-    const uint32_t d = pu - pi_biased;
-    if (member && (d & 0xffe0ffe0u) != 0u) {
-        cl_bias_far<HG>(cx, pu, pi_biased, out);
-        return;
-    }
-    const uint32_t idx = ((d >> 11) | (d & 31u)) & 1023u;   // the mask only matters for non-members (value unused)
-    if constexpr (HG == 2) {
-        const float2 v = lds_f2(cx.win + idx * 8u);
-        out[0] = v.x; out[1] = v.y;
-    } else {
-#pragma unroll
-        for (int hh = 0; hh < HG; ++hh) out[hh] = lds_f1(cx.win + (idx * HG + hh) * 4u);
-    }
+// a padded row (pos_u == kClPosInvalid) yields -inf
+static __device__ __noinline__ float cl_bias_far(const float *__restrict__ table, int H, int h, int w, int tw, uint32_t pu,
+                                          uint32_t pi_biased) {
+    if (pu == kClPosInvalid) return -INFINITY;
+    const uint32_t pi = pi_biased + kClPosBias;
+    const int dx = int(pu & 0xffffu) - int(pi & 0xffffu), dy = int(pu >> 16) - int(pi >> 16);
+    const int pe = (dy + w) * tw + dx + w;
+    return __ldg(table + int64_t(pe) * H + h) * kLog2e;
 }
 
 // fill the window for head group h0..h0+HG-1 (all threads of the CTA; caller synchronises)
@@ -136,6 +129,7 @@ __device__ __forceinline__ void cl_fill_window(float *win, const float *__restri
 #pragma unroll
         for (int hh = 0; hh < HG; ++hh) win[e * HG + hh] = ok ? __ldg(table + pe * H + h0 + hh) * kLog2e : 0.f;
     }
+    if (threadIdx.x < HG) win[kClWin * kClWin * HG + threadIdx.x] = -INFINITY;
 }
 
 }  // namespace affb200
