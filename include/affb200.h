@@ -292,8 +292,8 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
  *   pe_idx[b,i,j] = (y_u - y_i + w)*tw + (x_u - x_i + w),  w = rel_pos_width, tw = table_width = 2w+1.
  * affb200_cl_qplan_build verifies exactly that against nbhd_idx / cluster_mask / pe_idx / pos [B][N][2] (integer
  * coordinates in 0..32767) and emits, per tile of 64 tokens, the ascending union of referenced 8-row blocks (<= 64),
- * per token a 64-bit membership word over that union, the block ids, and positions packed (y << 16 | x) (padded to
- * a multiple of 8 rows with 0xffffffff).  stats[8] int32 (caller-zeroed): [0] tiles whose union exceeds 64 blocks,
+ * per token a 64-bit membership word over that union, the block ids, and positions packed (y << 16 | x); the last
+ * two arrays are padded per image to whole tiles (membership 0, position 0xffffffff).  stats[8] int32 (caller-zeroed): [0] tiles whose union exceeds 64 blocks,
  * [1] tiles that do not have the structure (AFFB200_CL_BAD in their header), [4] largest union, [2]/[5] the same for
  * affb200_cl_kplan_build (query tokens per tile of 64 key rows: overflow count over `kumax`, largest list).  A plan
  * with stats[0] | stats[1] | stats[2] != 0 must not be used: keep affb200_fused_attn_fwd/_bwd (any index tensor).
@@ -312,8 +312,8 @@ typedef struct {
     int32_t ucap;            /* union blocks the launch sizes shared memory for: >= stats[4], <= AFFB200_CL_UMAX */
     const int32_t *q_hdr;    /* [B][ceil(N/64)] */
     const uint16_t *q_ucl;   /* [B][ceil(N/64)][64] */
-    const uint64_t *q_mask;  /* [B][N] */
-    const uint32_t *pos16;   /* [B][ceil(N/8)*8] */
+    const uint64_t *q_mask;  /* [B][ceil(N/64)*64] */
+    const uint32_t *pos16;   /* [B][ceil(N/64)*64] */
     const uint16_t *blk;     /* [B][N][M/8] */
     int32_t kumax;           /* capacity of a key tile's token list (multiple of 16); 0: no key-tile plan */
     const int32_t *k_hdr;    /* [B][ceil(N/64)] */

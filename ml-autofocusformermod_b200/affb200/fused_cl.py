@@ -56,7 +56,7 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, want_k):
     B, n, M = nbhd_idx.shape
     dev = nbhd_idx.device
     pl = ClPlan(B, n, M, w, tw)
-    nblk8 = ((n + 7) // 8) * 8
+    npad = pl.tiles * CL_T
     skey = (B, n, M)
     static = _plan.is_static()
     obs = _plan._observed.get(("cl",) + skey)
@@ -68,8 +68,8 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, want_k):
         blk = torch.empty((B, n, M // 8), dtype=torch.int16, device=dev)
         hdr = torch.empty((B, pl.tiles), dtype=torch.int32, device=dev)
         ucl = torch.empty((B, pl.tiles, CL_UMAX), dtype=torch.int16, device=dev)
-        qmask = torch.empty((B, n), dtype=torch.int64, device=dev)
-        pos16 = torch.empty((B, nblk8), dtype=torch.int32, device=dev)
+        qmask = torch.empty((B, npad), dtype=torch.int64, device=dev)
+        pos16 = torch.empty((B, npad), dtype=torch.int32, device=dev)
         stats = torch.zeros(8, dtype=torch.int32, device=dev)
         posf = pos.detach().float().contiguous()
         N.check(N.LIB.affb200_cl_qplan_build(

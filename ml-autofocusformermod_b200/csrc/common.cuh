@@ -15,7 +15,7 @@
 // affb200_dsm` is the array's address in the shared window, a link-time constant.  Going through
 // __cvta_generic_to_shared(pointer) instead makes ptxas form the generic address first (S2R SR_CgaCtaId + LEA) and,
 // under register pressure, rebuild it in front of every store of an unrolled loop.
-extern __shared__ __align__(128) unsigned char affb200_dsm[];
+extern __shared__ __align__(1024) unsigned char affb200_dsm[];
 
 namespace affb200 {
 

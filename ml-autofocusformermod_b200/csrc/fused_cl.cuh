@@ -19,6 +19,7 @@
 //     union blocks its 8 tokens reference (~9 of the tile's ~30; each token uses 6).
 #pragma once
 #include "fused_attn.cuh"
+#include <cuda.h>
 
 namespace affb200 {
 
@@ -52,6 +53,43 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// tiled (TMA) copy of one box of a 3-D tensor: global -> shared, full box bytes completed on the mbarrier, out-of-range
+// elements zero-filled (SASS: UTMALDG)
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// Host: tensor map of a [B][N][W] (W contiguous) 2-byte tensor with element strides sB, sN, box {box_w, box_rows, 1},
+// 16-byte chunks XOR-swizzled inside 128-byte (or 64-byte) lines.  cuTensorMapEncodeTiled is resolved through the
+// runtime (no link-time dependency on libcuda).
+inline int cl_make_tensor_map(CUtensorMap *map, const void *base, int dtype, int64_t W, int64_t N, int64_t B, int64_t sN,
+                              int64_t sB, int box_w, int box_rows, bool swizzle64) {
+    typedef CUresult (*Fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                           const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                           CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static Fn fn = [] {
+        void *pfn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &pfn, cudaEnableDefault, &q) != cudaSuccess) pfn = nullptr;
+        return reinterpret_cast<Fn>(pfn);
+    }();
+    if (!fn) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return AFFB200_E_CUDA; }
+    const cuuint64_t dims[3] = {cuuint64_t(W), cuuint64_t(N), cuuint64_t(B)};
+    const cuuint64_t strides[2] = {cuuint64_t(sN) * 2u, cuuint64_t(B > 1 ? sB : sN * N) * 2u};
+    const cuuint32_t box[3] = {cuuint32_t(box_w), cuuint32_t(box_rows), 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = fn(map, dtype == AFFB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3,
+                          const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", int(r)); return AFFB200_E_CUDA; }
+    return AFFB200_OK;
 }
 
 __device__ __forceinline__ void cl_ldsm_x4(uint32_t (&r)[4], uint32_t addr) {

@@ -20,20 +20,23 @@
 
 namespace affb200 {
 
-template <int C, int HG> struct ClGeom {
-    static_assert(HG == 2, "rows 0-7 / 8-15 of the m16 tiles are the two heads of a group");
-    static constexpr int KVB = HG * 2 * C * 2;   // bytes of one row's K|V for the head group
-    static constexpr int KVS = KVB + 16;         // padded row stride
-    static constexpr int QB = HG * C * 2;
-    static constexpr int QS = QB + 16;
-    static constexpr int HB = 2 * C * 2;         // bytes between heads inside a K|V row
-    static constexpr int OFF_UCL = 16;
-    static constexpr int OFF_ACT = 144;          // per-warp list of referenced union blocks (8 x 64 bytes)
-    static constexpr int OFF_WIN = 768;
-    static constexpr int OFF_POS = OFF_WIN + ((kClWin * kClWin + 1) * HG * 4 + 127) / 128 * 128;
-    __host__ __device__ static constexpr int off_q(int ucap) { return OFF_POS + (ucap + 1) * 32; }
-    __host__ __device__ static constexpr int off_kv(int ucap) { return off_q(ucap) + kClT * QS; }
-    __host__ __device__ static constexpr int total(int ucap) { return off_kv(ucap) + (ucap + 1) * 8 * KVS; }
+// Shared-memory layout.  K|V blocks and the Q tile are written by TMA with the 128-byte (Q at head dim 16: 64-byte)
+// XOR swizzle: the 16-byte chunk j of row r of an 8-row x 128-byte tile sits at r*128 + ((j ^ r) << 4), so the eight
+// row addresses of an ldmatrix fall into eight different bank groups without padding.
+template <int C> struct ClGeom {
+    static constexpr int KVB = 8 * C;            // bytes of one row's K|V for a group of 2 heads: [K0 V0 K1 V1]
+    static constexpr int TPB = KVB / 128;        // 1024-byte tiles per block (head dim 32: one per head)
+    static constexpr int BLK = 8 * KVB;          // bytes of a staged block
+    static constexpr int QB = 4 * C;             // bytes of a token's Q (or output) row for the group
+    static constexpr int OFF_ACT = 128;          // per-warp list of referenced union blocks (8 x 64 bytes)
+    static constexpr int OFF_MK = 640;           // membership words of the tile's tokens [64] u64
+    static constexpr int OFF_PI = 1152;          // packed positions of the tile's tokens [64] u32
+    static constexpr int OFF_PU = 1408;          // packed positions of the union rows [64 blocks][8] u32
+    static constexpr int OFF_WIN = 3456;         // bias window [32*32 + 1][2] fp32
+    static constexpr int OFF_Q = 12288;          // Q tile / output staging [64][QB]
+    static constexpr int OFF_KV = OFF_Q + kClT * 128;
+    __host__ __device__ static constexpr int total(int ucap) { return OFF_KV + (ucap + 1) * BLK; }
+    static_assert(OFF_WIN + (kClWin * kClWin + 1) * 8 <= OFF_Q, "window overlaps the Q tile");
 };
 
 struct ClView {
@@ -42,7 +45,7 @@ struct ClView {
 };
 
 struct ClFwdParams {
-    ClView q, kv, out;     // kv: K of head h at p + b*sB + i*sN + h*sH, V follows at +C
+    ClView out;
     const float *table, *blank_k, *blank_v;
     const int32_t *hdr;
     const uint16_t *ucl;
@@ -58,52 +61,49 @@ template <typename T> __device__ __forceinline__ uint32_t cl_ones2();
 template <> __device__ __forceinline__ uint32_t cl_ones2<__nv_bfloat16>() { return 0x3f803f80u; }
 template <> __device__ __forceinline__ uint32_t cl_ones2<__half>() { return 0x3c003c00u; }
 
-// d += A_lo·B with only rows 0-7 of A (registers a0, a2) / only rows 8-15 (a1, a3); the other half is zero
-template <typename T> __device__ __forceinline__ void cl_mma_lo(float (&d)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
-    const uint32_t a[4] = {a0, 0u, a2, 0u};
-    f_mma<T>(d, a, b0, b1);
-}
-template <typename T> __device__ __forceinline__ void cl_mma_hi(float (&d)[4], uint32_t a1, uint32_t a3, uint32_t b0, uint32_t b1) {
-    const uint32_t a[4] = {0u, a1, 0u, a3};
-    f_mma<T>(d, a, b0, b1);
-}
+// swizzled byte offset of chunk j of row r inside a 1024-byte tile
+__device__ __forceinline__ uint32_t cl_sw(int r, int j) { return uint32_t(r * 128 + ((j ^ r) << 4)); }
 
-// S (16 x 8: rows 0-7 = head 0, rows 8-15 = head 1 of the warp's 8 tokens) for one staged block at `kb`
-template <typename T, int C, int KVS, int HB>
-__device__ __forceinline__ void cl_scores(float (&s)[4], const uint32_t (&qa)[C / 16][4], uint32_t kb, int lane) {
-    s[0] = s[1] = s[2] = s[3] = 0.f;
+// Scores of the warp's 16 rows (rows 0-7: its 8 tokens under head 0, rows 8-15: the same tokens under head 1) against
+// one staged block: s0 = A·K_h0^T is meaningful in its head-0 rows (registers 0, 1), s1 = A·K_h1^T in its head-1 rows
+// (registers 2, 3); the other halves are ignored products.
+template <typename T, int C>
+__device__ __forceinline__ void cl_scores(float (&s0)[4], float (&s1)[4], const uint32_t (&qa)[C / 16][4], uint32_t blk_addr,
+                                          int lane) {
+    const int r = lane & 7;
+    s0[0] = s0[1] = s0[2] = s0[3] = 0.f;
+    s1[0] = s1[1] = s1[2] = s1[3] = 0.f;
+    uint32_t kf[4];
     if constexpr (C == 32) {
-        uint32_t kf[4];
-        cl_ldsm_x4(kf, kb + (lane & 7) * KVS + (lane >> 3) * 16);
-        cl_mma_lo<T>(s, qa[0][0], qa[0][2], kf[0], kf[1]);
-        cl_mma_lo<T>(s, qa[1][0], qa[1][2], kf[2], kf[3]);
-        cl_ldsm_x4(kf, kb + (lane & 7) * KVS + HB + (lane >> 3) * 16);
-        cl_mma_hi<T>(s, qa[0][1], qa[0][3], kf[0], kf[1]);
-        cl_mma_hi<T>(s, qa[1][1], qa[1][3], kf[2], kf[3]);
+        cl_ldsm_x4(kf, blk_addr + cl_sw(r, lane >> 3));
+        f_mma<T>(s0, qa[0], kf[0], kf[1]);
+        f_mma<T>(s0, qa[1], kf[2], kf[3]);
+        cl_ldsm_x4(kf, blk_addr + 1024 + cl_sw(r, lane >> 3));
+        f_mma<T>(s1, qa[0], kf[0], kf[1]);
+        f_mma<T>(s1, qa[1], kf[2], kf[3]);
     } else {
-        uint32_t kf[4];   // (head 0: chunks 0,1), (head 1: chunks 0,1)
-        cl_ldsm_x4(kf, kb + (lane & 7) * KVS + (lane >> 4) * HB + ((lane >> 3) & 1) * 16);
-        cl_mma_lo<T>(s, qa[0][0], qa[0][2], kf[0], kf[1]);
-        cl_mma_hi<T>(s, qa[0][1], qa[0][3], kf[2], kf[3]);
+        cl_ldsm_x4(kf, blk_addr + cl_sw(r, (lane >> 4) * 4 + ((lane >> 3) & 1)));   // head 0: chunks 0,1; head 1: 4,5
+        f_mma<T>(s0, qa[0], kf[0], kf[1]);
+        f_mma<T>(s1, qa[0], kf[2], kf[3]);
     }
 }
 
-template <typename T, int C, int HG>
+template <typename T, int C>
 __global__ void __launch_bounds__(kClThreads, 2)
-fused_cl_fwd_kernel(const ClFwdParams p) {
-    using G = ClGeom<C, HG>;
+fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_constant__ CUtensorMap tm_q,
+                    const ClFwdParams p) {
+    using G = ClGeom<C>;
     constexpr int NT = C / 8;     // output n-tiles per head
     constexpr int KS = C / 16;    // k-steps of the S contraction per head
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, q4 = lane & 3;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, q4 = lane & 3, r8 = lane & 7;
     const uint32_t sm = dsm_addr();
-    const uint32_t bar = sm, s_act = sm + G::OFF_ACT + warp * 64, s_win = sm + G::OFF_WIN, s_pos = sm + G::OFF_POS;
-    const uint32_t s_q = sm + G::off_q(p.ucap), s_kv = sm + G::off_kv(p.ucap);
+    const uint32_t bar = sm, s_act = sm + G::OFF_ACT + warp * 64, s_win = sm + G::OFF_WIN, s_pu = sm + G::OFF_PU;
+    const uint32_t s_q = sm + G::OFF_Q, s_kv = sm + G::OFF_KV;
     unsigned char *gen = affb200_dsm;
     const int ucap = p.ucap;
-    const uint32_t items = uint32_t(p.H / HG) * p.B * p.n_tiles;
-    const T *qp = static_cast<const T *>(p.q.p), *kvp = static_cast<const T *>(p.kv.p);
+    const uint32_t items = uint32_t(p.H / 2) * p.B * p.n_tiles;
     T *outp = static_cast<T *>(const_cast<void *>(p.out.p));
-    const int nblk = (p.N + 7) >> 3;
+    const int64_t npad = int64_t(p.n_tiles) * kClT;
     const uint32_t onesb = g == 0 ? cl_ones2<T>() : 0u;   // B fragment of a column of ones (column 0)
 
     if (tid == 0) {
@@ -111,20 +111,35 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
         mbar_fence_init();
     }
     // rows 1..7 of the blank pseudo-block stay zero for the whole kernel
-    for (int e = tid; e < 8 * G::KVS / 16; e += kClThreads)
-        *reinterpret_cast<uint4 *>(gen + G::off_kv(ucap) + ucap * 8 * G::KVS + e * 16) = make_uint4(0u, 0u, 0u, 0u);
+    for (int e = tid; e < G::BLK / 16; e += kClThreads)
+        *reinterpret_cast<uint4 *>(gen + G::OFF_KV + ucap * G::BLK + e * 16) = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
 
     uint32_t phase = 0;
     int cur_hg = -1;
-
-    for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {
+    uint32_t item = blockIdx.x;
+    int hdr_n = 0;
+    uint32_t ucl_n = 0;
+    if (item < items) {
+        const uint32_t bt = item % (uint32_t(p.B) * p.n_tiles);   // (image, tile) index: hdr / ucl are shared by the head groups
+        hdr_n = __ldg(p.hdr + bt);
+        if (tid < kClUMax) ucl_n = __ldg(p.ucl + int64_t(bt) * kClUMax + tid);
+    }
+    while (item < items) {
+        const int hdr = hdr_n;
+        const int blk_mine = int(ucl_n);
         const int tile = int(item % uint32_t(p.n_tiles));
         const uint32_t ib = item / uint32_t(p.n_tiles);
         const int b = int(ib % uint32_t(p.B)), hg = int(ib / uint32_t(p.B));
-        const int h0 = hg * HG;
+        const int h0 = hg * 2;
         const int t0 = tile * kClT, ti = min(kClT, p.N - t0);
-        const int hdr = p.hdr[b * p.n_tiles + tile];
+        const uint32_t next = item + gridDim.x;
+        if (next < items) {   // next item's header and union list travel while this item is computed
+            const uint32_t bt = next % (uint32_t(p.B) * p.n_tiles);
+            hdr_n = __ldg(p.hdr + bt);
+            if (tid < kClUMax) ucl_n = __ldg(p.ucl + int64_t(bt) * kClUMax + tid);
+        }
+        item = next;
         const int U = hdr & AFFB200_PLAN_COUNT_MASK;
         const bool skip = (hdr & (AFFB200_PLAN_OVERFLOW | AFFB200_CL_BAD)) != 0 || U > ucap;
         T *out_tile = outp + int64_t(b) * p.out.sB + int64_t(t0) * p.out.sN + h0 * p.out.sH;
@@ -133,54 +148,48 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
                 const int row = e / (G::QB / 16), ch = e % (G::QB / 16);
                 *reinterpret_cast<uint4 *>(out_tile + int64_t(row) * p.out.sN + ch * 8) = make_uint4(0u, 0u, 0u, 0u);
             }
-            for (int e = tid; e < ti * HG; e += kClThreads)
+            for (int e = tid; e < ti * 2; e += kClThreads)
                 p.lse[(int64_t(b) * p.H + h0 + e / ti) * p.N + t0 + e % ti] = 0.f;
             if (tid == 0 && hg == 0) atomicAdd(p.guard, 1);
             continue;
         }
-        if (hg != cur_hg) {   // head group changed: table window and blank row of this group
+        if (hg != cur_hg) {   // head group changed: table window and blank row of this group (all warps are idle here)
             cur_hg = hg;
-            cl_fill_window<HG>(reinterpret_cast<float *>(gen + G::OFF_WIN), p.table, p.H, h0, p.w, p.tw);
-            for (int e = tid; e < HG * 2 * C; e += kClThreads) {
-                const int hh = e / (2 * C), r = e % (2 * C);
-                const float v = r < C ? __ldg(p.blank_k + (h0 + hh) * C + r) : __ldg(p.blank_v + (h0 + hh) * C + r - C);
-                reinterpret_cast<T *>(gen + G::off_kv(ucap) + ucap * 8 * G::KVS)[hh * 2 * C + r] = Elem<T>::from_acc(v);
+            cl_fill_window<2>(reinterpret_cast<float *>(gen + G::OFF_WIN), p.table, p.H, h0, p.w, p.tw);
+            for (int e = tid; e < 4 * C; e += kClThreads) {
+                const int hh = e / (2 * C), rr = e % (2 * C);
+                const float v = rr < C ? __ldg(p.blank_k + (h0 + hh) * C + rr) : __ldg(p.blank_v + (h0 + hh) * C + rr - C);
+                // row 0 of a swizzled tile is stored linearly; head dim 32 has one tile per head
+                reinterpret_cast<T *>(gen + G::OFF_KV + ucap * G::BLK + (C == 32 ? hh * 1024 : hh * 4 * C))[rr] = Elem<T>::from_acc(v);
             }
+            __syncthreads();
         }
-        const uint16_t *ucl_g = p.ucl + (int64_t(b) * p.n_tiles + tile) * kClUMax;
-        if (tid < U) reinterpret_cast<uint16_t *>(gen + G::OFF_UCL)[tid] = ucl_g[tid];
-        {
-            // rows of the union that exist: only the image's last block can be partial, and the union is ascending.
-            // Its missing rows are zeroed (they are masked, but 0 x garbage must stay 0 in P·V).
-            const int last = ucl_g[U - 1];
-            const int missing = last == nblk - 1 ? nblk * 8 - p.N : 0;
-            for (int e = tid; e < missing * (G::KVS / 16); e += kClThreads)
-                *reinterpret_cast<uint4 *>(gen + G::off_kv(ucap) + (U * 8 - missing) * G::KVS + e * 16) = make_uint4(0u, 0u, 0u, 0u);
-            if (tid == 0)
-                mbar_expect_tx(bar, uint32_t(U * 8 - missing) * G::KVB + uint32_t(ti) * G::QB + uint32_t(U) * 32u);
+        // ---- stage: TMA boxes of 8 rows x 128 bytes, the Q tile, and the tile's plan rows, on one mbarrier ----------
+        if (tid == 0) mbar_expect_tx(bar, uint32_t(U) * (G::BLK + 32u) + uint32_t(kClT) * G::QB + 512u + 256u);
+        if (tid < U) {
+#pragma unroll
+            for (int t = 0; t < G::TPB; ++t)
+                tma_load_3d(s_kv + (tid * G::TPB + t) * 1024, &tm_kv, h0 * 2 * C + t * 64, blk_mine * 8, b, bar);
+            bulk_g2s(s_pu + tid * 32, p.pos16 + int64_t(b) * npad + blk_mine * 8, 32u, bar);
+        } else if (tid == 64) {
+            tma_load_3d(s_q, &tm_q, h0 * C, t0, b, bar);
+        } else if (tid == 65) {
+            bulk_g2s(sm + G::OFF_MK, p.qmask + int64_t(b) * npad + t0, 512u, bar);
+        } else if (tid == 66) {
+            bulk_g2s(sm + G::OFF_PI, p.pos16 + int64_t(b) * npad + t0, 256u, bar);
         }
-        fence_proxy_async();
-        __syncthreads();
-        // ---- stage: one bulk copy per row ------------------------------------------------------------------
-        {
-            const T *kv_img = kvp + int64_t(b) * p.kv.sB + h0 * p.kv.sH;
-            for (int e = tid; e < U * 8; e += kClThreads) {
-                const int blk = reinterpret_cast<const uint16_t *>(gen + G::OFF_UCL)[e >> 3];
-                const int row = blk * 8 + (e & 7);
-                if (row < p.N) bulk_g2s(s_kv + e * G::KVS, kv_img + int64_t(row) * p.kv.sN, G::KVB, bar);
-            }
-            if (tid < ti)
-                bulk_g2s(s_q + tid * G::QS, qp + int64_t(b) * p.q.sB + int64_t(t0 + tid) * p.q.sN + h0 * p.q.sH, G::QB, bar);
-            if (tid >= 64 && tid - 64 < U) {
-                const int blk = reinterpret_cast<const uint16_t *>(gen + G::OFF_UCL)[tid - 64];
-                bulk_g2s(s_pos + (tid - 64) * 32, p.pos16 + int64_t(b) * nblk * 8 + blk * 8, 32u, bar);
-            }
-        }
-        // ---- per-token state and the warp's list of referenced blocks, while the copies fly --------------------
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+
+        // ---- per-token state and the warp's list of referenced blocks -------------------------------------------
         const int tok = warp * 8 + g;
         const bool live = tok < ti;
-        const unsigned long long mk = live ? p.qmask[int64_t(b) * p.N + t0 + tok] : 0ull;
-        const uint32_t pib = (live ? p.pos16[int64_t(b) * nblk * 8 + t0 + tok] : 0u) - kClPosBias;
+        unsigned long long mk;
+        {
+            const uint2 mw = lds_u64(sm + G::OFF_MK + tok * 8);
+            mk = (static_cast<unsigned long long>(mw.y) << 32) | mw.x;
+        }
+        const uint32_t pib = lds_u32(sm + G::OFF_PI + tok * 4) - kClPosBias;
         int n_act;
         {
             const uint32_t alo = __reduce_or_sync(0xffffffffu, uint32_t(mk)), ahi = __reduce_or_sync(0xffffffffu, uint32_t(mk >> 32));
@@ -190,31 +199,34 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
             if ((ahi >> lane) & 1u) gen[G::OFF_ACT + warp * 64 + clo + __popc(ahi & lt)] = uint8_t(32 + lane);
             n_act = clo + __popc(ahi);
         }
-        mbar_wait(bar, phase);
-        phase ^= 1u;
-
-        // ---- Q fragments (a0/a2: head 0, a1/a3: head 1), blank token ------------------------------------------
+        // ---- Q fragments: registers 0, 2 = head 0 (rows 0-7), 1, 3 = head 1 (rows 8-15); blank token --------------
         uint32_t qa[KS][4];
-#pragma unroll
-        for (int ks = 0; ks < KS; ++ks)
-            cl_ldsm_x4(qa[ks], s_q + (warp * 8 + (lane & 7)) * G::QS + ((lane >> 3) & 1) * C * 2 + ks * 32 + (lane >> 4) * 16);
-        float o[NT][4], ol[4], m[2];
         {
-            float s[4];
-            cl_scores<T, C, G::KVS, G::HB>(s, qa, s_kv + ucap * 8 * G::KVS, lane);
-            m[0] = __shfl_sync(0xffffffffu, s[0], lane & ~3) * p.scale_log2;
-            m[1] = __shfl_sync(0xffffffffu, s[2], lane & ~3) * p.scale_log2;
+            const int row = warp * 8 + r8, i = lane >> 3;
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks) {
+                if constexpr (C == 32) cl_ldsm_x4(qa[ks], s_q + row * 128 + ((((i & 1) * 4 + 2 * ks + (i >> 1)) ^ r8) << 4));
+                else cl_ldsm_x4(qa[ks], s_q + row * 64 + ((((i & 1) * 2 + (i >> 1)) ^ ((row >> 1) & 3)) << 4));
+            }
+        }
+        float oh0[NT][4], oh1[NT][4], ol[4], m[2];
+        {
+            float s0[4], s1[4];
+            cl_scores<T, C>(s0, s1, qa, s_kv + ucap * G::BLK, lane);
+            m[0] = __shfl_sync(0xffffffffu, s0[0], lane & ~3) * p.scale_log2;
+            m[1] = __shfl_sync(0xffffffffu, s1[2], lane & ~3) * p.scale_log2;
             ol[0] = ol[2] = q4 == 0 ? 1.f : 0.f;
             ol[1] = ol[3] = 0.f;
+            // blank_v as staged (rounded to T): row 0 of the blank block, V chunks
 #pragma unroll
-            for (int hh = 0; hh < 2; ++hh)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    const float2 bv = __ldg(reinterpret_cast<const float2 *>(p.blank_v + (h0 + hh) * C + nt * 8 + q4 * 2));
-                    // the staged blank_v is rounded to T like every other V row; use the same values
-                    o[nt][2 * hh] = Elem<T>::to_acc(Elem<T>::from_acc(bv.x));
-                    o[nt][2 * hh + 1] = Elem<T>::to_acc(Elem<T>::from_acc(bv.y));
-                }
+            for (int nt = 0; nt < NT; ++nt) {
+                const uint32_t a0 = C * 2 + nt * 16 + q4 * 4;
+                const uint32_t v0 = lds_u32(s_kv + ucap * G::BLK + a0);
+                const uint32_t v1 = lds_u32(s_kv + ucap * G::BLK + (C == 32 ? 1024 : 4 * C) + a0);
+                const T *e0 = reinterpret_cast<const T *>(&v0), *e1 = reinterpret_cast<const T *>(&v1);
+                oh0[nt][0] = Elem<T>::to_acc(e0[0]); oh0[nt][1] = Elem<T>::to_acc(e0[1]); oh0[nt][2] = oh0[nt][3] = 0.f;
+                oh1[nt][2] = Elem<T>::to_acc(e1[0]); oh1[nt][3] = Elem<T>::to_acc(e1[1]); oh1[nt][0] = oh1[nt][1] = 0.f;
+            }
         }
         __syncwarp();   // every lane has read its Q rows (they may now hold the output) and the list is written
 
@@ -229,7 +241,7 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
             float2 bias[2][2];   // [block][column] -> (head 0, head 1)
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
-                const uint2 pu = lds_u64(s_pos + (pj[j] * 8 + q4 * 2) * 4);
+                const uint2 pu = lds_u64(s_pu + (pj[j] * 8 + q4 * 2) * 4);
                 const bool mem = ((mk >> pj[j]) & 1ull) != 0ull && (j == 0 || has1);
                 const uint32_t i0 = cl_win_index(pu.x, pib, mem, far[j][0]), i1 = cl_win_index(pu.y, pib, mem, far[j][1]);
                 bias[j][0] = lds_f2(s_win + i0 * 8u);
@@ -239,7 +251,7 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
             if (__any_sync(0xffffffffu, anyfar)) {   // rare: an offset outside the window, or a padded row
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
-                    const uint2 pu = lds_u64(s_pos + (pj[j] * 8 + q4 * 2) * 4);
+                    const uint2 pu = lds_u64(s_pu + (pj[j] * 8 + q4 * 2) * 4);
 #pragma unroll
                     for (int cc = 0; cc < 2; ++cc)
                         if (far[j][cc]) {
@@ -248,19 +260,19 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
                         }
                 }
             }
-            float s[2][4];
+            float s0[2][4], s1[2][4];
 #pragma unroll
-            for (int j = 0; j < 2; ++j) cl_scores<T, C, G::KVS, G::HB>(s[j], qa, s_kv + pj[j] * 8 * G::KVS, lane);
-            // logits in the log2 domain: s[j][2*head + column]
+            for (int j = 0; j < 2; ++j) cl_scores<T, C>(s0[j], s1[j], qa, s_kv + pj[j] * G::BLK, lane);
+            // logits in the log2 domain: head 0 in s0[j][0..1], head 1 in s1[j][2..3]
             float lm[2] = {-INFINITY, -INFINITY};
 #pragma unroll
             for (int j = 0; j < 2; ++j)
 #pragma unroll
                 for (int cc = 0; cc < 2; ++cc) {
-                    s[j][cc] = fmaf(s[j][cc], p.scale_log2, bias[j][cc].x);
-                    s[j][2 + cc] = fmaf(s[j][2 + cc], p.scale_log2, bias[j][cc].y);
-                    lm[0] = fmaxf(lm[0], s[j][cc]);
-                    lm[1] = fmaxf(lm[1], s[j][2 + cc]);
+                    s0[j][cc] = fmaf(s0[j][cc], p.scale_log2, bias[j][cc].x);
+                    s1[j][2 + cc] = fmaf(s1[j][2 + cc], p.scale_log2, bias[j][cc].y);
+                    lm[0] = fmaxf(lm[0], s0[j][cc]);
+                    lm[1] = fmaxf(lm[1], s1[j][2 + cc]);
                 }
             const bool need = lm[0] > m[0] + 8.f || lm[1] > m[1] + 8.f;
             if (__any_sync(0xffffffffu, need)) {
@@ -274,42 +286,52 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
                     m[hh] = mn;
                     ol[2 * hh] *= f; ol[2 * hh + 1] *= f;
 #pragma unroll
-                    for (int nt = 0; nt < NT; ++nt) { o[nt][2 * hh] *= f; o[nt][2 * hh + 1] *= f; }
+                    for (int nt = 0; nt < NT; ++nt) {
+                        if (hh == 0) { oh0[nt][0] *= f; oh0[nt][1] *= f; }
+                        else { oh1[nt][2] *= f; oh1[nt][3] *= f; }
+                    }
                 }
             }
-#pragma unroll
-            for (int j = 0; j < 2; ++j)
-#pragma unroll
-                for (int cc = 0; cc < 2; ++cc) {
-                    s[j][cc] = f_ex2(s[j][cc] - m[0]);
-                    s[j][2 + cc] = f_ex2(s[j][2 + cc] - m[1]);
-                }
             uint32_t pa[4];
-            pa[0] = f_pack2<T>(s[0][0], s[0][1]); pa[1] = f_pack2<T>(s[0][2], s[0][3]);
-            pa[2] = f_pack2<T>(s[1][0], s[1][1]); pa[3] = f_pack2<T>(s[1][2], s[1][3]);
+            pa[0] = f_pack2<T>(f_ex2(s0[0][0] - m[0]), f_ex2(s0[0][1] - m[0]));
+            pa[1] = f_pack2<T>(f_ex2(s1[0][2] - m[1]), f_ex2(s1[0][3] - m[1]));
+            pa[2] = f_pack2<T>(f_ex2(s0[1][0] - m[0]), f_ex2(s0[1][1] - m[0]));
+            pa[3] = f_pack2<T>(f_ex2(s1[1][2] - m[1]), f_ex2(s1[1][3] - m[1]));
             f_mma<T>(ol, pa, onesb, onesb);   // row sums of the rounded probabilities (column 0)
-            const uint32_t vb = s_kv + (pj[(lane >> 3) & 1] * 8 + (lane & 7)) * G::KVS + C * 2 + (lane >> 4) * 16;
+            const uint32_t vblk = s_kv + pj[(lane >> 3) & 1] * G::BLK;
 #pragma unroll
             for (int np = 0; np < C / 16; ++np) {
                 uint32_t vf[4];
-                cl_ldsm_x4_t(vf, vb + np * 32);
-                cl_mma_lo<T>(o[2 * np], pa[0], pa[2], vf[0], vf[1]);
-                cl_mma_lo<T>(o[2 * np + 1], pa[0], pa[2], vf[2], vf[3]);
-                cl_ldsm_x4_t(vf, vb + G::HB + np * 32);
-                cl_mma_hi<T>(o[2 * np], pa[1], pa[3], vf[0], vf[1]);
-                cl_mma_hi<T>(o[2 * np + 1], pa[1], pa[3], vf[2], vf[3]);
+                if constexpr (C == 32) {
+                    cl_ldsm_x4_t(vf, vblk + cl_sw(r8, 4 + np * 2 + (lane >> 4)));
+                    f_mma<T>(oh0[2 * np], pa, vf[0], vf[1]);
+                    f_mma<T>(oh0[2 * np + 1], pa, vf[2], vf[3]);
+                    cl_ldsm_x4_t(vf, vblk + 1024 + cl_sw(r8, 4 + np * 2 + (lane >> 4)));
+                    f_mma<T>(oh1[2 * np], pa, vf[0], vf[1]);
+                    f_mma<T>(oh1[2 * np + 1], pa, vf[2], vf[3]);
+                } else {
+                    cl_ldsm_x4_t(vf, vblk + cl_sw(r8, 2 + (lane >> 4)));
+                    f_mma<T>(oh0[0], pa, vf[0], vf[1]);
+                    f_mma<T>(oh0[1], pa, vf[2], vf[3]);
+                    cl_ldsm_x4_t(vf, vblk + cl_sw(r8, 6 + (lane >> 4)));
+                    f_mma<T>(oh1[0], pa, vf[0], vf[1]);
+                    f_mma<T>(oh1[1], pa, vf[2], vf[3]);
+                }
             }
         }
 
-        // ---- epilogue ------------------------------------------------------------------------------------------
+        // ---- epilogue: O / l through the warp's Q rows (same swizzle), 16-byte stores ----------------------------
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
             const float l = __shfl_sync(0xffffffffu, ol[2 * hh], lane & ~3);
             const float inv = __fdividef(1.f, l);
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt)
-                *reinterpret_cast<uint32_t *>(gen + G::off_q(ucap) + tok * G::QS + (hh * C + nt * 8 + q4 * 2) * 2) =
-                    f_pack2<T>(o[nt][2 * hh] * inv, o[nt][2 * hh + 1] * inv);
+            for (int nt = 0; nt < NT; ++nt) {
+                const int j = hh * (C / 8) + nt;
+                const uint32_t a = C == 32 ? uint32_t(tok * 128 + ((j ^ (tok & 7)) << 4)) : uint32_t(tok * 64 + ((j ^ ((tok >> 1) & 3)) << 4));
+                const float x0 = hh == 0 ? oh0[nt][0] : oh1[nt][2], x1 = hh == 0 ? oh0[nt][1] : oh1[nt][3];
+                *reinterpret_cast<uint32_t *>(gen + G::OFF_Q + a + q4 * 4) = f_pack2<T>(x0 * inv, x1 * inv);
+            }
             if (q4 == 0 && live)
                 p.lse[(int64_t(b) * p.H + h0 + hh) * p.N + t0 + tok] = (m[hh] + __log2f(l)) * 0.6931471805599453f;
         }
@@ -317,26 +339,27 @@ fused_cl_fwd_kernel(const ClFwdParams p) {
 #pragma unroll
         for (int e = lane; e < 8 * (G::QB / 16); e += 32) {
             const int row = warp * 8 + e / (G::QB / 16), ch = e % (G::QB / 16);
+            const uint32_t a = C == 32 ? uint32_t(row * 128 + ((ch ^ (row & 7)) << 4)) : uint32_t(row * 64 + ((ch ^ ((row >> 1) & 3)) << 4));
             if (row < ti)
-                *reinterpret_cast<uint4 *>(out_tile + int64_t(row) * p.out.sN + ch * 8) =
-                    *reinterpret_cast<const uint4 *>(gen + G::off_q(ucap) + row * G::QS + ch * 16);
+                *reinterpret_cast<uint4 *>(out_tile + int64_t(row) * p.out.sN + ch * 8) = *reinterpret_cast<const uint4 *>(gen + G::OFF_Q + a);
         }
-        __syncthreads();   // all warps are done with this item's rows before the next copies land
+        fence_proxy_async();   // the staging writes above precede the next item's async-proxy writes to the same rows
+        __syncthreads();       // all warps are done with this item's rows before the next copies land
     }
 }
 
-template <typename T, int C, int HG>
-static int launch_cl_fwd(const ClFwdParams &p, cudaStream_t st) {
-    using G = ClGeom<C, HG>;
+template <typename T, int C>
+static int launch_cl_fwd(const CUtensorMap &tm_kv, const CUtensorMap &tm_q, const ClFwdParams &p, cudaStream_t st) {
+    using G = ClGeom<C>;
     const int smem = G::total(p.ucap);
     if (smem > 227 * 1024) { set_error("fused_cl_fwd: union of %d blocks does not fit shared memory", p.ucap); return AFFB200_E_ARG; }
-    auto kern = fused_cl_fwd_kernel<T, C, HG>;
+    auto kern = fused_cl_fwd_kernel<T, C>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) { set_error("fused_cl_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return AFFB200_E_CUDA; }
-    const int64_t items = int64_t(p.H / HG) * p.B * p.n_tiles;
+    const int64_t items = int64_t(p.H / 2) * p.B * p.n_tiles;
     if (items >= (int64_t(1) << 31)) { set_error("fused_cl_fwd: too many tiles"); return AFFB200_E_ARG; }
     const int grid = int(items < 2 * kNumSMs ? items : 2 * kNumSMs);
-    kern<<<grid, kClThreads, smem, st>>>(p);
+    kern<<<grid, kClThreads, smem, st>>>(tm_kv, tm_q, p);
     return check_launch("fused_cl_fwd");
 }
 
@@ -374,8 +397,6 @@ extern "C" int affb200_fused_cl_fwd(const affb200_view *q, const affb200_view *k
         return AFFB200_E_ARG;
     }
     ClFwdParams p;
-    p.q = ClView{q->p, q->sB, q->sN, q->sH};
-    p.kv = ClView{k->p, k->sB, k->sN, k->sH};
     p.out = ClView{out->p, out->sB, out->sN, out->sH};
     p.table = table; p.blank_k = blank_k; p.blank_v = blank_v;
     p.hdr = plan->q_hdr; p.ucl = plan->q_ucl; p.qmask = reinterpret_cast<const unsigned long long *>(plan->q_mask);
@@ -383,8 +404,13 @@ extern "C" int affb200_fused_cl_fwd(const affb200_view *q, const affb200_view *k
     p.B = int(B); p.H = int(H); p.N = int(N); p.n_tiles = int((N + kClT - 1) / kClT); p.ucap = plan->ucap;
     p.w = int(rel_pos_width); p.tw = int(table_width);
     p.scale_log2 = scale * kLog2e;
+    CUtensorMap tm_kv, tm_q;
+    int rc = cl_make_tensor_map(&tm_kv, k->p, dtype, 2 * H * c, N, B, k->sN, k->sB, 64, 8, false);
+    if (rc) return rc;
+    rc = cl_make_tensor_map(&tm_q, q->p, dtype, H * c, N, B, q->sN, q->sB, int(2 * c), kClT, c == 16);
+    if (rc) return rc;
     auto st = (cudaStream_t)stream;
     if (dtype == AFFB200_BF16)
-        return c == 32 ? launch_cl_fwd<__nv_bfloat16, 32, 2>(p, st) : launch_cl_fwd<__nv_bfloat16, 16, 2>(p, st);
-    return c == 32 ? launch_cl_fwd<__half, 32, 2>(p, st) : launch_cl_fwd<__half, 16, 2>(p, st);
+        return c == 32 ? launch_cl_fwd<__nv_bfloat16, 32>(tm_kv, tm_q, p, st) : launch_cl_fwd<__nv_bfloat16, 16>(tm_kv, tm_q, p, st);
+    return c == 32 ? launch_cl_fwd<__half, 32>(tm_kv, tm_q, p, st) : launch_cl_fwd<__half, 16>(tm_kv, tm_q, p, st);
 }

@@ -38,13 +38,16 @@ cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ ma
     __syncthreads();
     int bad = 0;
     // packed positions of the tile's own tokens (and the sentinel of the padded tail)
-    for (int t = tid; t < ti; t += kPlanThreads) {
-        const float x = pos[(bN + t0 + t) * 2], y = pos[(bN + t0 + t) * 2 + 1];
-        if (!(x >= 0.f && x <= 32767.f && y >= 0.f && y <= 32767.f) || x != floorf(x) || y != floorf(y)) bad = 1;
-        pos16[int64_t(b) * nblk * 8 + t0 + t] = (uint32_t(int(y)) << 16) | uint32_t(int(x));
+    const int64_t bP = int64_t(b) * n_tiles * kClT;   // qmask / pos16 rows are padded to whole tiles
+    for (int t = tid; t < kClT; t += kPlanThreads) {
+        uint32_t pk = kClPosInvalid;
+        if (t < ti) {
+            const float x = pos[(bN + t0 + t) * 2], y = pos[(bN + t0 + t) * 2 + 1];
+            if (!(x >= 0.f && x <= 32767.f && y >= 0.f && y <= 32767.f) || x != floorf(x) || y != floorf(y)) bad = 1;
+            pk = (uint32_t(int(y)) << 16) | uint32_t(int(x));
+        }
+        pos16[bP + t0 + t] = pk;
     }
-    if (tile == n_tiles - 1)
-        for (int r = N + tid; r < nblk * 8; r += kPlanThreads) pos16[int64_t(b) * nblk * 8 + r] = kClPosInvalid;
     // structure check + block ids
     for (int it = tid; it < ti * NB; it += kPlanThreads) {
         const int t = it / NB, q = it - t * NB;
@@ -122,7 +125,7 @@ cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ ma
         }
     }
     __syncthreads();
-    for (int t = tid; t < ti; t += kPlanThreads) qmask[bN + t0 + t] = qm[t];
+    for (int t = tid; t < kClT; t += kPlanThreads) qmask[bP + t0 + t] = t < ti ? qm[t] : 0ull;
     if (tid == 0) {
         const bool over = U > kClUMax;
         const bool isbad = bad_s != 0;
