@@ -294,10 +294,10 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
  * coordinates in 0..32767) and emits, per tile of 64 tokens, the ascending union of referenced 8-row blocks (<= 64),
  * per token a 64-bit membership word over that union, the block ids, and positions packed (y << 16 | x); the last
  * two arrays are padded per image to whole tiles (membership 0, position 0xffffffff).  stats[8] int32 (caller-zeroed): [0] tiles whose union exceeds 64 blocks,
- * [1] tiles that do not have the structure (AFFB200_CL_BAD in their header), [4] largest union, [2]/[5] the same for
- * affb200_cl_kplan_build (query tokens per tile of 64 key rows: overflow count over `kumax`, largest list).  A plan
- * with stats[0] | stats[1] | stats[2] != 0 must not be used: keep affb200_fused_attn_fwd/_bwd (any index tensor).
- * k_utok entries are (query token << 8) | (bit r set: the token references block 8*tile + r), ascending by token.
+ * [1] tiles that do not have the structure (AFFB200_CL_BAD in their header), [4] largest union; for
+ * affb200_cl_kplan_build (per 8-row key block the ascending list of query tokens that reference it): [2] blocks with
+ * more than `kbcap` references, [5] the longest list.  A plan with stats[0] | stats[1] | stats[2] != 0 must not be
+ * used: keep affb200_fused_attn_fwd/_bwd (any index tensor).
  *
  * The kernels stage a union row's K|V (both heads of a group, one 256-byte bulk-async copy) once per tile, form S by
  * blocks in tensor-core accumulators, take the bias from table[pos_u - pos_i] (a shared-memory window of `table`
@@ -315,21 +315,39 @@ typedef struct {
     const uint64_t *q_mask;  /* [B][ceil(N/64)*64] */
     const uint32_t *pos16;   /* [B][ceil(N/64)*64] */
     const uint16_t *blk;     /* [B][N][M/8] */
-    int32_t kumax;           /* capacity of a key tile's token list (multiple of 16); 0: no key-tile plan */
-    const int32_t *k_hdr;    /* [B][ceil(N/64)] */
-    const uint32_t *k_utok;  /* [B][ceil(N/64)][kumax] */
+    int32_t kbcap;           /* capacity of a key block's query list; 0: no key-side plan (forward only) */
+    const int32_t *kb_cnt;   /* [B][ceil(N/8)] number of query tokens that reference the block */
+    const uint32_t *kb_tok;  /* [B][ceil(N/8)][kbcap] those tokens, ascending */
+    const uint16_t *q_pe;    /* [B][N][M] packed bias index (pe | masked << 15) in ascending-block slot order, or NULL */
 } affb200_cl_plan;
 
 int64_t affb200_cl_tiles(int64_t n);
 int affb200_cl_qplan_build(const int64_t *nbhd_idx, const int64_t *mask, const int64_t *pe_idx, const float *pos,
                            int64_t B, int64_t N, int64_t M, int64_t rel_pos_width, int64_t table_width, uint16_t *blk,
                            int32_t *hdr, uint16_t *ucl, uint64_t *qmask, uint32_t *pos16, int32_t *stats, void *stream);
-int affb200_cl_kplan_build(const uint16_t *blk, int64_t B, int64_t N, int64_t M, int64_t kumax, int32_t *hdr,
-                           uint32_t *utok, int32_t *stats, void *stream);
+int affb200_cl_kplan_build(const uint16_t *blk, int64_t B, int64_t N, int64_t M, int64_t kbcap, int32_t *kb_cnt,
+                           uint32_t *kb_tok, int32_t *stats, void *stream);
+/* q_pe [B][N][M]: affb200_fused_attn_pack_pe's encoding with each token's 8-slot groups reordered by ascending block id —
+ * the slot order in which affb200_fused_cl_bwd writes ds_work (feed both to affb200_pe_feat_grad / the table histogram). */
+int affb200_cl_pack_pe_sorted(const int64_t *pe_idx, const int64_t *mask, const uint16_t *blk, int64_t B, int64_t N,
+                              int64_t M, uint16_t *out, int32_t *bad, void *stream);
 int affb200_fused_cl_fwd(const affb200_view *q, const affb200_view *k, const affb200_view *v, const affb200_view *out,
                          const float *table, const float *blank_k, const float *blank_v, const affb200_cl_plan *plan,
                          float *lse, int32_t *guard, int64_t B, int64_t H, int64_t N, int64_t c, int64_t rel_pos_width,
                          int64_t table_width, float scale, int dtype, void *stream);
+/* Backward: dq / dk / dv views as the forward's operands (fully overwritten); lse from the forward; delta [B][H][N] fp32
+ * scratch (dO·O, written by the first kernel, read by the second); ds_work [B][H][N][M] of `dtype`: dS in
+ * ascending-block slot order (pair it with plan->q_pe for the bias-table gradient); blank_part
+ * [affb200_fused_cl_bwd_grid(B, H, N)][H][2][c] fp32: per-CTA sums of d blank_k / d blank_v (sum over the first axis).
+ * Two launches: a query-major kernel (dQ, dS, delta, blank sums) and a key-major kernel in which a warp owns one 8-row
+ * block of K|V and accumulates dK / dV over the query tokens that reference it — no atomics, fixed summation order. */
+int64_t affb200_fused_cl_bwd_grid(int64_t B, int64_t H, int64_t N);
+int affb200_fused_cl_bwd(const affb200_view *q, const affb200_view *k, const affb200_view *v, const affb200_view *out,
+                         const affb200_view *dout, const affb200_view *dq, const affb200_view *dk, const affb200_view *dv,
+                         const float *table, const float *blank_k, const float *blank_v, const affb200_cl_plan *plan,
+                         const float *lse, float *delta, void *ds_work, float *blank_part, int32_t *guard, int64_t B,
+                         int64_t H, int64_t N, int64_t M, int64_t c, int64_t rel_pos_width, int64_t table_width,
+                         float scale, int dtype, void *stream);
 
 /* Gradient of the bias table's generator.  In ClusterAttention the table is pos_embed(pre_table) = feat·W^T + b
  * (reference aff_transformer.py:78,125) and only W and b receive its gradient, so the [P][H] histogram can be skipped:
@@ -340,6 +358,12 @@ int affb200_fused_cl_fwd(const affb200_view *q, const affb200_view *k, const aff
 int64_t affb200_pe_feat_grad_work_floats(int64_t B, int64_t H, int64_t NM);
 int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, const float *feat8, int64_t B, int64_t H, int64_t NM,
                          float *out, float *work, int dtype, void *stream);
+
+/* The [P][H] histogram form of the bias-table gradient from the backward's dS scratch: d_table[p][h] = sum of
+ * d_vals[b][h][slot] over the slots whose packed index (affb200_fused_attn_pack_pe / affb200_cl_pack_pe_sorted) is p —
+ * the gradient the reference obtains from pe_table.gather(...)'s backward (aff_transformer.py:131).  P <= 32768. */
+int affb200_table_grad_u16(const void *d_vals, const uint16_t *pe, int64_t B, int64_t H, int64_t NM, int64_t P,
+                           float *d_table, int dtype, void *stream);
 
 /* Same operator for small token sets (N <= AFFB200_FUSED_IMG_MAX_N, M even and <= 96): one CTA per (image, head) keeps the
  * image's K and V resident in shared memory, walks 32-row query tiles, and in the backward accumulates dK and dV on

@@ -72,8 +72,13 @@ SIGNATURES = {
     "affb200_cl_tiles": (_i64, [_i64]),
     "affb200_cl_qplan_build": (_int, [_ptr] * 4 + [_i64] * 5 + [_ptr] * 6 + [_ptr]),
     "affb200_cl_kplan_build": (_int, [_ptr] + [_i64] * 4 + [_ptr] * 3 + [_ptr]),
+    "affb200_cl_pack_pe_sorted": (_int, [_ptr] * 3 + [_i64] * 3 + [_ptr] * 3),
+    "affb200_fused_cl_bwd_grid": (_i64, [_i64] * 3),
+    "affb200_fused_cl_bwd": (_int, [_ptr] * 8 + [_ptr] * 3 + [_ptr] + [_ptr] * 5 + [_i64] * 7
+                             + [ctypes.c_float, _int, _ptr]),
     "affb200_fused_cl_fwd": (_int, [_ptr] * 4 + [_ptr] * 3 + [_ptr, _ptr, _ptr] + [_i64] * 6
                              + [ctypes.c_float, _int, _ptr]),
+    "affb200_table_grad_u16": (_int, [_ptr, _ptr] + [_i64] * 4 + [_ptr, _int, _ptr]),
     "affb200_pe_feat_grad_work_floats": (_i64, [_i64, _i64, _i64]),
     "affb200_pe_feat_grad": (_int, [_ptr, _ptr, _ptr, _i64, _i64, _i64, _ptr, _ptr, _int, _ptr]),
     "affb200_merge_fwd": (_int, [_ptr] * 7 + [_i64] * 5 + [_int, _int, _ptr]),

@@ -53,7 +53,11 @@ class CudaOps:
         self.select_merge_centers = P.select_merge_centers
         self.gather_rows = P.gather_rows
         self.reorder_tokens = P.reorder_tokens
-        self.fused_attention = None  # set by affb200.fused when available
+        from . import fused as FU
+        from . import fused_cl as FC
+        # the whole of ClusterAttention between the Linears as one operator; declines (None) what it does not cover
+        self.fused_attention = FU.fused_cluster_attention
+        self.hint_geometry = FC.hint_geometry
 
 
 _default_ops = None
@@ -321,6 +325,8 @@ class BasicLayer(nn.Module):
         else:
             pos, mean, _, _, reorder = ops.space_filling_cluster(pos, m, h, w, no_reorder=False)
         nbhd, mask, pe_idx, _ = ops.build_nbhd(pos, mean, m, self.nbhd_size, rel_pos_width)
+        if getattr(ops, 'hint_geometry', None) is not None:   # where nbhd / pe_idx came from: block-structured kernels
+            ops.hint_geometry(nbhd, pos, rel_pos_width, 2 * rel_pos_width + 1)
         if pre_table.shape[0] > COMPACT_ROWS_ABOVE and not (pe_idx.is_cuda and torch.cuda.is_current_stream_capturing()):
             pe_idx, pre_table = compact_table(pe_idx, pre_table)
         return pos, reorder, nbhd, mask, pe_idx, pre_table

@@ -255,6 +255,76 @@ class FusedClusterAttention(Function):
                 db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt), None, None, None, None)
 
 
+class FusedClusterAttentionCl(Function):
+    """Block-structured neighbourhoods (fused_cl.py): union blocks staged by TMA, bias from pos_u - pos_i, dK/dV
+    accumulated per key block on chip (csrc/fused_cl_fwd.cu, fused_cl_bwd.cu)."""
+
+    @staticmethod
+    def forward(ctx, q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, pe_feat, clp, meta):
+        H, scale = meta
+        B, n, hc = q_lin.shape
+        c = hc // H
+        dev = q_lin.device
+        q_lin = q_lin.contiguous()
+        kv_lin = kv_lin.contiguous()
+        table = _table_of(pe_table, pe_w, pe_b, pe_feat)
+        bk = blank_k.detach().float().contiguous()
+        bv = blank_v.detach().float().contiguous()
+        with torch.cuda.device(dev):
+            out = torch.empty_like(q_lin)
+            lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+            from .plan import guard_tensor
+            N.check(N.LIB.affb200_fused_cl_fwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), N.p(table), N.p(bk), N.p(bv),
+                clp.byref(), N.p(lse), N.p(guard_tensor(dev)), B, H, n, c, clp.w, clp.tw, float(scale),
+                N.dtype_enum(q_lin), N.stream_ptr(dev)), "fused_cl_fwd")
+        ctx.save_for_backward(q_lin, kv_lin, out, lse, table, bk, bv)
+        ctx.clp = clp
+        ctx.M = nbhd_idx.shape[2]
+        ctx.meta = (H, scale, None if pe_table is None else pe_table.dtype, blank_k.dtype, table.shape[0])
+        ctx.pe_lin = None if pe_w is None else (pe_feat, pe_w.shape[1], pe_w.dtype, pe_b.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        q_lin, kv_lin, out, lse, table, bk, bv = ctx.saved_tensors
+        H, scale, table_dt, blank_dt, P = ctx.meta
+        clp, M = ctx.clp, ctx.M
+        B, n, hc = q_lin.shape
+        c = hc // H
+        dev = q_lin.device
+        d_out = d_out.contiguous()
+        if d_out.dtype != q_lin.dtype:
+            d_out = d_out.to(q_lin.dtype)
+        with torch.cuda.device(dev):
+            from .plan import guard_tensor
+            grid = N.LIB.affb200_fused_cl_bwd_grid(B, H, n)
+            dq = torch.empty_like(q_lin)
+            dkv = torch.empty_like(kv_lin)
+            ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+            delta = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+            blank_part = torch.empty((grid, H, 2, c), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_fused_cl_bwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
+                _view(dq, n * hc, hc, c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c, c),
+                N.p(table), N.p(bk), N.p(bv), clp.byref(), N.p(lse), N.p(delta), N.p(ds), N.p(blank_part),
+                N.p(guard_tensor(dev)), B, H, n, M, c, clp.w, clp.tw, float(scale), N.dtype_enum(q_lin),
+                N.stream_ptr(dev)), "fused_cl_bwd")
+            db = _col_sum(blank_part.view(grid, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
+            dw = dpb = d_table = None
+            if ctx.pe_lin is not None:
+                pe_feat, F, w_dt, b_dt = ctx.pe_lin
+                dw, dpb = _pe_grad(ds, clp.q_pe, pe_feat, B, H, n * M, F, w_dt, b_dt)
+            else:
+                d_table = torch.empty((P, H), dtype=torch.float32, device=dev)
+                N.check(N.LIB.affb200_table_grad_u16(N.p(ds), N.p(clp.q_pe), B, H, n * M, P, N.p(d_table),
+                                                     N.dtype_enum(ds), N.stream_ptr(dev)), "table_grad_u16")
+        return (dq, dkv, None if d_table is None else d_table.to(table_dt), dw, dpb,
+                db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt), None, None, None, None)
+
+
 _ctypes_sigs_done = False
 
 
@@ -286,6 +356,12 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
     if c not in (16, 32) or P > 32768 or nbhd_idx.shape[2] > N.PLAN_MAX_M:
         return None
     plan = get_plan(nbhd_idx)
+    if not _use_img(n, nbhd_idx.shape[2]) and num_heads % 2 == 0 and num_heads * c <= 512:
+        from . import fused_cl
+        clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, P)
+        if clp is not None and (pe_w is None or (n * nbhd_idx.shape[2]) % 8 == 0):
+            return FusedClusterAttentionCl.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx,
+                                                 pe_feat, clp, (num_heads, scale))
     if _use_img(n, nbhd_idx.shape[2]):
         q_pe = _packed_pe(plan, pe_idx, cluster_mask)
         if q_pe is None:

@@ -4,8 +4,9 @@ The reference builds a neighbourhood from whole clusters of consecutive rows and
 difference (models/aff_transformer.py:476-487).  `BasicLayer` tells the plan of an index tensor where that structure
 came from (`hint_geometry`): positions, rel_pos_width and table_width.  `ClPlan` then verifies the structure on the
 device and holds the compact form the kernels read: union blocks per tile of 64 tokens, a 64-bit membership word per
-token, packed positions, and (for the backward) the list of query tokens per tile of 64 key rows.  If the structure
-does not hold — or no hint was given — `cl_plan()` returns None and the row-union kernels of fused.py run.
+token, packed positions, and (for the backward) per 8-row key block the list of query tokens that reference it plus
+the bias indices in the slot order the backward writes dS in.  If the structure does not hold — or no hint was given —
+`cl_plan()` returns None and the row-union kernels of fused.py run.
 """
 import ctypes
 import os
@@ -17,14 +18,15 @@ from . import plan as _plan
 
 CL_T = 64
 CL_UMAX = 64
-KUMAX_STEP = 64
+KBCAP_STEP = 16
 
 
 class ClPlanStruct(ctypes.Structure):
     """affb200_cl_plan (include/affb200.h)"""
     _fields_ = [("ucap", ctypes.c_int32), ("q_hdr", ctypes.c_void_p), ("q_ucl", ctypes.c_void_p),
                 ("q_mask", ctypes.c_void_p), ("pos16", ctypes.c_void_p), ("blk", ctypes.c_void_p),
-                ("kumax", ctypes.c_int32), ("k_hdr", ctypes.c_void_p), ("k_utok", ctypes.c_void_p)]
+                ("kbcap", ctypes.c_int32), ("kb_cnt", ctypes.c_void_p), ("kb_tok", ctypes.c_void_p),
+                ("q_pe", ctypes.c_void_p)]
 
 
 def enabled():
@@ -46,17 +48,19 @@ class ClPlan:
         self.struct = None
         self.keep = None
         self.ucap = 0
-        self.kumax = 0
+        self.kbcap = 0
+        self.q_pe = None
 
     def byref(self):
         return ctypes.byref(self.struct)
 
 
-def _build(nbhd_idx, mask, pe_idx, pos, w, tw, want_k):
+def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P):
     B, n, M = nbhd_idx.shape
     dev = nbhd_idx.device
     pl = ClPlan(B, n, M, w, tw)
     npad = pl.tiles * CL_T
+    nblk = (n + 7) // 8
     skey = (B, n, M)
     static = _plan.is_static()
     obs = _plan._observed.get(("cl",) + skey)
@@ -65,6 +69,7 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, want_k):
     if static and not obs["ok"]:
         return None
     with torch.cuda.device(dev):
+        sp = N.stream_ptr(dev)
         blk = torch.empty((B, n, M // 8), dtype=torch.int16, device=dev)
         hdr = torch.empty((B, pl.tiles), dtype=torch.int32, device=dev)
         ucl = torch.empty((B, pl.tiles, CL_UMAX), dtype=torch.int16, device=dev)
@@ -72,62 +77,65 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, want_k):
         pos16 = torch.empty((B, npad), dtype=torch.int32, device=dev)
         stats = torch.zeros(8, dtype=torch.int32, device=dev)
         posf = pos.detach().float().contiguous()
-        N.check(N.LIB.affb200_cl_qplan_build(
-            N.p(nbhd_idx.contiguous()), N.p(None if mask is None else mask.contiguous()), N.p(pe_idx.contiguous()),
-            N.p(posf), B, n, M, w, tw, N.p(blk), N.p(hdr), N.p(ucl), N.p(qmask), N.p(pos16), N.p(stats),
-            N.stream_ptr(dev)), "cl_qplan_build")
-        k_hdr = k_utok = None
-        if static:
-            kumax = obs["kumax"]
-        else:
+        nb_c, pe_c = nbhd_idx.contiguous(), pe_idx.contiguous()
+        mk_c = None if mask is None else mask.contiguous()
+        N.check(N.LIB.affb200_cl_qplan_build(N.p(nb_c), N.p(mk_c), N.p(pe_c), N.p(posf), B, n, M, w, tw, N.p(blk),
+                                             N.p(hdr), N.p(ucl), N.p(qmask), N.p(pos16), N.p(stats), sp),
+                "cl_qplan_build")
+        if not static:
             st = stats.tolist()
             if st[0] or st[1]:
                 _plan._observed[("cl",) + skey] = dict(ok=False)
                 return None
-            kumax = 0
-        if want_k:
-            guess = kumax if static else ((obs["kumax"] if obs and obs.get("ok") else 384))
-            while True:
-                k_hdr = torch.empty((B, pl.tiles), dtype=torch.int32, device=dev)
-                k_utok = torch.empty((B, pl.tiles, guess), dtype=torch.int32, device=dev)
-                N.check(N.LIB.affb200_cl_kplan_build(N.p(blk), B, n, M, guess, N.p(k_hdr), N.p(k_utok), N.p(stats),
-                                                     N.stream_ptr(dev)), "cl_kplan_build")
-                if static:
-                    break
-                st = stats.tolist()
-                if st[2] == 0:
-                    break
-                stats[2] = 0
-                guess = ((st[5] + KUMAX_STEP - 1) // KUMAX_STEP) * KUMAX_STEP
-            kumax = guess
+        kbcap = obs["kbcap"] if (obs and obs.get("ok")) else 96
+        while True:
+            kb_cnt = torch.empty((B, nblk), dtype=torch.int32, device=dev)
+            kb_tok = torch.empty((B, nblk, kbcap), dtype=torch.int32, device=dev)
+            N.check(N.LIB.affb200_cl_kplan_build(N.p(blk), B, n, M, kbcap, N.p(kb_cnt), N.p(kb_tok), N.p(stats), sp),
+                    "cl_kplan_build")
+            if static:
+                break
+            st = stats.tolist()
+            if st[2] == 0:
+                break
+            stats[2] = 0
+            kbcap = ((st[5] + KBCAP_STEP - 1) // KBCAP_STEP) * KBCAP_STEP
+        q_pe = None
+        bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        if P <= 32768:
+            q_pe = torch.empty((B, n, M), dtype=torch.int16, device=dev)
+            N.check(N.LIB.affb200_cl_pack_pe_sorted(N.p(pe_c), N.p(mk_c), N.p(blk), B, n, M, N.p(q_pe), N.p(bad), sp),
+                    "cl_pack_pe_sorted")
         if static:
             ucap = obs["ucap"]
-            _plan.guard_add((stats[0] != 0) | (stats[1] != 0) | (stats[2] != 0) | (stats[4] > ucap))
+            _plan.guard_add((stats[0] != 0) | (stats[1] != 0) | (stats[2] != 0) | (stats[4] > ucap) | (bad[0] != 0))
         else:
             st = stats.tolist()
-            ucap = min(CL_UMAX, ((st[4] + 3) // 4) * 4)
+            if int(bad.item()) != 0:
+                _plan._observed[("cl",) + skey] = dict(ok=False)
+                return None
+            ucap = min(CL_UMAX, st[4])
             if obs and obs.get("ok"):
                 ucap = max(ucap, obs["ucap"])
-                kumax_rec = max(kumax, obs["kumax"])
+                kbcap_rec = max(kbcap, obs["kbcap"])
             else:
-                kumax_rec = kumax
-            _plan._observed[("cl",) + skey] = dict(ok=True, ucap=ucap, kumax=kumax_rec)
-    pl.ucap, pl.kumax = ucap, kumax
+                kbcap_rec = kbcap
+            _plan._observed[("cl",) + skey] = dict(ok=True, ucap=ucap, kbcap=kbcap_rec)
+    pl.ucap, pl.kbcap, pl.q_pe = ucap, kbcap, q_pe
     s = ClPlanStruct()
     s.ucap = ucap
     s.q_hdr, s.q_ucl, s.q_mask, s.pos16, s.blk = (hdr.data_ptr(), ucl.data_ptr(), qmask.data_ptr(), pos16.data_ptr(),
                                                   blk.data_ptr())
-    s.kumax = kumax if want_k else 0
-    if want_k:
-        s.k_hdr, s.k_utok = k_hdr.data_ptr(), k_utok.data_ptr()
+    s.kbcap, s.kb_cnt, s.kb_tok = kbcap, kb_cnt.data_ptr(), kb_tok.data_ptr()
+    s.q_pe = 0 if q_pe is None else q_pe.data_ptr()
     pl.struct = s
-    pl.keep = (blk, hdr, ucl, qmask, pos16, stats, k_hdr, k_utok)
+    pl.keep = (blk, hdr, ucl, qmask, pos16, stats, kb_cnt, kb_tok, q_pe)
     pl.stats = stats
     return pl
 
 
-def cl_plan(nbhd_idx, mask, pe_idx, want_k=True):
-    """ClPlan of this index set, or None (no geometry hint, structure absent, disabled)."""
+def cl_plan(nbhd_idx, mask, pe_idx, P):
+    """ClPlan of this index set, or None (no geometry hint, structure absent, disabled).  P = rows of the bias table."""
     if not enabled():
         return None
     p = _plan.get_plan(nbhd_idx)
@@ -135,14 +143,15 @@ def cl_plan(nbhd_idx, mask, pe_idx, want_k=True):
     if hint is None:
         return None
     hit = getattr(p, "_cl", None)
-    key = (id(pe_idx), pe_idx._version, None if mask is None else id(mask), want_k)
-    if hit is not None and hit[0] == key[:3] and (hit[1] is None or hit[1].kumax > 0 or not want_k):
+    key = (id(pe_idx), pe_idx._version, None if mask is None else id(mask), P)
+    if hit is not None and hit[0] == key:
         return hit[1]
     pos, w, tw = hint
     B, n, M = nbhd_idx.shape
-    if M % 8 != 0 or M > 8 * CL_UMAX or pos.shape[0] != B or pos.shape[1] != n or tw != 2 * w + 1:
+    if M % 8 != 0 or M > 8 * CL_UMAX or pos.shape[0] != B or pos.shape[1] != n or tw != 2 * w + 1 or P != tw * tw \
+            or P > 32768:
         res = None
     else:
-        res = _build(nbhd_idx, mask, pe_idx, pos, w, tw, want_k)
-    p._cl = (key[:3], res)
+        res = _build(nbhd_idx, mask, pe_idx, pos, w, tw, P)
+    p._cl = (key, res)
     return res

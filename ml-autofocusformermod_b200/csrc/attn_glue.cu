@@ -380,3 +380,14 @@ extern "C" int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, co
     pe_feat_grad_finish_kernel<<<unsigned((H * 8 + 31) / 32), 1024, 0, st>>>(work, chunks, int(H * 8), out);
     return check_launch("pe_feat_grad_finish");
 }
+
+// d_table[p][h] = sum of d_vals[b][h][slot] over the slots whose packed bias index is p (masked slots included: their
+// d_vals are zero); d_vals [B][H][NM], pe [B][NM] packed as by affb200_fused_attn_pack_pe.  d_table fully overwritten.
+extern "C" int affb200_table_grad_u16(const void *d_vals, const uint16_t *pe, int64_t B, int64_t H, int64_t NM, int64_t P,
+                                      float *d_table, int dtype, void *stream) {
+    if (!d_vals || !pe || !d_table || B <= 0 || H <= 0 || NM <= 0 || P <= 0 || P > 32768) {
+        affb200::set_error("table_grad_u16: bad arguments");
+        return AFFB200_E_ARG;
+    }
+    return affb200::launch_table_grad_u16(d_vals, pe, B, H, NM, P, d_table, dtype, (cudaStream_t)stream);
+}

@@ -80,6 +80,9 @@ inline int cl_make_tensor_map(CUtensorMap *map, const void *base, int dtype, int
         return reinterpret_cast<Fn>(pfn);
     }();
     if (!fn) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return AFFB200_E_CUDA; }
+    // a thread that has only used the runtime through another thread's device (autograd's worker) may have no driver
+    // context bound yet: a no-op runtime call binds the device's primary context to this thread
+    cudaFree(nullptr);
     const cuuint64_t dims[3] = {cuuint64_t(W), cuuint64_t(N), cuuint64_t(B)};
     const cuuint64_t strides[2] = {cuuint64_t(sN) * 2u, cuuint64_t(B > 1 ? sB : sN * N) * 2u};
     const cuuint32_t box[3] = {cuuint32_t(box_w), cuuint32_t(box_rows), 1u};
@@ -168,6 +171,106 @@ __device__ __forceinline__ void cl_fill_window(float *win, const float *__restri
         for (int hh = 0; hh < HG; ++hh) win[e * HG + hh] = ok ? __ldg(table + pe * H + h0 + hh) * kLog2e : 0.f;
     }
     if (threadIdx.x < HG) win[kClWin * kClWin * HG + threadIdx.x] = -INFINITY;
+}
+
+// Shared-memory layout.  K|V blocks and the Q tile are written by TMA with the 128-byte (Q at head dim 16: 64-byte)
+// XOR swizzle: the 16-byte chunk j of row r of an 8-row x 128-byte tile sits at r*128 + ((j ^ r) << 4), so the eight
+// row addresses of an ldmatrix fall into eight different bank groups without padding.
+template <int C> struct ClGeom {
+    static constexpr int KVB = 8 * C;            // bytes of one row's K|V for a group of 2 heads: [K0 V0 K1 V1]
+    static constexpr int TPB = KVB / 128;        // 1024-byte tiles per block (head dim 32: one per head)
+    static constexpr int BLK = 8 * KVB;          // bytes of a staged block
+    static constexpr int QB = 4 * C;             // bytes of a token's Q (or output) row for the group
+    static constexpr int OFF_ACT = 128;          // per-warp list of referenced union blocks (8 x 64 bytes)
+    static constexpr int OFF_MK = 640;           // membership words of the tile's tokens [64] u64
+    static constexpr int OFF_PI = 1152;          // packed positions of the tile's tokens [64] u32
+    static constexpr int OFF_PU = 1408;          // packed positions of the union rows [64 blocks][8] u32
+    static constexpr int OFF_WIN = 3456;         // bias window [32*32 + 1][2] fp32
+    static constexpr int OFF_Q = 12288;          // Q tile / output staging [64][QB]
+    static constexpr int OFF_KV = OFF_Q + kClT * 128;
+    __host__ __device__ static constexpr int total(int ucap) { return OFF_KV + (ucap + 1) * BLK; }
+    static_assert(OFF_WIN + (kClWin * kClWin + 1) * 8 <= OFF_Q, "window overlaps the Q tile");
+};
+
+struct ClView {
+    const void *p;
+    int64_t sB, sN, sH;    // element strides
+};
+
+
+template <typename T> __device__ __forceinline__ uint32_t cl_ones2();
+template <> __device__ __forceinline__ uint32_t cl_ones2<__nv_bfloat16>() { return 0x3f803f80u; }
+template <> __device__ __forceinline__ uint32_t cl_ones2<__half>() { return 0x3c003c00u; }
+
+// swizzled byte offset of chunk j of row r inside a 1024-byte tile
+__device__ __forceinline__ uint32_t cl_sw(int r, int j) { return uint32_t(r * 128 + ((j ^ r) << 4)); }
+
+// Products of the warp's 16 rows (rows 0-7: its 8 tokens under head 0, rows 8-15: the same tokens under head 1) with
+// the rows of one staged block: s0 = A·X_h0^T is meaningful in its head-0 rows (registers 0, 1), s1 = A·X_h1^T in its
+// head-1 rows (registers 2, 3); the other halves are ignored products.  X = K (IS_V false) or V (true).
+template <typename T, int C, bool IS_V = false>
+__device__ __forceinline__ void cl_scores(float (&s0)[4], float (&s1)[4], const uint32_t (&qa)[C / 16][4], uint32_t blk_addr,
+                                          int lane) {
+    const int r = lane & 7;
+    s0[0] = s0[1] = s0[2] = s0[3] = 0.f;
+    s1[0] = s1[1] = s1[2] = s1[3] = 0.f;
+    uint32_t kf[4];
+    if constexpr (C == 32) {
+        cl_ldsm_x4(kf, blk_addr + cl_sw(r, (IS_V ? 4 : 0) + (lane >> 3)));
+        f_mma<T>(s0, qa[0], kf[0], kf[1]);
+        f_mma<T>(s0, qa[1], kf[2], kf[3]);
+        cl_ldsm_x4(kf, blk_addr + 1024 + cl_sw(r, (IS_V ? 4 : 0) + (lane >> 3)));
+        f_mma<T>(s1, qa[0], kf[0], kf[1]);
+        f_mma<T>(s1, qa[1], kf[2], kf[3]);
+    } else {
+        cl_ldsm_x4(kf, blk_addr + cl_sw(r, (lane >> 4) * 4 + (IS_V ? 2 : 0) + ((lane >> 3) & 1)));   // head 0 | head 1
+        f_mma<T>(s0, qa[0], kf[0], kf[1]);
+        f_mma<T>(s1, qa[0], kf[2], kf[3]);
+    }
+}
+
+// acc0[nt] += P·X_h0, acc1[nt] += P·X_h1 for the 16 rows of two staged blocks (k = the blocks' rows), X = V or K through
+// ldmatrix.trans; `blk_lane` = address of the block this lane addresses (lanes 8-15 and 24-31: the second block).
+// acc0 is meaningful in its head-0 rows (registers 0, 1), acc1 in its head-1 rows (registers 2, 3).
+template <typename T, int C, bool IS_V>
+__device__ __forceinline__ void cl_accum_rows(float (&acc0)[C / 8][4], float (&acc1)[C / 8][4], const uint32_t (&pa)[4],
+                                              uint32_t blk_lane, int lane) {
+    const int r = lane & 7;
+    uint32_t vf[4];
+    if constexpr (C == 32) {
+#pragma unroll
+        for (int np = 0; np < 2; ++np) {
+            cl_ldsm_x4_t(vf, blk_lane + cl_sw(r, (IS_V ? 4 : 0) + np * 2 + (lane >> 4)));
+            f_mma<T>(acc0[2 * np], pa, vf[0], vf[1]);
+            f_mma<T>(acc0[2 * np + 1], pa, vf[2], vf[3]);
+            cl_ldsm_x4_t(vf, blk_lane + 1024 + cl_sw(r, (IS_V ? 4 : 0) + np * 2 + (lane >> 4)));
+            f_mma<T>(acc1[2 * np], pa, vf[0], vf[1]);
+            f_mma<T>(acc1[2 * np + 1], pa, vf[2], vf[3]);
+        }
+    } else {
+        cl_ldsm_x4_t(vf, blk_lane + cl_sw(r, (IS_V ? 2 : 0) + (lane >> 4)));
+        f_mma<T>(acc0[0], pa, vf[0], vf[1]);
+        f_mma<T>(acc0[1], pa, vf[2], vf[3]);
+        cl_ldsm_x4_t(vf, blk_lane + cl_sw(r, 4 + (IS_V ? 2 : 0) + (lane >> 4)));
+        f_mma<T>(acc1[0], pa, vf[0], vf[1]);
+        f_mma<T>(acc1[1], pa, vf[2], vf[3]);
+    }
+}
+
+// A fragments of the warp's 8 token rows of a swizzled [64][2 heads x C] tile: registers 0, 2 = head 0 (rows 0-7 of the
+// m16 tile), 1, 3 = head 1 (rows 8-15)
+template <int C>
+__device__ __forceinline__ void cl_load_afrag(uint32_t (&qa)[C / 16][4], uint32_t tile_addr, int warp, int lane) {
+    const int r8 = lane & 7, row = warp * 8 + r8, i = lane >> 3;
+#pragma unroll
+    for (int ks = 0; ks < C / 16; ++ks) {
+        if constexpr (C == 32) cl_ldsm_x4(qa[ks], tile_addr + row * 128 + ((((i & 1) * 4 + 2 * ks + (i >> 1)) ^ r8) << 4));
+        else cl_ldsm_x4(qa[ks], tile_addr + row * 64 + ((((i & 1) * 2 + (i >> 1)) ^ ((row >> 1) & 3)) << 4));
+    }
+}
+// byte offset of chunk j of token row `tok` in such a tile
+template <int C> __device__ __forceinline__ uint32_t cl_tile_off(int tok, int j) {
+    return C == 32 ? uint32_t(tok * 128 + ((j ^ (tok & 7)) << 4)) : uint32_t(tok * 64 + ((j ^ ((tok >> 1) & 3)) << 4));
 }
 
 }  // namespace affb200

@@ -20,30 +20,6 @@
 
 namespace affb200 {
 
-// Shared-memory layout.  K|V blocks and the Q tile are written by TMA with the 128-byte (Q at head dim 16: 64-byte)
-// XOR swizzle: the 16-byte chunk j of row r of an 8-row x 128-byte tile sits at r*128 + ((j ^ r) << 4), so the eight
-// row addresses of an ldmatrix fall into eight different bank groups without padding.
-template <int C> struct ClGeom {
-    static constexpr int KVB = 8 * C;            // bytes of one row's K|V for a group of 2 heads: [K0 V0 K1 V1]
-    static constexpr int TPB = KVB / 128;        // 1024-byte tiles per block (head dim 32: one per head)
-    static constexpr int BLK = 8 * KVB;          // bytes of a staged block
-    static constexpr int QB = 4 * C;             // bytes of a token's Q (or output) row for the group
-    static constexpr int OFF_ACT = 128;          // per-warp list of referenced union blocks (8 x 64 bytes)
-    static constexpr int OFF_MK = 640;           // membership words of the tile's tokens [64] u64
-    static constexpr int OFF_PI = 1152;          // packed positions of the tile's tokens [64] u32
-    static constexpr int OFF_PU = 1408;          // packed positions of the union rows [64 blocks][8] u32
-    static constexpr int OFF_WIN = 3456;         // bias window [32*32 + 1][2] fp32
-    static constexpr int OFF_Q = 12288;          // Q tile / output staging [64][QB]
-    static constexpr int OFF_KV = OFF_Q + kClT * 128;
-    __host__ __device__ static constexpr int total(int ucap) { return OFF_KV + (ucap + 1) * BLK; }
-    static_assert(OFF_WIN + (kClWin * kClWin + 1) * 8 <= OFF_Q, "window overlaps the Q tile");
-};
-
-struct ClView {
-    const void *p;
-    int64_t sB, sN, sH;    // element strides
-};
-
 struct ClFwdParams {
     ClView out;
     const float *table, *blank_k, *blank_v;
@@ -56,37 +32,6 @@ struct ClFwdParams {
     int B, H, N, n_tiles, ucap, w, tw;
     float scale_log2;
 };
-
-template <typename T> __device__ __forceinline__ uint32_t cl_ones2();
-template <> __device__ __forceinline__ uint32_t cl_ones2<__nv_bfloat16>() { return 0x3f803f80u; }
-template <> __device__ __forceinline__ uint32_t cl_ones2<__half>() { return 0x3c003c00u; }
-
-// swizzled byte offset of chunk j of row r inside a 1024-byte tile
-__device__ __forceinline__ uint32_t cl_sw(int r, int j) { return uint32_t(r * 128 + ((j ^ r) << 4)); }
-
-// Scores of the warp's 16 rows (rows 0-7: its 8 tokens under head 0, rows 8-15: the same tokens under head 1) against
-// one staged block: s0 = A·K_h0^T is meaningful in its head-0 rows (registers 0, 1), s1 = A·K_h1^T in its head-1 rows
-// (registers 2, 3); the other halves are ignored products.
-template <typename T, int C>
-__device__ __forceinline__ void cl_scores(float (&s0)[4], float (&s1)[4], const uint32_t (&qa)[C / 16][4], uint32_t blk_addr,
-                                          int lane) {
-    const int r = lane & 7;
-    s0[0] = s0[1] = s0[2] = s0[3] = 0.f;
-    s1[0] = s1[1] = s1[2] = s1[3] = 0.f;
-    uint32_t kf[4];
-    if constexpr (C == 32) {
-        cl_ldsm_x4(kf, blk_addr + cl_sw(r, lane >> 3));
-        f_mma<T>(s0, qa[0], kf[0], kf[1]);
-        f_mma<T>(s0, qa[1], kf[2], kf[3]);
-        cl_ldsm_x4(kf, blk_addr + 1024 + cl_sw(r, lane >> 3));
-        f_mma<T>(s1, qa[0], kf[0], kf[1]);
-        f_mma<T>(s1, qa[1], kf[2], kf[3]);
-    } else {
-        cl_ldsm_x4(kf, blk_addr + cl_sw(r, (lane >> 4) * 4 + ((lane >> 3) & 1)));   // head 0: chunks 0,1; head 1: 4,5
-        f_mma<T>(s0, qa[0], kf[0], kf[1]);
-        f_mma<T>(s1, qa[0], kf[2], kf[3]);
-    }
-}
 
 template <typename T, int C>
 __global__ void __launch_bounds__(kClThreads, 2)
@@ -201,14 +146,7 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
         }
         // ---- Q fragments: registers 0, 2 = head 0 (rows 0-7), 1, 3 = head 1 (rows 8-15); blank token --------------
         uint32_t qa[KS][4];
-        {
-            const int row = warp * 8 + r8, i = lane >> 3;
-#pragma unroll
-            for (int ks = 0; ks < KS; ++ks) {
-                if constexpr (C == 32) cl_ldsm_x4(qa[ks], s_q + row * 128 + ((((i & 1) * 4 + 2 * ks + (i >> 1)) ^ r8) << 4));
-                else cl_ldsm_x4(qa[ks], s_q + row * 64 + ((((i & 1) * 2 + (i >> 1)) ^ ((row >> 1) & 3)) << 4));
-            }
-        }
+        cl_load_afrag<C>(qa, s_q, warp, lane);
         float oh0[NT][4], oh1[NT][4], ol[4], m[2];
         {
             float s0[4], s1[4];
@@ -298,26 +236,7 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
             pa[2] = f_pack2<T>(f_ex2(s0[1][0] - m[0]), f_ex2(s0[1][1] - m[0]));
             pa[3] = f_pack2<T>(f_ex2(s1[1][2] - m[1]), f_ex2(s1[1][3] - m[1]));
             f_mma<T>(ol, pa, onesb, onesb);   // row sums of the rounded probabilities (column 0)
-            const uint32_t vblk = s_kv + pj[(lane >> 3) & 1] * G::BLK;
-#pragma unroll
-            for (int np = 0; np < C / 16; ++np) {
-                uint32_t vf[4];
-                if constexpr (C == 32) {
-                    cl_ldsm_x4_t(vf, vblk + cl_sw(r8, 4 + np * 2 + (lane >> 4)));
-                    f_mma<T>(oh0[2 * np], pa, vf[0], vf[1]);
-                    f_mma<T>(oh0[2 * np + 1], pa, vf[2], vf[3]);
-                    cl_ldsm_x4_t(vf, vblk + 1024 + cl_sw(r8, 4 + np * 2 + (lane >> 4)));
-                    f_mma<T>(oh1[2 * np], pa, vf[0], vf[1]);
-                    f_mma<T>(oh1[2 * np + 1], pa, vf[2], vf[3]);
-                } else {
-                    cl_ldsm_x4_t(vf, vblk + cl_sw(r8, 2 + (lane >> 4)));
-                    f_mma<T>(oh0[0], pa, vf[0], vf[1]);
-                    f_mma<T>(oh0[1], pa, vf[2], vf[3]);
-                    cl_ldsm_x4_t(vf, vblk + cl_sw(r8, 6 + (lane >> 4)));
-                    f_mma<T>(oh1[0], pa, vf[0], vf[1]);
-                    f_mma<T>(oh1[1], pa, vf[2], vf[3]);
-                }
-            }
+            cl_accum_rows<T, C, true>(oh0, oh1, pa, s_kv + pj[(lane >> 3) & 1] * G::BLK, lane);
         }
 
         // ---- epilogue: O / l through the warp's Q rows (same swizzle), 16-byte stores ----------------------------
@@ -328,7 +247,7 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
                 const int j = hh * (C / 8) + nt;
-                const uint32_t a = C == 32 ? uint32_t(tok * 128 + ((j ^ (tok & 7)) << 4)) : uint32_t(tok * 64 + ((j ^ ((tok >> 1) & 3)) << 4));
+                const uint32_t a = cl_tile_off<C>(tok, j);
                 const float x0 = hh == 0 ? oh0[nt][0] : oh1[nt][2], x1 = hh == 0 ? oh0[nt][1] : oh1[nt][3];
                 *reinterpret_cast<uint32_t *>(gen + G::OFF_Q + a + q4 * 4) = f_pack2<T>(x0 * inv, x1 * inv);
             }
@@ -339,7 +258,7 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
 #pragma unroll
         for (int e = lane; e < 8 * (G::QB / 16); e += 32) {
             const int row = warp * 8 + e / (G::QB / 16), ch = e % (G::QB / 16);
-            const uint32_t a = C == 32 ? uint32_t(row * 128 + ((ch ^ (row & 7)) << 4)) : uint32_t(row * 64 + ((ch ^ ((row >> 1) & 3)) << 4));
+            const uint32_t a = cl_tile_off<C>(row, ch);
             if (row < ti)
                 *reinterpret_cast<uint4 *>(out_tile + int64_t(row) * p.out.sN + ch * 8) = *reinterpret_cast<const uint4 *>(gen + G::OFF_Q + a);
         }

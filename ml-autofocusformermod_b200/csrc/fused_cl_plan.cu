@@ -136,18 +136,20 @@ cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ ma
     }
 }
 
-// one CTA per (key tile, image): scan all query tokens in order, keep those referencing blocks [8*kt, 8*kt+8)
-__global__ void __launch_bounds__(kPlanThreads)
-cl_kplan_kernel(const uint16_t *__restrict__ blk, int N, int NB, int kumax, int32_t *__restrict__ hdr,
-                uint32_t *__restrict__ utok, int32_t *__restrict__ stats) {
-    __shared__ int warp_tot[kPlanThreads / 32];
-    __shared__ int base_s;
-    const int tid = threadIdx.x, kt = blockIdx.x, b = blockIdx.y, n_tiles = gridDim.x;
-    const int lane = tid & 31, warp = tid >> 5;
-    uint32_t *out = utok + (int64_t(b) * n_tiles + kt) * kumax;
-    if (tid == 0) base_s = 0;
+// One CTA per (tile of 8 key blocks, image): every query token's block list is scanned once, in token order, and the
+// token is appended to the list of each of the tile's blocks it references (ordered compaction by ballots), so every
+// list is ascending — the summation order of the dK / dV kernel.
+constexpr int kKpThreads = 256;
+__global__ void __launch_bounds__(kKpThreads)
+cl_kplan_kernel(const uint16_t *__restrict__ blk, int N, int NB, int kbcap, int32_t *__restrict__ kb_cnt,
+                uint32_t *__restrict__ kb_tok, int32_t *__restrict__ stats) {
+    __shared__ int warp_tot[kKpThreads / 32][8];
+    __shared__ int base_s[8];
+    const int tid = threadIdx.x, kt = blockIdx.x, b = blockIdx.y;
+    const int lane = tid & 31, warp = tid >> 5, nblk = (N + 7) >> 3;
+    if (tid < 8) base_s[tid] = 0;
     __syncthreads();
-    for (int i0 = 0; i0 < N; i0 += kPlanThreads) {
+    for (int i0 = 0; i0 < N; i0 += kKpThreads) {
         const int i = i0 + tid;
         uint32_t bits = 0u;
         if (i < N) {
@@ -157,27 +159,61 @@ cl_kplan_kernel(const uint16_t *__restrict__ blk, int N, int NB, int kumax, int3
                 if ((v >> 3) == kt) bits |= 1u << (v & 7);
             }
         }
-        const uint32_t bal = __ballot_sync(0xffffffffu, bits != 0u);
-        if (lane == 0) warp_tot[warp] = __popc(bal);
+        uint32_t bal[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            bal[r] = __ballot_sync(0xffffffffu, (bits >> r) & 1u);
+            if (lane == r) warp_tot[warp][r] = __popc(bal[r]);
+        }
         __syncthreads();
-        int off = base_s;
-        for (int k = 0; k < warp; ++k) off += warp_tot[k];
-        off += __popc(bal & ((1u << lane) - 1u));
-        if (bits != 0u && off < kumax) out[off] = (uint32_t(i) << 8) | bits;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if ((bits >> r) & 1u) {
+                int off = base_s[r];
+                for (int k = 0; k < warp; ++k) off += warp_tot[k][r];
+                off += __popc(bal[r] & ((1u << lane) - 1u));
+                const int kb = kt * 8 + r;
+                if (off < kbcap && kb < nblk) kb_tok[(int64_t(b) * nblk + kb) * kbcap + off] = uint32_t(i);
+            }
+        }
         __syncthreads();
-        if (tid == 0) {
+        if (tid < 8) {
             int t = 0;
-            for (int k = 0; k < kPlanThreads / 32; ++k) t += warp_tot[k];
-            base_s += t;
+            for (int k = 0; k < kKpThreads / 32; ++k) t += warp_tot[k][tid];
+            base_s[tid] += t;
         }
         __syncthreads();
     }
-    if (tid == 0) {
-        const int U = base_s;
-        hdr[int64_t(b) * n_tiles + kt] = U | (U > kumax ? AFFB200_PLAN_OVERFLOW : 0);
-        if (U > kumax) atomicAdd(&stats[2], 1);
+    if (tid < 8 && kt * 8 + tid < nblk) {
+        const int U = base_s[tid];
+        kb_cnt[int64_t(b) * nblk + kt * 8 + tid] = U;
+        if (U > kbcap) atomicAdd(&stats[2], 1);
         atomicMax(&stats[5], U);
     }
+}
+
+// packed bias indices in ascending-block slot order (the order fused_cl_bwd writes dS in)
+__global__ void __launch_bounds__(256)
+cl_pack_pe_sorted_kernel(const int64_t *__restrict__ pe_idx, const int64_t *__restrict__ mask, const uint16_t *__restrict__ blk,
+                         int64_t total, int NB, uint16_t *__restrict__ out, int32_t *__restrict__ bad) {
+    const int64_t t = int64_t(blockIdx.x) * 256 + threadIdx.x;   // (token, group of 8 slots)
+    if (t >= total) return;
+    const int64_t tokn = t / NB;
+    const int q = int(t - tokn * NB);
+    const uint16_t *bp = blk + tokn * NB;
+    const int mine = bp[q];
+    int rank = 0;
+    for (int k = 0; k < NB; ++k) rank += (bp[k] < mine || (bp[k] == mine && k < q)) ? 1 : 0;
+    const int64_t src = t * 8, dst = (tokn * NB + rank) * 8;
+    uint16_t v[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int64_t pe = __ldg(pe_idx + src + r);
+        const bool masked = mask && __ldg(mask + src + r) == 0;
+        if (pe < 0 || pe >= 32768) { if (!masked) atomicAdd(bad, 1); v[r] = masked ? 0x8000u : 0u; }
+        else v[r] = uint16_t(pe) | (masked ? 0x8000u : 0u);
+    }
+    *reinterpret_cast<uint4 *>(out + dst) = *reinterpret_cast<const uint4 *>(v);
 }
 
 }  // namespace affb200
@@ -209,15 +245,26 @@ extern "C" int affb200_cl_qplan_build(const int64_t *nbhd_idx, const int64_t *ma
     return check_launch("cl_qplan_build");
 }
 
-extern "C" int affb200_cl_kplan_build(const uint16_t *blk, int64_t B, int64_t N, int64_t M, int64_t kumax,
-                                      int32_t *hdr, uint32_t *utok, int32_t *stats, void *stream) {
-    if (B <= 0 || B > 65535 || N <= 0 || N >= (1 << 24) || M <= 0 || M % 8 != 0 || kumax <= 0 || kumax % 16 != 0) {
+extern "C" int affb200_cl_kplan_build(const uint16_t *blk, int64_t B, int64_t N, int64_t M, int64_t kbcap,
+                                      int32_t *kb_cnt, uint32_t *kb_tok, int32_t *stats, void *stream) {
+    if (B <= 0 || B > 65535 || N <= 0 || N >= (1 << 24) || M <= 0 || M % 8 != 0 || kbcap <= 0) {
         set_error("cl_kplan_build: unsupported dimensions");
         return AFFB200_E_ARG;
     }
-    if (!blk || !hdr || !utok || !stats) { set_error("cl_kplan_build: null pointer"); return AFFB200_E_ARG; }
+    if (!blk || !kb_cnt || !kb_tok || !stats) { set_error("cl_kplan_build: null pointer"); return AFFB200_E_ARG; }
     const dim3 grid{unsigned((N + kClT - 1) / kClT), unsigned(B), 1u};
-    cl_kplan_kernel<<<grid, kPlanThreads, 0, (cudaStream_t)stream>>>(blk, int(N), int(M / 8), int(kumax), hdr, utok,
-                                                                   stats);
+    cl_kplan_kernel<<<grid, kKpThreads, 0, (cudaStream_t)stream>>>(blk, int(N), int(M / 8), int(kbcap), kb_cnt, kb_tok, stats);
     return check_launch("cl_kplan_build");
+}
+
+extern "C" int affb200_cl_pack_pe_sorted(const int64_t *pe_idx, const int64_t *mask, const uint16_t *blk, int64_t B,
+                                         int64_t N, int64_t M, uint16_t *out, int32_t *bad, void *stream) {
+    if (B <= 0 || N <= 0 || M <= 0 || M % 8 != 0 || !pe_idx || !blk || !out || !bad) {
+        set_error("cl_pack_pe_sorted: bad arguments");
+        return AFFB200_E_ARG;
+    }
+    const int64_t total = B * N * (M / 8);
+    cl_pack_pe_sorted_kernel<<<unsigned((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pe_idx, mask, blk, total, int(M / 8),
+                                                                                              out, bad);
+    return check_launch("cl_pack_pe_sorted");
 }

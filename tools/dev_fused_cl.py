@@ -62,8 +62,8 @@ def case(h, w, n, B, H, c, m, nbhd_size, img, dtype=torch.bfloat16, check_ref=Fa
     p_s, mean, _, _, _ = space_filling_cluster(pos, m, h, w)
     nbhd, mask, pe_idx, _ = build_nbhd(p_s, mean, m, nbhd_size, rpw)
     fused_cl.hint_geometry(nbhd, p_s, rpw, tw)
-    pl = fused_cl.cl_plan(nbhd, mask, pe_idx, want_k=True)
-    print("case", (h, w, n, B, H, c, m, nbhd_size), "plan:", None if pl is None else (pl.ucap, pl.kumax, pl.stats.tolist()))
+    pl = fused_cl.cl_plan(nbhd, mask, pe_idx, P)
+    print("case", (h, w, n, B, H, c, m, nbhd_size), "plan:", None if pl is None else (pl.ucap, pl.kbcap, pl.stats.tolist()))
     if pl is None:
         return
     g = torch.Generator().manual_seed(7 + n)
