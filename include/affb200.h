@@ -338,7 +338,7 @@ int affb200_fused_cl_fwd(const affb200_view *q, const affb200_view *k, const aff
 /* Backward: dq / dk / dv views as the forward's operands (fully overwritten); lse from the forward; delta [B][H][N] fp32
  * scratch (dO·O, written by the first kernel, read by the second); ds_work [B][H][N][M] of `dtype`: dS in
  * ascending-block slot order (pair it with plan->q_pe for the bias-table gradient); blank_part
- * [affb200_fused_cl_bwd_grid(B, H, N)][H][2][c] fp32: per-CTA sums of d blank_k / d blank_v (sum over the first axis).
+ * [affb200_fused_cl_bwd_grid(B, H, N) * 8][H][2][c] fp32: per-warp sums of d blank_k / d blank_v (sum over the first axis).
  * Two launches: a query-major kernel (dQ, dS, delta, blank sums) and a key-major kernel in which a warp owns one 8-row
  * block of K|V and accumulates dK / dV over the query tokens that reference it — no atomics, fixed summation order. */
 int64_t affb200_fused_cl_bwd_grid(int64_t B, int64_t H, int64_t N);

@@ -304,7 +304,7 @@ class FusedClusterAttentionCl(Function):
             dkv = torch.empty_like(kv_lin)
             ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
             delta = torch.empty((B, H, n), dtype=torch.float32, device=dev)
-            blank_part = torch.empty((grid, H, 2, c), dtype=torch.float32, device=dev)
+            blank_part = torch.empty((grid * 8, H, 2, c), dtype=torch.float32, device=dev)
             N.check(N.LIB.affb200_fused_cl_bwd(
                 _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
                 _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
@@ -312,7 +312,7 @@ class FusedClusterAttentionCl(Function):
                 N.p(table), N.p(bk), N.p(bv), clp.byref(), N.p(lse), N.p(delta), N.p(ds), N.p(blank_part),
                 N.p(guard_tensor(dev)), B, H, n, M, c, clp.w, clp.tw, float(scale), N.dtype_enum(q_lin),
                 N.stream_ptr(dev)), "fused_cl_bwd")
-            db = _col_sum(blank_part.view(grid, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
+            db = _col_sum(blank_part.view(grid * 8, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
             dw = dpb = d_table = None
             if ctx.pe_lin is not None:
                 pe_feat, F, w_dt, b_dt = ctx.pe_lin

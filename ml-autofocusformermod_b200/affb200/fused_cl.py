@@ -19,6 +19,7 @@ from . import plan as _plan
 CL_T = 64
 CL_UMAX = 64
 KBCAP_STEP = 16
+UCAP_SLACK = 3
 
 
 class ClPlanStruct(ctypes.Structure):
@@ -39,6 +40,12 @@ def hint_geometry(nbhd_idx, pos, rel_pos_width, table_width):
     p = _plan.get_plan(nbhd_idx)
     p._cl_hint = (pos, int(rel_pos_width), int(table_width))
     p._cl = None
+
+
+def observed(skey):
+    """What eager passes recorded for index tensors of shape skey = (B, N, M): dict(ok, ucap, kbcap) or None.  Static
+    (graph-capture) builds size their launches from it; tests replace it to force a failed speculation."""
+    return _plan._observed.get(("cl",) + skey)
 
 
 class ClPlan:
@@ -63,7 +70,7 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P):
     nblk = (n + 7) // 8
     skey = (B, n, M)
     static = _plan.is_static()
-    obs = _plan._observed.get(("cl",) + skey)
+    obs = observed(skey)
     if static and obs is None:
         raise RuntimeError("affb200.fused_cl: static mode needs an eager pass over shape %s first" % (skey,))
     if static and not obs["ok"]:
@@ -107,7 +114,8 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P):
             N.check(N.LIB.affb200_cl_pack_pe_sorted(N.p(pe_c), N.p(mk_c), N.p(blk), B, n, M, N.p(q_pe), N.p(bad), sp),
                     "cl_pack_pe_sorted")
         if static:
-            ucap = obs["ucap"]
+            # a little room above the largest union seen: neighbourhoods of the data-dependent stages vary per batch
+            ucap = min(CL_UMAX, obs["ucap"] + UCAP_SLACK)
             _plan.guard_add((stats[0] != 0) | (stats[1] != 0) | (stats[2] != 0) | (stats[4] > ucap) | (bad[0] != 0))
         else:
             st = stats.tolist()

@@ -80,17 +80,24 @@ inline int cl_make_tensor_map(CUtensorMap *map, const void *base, int dtype, int
         return reinterpret_cast<Fn>(pfn);
     }();
     if (!fn) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return AFFB200_E_CUDA; }
-    // a thread that has only used the runtime through another thread's device (autograd's worker) may have no driver
-    // context bound yet: a no-op runtime call binds the device's primary context to this thread
-    cudaFree(nullptr);
+
     const cuuint64_t dims[3] = {cuuint64_t(W), cuuint64_t(N), cuuint64_t(B)};
     const cuuint64_t strides[2] = {cuuint64_t(sN) * 2u, cuuint64_t(B > 1 ? sB : sN * N) * 2u};
     const cuuint32_t box[3] = {cuuint32_t(box_w), cuuint32_t(box_rows), 1u};
     const cuuint32_t estr[3] = {1u, 1u, 1u};
-    const CUresult r = fn(map, dtype == AFFB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3,
-                          const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                          swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
-                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    auto encode = [&]() {
+        return fn(map, dtype == AFFB200_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3,
+                  const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    };
+    CUresult r = encode();
+    if (r == CUDA_ERROR_INVALID_CONTEXT) {
+        // a thread that only ever inherited its device (autograd's worker) has no driver context bound: setting the
+        // current device again binds the primary context to this thread (and is legal under stream capture)
+        int dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess) r = encode();
+    }
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", int(r)); return AFFB200_E_CUDA; }
     return AFFB200_OK;
 }

@@ -32,9 +32,7 @@ template <int C> struct ClGeomB {
     static constexpr int OFF_Q = G::OFF_Q;                 // Q tile, later the dQ staging rows
     static constexpr int OFF_DO = OFF_Q + kClT * 128;      // dO tile
     static constexpr int OFF_KV = OFF_DO + kClT * 128;
-    __host__ __device__ static constexpr int off_bp(int ucap) { return OFF_KV + (ucap + 1) * G::BLK; }
-    // per-warp running sums of the blank-token gradients [8 warps][H][2][C] fp32
-    __host__ __device__ static constexpr int total(int ucap, int H) { return off_bp(ucap) + 8 * H * 2 * C * 4; }
+    __host__ __device__ static constexpr int total(int ucap) { return OFF_KV + (ucap + 1) * G::BLK; }
 };
 
 struct ClBwdQParams {
@@ -47,7 +45,7 @@ struct ClBwdQParams {
     const float *lse;
     float *delta;          // [B][H][N]
     void *ds;              // [B][H][N][M] of T, slot order = ascending block id
-    float *blank_part;     // [grid][H][2][C]
+    float *blank_part;     // [grid][8 warps][H][2][C]: running sums of d blank_k / d blank_v per warp
     int32_t *guard;
     int B, H, N, M, n_tiles, ucap, w, tw;
     float scale, scale_log2;
@@ -66,7 +64,7 @@ fused_cl_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
     const uint32_t s_q = sm + GB::OFF_Q, s_do = sm + GB::OFF_DO, s_kv = sm + GB::OFF_KV;
     unsigned char *gen = affb200_dsm;
     const int ucap = p.ucap;
-    float *bp = reinterpret_cast<float *>(gen + GB::off_bp(ucap)) + warp * p.H * 2 * C;
+    float *bp = p.blank_part + (int64_t(blockIdx.x) * 8 + warp) * p.H * 2 * C;
     const uint32_t items = uint32_t(p.H / 2) * p.B * p.n_tiles;
     const T *op = static_cast<const T *>(p.o.p);
     T *dqp = static_cast<T *>(const_cast<void *>(p.dq.p));
@@ -79,7 +77,7 @@ fused_cl_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
     }
     for (int e = tid; e < G::BLK / 16; e += kClThreads)
         *reinterpret_cast<uint4 *>(gen + GB::OFF_KV + ucap * G::BLK + e * 16) = make_uint4(0u, 0u, 0u, 0u);
-    for (int e = tid; e < 8 * p.H * 2 * C; e += kClThreads) reinterpret_cast<float *>(gen + GB::off_bp(ucap))[e] = 0.f;
+    for (int e = tid; e < 8 * p.H * 2 * C; e += kClThreads) p.blank_part[int64_t(blockIdx.x) * 8 * p.H * 2 * C + e] = 0.f;
     __syncthreads();
 
     uint32_t phase = 0;
@@ -253,8 +251,9 @@ fused_cl_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
                         f_mma<T>(acc, aw[kind], bf[nt], 0u);
                         if (g == 0) {   // kind 0 -> d blank_v (index 1), kind 1 -> d blank_k (index 0)
                             float *dst = bp + ((h0 + hh) * 2 + (1 - kind)) * C + nt * 8 + q4 * 2;
-                            dst[0] += acc[2 * hh];
-                            dst[1] += acc[2 * hh + 1];
+                            const float sc = kind == 0 ? 1.f : p.scale;   // d blank_k carries the logit scale
+                            dst[0] += acc[2 * hh] * sc;
+                            dst[1] += acc[2 * hh + 1] * sc;
                         }
                     }
                 }
@@ -342,22 +341,12 @@ fused_cl_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
         fence_proxy_async();
         __syncthreads();
     }
-    // blank-token gradients of this CTA: the 8 warps' running sums in warp order
-    __syncthreads();
-    for (int e = tid; e < p.H * 2 * C; e += kClThreads) {
-        const float *src = reinterpret_cast<const float *>(gen + GB::off_bp(ucap)) + e;
-        float a = 0.f;
-#pragma unroll
-        for (int w8 = 0; w8 < 8; ++w8) a += src[w8 * p.H * 2 * C];
-        // d blank_k carries the logit scale
-        p.blank_part[int64_t(blockIdx.x) * p.H * 2 * C + e] = ((e / C) & 1) == 0 ? a * p.scale : a;
-    }
 }
 
 template <typename T, int C>
 static int launch_cl_bwd_dq(const CUtensorMap &tm_kv, const CUtensorMap &tm_q, const CUtensorMap &tm_do,
                             const ClBwdQParams &p, int grid, cudaStream_t st) {
-    const int smem = ClGeomB<C>::total(p.ucap, p.H);
+    const int smem = ClGeomB<C>::total(p.ucap);
     if (smem > 227 * 1024) { set_error("fused_cl_bwd: union of %d blocks does not fit shared memory", p.ucap); return AFFB200_E_ARG; }
     auto kern = fused_cl_bwd_dq_kernel<T, C>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);

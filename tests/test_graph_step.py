@@ -127,6 +127,11 @@ def test_failed_speculation_is_redone_eagerly(monkeypatch):
     o2 = torch.optim.AdamW(m2.parameters(), lr=0.0, weight_decay=0.0, fused=True)
     real_cap = plan.observed_umax_cap
     monkeypatch.setattr(plan, "observed_umax_cap", lambda kind, key: min(real_cap(kind, key) or 31, 31))
+    # the block-structured kernels size their launches from the recorded largest union of 8-row blocks: cap it at 8
+    from affb200 import fused_cl
+    real_obs = fused_cl.observed
+    monkeypatch.setattr(fused_cl, "observed",
+                        lambda skey: (lambda o: o if not (o and o.get("ok")) else dict(o, ucap=min(o["ucap"], 8)))(real_obs(skey)))
     step = GraphedTrainStep(m1, o1, torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1)
     step.max_recaptures = 1
     for i, (x, y) in enumerate(zip(xs[1:], ys[1:])):
@@ -140,6 +145,7 @@ def test_failed_speculation_is_redone_eagerly(monkeypatch):
         assert all(bool(torch.isfinite(p).all()) for p in m1.parameters())
     assert step.recaptures == 1
     monkeypatch.setattr(plan, "observed_umax_cap", real_cap)
+    monkeypatch.setattr(fused_cl, "observed", real_obs)
     step.max_recaptures = 2
     step(xs[0], ys[0])                    # falls back once more, re-captures with the real bounds ...
     n = step.fallbacks
