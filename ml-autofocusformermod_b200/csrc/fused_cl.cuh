@@ -30,6 +30,7 @@ constexpr int kClWin = 32;      // side of the shared-memory window of the relat
 constexpr int kClWinHalf = 16;  // offsets -16 .. 15 are served from the window, the rest from the global table
 constexpr uint32_t kClPosBias = (uint32_t(kClWinHalf) << 16) | uint32_t(kClWinHalf);
 constexpr uint32_t kClPosInvalid = 0xffffffffu;   // packed position of a padded row (>= N)
+constexpr int kClAbsent = 0xffff;                 // block id of a fully padded group of 8 slots
 
 // ---- mbarrier + bulk async copy (PTX ISA 8.x; SASS: SYNCS.*, UBLKCP) --------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {

@@ -263,6 +263,15 @@ fused_cl_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
 
         T *ds_tok = dsp + ((int64_t(b) * p.H + h0) * p.N + t0 + tok) * p.M;
         const int64_t ds_head = int64_t(p.N) * p.M;
+        {
+            // slots behind the token's real blocks (fully padded groups of the last cluster): dS = 0
+            const int first = __popcll(mk) * 8;
+            if (live)
+                for (int e = first + q4 * 2; e < p.M; e += 8) {
+                    *reinterpret_cast<uint32_t *>(ds_tok + e) = 0u;
+                    *reinterpret_cast<uint32_t *>(ds_tok + ds_head + e) = 0u;
+                }
+        }
         for (int k = 0; k < n_act; k += 2) {
             const uint32_t two = lds_u16(s_act + k);
             const bool has1 = k + 1 < n_act;

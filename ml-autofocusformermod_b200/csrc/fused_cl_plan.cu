@@ -54,7 +54,13 @@ cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ ma
         const int64_t so = (bN + t0 + t) * M + q * 8;
         const int64_t base = nbhd[so];
         int blk = 0;
-        if (base < 0 || base >= N || (base & 7) != 0) {
+        if (mask && mask[so] == 0) {
+            // a block that lies entirely in the padding of the last cluster (clusters of 16, 24 ... rows): all 8 slots
+            // masked; it joins no union and its slots sort behind the token's real blocks
+            for (int r = 1; r < 8; ++r)
+                if (mask[so + r] != 0) bad = 1;
+            blk = kClAbsent;
+        } else if (base < 0 || base >= N || (base & 7) != 0) {
             bad = 1;
         } else {
             blk = int(base >> 3);
@@ -118,6 +124,7 @@ cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ ma
     if (U <= kClUMax) {
         for (int it = tid; it < ti * NB; it += kPlanThreads) {
             const int t = it / NB, blk = blk_s[it];
+            if (blk == kClAbsent) continue;
             const int loc = int(pre[blk >> 5]) + __popc(bitmap[blk >> 5] & ((1u << (blk & 31)) - 1u));
             const unsigned long long bitv = 1ull << loc;
             const unsigned long long old = atomicOr(&qm[t], bitv);
@@ -156,7 +163,7 @@ cl_kplan_kernel(const uint16_t *__restrict__ blk, int N, int NB, int kbcap, int3
             const uint16_t *bp = blk + (int64_t(b) * N + i) * NB;
             for (int q = 0; q < NB; ++q) {
                 const int v = bp[q];
-                if ((v >> 3) == kt) bits |= 1u << (v & 7);
+                if (v != kClAbsent && (v >> 3) == kt) bits |= 1u << (v & 7);
             }
         }
         uint32_t bal[8];

@@ -1,0 +1,213 @@
+"""GPU parity of the block-structured fused neighbourhood attention (csrc/fused_cl_fwd.cu, fused_cl_bwd.cu,
+fused_cl_plan.cu) against the reference's expression chain (aff_transformer.py:103-156) evaluated in fp64 by the
+oracle's operators, on neighbourhoods produced by the real index pipeline (positions -> clustering -> kNN -> nbhd /
+pe_idx build) with the geometry hint the stage index build gives (affb200.fused_cl.hint_geometry)."""
+import pytest
+import torch
+
+from tests.util import rel_err
+from tests.test_fused_attn import _positions, _reference
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(h, w, n, B, m, nbhd_size, img, hint=True):
+    from affb200.point_utils import space_filling_cluster, build_nbhd
+    from affb200 import fused_cl
+    rpw = img // 4 - 1
+    pos = _positions(h, w, n, B, seed=n).cuda()
+    p_s, mean, _, _, _ = space_filling_cluster(pos, m, h, w)
+    nbhd, mask, pe_idx, _ = build_nbhd(p_s, mean, m, nbhd_size, rpw)
+    if hint:
+        fused_cl.hint_geometry(nbhd, p_s, rpw, 2 * rpw + 1)
+    return nbhd, mask, pe_idx, rpw, p_s
+
+
+def _operands(B, n, H, c, P, dtype, seed):
+    g = torch.Generator().manual_seed(seed)
+    hc = H * c
+    q = torch.randn(B, n, hc, generator=g).to(dtype).cuda().requires_grad_(True)
+    kv = torch.randn(B, n, 2 * hc, generator=g).to(dtype).cuda().requires_grad_(True)
+    table = (0.5 * torch.randn(P, H, generator=g)).to(dtype).cuda().requires_grad_(True)
+    bk = torch.randn(hc, generator=g).cuda().requires_grad_(True)
+    bv = torch.randn(hc, generator=g).cuda().requires_grad_(True)
+    go = torch.randn(B, n, hc, generator=g).to(dtype).cuda()
+    return q, kv, table, bk, bv, go
+
+
+@pytest.fixture
+def cl_calls(monkeypatch):
+    """counts the calls that took the block-structured kernels"""
+    from affb200 import fused
+    monkeypatch.setenv("AFFB200_FUSED_IMG", "0")
+    hits = []
+    real = fused.FusedClusterAttentionCl.apply
+
+    def spy(*a):
+        hits.append(1)
+        return real(*a)
+    monkeypatch.setattr(fused.FusedClusterAttentionCl, "apply", spy)
+    return hits
+
+
+CASES = [  # (h, w, n, B, H, c, m, nbhd, img)
+    (56, 56, 3136, 2, 2, 32, 8, 48, 224),     # AFF-Tiny stage 1: the full grid
+    (56, 56, 627, 3, 4, 32, 8, 48, 224),      # stage 2 of the 1/5 models: padded last cluster, two head groups
+    (56, 56, 784, 2, 4, 16, 8, 48, 224),      # head dim 16 (AFF-Mini)
+    (56, 56, 300, 2, 2, 32, 8, 48, 224),      # sparse tokens: offsets beyond the 32 x 32 window take the global table
+    (56, 56, 1000, 1, 8, 32, 24, 144, 224),   # clusters of 24 rows (3 blocks each), 18 blocks per token, 4 head groups
+    (56, 56, 321, 2, 2, 16, 16, 64, 224),     # clusters of 16, odd token count: last tile nearly empty
+    (28, 28, 260, 2, 6, 32, 8, 48, 224),      # three head groups, M = 48 > tokens of the last tile
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("case", CASES)
+def test_block_structured_attention_matches_reference_chain(case, dtype, cl_calls):
+    from affb200.fused import fused_cluster_attention
+    h, w, n, B, H, c, m, nbhd_size, img = case
+    nbhd, mask, pe_idx, rpw, _ = _setup(h, w, n, B, m, nbhd_size, img)
+    P = (2 * rpw + 1) ** 2
+    q, kv, table, bk, bv, go = _operands(B, n, H, c, P, dtype, 7 + n)
+    scale = c ** -0.5
+    out = fused_cluster_attention(q, kv, H, scale, nbhd, pe_idx, mask, table, bk, bv)
+    assert out is not None and out.shape == q.shape and out.dtype == dtype
+    assert cl_calls == [1], "the block-structured kernels did not take this case"
+    out.backward(go)
+    ref = _reference(q, kv, H, scale, nbhd, pe_idx, mask, table, bk.to(dtype), bv.to(dtype), go)
+    tol = 1e-2 if dtype == torch.bfloat16 else 2e-3   # north_star: 1e-2 relative in bf16 (f16 held to 2e-3)
+    for nm, a, r in zip(["out", "d_q", "d_kv", "d_table", "d_blank_k", "d_blank_v"],
+                        [out, q.grad, kv.grad, table.grad, bk.grad, bv.grad], ref):
+        assert torch.isfinite(a.float()).all(), nm
+        e = rel_err(a, r)
+        assert e < tol, (nm, e)
+
+
+def test_block_structured_attention_is_deterministic(cl_calls):
+    from affb200.fused import fused_cluster_attention
+    nbhd, mask, pe_idx, rpw, _ = _setup(56, 56, 627, 3, 8, 48, 224)
+    q, kv, table, bk, bv, go = _operands(3, 627, 4, 32, (2 * rpw + 1) ** 2, torch.bfloat16, 3)
+    outs = []
+    for _ in range(2):
+        a = [x.detach().clone().requires_grad_(True) for x in (q, kv, table, bk, bv)]
+        o = fused_cluster_attention(a[0], a[1], 4, 32 ** -0.5, nbhd, pe_idx, mask, a[2], a[3], a[4])
+        o.backward(go)
+        outs.append([o.detach()] + [x.grad for x in a])
+    assert cl_calls == [1, 1]
+    for x, y in zip(*outs):
+        assert torch.equal(x, y)
+
+
+def test_plan_declines_what_is_not_block_structured(cl_calls):
+    """Random neighbourhoods (the reference's own unit-test distribution, clusten/test_qk_kernel.py:25), a bias index
+    that is not the position difference, fractional positions, or no geometry hint at all: the plan is None and the
+    row-union kernels run, still matching the oracle."""
+    from affb200 import fused_cl
+    from affb200.fused import fused_cluster_attention
+    B, n, H, c, M, P = 2, 400, 2, 32, 48, 111 * 111
+    g = torch.Generator().manual_seed(5)
+    nbhd = torch.randint(0, n, (B, n, M), generator=g).cuda()
+    pe_idx = torch.randint(0, P, (B, n, M), generator=g).cuda()
+    pos = torch.randint(0, 56, (B, n, 2), generator=g).float().cuda()
+    fused_cl.hint_geometry(nbhd, pos, 55, 111)
+    assert fused_cl.cl_plan(nbhd, None, pe_idx, P) is None
+    # the real structure, but pe_idx shifted by one table row / positions off the integer grid / no hint
+    nb2, mask2, pe2, rpw, p_s = _setup(56, 56, 627, 2, 8, 48, 224, hint=False)
+    assert fused_cl.cl_plan(nb2, mask2, pe2, P) is None
+    pe_bad = pe2 + 111
+    fused_cl.hint_geometry(nb2, p_s, rpw, 111)
+    assert fused_cl.cl_plan(nb2, mask2, pe_bad, P) is None
+    fused_cl.hint_geometry(nb2, p_s + 0.5, rpw, 111)
+    assert fused_cl.cl_plan(nb2, mask2, pe2, P) is None
+    fused_cl.hint_geometry(nb2, p_s, rpw, 111)
+    assert fused_cl.cl_plan(nb2, mask2, pe2, P) is not None
+    q, kv, table, bk, bv, go = _operands(2, 627, 4, 32, P, torch.bfloat16, 9)
+    out = fused_cluster_attention(q, kv, 4, 32 ** -0.5, nb2, pe_bad, mask2, table, bk, bv)   # declined -> row-union kernels
+    assert out is not None and cl_calls == []
+    out.backward(go)
+    ref = _reference(q, kv, 4, 32 ** -0.5, nb2, pe_bad, mask2, table, bk.bfloat16(), bv.bfloat16(), go)
+    for a, r in zip([out, q.grad, kv.grad, table.grad], ref):
+        assert rel_err(a, r) < 1e-2
+
+
+def test_plan_contents_against_a_direct_restatement():
+    """Union blocks, membership words, packed positions, per-block query lists and the sorted bias indices of the plan,
+    restated with torch on the host from nbhd_idx / pe_idx."""
+    from affb200 import fused_cl
+    nbhd, mask, pe_idx, rpw, p_s = _setup(56, 56, 627, 2, 8, 48, 224)
+    B, n, M = nbhd.shape
+    pl = fused_cl.cl_plan(nbhd, mask, pe_idx, (2 * rpw + 1) ** 2)
+    assert pl is not None
+    blk, hdr, ucl, qmask, pos16, stats, kb_cnt, kb_tok, q_pe = [None if t is None else t.cpu() for t in pl.keep]
+    nb, mk, pe, pos = nbhd.cpu(), mask.cpu(), pe_idx.cpu(), p_s.cpu()
+    blocks = nb[:, :, ::8] // 8                               # [B, n, 6]: every group of 8 slots is one aligned block
+    assert torch.equal(blk.long() & 0xffff, blocks)
+    tiles = (n + 63) // 64
+    nblk = (n + 7) // 8
+    for b in range(B):
+        refs = [[] for _ in range(nblk)]
+        for t in range(tiles):
+            toks = range(t * 64, min(n, t * 64 + 64))
+            union = sorted(set(blocks[b, t * 64:t * 64 + 64].reshape(-1).tolist()))
+            assert (hdr[b, t].item() & 0x0fffffff) == len(union) and hdr[b, t].item() >> 28 == 0
+            assert (ucl[b, t, :len(union)].long() & 0xffff).tolist() == union
+            for i in toks:
+                want = 0
+                for q in blocks[b, i].tolist():
+                    want |= 1 << union.index(q)
+                assert (qmask[b, i].item() & (2 ** 64 - 1)) == want
+                assert (pos16[b, i].item() & 0xffffffff) == (int(pos[b, i, 1]) << 16 | int(pos[b, i, 0]))
+        for i in range(n):
+            for q in blocks[b, i].tolist():
+                refs[q].append(i)
+        for k in range(nblk):
+            assert kb_cnt[b, k].item() == len(refs[k])
+            assert kb_tok[b, k, :len(refs[k])].tolist() == refs[k]          # ascending: the dK / dV summation order
+        # bias indices regrouped by ascending block id, padded slots flagged
+        order = blocks[b].argsort(dim=1, stable=True)                          # [n, 6]
+        pe_s = pe[b].reshape(n, 6, 8).gather(1, order[:, :, None].expand(-1, -1, 8)).reshape(n, M)
+        mk_s = mk[b].reshape(n, 6, 8).gather(1, order[:, :, None].expand(-1, -1, 8)).reshape(n, M)
+        want = (pe_s & 0x7fff) | ((mk_s == 0).long() << 15)
+        assert torch.equal(q_pe[b].long() & 0xffff, want)
+    assert stats[4].item() == max(hdr.reshape(-1).tolist()) & 0x0fffffff
+
+
+@pytest.mark.parametrize("autocast", [False, True])
+def test_block_structured_pos_embed_form(autocast, cl_calls):
+    """pos_embed=(pre_table, W, b), the form ClusterAttention passes: identical output / d_q / d_kv to the table form, and
+    dW / db equal to the chain rule through the table form's own [P, H] gradient."""
+    from affb200.fused import fused_cluster_attention
+    from affb200.aff_transformer import build_pe_lookup
+    nbhd, mask, pe_idx, rpw, _ = _setup(56, 56, 627, 3, 8, 48, 224)
+    pre_table = build_pe_lookup(224)[2].cuda()
+    B, n, H, c, dt = 3, 627, 4, 32, torch.bfloat16
+    g = torch.Generator().manual_seed(21)
+    q0 = torch.randn(B, n, H * c, generator=g).to(dt).cuda()
+    kv0 = torch.randn(B, n, 2 * H * c, generator=g).to(dt).cuda()
+    W = (0.2 * torch.randn(H, 5, generator=g)).cuda().requires_grad_(True)
+    b = (0.2 * torch.randn(H, generator=g)).cuda().requires_grad_(True)
+    bk, bv = torch.randn(H * c, generator=g).cuda(), torch.randn(H * c, generator=g).cuda()
+    go = torch.randn(B, n, H * c, generator=g).to(dt).cuda()
+
+    def run(form):
+        q, kv = q0.clone().requires_grad_(True), kv0.clone().requires_grad_(True)
+        with torch.autocast("cuda", dtype=dt, enabled=autocast):
+            if form == "linear":
+                out = fused_cluster_attention(q, kv, H, c ** -0.5, nbhd, pe_idx, mask, None, bk, bv, pos_embed=(pre_table, W, b))
+                tab = None
+            else:
+                tab = torch.nn.functional.linear(pre_table, W, b).detach().float().requires_grad_(True)
+                out = fused_cluster_attention(q, kv, H, c ** -0.5, nbhd, pe_idx, mask, tab, bk, bv)
+        out.backward(go)
+        if tab is not None:
+            return out.detach(), q.grad, kv.grad, None, None, tab.grad
+        res = (out.detach(), q.grad, kv.grad, W.grad.clone(), b.grad.clone(), None)
+        W.grad = b.grad = None
+        return res
+    lin, tab = run("linear"), run("table")
+    assert cl_calls == [1, 1]
+    assert torch.equal(lin[0], tab[0]) and torch.equal(lin[1], tab[1]) and torch.equal(lin[2], tab[2])
+    feat = (pre_table.to(dt) if autocast else pre_table).double()
+    dT = tab[5].double()
+    assert rel_err(lin[3], dT.t() @ feat) < 1e-4
+    assert rel_err(lin[4], dT.sum(0)) < 1e-4
