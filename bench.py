@@ -289,6 +289,8 @@ def main():
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu_base}
         if graph_fallbacks is not None:
             line["config"]["graph_fallbacks"] = graph_fallbacks
+        if isinstance(roof, dict) and roof.get("fused_stages") is not None:
+            line["config"]["fused_stages"] = roof.pop("fused_stages")   # which attention kernels each stage ran
         print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()

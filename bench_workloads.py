@@ -167,6 +167,56 @@ def get(name):
     return WORKLOADS[name or DEFAULT]()
 
 
+def merge_rows(merges, infer):
+    """CUDA-event times of the merge operators at the model's three merges with the model's own neighbourhoods: the
+    fused merge (affb200_merge_fwd/_bwd, what the step runs) and the drop-in WF operator on materialised weights
+    (affb200_wf_fwd/_bwd).  Algorithmic bytes are SURVEY.md 8(d)'s WF figures (weights at the activation type, idx at
+    8 B); the fused merge reads the same feature rows and writes the same output without the weights tensor, so the
+    same byte count is used for both (it over-credits the fused form by the weights it never touches)."""
+    from affb200 import _native as N
+    from affb200.plan import get_plan
+    rows = []
+    for st, (table, pe_idx, lp, mask, feat, member) in enumerate(merges):
+        B, Nq, M = member.shape
+        Nk, C = feat.shape[1], feat.shape[2]
+        dev = feat.device
+        s = feat.element_size()
+        featc = feat.detach().contiguous()
+        lpc = lp.detach().reshape(B, Nk).contiguous()
+        tab = table.detach().float().contiguous()
+        pe_c, nb_c = pe_idx.contiguous(), member.contiguous()
+        mk_c = None if mask is None else mask.contiguous()
+        out = torch.empty((B, Nq, 4 * C), dtype=torch.float32, device=dev)
+        d_out = torch.randn_like(out)
+        off, ent = get_plan(member).csr(nb_c, Nk)
+        d_wt = torch.empty((B, Nq, M, 4), dtype=torch.float32, device=dev)
+        d_lp = torch.empty((B, Nk), dtype=torch.float32, device=dev)
+        d_feat = torch.empty_like(featc)
+        sp, de, le = N.stream_ptr(dev), N.dtype_enum(featc), N.DTYPE_ENUM[lpc.dtype]
+        P = N.p
+        fwd_b = s * (B * Nq * M * 4 + B * Nk * C + B * Nq * 4 * C) + 8 * B * Nq * M
+        bwd_b = s * (B * Nq * 4 * C + 2 * B * Nq * M * 4 + 2 * B * Nk * C) + 8 * B * Nq * M
+        w = (tab[pe_c] * lpc.float().gather(1, nb_c.reshape(B, -1)).reshape(B, Nq, M, 1)).to(featc.dtype).contiguous()
+        o_wf, dw, go = torch.empty((B, Nq, 4, C), dtype=featc.dtype, device=dev), torch.empty_like(w), None
+        go = torch.randn_like(o_wf)
+        pl = get_plan(member)
+        pb = pl.struct(member, Nk, False, True)
+        A = (B, Nq, Nk, M, 4, C, de, sp)
+        ops = [("merge_fwd", lambda: N.LIB.affb200_merge_fwd(P(tab), P(pe_c), P(nb_c), P(mk_c), P(lpc), P(featc), P(out),
+                                                             B, Nq, Nk, M, C, le, de, sp), fwd_b),
+               ("wf_fwd", lambda: N.LIB.affb200_wf_fwd(P(w), P(featc), P(nb_c), None, P(o_wf), *A), fwd_b)]
+        if not infer:
+            ops += [("merge_bwd", lambda: N.LIB.affb200_merge_bwd(P(d_out), P(tab), P(pe_c), P(nb_c), P(mk_c), P(lpc),
+                                                                  P(featc), P(off), P(ent), P(d_wt), P(d_lp), P(d_feat),
+                                                                  B, Nq, Nk, M, C, le, de, sp), bwd_b),
+                    ("wf_bwd", lambda: N.LIB.affb200_wf_bwd(P(go), P(w), P(featc), P(nb_c), pb, P(dw), P(d_feat), *A), bwd_b)]
+        for name, fn, nbytes in ops:
+            ms = _time_op(fn)
+            rows.append({"kernel": "%s@merge%d" % (name, st + 1), "ms": ms, "calls_per_step": 1 if name.startswith("merge") else 0,
+                         "bytes": nbytes, "GBps": nbytes / ms / 1e6})
+    return rows
+
+
 class AffTrain:
     """The workload BASELINE.json's metric is quoted on: AFF-Tiny-1/5 224x224 forward + backward (+ AdamW step) in
     bf16 autocast, random-init weights, synthetic images, per-GPU batch 256 (configs/aff_tiny_1_5th.yaml:17),
@@ -272,13 +322,30 @@ class _AffRun:
         followed by the unfused CLUSTEN operators for reference.  Algorithmic bytes of the fused op = its API-visible
         operands once: fwd q + kv + out at s bytes, nbhd_idx + pe_idx (+ mask) at 8 B; bwd q, kv, out, d_out read and
         d_q, d_kv written, plus the same index tensors."""
-        cap = []
+        cap, merges = [], []
         hooks = [layer.blocks[0].register_forward_pre_hook(lambda m, a: cap.append((a[1], a[2], a[3], a[5])))
                  for layer in self.model.layers[:3]]
+        real_merge = getattr(self.ops, "merge_wf", None)
+        if real_merge is not None:     # operands of the three merges (ClusterMerging: aff_transformer.py:343-361)
+            def spy(table, pe_idx, lp, mask, feat, member):
+                merges.append((table, pe_idx, lp, mask, feat, member))
+                return real_merge(table, pe_idx, lp, mask, feat, member)
+            self.ops.merge_wf = spy
+        from affb200 import fused as _fused
+        _fused.trace = []
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
             self.model(torch.randn(self.B, 3, self.wl.img, self.wl.img, device=self.device))
+        calls, _fused.trace = _fused.trace, None
+        if real_merge is not None:
+            self.ops.merge_wf = real_merge
         for h in hooks:
             h.remove()
+        # which kernels each stage's blocks ran (stages in forward order; one entry per distinct token count)
+        stages = []
+        for n, H, fam in calls:
+            if not stages or stages[-1]["tokens"] != n:
+                stages.append({"tokens": n, "heads": H, "blocks": 0, "kernels": fam or "unfused operators"})
+            stages[-1]["blocks"] += 1
         rows = []
         if self.ops.fused_attention is not None:
             from affb200 import fused
@@ -301,24 +368,28 @@ class _AffRun:
                     rows.append({"kernel": "%s@stage%d" % (nm, st + 1), "ms": ms, "calls_per_step": layer.depth,
                                  "bytes": nbytes, "GBps": nbytes / ms / 1e6})
                 del q, kv, calls
+        rows += merge_rows(merges, self.infer)
         top = max(rows, key=lambda r: r["ms"] * r["calls_per_step"]) if rows else None
         unfused = clusten_roofline(self.B, self.device, torch.bfloat16, [c[0] for c in cap], peak, peak_src)
         if top is None:
             return unfused
         fmt = lambda r: {"kernel": r["kernel"], "ms": round(r["ms"], 4), "GBps": round(r["GBps"], 1),
                          "frac": round(r["GBps"] / peak, 3), "calls_per_step": r["calls_per_step"]}
-        # measured DRAM bytes of the same launch group from the committed ncu pass (profiles/r01_ncu_traffic.json)
-        traffic = None
+        # measured DRAM bytes (ncu dram__bytes_read + write) of the same launch group: from the capture of THIS build's
+        # kernels committed under profiles/ (the file names the git commit it was taken at); null when that file does
+        # not list the group — never a number from another build
+        traffic, traffic_src = None, None
         try:
             import json
-            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_ncu_traffic.json")))
+            tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_ncu_traffic.json")))
             traffic = tj["per_launch_group"].get(top["kernel"], {}).get("dram_bytes")
+            traffic_src = "profiles/r02_ncu_traffic.json @ %s" % tj.get("commit")
         except Exception:
             traffic = None
         return {"bound": "hbm", "kernel": top["kernel"], "achieved": top["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": top["GBps"] / peak, "traffic": traffic, "peak_source": peak_src,
+                "frac": top["GBps"] / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": top["bytes"], "avg_launch_ms": top["ms"],
-                "all": [fmt(r) for r in rows], "unfused_clusten_ops": unfused["all"]}
+                "all": [fmt(r) for r in rows], "unfused_clusten_ops": unfused["all"], "fused_stages": stages}
 
 
 class AffTinyTrain(AffTrain):

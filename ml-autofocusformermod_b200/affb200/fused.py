@@ -328,6 +328,14 @@ class FusedClusterAttentionCl(Function):
 _ctypes_sigs_done = False
 
 
+trace = None   # set to a list to record (tokens, heads, kernel family | None) of every call (bench: config.fused_stages)
+
+
+def _note(n, H, family):
+    if trace is not None:
+        trace.append((int(n), int(H), family))
+
+
 def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k,
                             blank_v, pos_embed=None):
     """Returns out [B, N, H*c], or None when this case must take the unfused operators.
@@ -354,29 +362,38 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
     else:
         P = pe_table.shape[0]
     if c not in (16, 32) or P > 32768 or nbhd_idx.shape[2] > N.PLAN_MAX_M:
+        _note(n, num_heads, None)
         return None
     plan = get_plan(nbhd_idx)
-    if not _use_img(n, nbhd_idx.shape[2]) and num_heads % 2 == 0 and num_heads * c <= 512:
+    cl_first = os.environ.get("AFFB200_CL_FIRST", "0") != "0"   # block-structured kernels also for small token sets
+    if (cl_first or not _use_img(n, nbhd_idx.shape[2])) and num_heads % 2 == 0 and num_heads * c <= 512:
         from . import fused_cl
         clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, P)
         if clp is not None and (pe_w is None or (n * nbhd_idx.shape[2]) % 8 == 0):
+            _note(n, num_heads, "block-structured")
             return FusedClusterAttentionCl.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx,
                                                  pe_feat, clp, (num_heads, scale))
     if _use_img(n, nbhd_idx.shape[2]):
         q_pe = _packed_pe(plan, pe_idx, cluster_mask)
         if q_pe is None:
+            _note(n, num_heads, None)
             return None
         col, dupf = _img_prep(plan, nbhd_idx, q_pe)
+        _note(n, num_heads, "resident-key")
         return FusedClusterAttentionImg.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, q_pe, col,
                                               dupf, pe_feat, (num_heads, scale))
     if plan.qplan(nbhd_idx, n) is None or plan.kplan(nbhd_idx, n) is None:
+        _note(n, num_heads, None)
         return None
     umax = plan.stats["q"]["umax"]
     if umax > N.PLAN_UMAX - 1:
+        _note(n, num_heads, None)
         return None
     q_pe = _packed_pe(plan, pe_idx, cluster_mask)
     if q_pe is None:
+        _note(n, num_heads, None)
         return None
+    _note(n, num_heads, "row-union")
     return FusedClusterAttention.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, q_pe, pe_feat,
                                        (num_heads, scale, umax))
 
@@ -407,6 +424,12 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
     M = nbhd_idx.shape[2]
     dev = q_lin.device
     plan = get_plan(nbhd_idx)
+    cl_first = os.environ.get("AFFB200_CL_FIRST", "0") != "0"
+    if (cl_first or not _use_img(n, M)) and H % 2 == 0 and H * c <= 512 and c in (16, 32):
+        from . import fused_cl
+        clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, pe_table.shape[0])
+        if clp is not None:
+            return _raw_calls_cl(clp, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, blank_v, pre_table)
     if _use_img(n, M):
         return _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v,
                               pre_table)
@@ -447,6 +470,51 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
             pe_grad()
 
     fwd._keep = keep
+    return fwd, bwd
+
+
+def _raw_calls_cl(clp, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, blank_v, pre_table=None):
+    """(fwd, bwd) closures of the block-structured kernels on preallocated buffers; bwd = the two backward kernels and
+    the bias-generator gradient from dS (what the model's backward launches, minus the column sums of the blank-token
+    partials).  fwd.family names the kernels."""
+    from .plan import guard_tensor
+    B, n, hc = q_lin.shape
+    c = hc // H
+    M = nbhd_idx.shape[2]
+    dev = q_lin.device
+    table = pe_table.detach().float().contiguous()
+    bk, bv = blank_k.detach().float().contiguous(), blank_v.detach().float().contiguous()
+    out, dq, dkv, dout = torch.empty_like(q_lin), torch.empty_like(q_lin), torch.empty_like(kv_lin), torch.randn_like(q_lin)
+    lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+    delta = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+    ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+    grid = N.LIB.affb200_fused_cl_bwd_grid(B, H, n)
+    blank_part = torch.empty((grid * 8, H, 2, c), dtype=torch.float32, device=dev)
+    d_table = torch.empty((table.shape[0], H), dtype=torch.float32, device=dev)
+    guard = guard_tensor(dev)
+    de, sp = N.dtype_enum(q_lin), N.stream_ptr(dev)
+    keep = [clp, table, bk, bv, out, dq, dkv, dout, lse, delta, ds, blank_part, d_table]
+    pe_grad = _raw_pe_grad(pre_table, ds, clp.q_pe, B, H, n * M, keep)
+    V = lambda t, off=0, kv=False: _view(t, n * (2 * hc if kv else hc), 2 * hc if kv else hc, 2 * c if kv else c, off)
+
+    def fwd():
+        N.check(N.LIB.affb200_fused_cl_fwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), N.p(table), N.p(bk),
+                                           N.p(bv), clp.byref(), N.p(lse), N.p(guard), B, H, n, c, clp.w, clp.tw,
+                                           float(scale), de, sp), "fused_cl_fwd")
+
+    def bwd():
+        N.check(N.LIB.affb200_fused_cl_bwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), V(dout), V(dq),
+                                           V(dkv, 0, True), V(dkv, c, True), N.p(table), N.p(bk), N.p(bv), clp.byref(),
+                                           N.p(lse), N.p(delta), N.p(ds), N.p(blank_part), N.p(guard), B, H, n, M, c,
+                                           clp.w, clp.tw, float(scale), de, sp), "fused_cl_bwd")
+        if pe_grad is not None:
+            pe_grad()
+        else:
+            N.check(N.LIB.affb200_table_grad_u16(N.p(ds), N.p(clp.q_pe), B, H, n * M, table.shape[0], N.p(d_table), de, sp),
+                    "table_grad_u16")
+
+    fwd._keep = keep
+    fwd.family = "block-structured"
     return fwd, bwd
 
 
