@@ -364,6 +364,8 @@ class _AffRun:
                 nidx = 8 * B * n * M * (3 if mask is not None else 2)
                 for nm, fn, nbytes in (("fused_attn_fwd", calls[0], 2 * 4 * B * n * hc + nidx),
                                        ("fused_attn_bwd", calls[1], 2 * 8 * B * n * hc + nidx)):
+                    if fn is None or (self.infer and nm.endswith("bwd")):
+                        continue
                     ms = _time_op(fn)
                     rows.append({"kernel": "%s@stage%d" % (nm, st + 1), "ms": ms, "calls_per_step": layer.depth,
                                  "bytes": nbytes, "GBps": nbytes / ms / 1e6})

@@ -327,7 +327,11 @@ class BasicLayer(nn.Module):
         nbhd, mask, pe_idx, _ = ops.build_nbhd(pos, mean, m, self.nbhd_size, rel_pos_width)
         if getattr(ops, 'hint_geometry', None) is not None:   # where nbhd / pe_idx came from: block-structured kernels
             ops.hint_geometry(nbhd, pos, rel_pos_width, 2 * rel_pos_width + 1)
-        if pre_table.shape[0] > COMPACT_ROWS_ABOVE and not (pe_idx.is_cuda and torch.cuda.is_current_stream_capturing()):
+        if pre_table.shape[0] > COMPACT_ROWS_ABOVE and not (pe_idx.is_cuda and torch.cuda.is_current_stream_capturing()) \
+                and not (not torch.is_grad_enabled() and getattr(ops, 'hint_geometry', None) is not None
+                         and pre_table.shape[0] == (2 * rel_pos_width + 1) ** 2 and pre_table.shape[0] <= 65536):
+            # (inference keeps the full table of the 384-pixel configs: the block-structured forward takes the bias
+            # from position differences and has no row limit)
             pe_idx, pre_table = compact_table(pe_idx, pre_table)
         return pos, reorder, nbhd, mask, pe_idx, pre_table
 

@@ -361,7 +361,7 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
             pe_table = None
     else:
         P = pe_table.shape[0]
-    if c not in (16, 32) or P > 32768 or nbhd_idx.shape[2] > N.PLAN_MAX_M:
+    if c not in (16, 32) or nbhd_idx.shape[2] > N.PLAN_MAX_M:
         _note(n, num_heads, None)
         return None
     plan = get_plan(nbhd_idx)
@@ -369,10 +369,15 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
     if (cl_first or not _use_img(n, nbhd_idx.shape[2])) and num_heads % 2 == 0 and num_heads * c <= 512:
         from . import fused_cl
         clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, P)
-        if clp is not None and (pe_w is None or (n * nbhd_idx.shape[2]) % 8 == 0):
+        needs_grad = torch.is_grad_enabled() and any(
+            t is not None and t.requires_grad for t in (q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v))
+        if clp is not None and (pe_w is None or (n * nbhd_idx.shape[2]) % 8 == 0) and (clp.q_pe is not None or not needs_grad):
             _note(n, num_heads, "block-structured")
             return FusedClusterAttentionCl.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx,
                                                  pe_feat, clp, (num_heads, scale))
+    if P > 32768:     # the row-union and resident-key kernels pack the bias index into 15 bits
+        _note(n, num_heads, None)
+        return None
     if _use_img(n, nbhd_idx.shape[2]):
         q_pe = _packed_pe(plan, pe_idx, cluster_mask)
         if q_pe is None:
@@ -515,7 +520,7 @@ def _raw_calls_cl(clp, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, bla
 
     fwd._keep = keep
     fwd.family = "block-structured"
-    return fwd, bwd
+    return fwd, (bwd if clp.q_pe is not None else None)   # tables above 32 768 rows: forward only
 
 
 def _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v, pre_table=None):

@@ -143,7 +143,8 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P):
 
 
 def cl_plan(nbhd_idx, mask, pe_idx, P):
-    """ClPlan of this index set, or None (no geometry hint, structure absent, disabled).  P = rows of the bias table."""
+    """ClPlan of this index set, or None (no geometry hint, structure absent, disabled).  P = rows of the bias table;
+    above 32 768 rows the packed bias indices of the backward do not exist (plan.q_pe is None): forward only."""
     if not enabled():
         return None
     p = _plan.get_plan(nbhd_idx)
@@ -156,8 +157,7 @@ def cl_plan(nbhd_idx, mask, pe_idx, P):
         return hit[1]
     pos, w, tw = hint
     B, n, M = nbhd_idx.shape
-    if M % 8 != 0 or M > 8 * CL_UMAX or pos.shape[0] != B or pos.shape[1] != n or tw != 2 * w + 1 or P != tw * tw \
-            or P > 32768:
+    if M % 8 != 0 or M > 8 * CL_UMAX or pos.shape[0] != B or pos.shape[1] != n or tw != 2 * w + 1 or P != tw * tw:
         res = None
     else:
         res = _build(nbhd_idx, mask, pe_idx, pos, w, tw, P)

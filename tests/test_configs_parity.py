@@ -17,7 +17,9 @@ def _capture(model):
     hooks = []
     for si, layer in enumerate(model.layers):
         def hook(m, args, si=si):
-            cap["stage%d" % si] = (args[1], args[2], args[3])   # member_idx, cluster_mask, pe_idx of the first block
+            # member_idx, cluster_mask, pe_idx of the first block, and the table rows pe_idx indexes (the 384-pixel
+            # configs cut the 191 x 191 table to the referenced rows, except where the block-structured kernels take it whole)
+            cap["stage%d" % si] = (args[1], args[2], args[3], args[5])
         if len(layer.blocks):
             hooks.append(layer.blocks[0].register_forward_pre_hook(hook))
     return cap, hooks
@@ -52,9 +54,11 @@ def test_reference_config_inference_matches_oracle_ops(name, batch):
         h.remove()
     assert set(cap_g) == set(cap_c)
     for k in cap_c:
-        for a, b, what in zip(cap_g[k], cap_c[k], ("member_idx", "cluster_mask", "pe_idx")):
+        for a, b, what in zip(cap_g[k][:3], cap_c[k][:3], ("member_idx", "cluster_mask", "pe_idx")):
             if b is None:
                 assert a is None, (k, what)
+            elif what == "pe_idx":   # the same relative-position rows, whichever table form each side indexes
+                assert torch.equal(cap_g[k][3][a].cpu(), cap_c[k][3][b]), (k, what)
             else:
                 assert torch.equal(a.cpu(), b), (k, what)
     assert torch.isfinite(y_gpu).all()
