@@ -167,6 +167,22 @@ def get(name):
     return WORKLOADS[name or DEFAULT]()
 
 
+def _host_glue():
+    """The module tree (affb200/aff_transformer.py: written against an operator table, no top-level dependency on the
+    CUDA library) loaded by path, so that the CPU reference arm never maps libaffb200.so — importing the `affb200`
+    package would dlopen it."""
+    import importlib.util
+    name = "affb200_host_glue"
+    if name in sys.modules:
+        return sys.modules[name]
+    path = os.path.join(ROOT, "ml-autofocusformermod_b200", "affb200", "aff_transformer.py")
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def merge_rows(merges, infer):
     """CUDA-event times of the merge operators at the model's three merges with the model's own neighbourhoods: the
     fused merge (affb200_merge_fwd/_bwd, what the step runs) and the drop-in WF operator on materialised weights
@@ -241,7 +257,7 @@ class AffTrain:
         return _AffRun(self, B, device, world)
 
     def cpu_reference(self, sample_b):
-        from affb200.aff_transformer import build_aff
+        build_aff = _host_glue().build_aff
         from oracle.aff_ops_ref import OracleOps  # the checker, timed here as the CPU baseline only
         torch.manual_seed(0)
         model = build_aff(self.model_name, ops=OracleOps()).train()
@@ -415,7 +431,7 @@ class AffInfer(AffTrain):
         return c
 
     def cpu_reference(self, sample_b):
-        from affb200.aff_transformer import build_aff
+        build_aff = _host_glue().build_aff
         from oracle.aff_ops_ref import OracleOps  # the checker, timed here as the CPU baseline only
         torch.manual_seed(0)
         model = build_aff(self.model_name, ops=OracleOps()).eval()

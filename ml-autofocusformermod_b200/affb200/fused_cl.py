@@ -95,6 +95,8 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P):
                 _plan._observed[("cl",) + skey] = dict(ok=False)
                 return None
         kbcap = obs["kbcap"] if (obs and obs.get("ok")) else 96
+        if static:
+            kbcap += KBCAP_STEP     # room for a block that more tokens reference than in the recorded passes
         while True:
             kb_cnt = torch.empty((B, nblk), dtype=torch.int32, device=dev)
             kb_tok = torch.empty((B, nblk, kbcap), dtype=torch.int32, device=dev)

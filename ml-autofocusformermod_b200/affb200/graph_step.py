@@ -29,9 +29,17 @@ from . import plan as _plan
 
 
 class GraphedTrainStep:
+    """See the module docstring.  The caller's optimizer stays the place where hyper-parameters live: its param groups'
+    `lr` (and any other hyper-parameter) are read before every step, so an LR scheduler attached to it works as in the
+    reference's loop (main.py:262-267: `lr_scheduler.step_update`); `clip_grad_norm` reproduces `clip_grad` between
+    backward and step (utils.py:186); `optimizer_state_dict()` / `load_optimizer_state_dict()` checkpoint the state of
+    the optimizer that actually steps (utils.py:55-77 saves `optimizer.state_dict()`)."""
+
     def __init__(self, model, optimizer, loss_fn, example_x, example_y, world=1, autocast_dtype=torch.bfloat16,
-                 warmup=3, flat_optimizer=True):
+                 warmup=3, flat_optimizer=True, clip_grad_norm=None):
         self.model, self.opt, self.loss_fn, self.world = model, optimizer, loss_fn, world
+        self.user_opt = optimizer
+        self.clip_grad_norm = clip_grad_norm
         self.autocast_dtype = autocast_dtype
         dev = example_x.device
         self.device = dev
@@ -68,6 +76,18 @@ class GraphedTrainStep:
             p._affb200_sink = True
         if flat_optimizer:
             self.opt = self._flat_optimizer(optimizer, group_counts, offs, n) or optimizer
+        # learning rates as device tensors: the captured optimizer step reads them, __call__ refreshes them from the
+        # caller's optimizer (a Python float would be baked into the graph)
+        self._lr_seen = []
+        for g in self.opt.param_groups:
+            self._lr_seen.append(float(g["lr"]))
+            if type(self.opt) in (torch.optim.Adam, torch.optim.AdamW) and g.get("capturable", False):
+                g["lr"] = torch.tensor(float(g["lr"]), dtype=torch.float32, device=dev)
+        self._hp_seen = self._hyper()
+        # buffers the training forward updates in place (BatchNorm running statistics): saved at the start of every
+        # replay so that a step redone eagerly does not apply the update twice
+        self._bufs = [b for b in model.buffers()]
+        self._buf_snap = [torch.empty_like(b) for b in self._bufs]
         self.sync_params()
         self.x = example_x.clone()
         self.y = example_y.clone()
@@ -80,6 +100,7 @@ class GraphedTrainStep:
             for _ in range(max(1, warmup)):
                 self._fwd_bwd()
                 self._reduce()
+                self._clip()
                 self.opt.step()
                 self.sync_params()
         torch.cuda.current_stream(dev).wait_stream(side)
@@ -121,11 +142,12 @@ class GraphedTrainStep:
         l0 = N.LIB.affb200_launch_count()
         self.g_fb = torch.cuda.CUDAGraph()
         with _plan.static_plans(), torch.cuda.graph(self.g_fb):
-            self.loss = self._fwd_bwd()
+            self.loss = self._fwd_bwd(snapshot=True)
         # libaffb200 kernels recorded in the graph = launched by every replay
         self.kernels_per_step = int(N.LIB.affb200_launch_count() - l0)
         self.g_opt = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.g_opt, pool=self.g_fb.pool()):
+            self._clip()
             self.opt.step()
             self.sync_params()
 
@@ -134,7 +156,72 @@ class GraphedTrainStep:
         load_state_dict; the optimizer graph does it after every step)."""
         self.flat_lp.copy_(self.flat_param)
 
-    def _fwd_bwd(self):
+    def _groups(self):
+        """(caller's group, stepping group) pairs; the flat optimizer keeps the caller's non-empty groups in order"""
+        ug = [g for g in self.user_opt.param_groups if any(p.requires_grad for p in g["params"])] \
+            if self.opt is not self.user_opt else list(self.user_opt.param_groups)
+        return list(zip(ug, self.opt.param_groups)) if len(ug) == len(self.opt.param_groups) else []
+
+    def _hyper(self):
+        return [tuple(sorted((k, v) for k, v in g.items() if k not in ("params", "lr") and isinstance(v, (int, float, bool, tuple))))
+                for g, _ in self._groups()]
+
+    def _sync_hyper(self):
+        """Bring the stepping optimizer's hyper-parameters up to date with the caller's before a step.  Learning rates
+        are device tensors (one scalar fill when a value changed); anything else that changed (weight decay, betas ...)
+        is a constant of the captured step, so the optimizer graph is captured again."""
+        pairs = self._groups()
+        for i, (ug, sg) in enumerate(pairs):
+            lr = float(ug["lr"])
+            if lr != self._lr_seen[i]:
+                self._lr_seen[i] = lr
+                if torch.is_tensor(sg["lr"]):
+                    sg["lr"].fill_(lr)
+                else:
+                    sg["lr"] = lr
+                    self._hp_seen = None
+        hp = self._hyper()
+        if hp != self._hp_seen:
+            for ug, sg in pairs:
+                if sg is not ug:
+                    for k, v in ug.items():
+                        if k not in ("params", "lr"):
+                            sg[k] = v
+            self._hp_seen = hp
+            torch.cuda.synchronize(self.device)
+            self.g_opt = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g_opt, pool=self.g_fb.pool()):
+                self._clip()
+                self.opt.step()
+                self.sync_params()
+
+    def optimizer_state_dict(self):
+        """state_dict (a copy) of the optimizer that steps: one flat tensor per param group when flat_optimizer took
+        effect, laid out as the model's parameters in optimizer-group order, each padded to 8 elements."""
+        import copy
+        return copy.deepcopy(self.opt.state_dict())
+
+    def load_optimizer_state_dict(self, sd):
+        """Restore a state saved by optimizer_state_dict(): the values are copied INTO the existing state tensors (the
+        captured optimizer step holds their addresses).  Hyper-parameters keep coming from the caller's optimizer."""
+        params = [p for g in self.opt.param_groups for p in g["params"]]
+        for idx, st in sd["state"].items():
+            cur = self.opt.state[params[int(idx)]]
+            for k, v in st.items():
+                if torch.is_tensor(v) and torch.is_tensor(cur.get(k)):
+                    cur[k].copy_(v)
+                else:
+                    cur[k] = v
+
+    def _clip(self):
+        if self.clip_grad_norm is not None:      # clip_grad_norm_ on the flat gradient: no host read
+            norm = torch.linalg.vector_norm(self.flat_grad)
+            self.flat_grad.mul_(torch.clamp(self.clip_grad_norm / (norm + 1e-6), max=1.0))
+
+    def _fwd_bwd(self, snapshot=False):
+        if snapshot:
+            for b, sn in zip(self._bufs, self._buf_snap):
+                sn.copy_(b)
         self.flat_grad.zero_()
         with torch.autocast("cuda", dtype=self.autocast_dtype):
             out = self.model(self.x)
@@ -144,7 +231,11 @@ class GraphedTrainStep:
 
     def _reduce(self):
         if self.world > 1:
-            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.AVG)
+            if dist.get_backend() == "nccl":
+                dist.all_reduce(self.flat_grad, op=dist.ReduceOp.AVG)
+            else:   # gloo (tests on one device): no AVG
+                dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM)
+                self.flat_grad.div_(self.world)
 
     def __call__(self, x, y):
         self.x.copy_(x, non_blocking=True)
@@ -154,11 +245,15 @@ class GraphedTrainStep:
         # replay skipped tiles (zeros, see csrc): the gradients are discarded and the step is redone eagerly with exact
         # plans before the optimizer sees anything; the graphs are then re-captured with the larger sizes now on record.
         guard = _plan.guard_tensor(self.device)
+        self._sync_hyper()
         if int(guard.item()) != 0:
             guard.zero_()
             self.fallbacks += 1
+            for b, sn in zip(self._bufs, self._buf_snap):     # undo the failed replay's in-place buffer updates
+                b.copy_(sn)
             loss = self._fwd_bwd()
             self._reduce()
+            self._clip()
             self.opt.step()
             self.sync_params()
             if self.recaptures < self.max_recaptures:

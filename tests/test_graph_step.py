@@ -229,3 +229,57 @@ def test_flat_optimizer_performs_the_per_tensor_update():
     for x, y in zip(xs[1:], ys[1:]):
         l1, l2 = float(s1(x, y)), float(s2(x, y))
         assert abs(l1 - l2) < 2e-2 * abs(l2), (l1, l2)
+
+
+def test_caller_optimizer_hyperparameters_clip_and_state_dict():
+    """The caller's optimizer stays authoritative: a learning rate changed on it (what an LR scheduler does every
+    iteration, reference main.py:262-267) reaches the captured optimizer step; clip_grad_norm bounds the flat gradient
+    between the two graphs (utils.py:186); the stepping optimizer's state can be saved and restored (utils.py:55-77)."""
+    from affb200.graph_step import GraphedTrainStep
+    m1, m2 = _models()
+    xs, ys = _batches(4)
+    o1 = torch.optim.AdamW(m1.parameters(), lr=0.0, weight_decay=0.0, fused=True, capturable=True)
+    o2 = torch.optim.AdamW(m2.parameters(), lr=0.0, weight_decay=0.0, fused=True)
+    step = GraphedTrainStep(m1, o1, torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1, clip_grad_norm=0.05)
+    before = step.flat_param.clone()
+    step(xs[1], ys[1])
+    assert torch.equal(step.flat_param, before)                       # lr = 0: nothing moves
+    assert float(step.flat_grad.norm()) <= 0.05 * 1.001               # clipped in place before the step
+    for o in (o1, o2):
+        for g in o.param_groups:
+            g["lr"] = 1e-3                                            # "scheduler": the caller's optimizer only
+    sd = step.optimizer_state_dict()
+    n_steps = float(list(sd["state"].values())[0]["step"])
+    step(xs[2], ys[2])
+    _eager_step(m2, o2, xs[2], ys[2])                                  # (eager: unclipped, Adam normalises the scale)
+    moved = float((step.flat_param - before).abs().max())
+    assert 5e-4 < moved < 2e-3, moved                                 # one Adam step of size lr
+    assert float(list(step.optimizer_state_dict()["state"].values())[0]["step"]) == n_steps + 1
+    step.load_optimizer_state_dict(sd)                                # back to the saved moment estimates
+    assert float(list(step.optimizer_state_dict()["state"].values())[0]["step"]) == n_steps
+    step(xs[3], ys[3])
+    assert bool(torch.isfinite(step.flat_param).all())
+
+
+def test_redone_step_does_not_update_batchnorm_statistics_twice(monkeypatch):
+    """A replay whose speculation failed has already moved the BatchNorm running statistics; the eager redo must start
+    from the values before the replay (one momentum update per step, as an eager step makes)."""
+    from affb200 import fused_cl
+    from affb200.graph_step import GraphedTrainStep
+    m1, m2 = _models()
+    xs, ys = _batches(3)
+    o1 = torch.optim.AdamW(m1.parameters(), lr=0.0, weight_decay=0.0, fused=True, capturable=True)
+    o2 = torch.optim.AdamW(m2.parameters(), lr=0.0, weight_decay=0.0, fused=True)
+    real_obs = fused_cl.observed
+    monkeypatch.setattr(fused_cl, "observed",
+                        lambda skey: (lambda o: o if not (o and o.get("ok")) else dict(o, ucap=min(o["ucap"], 8)))(real_obs(skey)))
+    step = GraphedTrainStep(m1, o1, torch.nn.functional.cross_entropy, xs[0], ys[0], warmup=1)
+    step.max_recaptures = 0
+    _eager_step(m2, o2, xs[0], ys[0])          # the warm-up pass of the graphed model
+    for x, y in zip(xs[1:], ys[1:]):
+        step(x, y)
+        _eager_step(m2, o2, x, y)
+    assert step.fallbacks == 2
+    b1 = {k: v for k, v in m1.named_buffers()}
+    for k, v in m2.named_buffers():
+        assert torch.allclose(b1[k].float(), v.float(), rtol=2e-3, atol=1e-5), k
