@@ -211,3 +211,58 @@ def test_block_structured_pos_embed_form(autocast, cl_calls):
     dT = tab[5].double()
     assert rel_err(lin[3], dT.t() @ feat) < 1e-4
     assert rel_err(lin[4], dT.sum(0)) < 1e-4
+
+
+def test_kernels_write_only_their_outputs():
+    """compute-sanitizer is closed on this pool (profiles/r02_sanitizer_refused.log), so the write side of memcheck is
+    restated here: every output of the forward and backward entry points lives between guard bands of a sentinel
+    pattern inside one allocation; after the launches the bands are intact and every output element was written."""
+    import ctypes
+    from affb200 import _native as N
+    from affb200 import fused_cl
+    from affb200.fused import _view
+    from affb200.plan import guard_tensor
+    B, n, H, c, M = 3, 627, 4, 32, 48
+    nbhd, mask, pe_idx, rpw, _ = _setup(56, 56, n, B, 8, M, 224)
+    P = (2 * rpw + 1) ** 2
+    clp = fused_cl.cl_plan(nbhd, mask, pe_idx, P)
+    assert clp is not None
+    q, kv, table, bk, bv, go = [t.detach() for t in _operands(B, n, H, c, P, torch.bfloat16, 13)]
+    hc = H * c
+    grid = N.LIB.affb200_fused_cl_bwd_grid(B, H, n)
+    GUARD = 4096
+    shapes = {"out": ((B, n, hc), torch.bfloat16), "lse": ((B, H, n), torch.float32), "dq": ((B, n, hc), torch.bfloat16),
+              "dkv": ((B, n, 2 * hc), torch.bfloat16), "ds": ((B, H, n, M), torch.bfloat16),
+              "delta": ((B, H, n), torch.float32), "blank": ((grid * 8, H, 2, c), torch.float32)}
+    total = GUARD
+    offs = {}
+    for k, (shp, dt) in shapes.items():
+        nb = torch.empty(shp, dtype=dt).numel() * torch.empty((), dtype=dt).element_size()
+        offs[k] = (total, nb)
+        total += (nb + 255) // 256 * 256 + GUARD
+    arena = torch.full((total,), 0xA5, dtype=torch.uint8, device="cuda")
+    t = {k: arena[o:o + nb].view(shapes[k][1]).view(shapes[k][0]) for k, (o, nb) in offs.items()}
+    for k in ("lse", "delta", "blank"):
+        t[k].fill_(float("nan"))
+    dev = q.device
+    tab = table.float().contiguous()
+    V = lambda x, off=0, is_kv=False: _view(x, n * (2 * hc if is_kv else hc), 2 * hc if is_kv else hc, 2 * c if is_kv else c, off)
+    de, sp, guard = N.dtype_enum(q), N.stream_ptr(dev), guard_tensor(dev)
+    guard.zero_()
+    N.check(N.LIB.affb200_fused_cl_fwd(V(q), V(kv, 0, True), V(kv, c, True), V(t["out"]), N.p(tab), N.p(bk), N.p(bv),
+                                       clp.byref(), N.p(t["lse"]), N.p(guard), B, H, n, c, clp.w, clp.tw, c ** -0.5, de, sp), "fwd")
+    N.check(N.LIB.affb200_fused_cl_bwd(V(q), V(kv, 0, True), V(kv, c, True), V(t["out"]), V(go), V(t["dq"]),
+                                       V(t["dkv"], 0, True), V(t["dkv"], c, True), N.p(tab), N.p(bk), N.p(bv), clp.byref(),
+                                       N.p(t["lse"]), N.p(t["delta"]), N.p(t["ds"]), N.p(t["blank"]), N.p(guard), B, H, n, M, c,
+                                       clp.w, clp.tw, c ** -0.5, de, sp), "bwd")
+    torch.cuda.synchronize()
+    assert int(guard.item()) == 0
+    keep = torch.ones(total, dtype=torch.bool, device="cuda")
+    for k, (o, nb) in offs.items():
+        keep[o:o + nb] = False
+    assert bool((arena[keep] == 0xA5).all()), "a kernel wrote outside its outputs"
+    for k in shapes:
+        x = t[k].float()
+        assert bool(torch.isfinite(x).all()), k                                   # fp32 outputs: no NaN left
+        if shapes[k][1] == torch.bfloat16:                                          # 0xA5A5 as bf16 = -7.2e-16
+            assert float((t[k].view(torch.int16) == -23131).float().mean()) < 1e-3, k
