@@ -125,7 +125,7 @@ def run_reference(args, rank, world):
     wl = W.get(args.workload)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sample_b = args.ref_batch
+    sample_b = args.ref_batch or getattr(wl, "ref_batch", 4)
     ref = wl.cpu_reference(sample_b)
     for _ in range(max(1, min(args.warmup, 2))):
         ref()
@@ -155,7 +155,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=0, help="images per GPU (0 = the workload's default)")
     ap.add_argument("--workload", default="")
-    ap.add_argument("--ref-batch", type=int, default=4, help="images per CPU-reference step")
+    ap.add_argument("--ref-batch", type=int, default=0, help="images per CPU-reference step (0 = the workload's: 4 unless it says otherwise)")
     ap.add_argument("--ref-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -266,7 +266,8 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        ref = wl.cpu_reference(args.ref_batch)
+        ref_b = args.ref_batch or getattr(wl, "ref_batch", 4)
+        ref = wl.cpu_reference(ref_b)
         ref()
         t0 = time.perf_counter()
         n = 0
@@ -274,9 +275,9 @@ def main():
             ref()
             n += 1
         dt = time.perf_counter() - t0
-        cpu_base = {"value": args.ref_batch * n / dt, "unit": wl.unit, "cores": cores, "kind": "port",
+        cpu_base = {"value": ref_b * n / dt, "unit": wl.unit, "cores": cores, "kind": "port",
                     "sample": "%d images per step x %d steps of the same workload, fp32, %d torch threads" %
-                              (args.ref_batch, n, cores)}
+                              (ref_b, n, cores)}
 
     if rank == 0:
         line = {"metric": wl.metric, "value": value, "unit": wl.unit, "n_gpus": world, "steps": args.steps,

@@ -167,20 +167,22 @@ def get(name):
     return WORKLOADS[name or DEFAULT]()
 
 
+def _load_host_module(name):
+    """A module of the host-side tree (affb200/<name>.py: written against an operator table, no top-level dependency
+    on the CUDA library) loaded under a stand-in package, so that the CPU reference arm never maps libaffb200.so —
+    importing the real `affb200` package would dlopen it."""
+    import importlib
+    import types
+    pkg = "affb200_host"
+    if pkg not in sys.modules:
+        m = types.ModuleType(pkg)
+        m.__path__ = [os.path.join(ROOT, "ml-autofocusformermod_b200", "affb200")]
+        sys.modules[pkg] = m
+    return importlib.import_module(pkg + "." + name)
+
+
 def _host_glue():
-    """The module tree (affb200/aff_transformer.py: written against an operator table, no top-level dependency on the
-    CUDA library) loaded by path, so that the CPU reference arm never maps libaffb200.so — importing the `affb200`
-    package would dlopen it."""
-    import importlib.util
-    name = "affb200_host_glue"
-    if name in sys.modules:
-        return sys.modules[name]
-    path = os.path.join(ROOT, "ml-autofocusformermod_b200", "affb200", "aff_transformer.py")
-    spec = importlib.util.spec_from_file_location(name, path)
-    mod = importlib.util.module_from_spec(spec)
-    sys.modules[name] = mod
-    spec.loader.exec_module(mod)
-    return mod
+    return _load_host_module("aff_transformer")
 
 
 def merge_rows(merges, infer):
@@ -285,8 +287,10 @@ class _AffRun:
                 pass
         self.ops = ops
         self.infer = bool(getattr(wl, "infer", False))
-        model = build_aff(wl.model_name, ops=ops).to(device)
+        model = (wl.build_model(ops) if hasattr(wl, "build_model") else build_aff(wl.model_name, ops=ops)).to(device)
         model = model.eval() if self.infer else model.train()
+        self.hw = getattr(wl, "img_hw", (wl.img, wl.img))
+        self.stage_layers = wl.stage_layers(model) if hasattr(wl, "stage_layers") else list(model.layers[:3])
         self.model = model
         # default: the step replayed as CUDA graphs (affb200/graph_step.py; gradients averaged with one flat NCCL
         # all-reduce).  AFFB200_GRAPH=0: eager launches, DistributedDataParallel for world > 1 as the reference does.
@@ -301,7 +305,7 @@ class _AffRun:
 
     def make_host_batch(self, i):
         g = torch.Generator().manual_seed(1000 + i)
-        x = torch.randn(self.B, 3, self.wl.img, self.wl.img, generator=g).pin_memory()
+        x = torch.randn(self.B, 3, *self.hw, generator=g).pin_memory()
         y = torch.randint(0, 1000, (self.B,), generator=g).pin_memory()
         return [x, y]
 
@@ -340,7 +344,7 @@ class _AffRun:
         d_q, d_kv written, plus the same index tensors."""
         cap, merges = [], []
         hooks = [layer.blocks[0].register_forward_pre_hook(lambda m, a: cap.append((a[1], a[2], a[3], a[5])))
-                 for layer in self.model.layers[:3]]
+                 for layer in self.stage_layers]
         real_merge = getattr(self.ops, "merge_wf", None)
         if real_merge is not None:     # operands of the three merges (ClusterMerging: aff_transformer.py:343-361)
             def spy(table, pe_idx, lp, mask, feat, member):
@@ -350,7 +354,7 @@ class _AffRun:
         from affb200 import fused as _fused
         _fused.trace = []
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
-            self.model(torch.randn(self.B, 3, self.wl.img, self.wl.img, device=self.device))
+            self.model(torch.randn(self.B, 3, *self.hw, device=self.device))
         calls, _fused.trace = _fused.trace, None
         if real_merge is not None:
             self.ops.merge_wf = real_merge
@@ -366,7 +370,7 @@ class _AffRun:
         if self.ops.fused_attention is not None:
             from affb200 import fused
             for st, (nbhd, mask, pe_idx, stage_table) in enumerate(cap):   # stage_table: the (compacted) rows pe_idx indexes
-                layer = self.model.layers[st]
+                layer = self.stage_layers[st]
                 attn = layer.blocks[0].attn
                 B, n, M = nbhd.shape
                 H, hc = attn.num_heads, attn.dim
@@ -456,6 +460,46 @@ class AffTinyInfer(AffInfer):
     metric = "AFF-Tiny-1/5 224x224 inference img/s"
 
 
-WORKLOADS.update({"aff_tiny_1_5th": AffTrain, "aff_tiny": AffTinyTrain, "aff_mini_infer": AffInfer,
+class MaskfinerUDSmallInfer(AffInfer):
+    """BASELINE config 5: the fork's seven-backbone U-shaped classifier (configs/maskfiner_up_down_small.yaml) at
+    1024 x 2048, batch 1, forward only (model.eval(), bf16 autocast).  The reference publishes no number for it."""
+    model_name = "maskfiner_up_down_small"
+    metric = "maskfiner_up_down_small 1024x2048 inference img/s"
+    default_batch = 1
+    ref_batch = 1
+    img_hw = (1024, 2048)
+
+    def config(self, B, world):
+        c = super().config(B, world)
+        c.update(workload="maskfiner_ud_small_1024x2048_infer",
+                 tokens_per_stage=[2048, 6144, 14336, 30720, 14336, 6144, 2048],
+                 step="model.eval() forward of the 7-backbone chain, bf16 autocast; importance scores ~ N(0,1) per step "
+                      "as the reference draws them (maskfiner_up_down.py:147-149)")
+        return c
+
+    def build_model(self, ops):
+        from affb200.maskfiner_up_down import build_maskfiner_up_down
+        return build_maskfiner_up_down(num_classes=1000, ops=ops)
+
+    def stage_layers(self, model):
+        return [bb.layers for bb in model.backbones if hasattr(bb.layers, "nbhd_size")]
+
+    def cpu_reference(self, sample_b):
+        from oracle.aff_ops_ref import OracleOps  # the checker, timed here as the CPU baseline only
+        torch.manual_seed(0)
+        ud = _load_host_module("maskfiner_up_down")
+        stable = lambda s: s.sort(dim=1, stable=True)[1]
+        l1 = lambda a, b: torch.cat([torch.cdist(a[:, i:i + 1024].float(), b.float(), p=1).argmin(dim=2)
+                                     for i in range(0, a.shape[1], 1024)], dim=1)
+        model = ud.build_maskfiner_up_down(num_classes=1000, ops=OracleOps(), argsort=stable, find_order=l1).eval()
+        x = torch.randn(sample_b, 3, *self.img_hw, generator=torch.Generator().manual_seed(1))
+
+        def go():
+            with torch.no_grad():
+                model(x)
+        return go
+
+
+WORKLOADS.update({"maskfiner_ud_small_1024x2048_infer": MaskfinerUDSmallInfer, "aff_tiny_1_5th": AffTrain, "aff_tiny": AffTinyTrain, "aff_mini_infer": AffInfer,
                   "aff_base_384_infer": AffBase384Infer, "aff_tiny_1_5th_infer": AffTinyInfer})
 DEFAULT = "aff_tiny_1_5th"

@@ -308,6 +308,7 @@ int affb200_fused_attn_bwd(const affb200_view *q, const affb200_view *k, const a
  * ---------------------------------------------------------------------------------------------------------- */
 #define AFFB200_CL_UMAX 64
 #define AFFB200_CL_BAD 0x10000000
+#define AFFB200_CL_SPLIT 0x20000000   /* header flag: the tile carries one union per half of 32 tokens (see q_hdr2) */
 typedef struct {
     int32_t ucap;            /* union blocks the launch sizes shared memory for: >= stats[4], <= AFFB200_CL_UMAX */
     const int32_t *q_hdr;    /* [B][ceil(N/64)] */
@@ -319,12 +320,25 @@ typedef struct {
     const int32_t *kb_cnt;   /* [B][ceil(N/8)] number of query tokens that reference the block */
     const uint32_t *kb_tok;  /* [B][ceil(N/8)][kbcap] those tokens, ascending */
     const uint16_t *q_pe;    /* [B][N][M] packed bias index (pe | masked << 15) in ascending-block slot order, or NULL */
+    /* Split tiles (affb200_cl_qplan_build_split; forward only).  A tile whose 64 tokens reference more than 64 blocks
+     * (mixed-resolution token sets) gets AFFB200_CL_SPLIT in q_hdr with the union of tokens 0..31 in q_hdr / q_ucl and
+     * the union of tokens 32..63 here; membership words are relative to the token's own half.  NULL: no split tiles. */
+    const int32_t *q_hdr2;   /* [B][ceil(N/64)] union size of the second half (0 for tiles that are not split) */
+    const uint16_t *q_ucl2;  /* [B][ceil(N/64)][64] */
 } affb200_cl_plan;
 
 int64_t affb200_cl_tiles(int64_t n);
 int affb200_cl_qplan_build(const int64_t *nbhd_idx, const int64_t *mask, const int64_t *pe_idx, const float *pos,
                            int64_t B, int64_t N, int64_t M, int64_t rel_pos_width, int64_t table_width, uint16_t *blk,
                            int32_t *hdr, uint16_t *ucl, uint64_t *qmask, uint32_t *pos16, int32_t *stats, void *stream);
+/* As affb200_cl_qplan_build, with room for split tiles: hdr2 / ucl2 as in affb200_cl_plan (both required).  stats[0]
+ * then counts only tiles that overflow even per half, stats[3] the split tiles, stats[4] the largest union after
+ * splitting; stats[6] (both forms) the largest |dx| or |dy| between a token and a key of its neighbourhood.  Plans with
+ * stats[3] != 0 are for affb200_fused_cl_fwd only. */
+int affb200_cl_qplan_build_split(const int64_t *nbhd_idx, const int64_t *mask, const int64_t *pe_idx, const float *pos,
+                                 int64_t B, int64_t N, int64_t M, int64_t rel_pos_width, int64_t table_width,
+                                 uint16_t *blk, int32_t *hdr, uint16_t *ucl, int32_t *hdr2, uint16_t *ucl2,
+                                 uint64_t *qmask, uint32_t *pos16, int32_t *stats, void *stream);
 int affb200_cl_kplan_build(const uint16_t *blk, int64_t B, int64_t N, int64_t M, int64_t kbcap, int32_t *kb_cnt,
                            uint32_t *kb_tok, int32_t *stats, void *stream);
 /* q_pe [B][N][M]: affb200_fused_attn_pack_pe's encoding with each token's 8-slot groups reordered by ascending block id —

@@ -101,6 +101,22 @@ def _pe_features(pre_table, dt):
     return hit[:2]
 
 
+_sub_cache = {}
+
+
+def _sub_features(pe_feat, w, tw, r):
+    """rows of the feature table for offsets |dx|, |dy| <= r (the central (2r+1)^2 of the tw x tw table); cached"""
+    lp = pe_feat[0]
+    key = (lp.data_ptr(), lp._version, w, tw, r)
+    hit = _sub_cache.get(key)
+    if hit is None or hit[1]() is not lp:
+        if len(_sub_cache) > 16:
+            _sub_cache.clear()
+        sub = lp.view(tw, tw, lp.shape[1])[w - r:w + r + 1, w - r:w + r + 1].reshape(-1, lp.shape[1]).contiguous()
+        hit = _sub_cache[key] = (sub, weakref.ref(lp))
+    return hit[0]
+
+
 def _table_of(pe_table, pe_w, pe_b, pe_feat):
     """fp32 [P, H] bias table: given, or pos_embed evaluated the way autocast evaluates the nn.Linear."""
     if pe_w is None:
@@ -267,7 +283,15 @@ class FusedClusterAttentionCl(Function):
         dev = q_lin.device
         q_lin = q_lin.contiguous()
         kv_lin = kv_lin.contiguous()
-        table = _table_of(pe_table, pe_w, pe_b, pe_feat)
+        w_tab, tw_tab = clp.w, clp.tw
+        if clp.sub_r is not None and pe_w is not None and clp.q_pe is None:
+            # forward only over a large table (MixRes: 1023 x 1023 rows): every offset of this index set lies within
+            # clp.sub_r of the centre, so pos_embed is evaluated on those rows alone; the kernel forms its bias index
+            # from position differences with the geometry it is given
+            w_tab, tw_tab = clp.sub_r, 2 * clp.sub_r + 1
+            table = _table_of(None, pe_w, pe_b, (_sub_features(pe_feat, clp.w, clp.tw, clp.sub_r), None))
+        else:
+            table = _table_of(pe_table, pe_w, pe_b, pe_feat)
         bk = blank_k.detach().float().contiguous()
         bv = blank_v.detach().float().contiguous()
         with torch.cuda.device(dev):
@@ -277,8 +301,11 @@ class FusedClusterAttentionCl(Function):
             N.check(N.LIB.affb200_fused_cl_fwd(
                 _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
                 _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), N.p(table), N.p(bk), N.p(bv),
-                clp.byref(), N.p(lse), N.p(guard_tensor(dev)), B, H, n, c, clp.w, clp.tw, float(scale),
+                clp.byref(), N.p(lse), N.p(guard_tensor(dev)), B, H, n, c, w_tab, tw_tab, float(scale),
                 N.dtype_enum(q_lin), N.stream_ptr(dev)), "fused_cl_fwd")
+        if tw_tab != clp.tw:
+            ctx.mark_non_differentiable(out)
+            return out
         ctx.save_for_backward(q_lin, kv_lin, out, lse, table, bk, bv)
         ctx.clp = clp
         ctx.M = nbhd_idx.shape[2]

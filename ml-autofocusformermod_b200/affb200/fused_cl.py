@@ -20,6 +20,9 @@ CL_T = 64
 CL_UMAX = 64
 KBCAP_STEP = 16
 UCAP_SLACK = 3
+UCAP_TWO_CTAS = 44     # largest union for which two CTAs of the forward kernel share an SM at head dim 32
+SUB_RADII = (31, 63, 127, 255)     # forward-only plans over a large table: the bias table is evaluated on the central
+                                   # (2R+1)^2 rows only, R the smallest of these that covers every (token, key) offset
 
 
 class ClPlanStruct(ctypes.Structure):
@@ -27,7 +30,11 @@ class ClPlanStruct(ctypes.Structure):
     _fields_ = [("ucap", ctypes.c_int32), ("q_hdr", ctypes.c_void_p), ("q_ucl", ctypes.c_void_p),
                 ("q_mask", ctypes.c_void_p), ("pos16", ctypes.c_void_p), ("blk", ctypes.c_void_p),
                 ("kbcap", ctypes.c_int32), ("kb_cnt", ctypes.c_void_p), ("kb_tok", ctypes.c_void_p),
-                ("q_pe", ctypes.c_void_p)]
+                ("q_pe", ctypes.c_void_p), ("q_hdr2", ctypes.c_void_p), ("q_ucl2", ctypes.c_void_p)]
+
+
+last_eager_stats = None  # stats[8] (affb200_cl_qplan_build_split) of the most recent plan built outside graph capture
+debug_static = None     # set to a list: every statically built plan appends (shape, ucap, sub_r, stats, bad) tensors
 
 
 def enabled():
@@ -57,12 +64,20 @@ class ClPlan:
         self.ucap = 0
         self.kbcap = 0
         self.q_pe = None
+        self.sub_r = None      # table radius the forward may use instead of w (see SUB_RADII), or None
 
     def byref(self):
         return ctypes.byref(self.struct)
 
 
-def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P):
+def _radius(maxoff, w):
+    for r in SUB_RADII:
+        if maxoff <= r and r < w:
+            return r
+    return None
+
+
+def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P, need_bwd=True):
     B, n, M = nbhd_idx.shape
     dev = nbhd_idx.device
     pl = ClPlan(B, n, M, w, tw)
@@ -86,67 +101,95 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P):
         posf = pos.detach().float().contiguous()
         nb_c, pe_c = nbhd_idx.contiguous(), pe_idx.contiguous()
         mk_c = None if mask is None else mask.contiguous()
-        N.check(N.LIB.affb200_cl_qplan_build(N.p(nb_c), N.p(mk_c), N.p(pe_c), N.p(posf), B, n, M, w, tw, N.p(blk),
-                                             N.p(hdr), N.p(ucl), N.p(qmask), N.p(pos16), N.p(stats), sp),
-                "cl_qplan_build")
+        # tiles whose 64 tokens reference more than 64 blocks get one union per half (forward kernel only)
+        hdr2 = torch.empty((B, pl.tiles), dtype=torch.int32, device=dev)
+        ucl2 = torch.empty((B, pl.tiles, CL_UMAX), dtype=torch.int16, device=dev)
+        N.check(N.LIB.affb200_cl_qplan_build_split(N.p(nb_c), N.p(mk_c), N.p(pe_c), N.p(posf), B, n, M, w, tw, N.p(blk),
+                                                   N.p(hdr), N.p(ucl), N.p(hdr2), N.p(ucl2), N.p(qmask), N.p(pos16),
+                                                   N.p(stats), sp), "cl_qplan_build")
         if not static:
             st = stats.tolist()
-            if st[0] or st[1]:
+            if st[1]:          # the structure is absent: remembered for the shape
                 _plan._observed[("cl",) + skey] = dict(ok=False)
                 return None
-        kbcap = obs["kbcap"] if (obs and obs.get("ok")) else 96
-        if static:
-            kbcap += KBCAP_STEP     # room for a block that more tokens reference than in the recorded passes
-        while True:
-            kb_cnt = torch.empty((B, nblk), dtype=torch.int32, device=dev)
-            kb_tok = torch.empty((B, nblk, kbcap), dtype=torch.int32, device=dev)
-            N.check(N.LIB.affb200_cl_kplan_build(N.p(blk), B, n, M, kbcap, N.p(kb_cnt), N.p(kb_tok), N.p(stats), sp),
-                    "cl_kplan_build")
-            if static:
-                break
-            st = stats.tolist()
-            if st[2] == 0:
-                break
-            stats[2] = 0
-            kbcap = ((st[5] + KBCAP_STEP - 1) // KBCAP_STEP) * KBCAP_STEP
-        q_pe = None
+            global last_eager_stats
+            last_eager_stats = list(st)
+            if st[0] or (st[3] and need_bwd):   # a tile beyond the kernels' limits (the backward takes no split tiles):
+                return None                      # this call only
+        kbcap, kb_cnt, kb_tok, q_pe = 0, None, None, None
         bad = torch.zeros(1, dtype=torch.int32, device=dev)
-        if P <= 32768:
-            q_pe = torch.empty((B, n, M), dtype=torch.int16, device=dev)
-            N.check(N.LIB.affb200_cl_pack_pe_sorted(N.p(pe_c), N.p(mk_c), N.p(blk), B, n, M, N.p(q_pe), N.p(bad), sp),
-                    "cl_pack_pe_sorted")
+        if need_bwd:
+            kbcap = obs["kbcap"] if (obs and obs.get("ok") and obs.get("kbcap")) else 96
+            if static:
+                kbcap += KBCAP_STEP     # room for a block that more tokens reference than in the recorded passes
+            while True:
+                kb_cnt = torch.empty((B, nblk), dtype=torch.int32, device=dev)
+                kb_tok = torch.empty((B, nblk, kbcap), dtype=torch.int32, device=dev)
+                N.check(N.LIB.affb200_cl_kplan_build(N.p(blk), B, n, M, kbcap, N.p(kb_cnt), N.p(kb_tok), N.p(stats), sp),
+                        "cl_kplan_build")
+                if static:
+                    break
+                st = stats.tolist()
+                if st[2] == 0:
+                    break
+                stats[2] = 0
+                kbcap = ((st[5] + KBCAP_STEP - 1) // KBCAP_STEP) * KBCAP_STEP
+            if P <= 32768:
+                q_pe = torch.empty((B, n, M), dtype=torch.int16, device=dev)
+                N.check(N.LIB.affb200_cl_pack_pe_sorted(N.p(pe_c), N.p(mk_c), N.p(blk), B, n, M, N.p(q_pe), N.p(bad), sp),
+                        "cl_pack_pe_sorted")
+        sub_r = None
+        want_sub = (not need_bwd) and P > 32768
         if static:
             # a little room above the largest union seen: neighbourhoods of the data-dependent stages vary per batch
             ucap = min(CL_UMAX, obs["ucap"] + UCAP_SLACK)
-            _plan.guard_add((stats[0] != 0) | (stats[1] != 0) | (stats[2] != 0) | (stats[4] > ucap) | (bad[0] != 0))
+            if ucap > UCAP_TWO_CTAS:     # one CTA per SM either way: take the kernels' limit, nothing to speculate on
+                ucap = CL_UMAX
+            trip = (stats[0] != 0) | (stats[1] != 0) | (stats[2] != 0) | (stats[4] > ucap) | (bad[0] != 0)
+            if need_bwd:
+                trip = trip | (stats[3] != 0)
+            if want_sub:
+                sub_r = _radius(2 * obs.get("maxoff", w), w)     # room for draws with longer offsets than recorded
+                if sub_r is not None:
+                    trip = trip | (stats[6] > sub_r)
+            _plan.guard_add(trip)
+            if debug_static is not None:
+                debug_static.append((skey, ucap, sub_r, stats, bad))
         else:
             st = stats.tolist()
             if int(bad.item()) != 0:
                 _plan._observed[("cl",) + skey] = dict(ok=False)
                 return None
             ucap = min(CL_UMAX, st[4])
+            maxoff = st[6]
+            if want_sub:
+                sub_r = _radius(maxoff, w)
             if obs and obs.get("ok"):
                 ucap = max(ucap, obs["ucap"])
-                kbcap_rec = max(kbcap, obs["kbcap"])
+                kbcap_rec = max(kbcap, obs.get("kbcap", 0))
+                maxoff = max(maxoff, obs.get("maxoff", 0))
             else:
                 kbcap_rec = kbcap
-            _plan._observed[("cl",) + skey] = dict(ok=True, ucap=ucap, kbcap=kbcap_rec)
-    pl.ucap, pl.kbcap, pl.q_pe = ucap, kbcap, q_pe
+            _plan._observed[("cl",) + skey] = dict(ok=True, ucap=ucap, kbcap=kbcap_rec, maxoff=maxoff)
+    pl.ucap, pl.kbcap, pl.q_pe, pl.sub_r = ucap, kbcap, q_pe, sub_r
     s = ClPlanStruct()
     s.ucap = ucap
     s.q_hdr, s.q_ucl, s.q_mask, s.pos16, s.blk = (hdr.data_ptr(), ucl.data_ptr(), qmask.data_ptr(), pos16.data_ptr(),
                                                   blk.data_ptr())
-    s.kbcap, s.kb_cnt, s.kb_tok = kbcap, kb_cnt.data_ptr(), kb_tok.data_ptr()
+    s.kbcap = kbcap
+    s.kb_cnt, s.kb_tok = (0, 0) if kb_cnt is None else (kb_cnt.data_ptr(), kb_tok.data_ptr())
     s.q_pe = 0 if q_pe is None else q_pe.data_ptr()
+    s.q_hdr2, s.q_ucl2 = hdr2.data_ptr(), ucl2.data_ptr()
     pl.struct = s
-    pl.keep = (blk, hdr, ucl, qmask, pos16, stats, kb_cnt, kb_tok, q_pe)
+    pl.keep = (blk, hdr, ucl, qmask, pos16, stats, kb_cnt, kb_tok, q_pe, hdr2, ucl2)
     pl.stats = stats
     return pl
 
 
 def cl_plan(nbhd_idx, mask, pe_idx, P):
     """ClPlan of this index set, or None (no geometry hint, structure absent, disabled).  P = rows of the bias table;
-    above 32 768 rows the packed bias indices of the backward do not exist (plan.q_pe is None): forward only."""
+    above 32 768 rows the packed bias indices of the backward do not exist (plan.q_pe is None): forward only.  Built
+    under torch.no_grad() the plan is forward-only as well (no key-major lists, no packed bias indices)."""
     if not enabled():
         return None
     p = _plan.get_plan(nbhd_idx)
@@ -154,7 +197,8 @@ def cl_plan(nbhd_idx, mask, pe_idx, P):
     if hint is None:
         return None
     hit = getattr(p, "_cl", None)
-    key = (id(pe_idx), pe_idx._version, None if mask is None else id(mask), P)
+    need_bwd = torch.is_grad_enabled()     # forward-only plans (inference) carry no key-major lists
+    key = (id(pe_idx), pe_idx._version, None if mask is None else id(mask), P, need_bwd)
     if hit is not None and hit[0] == key:
         return hit[1]
     pos, w, tw = hint
@@ -162,6 +206,6 @@ def cl_plan(nbhd_idx, mask, pe_idx, P):
     if M % 8 != 0 or M > 8 * CL_UMAX or pos.shape[0] != B or pos.shape[1] != n or tw != 2 * w + 1 or P != tw * tw:
         res = None
     else:
-        res = _build(nbhd_idx, mask, pe_idx, pos, w, tw, P)
+        res = _build(nbhd_idx, mask, pe_idx, pos, w, tw, P, need_bwd)
     p._cl = (key, res)
     return res

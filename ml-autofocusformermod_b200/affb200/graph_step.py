@@ -319,6 +319,7 @@ class GraphedForward:
     def _capture(self):
         from . import _native as N
         l0 = N.LIB.affb200_launch_count()
+        self._snap = _plan.observed_snapshot()
         self.g = torch.cuda.CUDAGraph()
         with _plan.static_plans(), torch.cuda.graph(self.g):
             self.out = self._fwd()
@@ -332,7 +333,9 @@ class GraphedForward:
             guard.zero_()
             self.fallbacks += 1
             out = self._fwd()
-            if self.recaptures < self.max_recaptures:
+            # re-capture only when the eager pass put larger sizes on record: a draw that no captured size could hold
+            # (a tile whose union exceeds the kernels' limit) is simply served by this eager pass
+            if self.recaptures < self.max_recaptures and _plan.observed_snapshot() != self._snap:
                 self.recaptures += 1
                 torch.cuda.synchronize(self.device)
                 self._capture()

@@ -64,6 +64,8 @@ class BasicLayer(nn.Module):
         else:
             pos, mean, _, _, reorder = ops.space_filling_cluster(pos, m, h, w, no_reorder=False)
         nbhd, mask, pe_idx, _ = ops.build_nbhd(pos, mean, m, self.nbhd_size, REL_POS_WIDTH, clamp=True)
+        if getattr(ops, 'hint_geometry', None) is not None:   # where nbhd / pe_idx came from: block-structured kernels
+            ops.hint_geometry(nbhd, pos, REL_POS_WIDTH, TABLE_WIDTH)
         return pos, reorder, nbhd, mask, pe_idx
 
     def forward(self, pos, feat, h, w, on_grid):
@@ -95,7 +97,11 @@ class BasicLayer(nn.Module):
             if reorder is not None:
                 feat = getattr(ops, 'reorder_tokens', _gather_tokens)(feat, reorder)
                 pos_scale = pos_scale.gather(1, reorder)
-        if self.compact:
+        # inference with the block-structured forward keeps the full table: that kernel takes the bias from position
+        # differences and has no row limit, and the unique() of the compaction is a host sync (no graph capture)
+        keep_full = (not torch.is_grad_enabled() and not global_attn and feat.is_cuda
+                     and getattr(ops, 'hint_geometry', None) is not None and getattr(ops, 'fused_attention', None) is not None)
+        if self.compact and not keep_full:
             pe_idx, table = compact_table(pe_idx, table)
         for blk in self.blocks:
             feat = blk(feat, member_idx, cluster_mask, pe_idx, global_attn, table, ops)

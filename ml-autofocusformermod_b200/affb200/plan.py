@@ -31,6 +31,12 @@ from . import _native as N
 _lock = threading.Lock()
 _plans = {}  # id(tensor) -> (weakref, version, NbhdPlan)
 _observed = {}  # (kind, B, Nq, Nk, M) -> dict(T=tile size that did not overflow, umax=largest union seen)
+
+
+def observed_snapshot():
+    """Hashable copy of what the eager passes have on record: a captured graph sized from it is still the best one can
+    capture as long as this has not changed (a failed speculation that taught nothing new needs no re-capture)."""
+    return repr(sorted((k, sorted(v.items())) for k, v in _observed.items()))
 _static = False
 _guards = {}  # device index -> int32[1] tensor, non-zero after a failed speculation
 

@@ -163,7 +163,10 @@ static __device__ __noinline__ float cl_bias_far(const float *__restrict__ table
                                           uint32_t pi_biased) {
     if (pu == kClPosInvalid) return -INFINITY;
     const uint32_t pi = pi_biased + kClPosBias;
-    const int dx = int(pu & 0xffffu) - int(pi & 0xffffu), dy = int(pu >> 16) - int(pi >> 16);
+    // clamped into the table: a replayed launch whose speculated table radius did not hold (the plan's guard reports
+    // it and the result is discarded) must still not read outside the table
+    const int dx = max(-w, min(w, int(pu & 0xffffu) - int(pi & 0xffffu)));
+    const int dy = max(-w, min(w, int(pu >> 16) - int(pi >> 16)));
     const int pe = (dy + w) * tw + dx + w;
     return __ldg(table + int64_t(pe) * H + h) * kLog2e;
 }

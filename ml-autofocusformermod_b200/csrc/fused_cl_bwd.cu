@@ -106,7 +106,8 @@ fused_cl_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
         }
         item = next;
         const int U = hdr & AFFB200_PLAN_COUNT_MASK;
-        const bool skip = (hdr & (AFFB200_PLAN_OVERFLOW | AFFB200_CL_BAD)) != 0 || U > ucap;
+        // (split tiles are a forward-only feature: a plan that carries them is not handed to the backward)
+        const bool skip = (hdr & (AFFB200_PLAN_OVERFLOW | AFFB200_CL_BAD | AFFB200_CL_SPLIT)) != 0 || U > ucap;
         T *dq_tile = dqp + int64_t(b) * p.dq.sB + int64_t(t0) * p.dq.sN + h0 * p.dq.sH;
         const int tok = warp * 8 + g;
         const bool live = tok < ti;

@@ -27,6 +27,8 @@ struct ClFwdParams {
     const uint16_t *ucl;
     const unsigned long long *qmask;
     const uint32_t *pos16;
+    const int32_t *hdr2;   // second-half union size of split tiles (AFFB200_CL_SPLIT), or nullptr
+    const uint16_t *ucl2;  // second-half union list
     float *lse;
     int32_t *guard;        // incremented when a tile had to be skipped (speculated plans)
     int B, H, N, n_tiles, ucap, w, tw;
@@ -86,7 +88,12 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
         }
         item = next;
         const int U = hdr & AFFB200_PLAN_COUNT_MASK;
-        const bool skip = (hdr & (AFFB200_PLAN_OVERFLOW | AFFB200_CL_BAD)) != 0 || U > ucap;
+        // a split tile (its 64 tokens reference more than 64 blocks) carries one union per half of 32 tokens: two
+        // passes over the tile, warps 0-3 compute in the first, warps 4-7 in the second
+        const bool split = (hdr & AFFB200_CL_SPLIT) != 0;
+        const int64_t bt_cur = int64_t(b) * p.n_tiles + tile;
+        const int U2 = split && p.hdr2 ? (__ldg(p.hdr2 + bt_cur) & AFFB200_PLAN_COUNT_MASK) : 0;
+        const bool skip = (hdr & (AFFB200_PLAN_OVERFLOW | AFFB200_CL_BAD)) != 0 || U > ucap || U2 > ucap || (split && !p.hdr2);
         T *out_tile = outp + int64_t(b) * p.out.sB + int64_t(t0) * p.out.sN + h0 * p.out.sH;
         if (skip) {   // speculated plan that did not hold: defined output, guard tripped
             for (int e = tid; e < ti * (G::QB / 16); e += kClThreads) {
@@ -109,13 +116,20 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
             }
             __syncthreads();
         }
+        for (int pass = 0; pass < (split ? 2 : 1); ++pass) {
+        int Up = U, blk_p = blk_mine;
+        if (pass == 1) {
+            Up = U2;
+            blk_p = tid < kClUMax ? int(__ldg(p.ucl2 + bt_cur * kClUMax + tid)) : 0;
+        }
+        const bool wact = !split || (warp >> 2) == pass;
         // ---- stage: TMA boxes of 8 rows x 128 bytes, the Q tile, and the tile's plan rows, on one mbarrier ----------
-        if (tid == 0) mbar_expect_tx(bar, uint32_t(U) * (G::BLK + 32u) + uint32_t(kClT) * G::QB + 512u + 256u);
-        if (tid < U) {
+        if (tid == 0) mbar_expect_tx(bar, uint32_t(Up) * (G::BLK + 32u) + uint32_t(kClT) * G::QB + 512u + 256u);
+        if (tid < Up) {
 #pragma unroll
             for (int t = 0; t < G::TPB; ++t)
-                tma_load_3d(s_kv + (tid * G::TPB + t) * 1024, &tm_kv, h0 * 2 * C + t * 64, blk_mine * 8, b, bar);
-            bulk_g2s(s_pu + tid * 32, p.pos16 + int64_t(b) * npad + blk_mine * 8, 32u, bar);
+                tma_load_3d(s_kv + (tid * G::TPB + t) * 1024, &tm_kv, h0 * 2 * C + t * 64, blk_p * 8, b, bar);
+            bulk_g2s(s_pu + tid * 32, p.pos16 + int64_t(b) * npad + blk_p * 8, 32u, bar);
         } else if (tid == 64) {
             tma_load_3d(s_q, &tm_q, h0 * C, t0, b, bar);
         } else if (tid == 65) {
@@ -126,6 +140,7 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
         mbar_wait(bar, phase);
         phase ^= 1u;
 
+        if (wact) {
         // ---- per-token state and the warp's list of referenced blocks -------------------------------------------
         const int tok = warp * 8 + g;
         const bool live = tok < ti;
@@ -262,8 +277,10 @@ fused_cl_fwd_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_cons
             if (row < ti)
                 *reinterpret_cast<uint4 *>(out_tile + int64_t(row) * p.out.sN + ch * 8) = *reinterpret_cast<const uint4 *>(gen + G::OFF_Q + a);
         }
+        }
         fence_proxy_async();   // the staging writes above precede the next item's async-proxy writes to the same rows
         __syncthreads();       // all warps are done with this item's rows before the next copies land
+        }
     }
 }
 
@@ -320,6 +337,8 @@ extern "C" int affb200_fused_cl_fwd(const affb200_view *q, const affb200_view *k
     p.table = table; p.blank_k = blank_k; p.blank_v = blank_v;
     p.hdr = plan->q_hdr; p.ucl = plan->q_ucl; p.qmask = reinterpret_cast<const unsigned long long *>(plan->q_mask);
     p.pos16 = plan->pos16; p.lse = lse; p.guard = guard;
+    p.hdr2 = plan->q_hdr2; p.ucl2 = plan->q_hdr2 ? plan->q_ucl2 : nullptr;
+    if (plan->q_hdr2 && !plan->q_ucl2) { set_error("fused_cl_fwd: q_hdr2 without q_ucl2"); return AFFB200_E_ARG; }
     p.B = int(B); p.H = int(H); p.N = int(N); p.n_tiles = int((N + kClT - 1) / kClT); p.ucap = plan->ucap;
     p.w = int(rel_pos_width); p.tw = int(table_width);
     p.scale_log2 = scale * kLog2e;

@@ -17,26 +17,82 @@ namespace affb200 {
 
 constexpr int kPlanThreads = 128;
 
+// Ascending list of the set bits of bitmap[W] (block ids) -> ul[0..63], and pre[w] = number of set bits below word w.
+// Returns the number of set bits to every thread.  Ends on a barrier.
+__device__ __forceinline__ int cl_union_list(const uint32_t *bitmap, uint32_t *pre, int W, int *warp_tot, uint16_t *ul) {
+    const int tid = threadIdx.x;
+    const int wpt = (W + kPlanThreads - 1) / kPlanThreads;
+    int local = 0;
+    for (int k = 0; k < wpt; ++k) {
+        const int wi = tid * wpt + k;
+        if (wi < W) local += __popc(bitmap[wi]);
+    }
+    int incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += v;
+    }
+    if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
+    __syncthreads();
+    int woff = 0, U = 0;
+#pragma unroll
+    for (int k = 0; k < kPlanThreads / 32; ++k) {
+        if (k < (tid >> 5)) woff += warp_tot[k];
+        U += warp_tot[k];
+    }
+    int run = woff + incl - local;
+    for (int k = 0; k < wpt; ++k) {
+        const int wi = tid * wpt + k;
+        if (wi < W) {
+            pre[wi] = uint32_t(run);
+            uint32_t bits = bitmap[wi];
+            while (bits) {
+                const int bit = __ffs(bits) - 1;
+                bits &= bits - 1;
+                if (run < kClUMax) ul[run] = uint16_t(wi * 32 + bit);
+                ++run;
+            }
+        }
+    }
+    __syncthreads();
+    return U;
+}
+
+// membership words of tokens [ta, tb): bit = position of each of the token's blocks in the union list
+__device__ __forceinline__ void cl_membership(const uint32_t *bitmap, const uint32_t *pre, const uint16_t *blk_s,
+                                              unsigned long long *qm, int *bad_s, int ta, int tb, int NB) {
+    for (int it = ta * NB + threadIdx.x; it < tb * NB; it += kPlanThreads) {
+        const int t = it / NB, blk = blk_s[it];
+        if (blk == kClAbsent) continue;
+        const int loc = int(pre[blk >> 5]) + __popc(bitmap[blk >> 5] & ((1u << (blk & 31)) - 1u));
+        const unsigned long long bitv = 1ull << loc;
+        const unsigned long long old = atomicOr(&qm[t], bitv);
+        if (old & bitv) atomicOr(bad_s, 1);   // a token lists a block twice
+    }
+}
+
 __global__ void __launch_bounds__(kPlanThreads)
 cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ mask, const int64_t *__restrict__ pe_idx,
                 const float *__restrict__ pos, int N, int M, int w, int tw, uint16_t *__restrict__ blk_out,
-                int32_t *__restrict__ hdr, uint16_t *__restrict__ ucl, unsigned long long *__restrict__ qmask,
-                uint32_t *__restrict__ pos16, int32_t *__restrict__ stats) {
+                int32_t *__restrict__ hdr, uint16_t *__restrict__ ucl, int32_t *__restrict__ hdr2,
+                uint16_t *__restrict__ ucl2, unsigned long long *__restrict__ qmask, uint32_t *__restrict__ pos16,
+                int32_t *__restrict__ stats) {
     unsigned char *smem = affb200_dsm;
     const int nblk = (N + 7) >> 3, W = (nblk + 31) >> 5, NB = M >> 3;
     uint32_t *bitmap = reinterpret_cast<uint32_t *>(smem);          // [W]
     uint32_t *pre = bitmap + W;                                      // [W] exclusive popcount prefix
     unsigned long long *qm = reinterpret_cast<unsigned long long *>(pre + W);  // [64] (2W words: 8-byte aligned)
     uint16_t *blk_s = reinterpret_cast<uint16_t *>(qm + kClT);       // [64 * NB]
-    __shared__ int bad_s, warp_tot[kPlanThreads / 32];
+    __shared__ int bad_s, off_s, warp_tot[kPlanThreads / 32];
     const int tid = threadIdx.x, tile = blockIdx.x, b = blockIdx.y, n_tiles = gridDim.x;
     const int t0 = tile * kClT, ti = min(kClT, N - t0);
     const int64_t bN = int64_t(b) * N;
     for (int i = tid; i < W; i += kPlanThreads) bitmap[i] = 0u;
     if (tid < kClT) qm[tid] = 0ull;
-    if (tid == 0) bad_s = 0;
+    if (tid == 0) { bad_s = 0; off_s = 0; }
     __syncthreads();
-    int bad = 0;
+    int bad = 0, max_off = 0;
     // packed positions of the tile's own tokens (and the sentinel of the padded tail)
     const int64_t bP = int64_t(b) * n_tiles * kClT;   // qmask / pos16 rows are padded to whole tiles
     for (int t = tid; t < kClT; t += kPlanThreads) {
@@ -73,6 +129,7 @@ cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ ma
                     const float xu = pos[(bN + row) * 2], yu = pos[(bN + row) * 2 + 1];
                     const int64_t want = int64_t(int(yu) - int(yi) + w) * tw + (int(xu) - int(xi) + w);
                     if (pe_idx[so + r] != want) bad = 1;
+                    max_off = max(max_off, max(abs(int(yu) - int(yi)), abs(int(xu) - int(xi))));
                 } else if (!mask || mask[so + r] != 0) {
                     bad = 1;
                 }
@@ -83,63 +140,45 @@ cl_qplan_kernel(const int64_t *__restrict__ nbhd, const int64_t *__restrict__ ma
         blk_out[(bN + t0 + t) * NB + q] = uint16_t(blk);
     }
     if (bad) atomicOr(&bad_s, 1);
+    if (max_off > 0) atomicMax(&off_s, max_off);
     __syncthreads();
-    // exclusive prefix of the per-word popcounts
-    const int wpt = (W + kPlanThreads - 1) / kPlanThreads;
-    int local = 0;
-    for (int k = 0; k < wpt; ++k) {
-        const int wi = tid * wpt + k;
-        if (wi < W) local += __popc(bitmap[wi]);
-    }
-    int incl = local;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if ((tid & 31) >= o) incl += v;
-    }
-    if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
-    __syncthreads();
-    int woff = 0, U = 0;
-#pragma unroll
-    for (int k = 0; k < kPlanThreads / 32; ++k) {
-        if (k < (tid >> 5)) woff += warp_tot[k];
-        U += warp_tot[k];
-    }
-    int run = woff + incl - local;
-    for (int k = 0; k < wpt; ++k) {
-        const int wi = tid * wpt + k;
-        if (wi < W) {
-            pre[wi] = uint32_t(run);
-            uint32_t bits = bitmap[wi];
-            uint16_t *ul = ucl + (int64_t(b) * n_tiles + tile) * kClUMax;
-            while (bits) {
-                const int bit = __ffs(bits) - 1;
-                bits &= bits - 1;
-                if (run < kClUMax) ul[run] = uint16_t(wi * 32 + bit);
-                ++run;
+    uint16_t *ul = ucl + (int64_t(b) * n_tiles + tile) * kClUMax;
+    int U = cl_union_list(bitmap, pre, W, warp_tot, ul), U2 = 0;
+    bool split = false;
+    if (U > kClUMax && hdr2 != nullptr && ti > kClT / 2) {
+        // more than 64 blocks for the 64 tokens (mixed-resolution token sets): one union per half of 32 tokens
+        split = true;
+        for (int half = 0; half < 2; ++half) {
+            const int ta = half * (kClT / 2), tb = min(ti, ta + kClT / 2);
+            __syncthreads();
+            for (int i = tid; i < W; i += kPlanThreads) bitmap[i] = 0u;
+            __syncthreads();
+            for (int it = ta * NB + tid; it < tb * NB; it += kPlanThreads) {
+                const int blk = blk_s[it];
+                if (blk != kClAbsent) atomicOr(&bitmap[blk >> 5], 1u << (blk & 31));
             }
+            __syncthreads();
+            const int Uh = cl_union_list(bitmap, pre, W, warp_tot,
+                                         half == 0 ? ul : ucl2 + (int64_t(b) * n_tiles + tile) * kClUMax);
+            if (Uh <= kClUMax) cl_membership(bitmap, pre, blk_s, qm, &bad_s, ta, tb, NB);
+            if (half == 0) U = Uh; else U2 = Uh;
         }
-    }
-    __syncthreads();
-    if (U <= kClUMax) {
-        for (int it = tid; it < ti * NB; it += kPlanThreads) {
-            const int t = it / NB, blk = blk_s[it];
-            if (blk == kClAbsent) continue;
-            const int loc = int(pre[blk >> 5]) + __popc(bitmap[blk >> 5] & ((1u << (blk & 31)) - 1u));
-            const unsigned long long bitv = 1ull << loc;
-            const unsigned long long old = atomicOr(&qm[t], bitv);
-            if (old & bitv) atomicOr(&bad_s, 1);   // a token lists a block twice
-        }
+    } else if (U <= kClUMax) {
+        cl_membership(bitmap, pre, blk_s, qm, &bad_s, 0, ti, NB);
     }
     __syncthreads();
     for (int t = tid; t < kClT; t += kPlanThreads) qmask[bP + t0 + t] = t < ti ? qm[t] : 0ull;
     if (tid == 0) {
-        const bool over = U > kClUMax;
+        const bool over = U > kClUMax || U2 > kClUMax;
         const bool isbad = bad_s != 0;
-        hdr[int64_t(b) * n_tiles + tile] = U | (over ? AFFB200_PLAN_OVERFLOW : 0) | (isbad ? AFFB200_CL_BAD : 0);
+        hdr[int64_t(b) * n_tiles + tile] = U | (over ? AFFB200_PLAN_OVERFLOW : 0) | (isbad ? AFFB200_CL_BAD : 0) |
+                                           (split ? AFFB200_CL_SPLIT : 0);
+        if (hdr2) hdr2[int64_t(b) * n_tiles + tile] = U2;
         if (over) atomicAdd(&stats[0], 1);
         if (isbad) atomicAdd(&stats[1], 1);
-        atomicMax(&stats[4], U);
+        if (split) atomicAdd(&stats[3], 1);
+        atomicMax(&stats[4], max(U, U2));
+        atomicMax(&stats[6], off_s);     // largest |dx| or |dy| of a (token, key) pair: bounds the table rows in use
     }
 }
 
@@ -229,17 +268,18 @@ using namespace affb200;
 
 extern "C" int64_t affb200_cl_tiles(int64_t n) { return n <= 0 ? 0 : (n + kClT - 1) / kClT; }
 
-extern "C" int affb200_cl_qplan_build(const int64_t *nbhd_idx, const int64_t *mask, const int64_t *pe_idx,
-                                      const float *pos, int64_t B, int64_t N, int64_t M, int64_t rel_pos_width,
-                                      int64_t table_width, uint16_t *blk, int32_t *hdr, uint16_t *ucl, uint64_t *qmask,
-                                      uint32_t *pos16, int32_t *stats, void *stream) {
+extern "C" int affb200_cl_qplan_build_split(const int64_t *nbhd_idx, const int64_t *mask, const int64_t *pe_idx,
+                                            const float *pos, int64_t B, int64_t N, int64_t M, int64_t rel_pos_width,
+                                            int64_t table_width, uint16_t *blk, int32_t *hdr, uint16_t *ucl,
+                                            int32_t *hdr2, uint16_t *ucl2, uint64_t *qmask, uint32_t *pos16,
+                                            int32_t *stats, void *stream) {
     if (B <= 0 || B > 65535 || N <= 0 || N > 32767 * 8 || M <= 0 || M % 8 != 0 || M > 8 * kClUMax
         || rel_pos_width < 0 || table_width != 2 * rel_pos_width + 1) {
         set_error("cl_qplan_build: unsupported dimensions (B=%lld N=%lld M=%lld w=%lld tw=%lld)", (long long)B,
                   (long long)N, (long long)M, (long long)rel_pos_width, (long long)table_width);
         return AFFB200_E_ARG;
     }
-    if (!nbhd_idx || !pe_idx || !pos || !blk || !hdr || !ucl || !qmask || !pos16 || !stats) {
+    if (!nbhd_idx || !pe_idx || !pos || !blk || !hdr || !ucl || !qmask || !pos16 || !stats || (hdr2 != nullptr) != (ucl2 != nullptr)) {
         set_error("cl_qplan_build: null pointer");
         return AFFB200_E_ARG;
     }
@@ -247,9 +287,17 @@ extern "C" int affb200_cl_qplan_build(const int64_t *nbhd_idx, const int64_t *ma
     const size_t smem = size_t(2 * W) * 4 + size_t(kClT) * 8 + size_t(kClT) * NB * 2;
     const dim3 grid{unsigned((N + kClT - 1) / kClT), unsigned(B), 1u};
     cl_qplan_kernel<<<grid, kPlanThreads, smem, (cudaStream_t)stream>>>(
-        nbhd_idx, mask, pe_idx, pos, int(N), int(M), int(rel_pos_width), int(table_width), blk, hdr, ucl,
+        nbhd_idx, mask, pe_idx, pos, int(N), int(M), int(rel_pos_width), int(table_width), blk, hdr, ucl, hdr2, ucl2,
         reinterpret_cast<unsigned long long *>(qmask), pos16, stats);
     return check_launch("cl_qplan_build");
+}
+
+extern "C" int affb200_cl_qplan_build(const int64_t *nbhd_idx, const int64_t *mask, const int64_t *pe_idx,
+                                      const float *pos, int64_t B, int64_t N, int64_t M, int64_t rel_pos_width,
+                                      int64_t table_width, uint16_t *blk, int32_t *hdr, uint16_t *ucl, uint64_t *qmask,
+                                      uint32_t *pos16, int32_t *stats, void *stream) {
+    return affb200_cl_qplan_build_split(nbhd_idx, mask, pe_idx, pos, B, N, M, rel_pos_width, table_width, blk, hdr, ucl,
+                                        nullptr, nullptr, qmask, pos16, stats, stream);
 }
 
 extern "C" int affb200_cl_kplan_build(const uint16_t *blk, int64_t B, int64_t N, int64_t M, int64_t kbcap,

@@ -7,10 +7,10 @@
 // explicit round-to-nearest intrinsics (no FMA contraction), and orderings follow the rules of the library kernels
 // the reference calls (stable ascending sort; kNN ties -> lowest index).
 //
-// Sorting is a rank sort: rank(i) = #{j : (key_j, j) < (key_i, i)}.  The slices are short (N <= 30 720 tokens per
-// image), every (i, j) pair is independent, keys are staged once per CTA in shared memory, and the result is stable
-// by construction; at the model's sizes this is a few microseconds of integer compares spread over all SMs, with
-// none of the multi-pass global traffic of a radix sort.
+// Sorting works on 64-bit composites (key bits, token index) — unique, so the result is the stable sort by
+// construction: tiles of 2048 are sorted in shared memory and merged by rank (see tile_sort_kernel below).  The
+// slices are short (N <= 30 720 tokens per image); a radix sort's multi-pass global traffic and fixed launch chain
+// (torch.sort: ~70 us at every N here) is what this avoids.
 #include "common.cuh"
 #include <algorithm>
 #include <cmath>
@@ -212,35 +212,84 @@ f32_key_kernel(const float *__restrict__ x, int64_t total, int N, int descending
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Rank sort of 64-bit composites.  grid (ceil(N/kIT), B, JS): CTA (ib, b, js) ranks its kIT elements against
-// the js-th slice of the j range; partial ranks are combined with one atomicAdd per element when JS > 1.
-// order[b][rank] = i is written by the scatter kernel once all partial ranks are in.
+// Sort of 64-bit composites (key bits << 32 | token index: unique, so any comparison sort is the stable sort).
+//   1. tile_sort_kernel: every CTA sorts one tile of 2048 composites in shared memory (bitonic network).  A slice
+//      that fits one tile is finished here: order / pos_sorted are written directly.
+//   2. tile_rank_kernel: rank(e) = position in its own sorted tile + sum over the other tiles of lower_bound(tile, e),
+//      a binary search in the tile staged in shared memory.  grid (T, B, JS): CTA (ti, b, js) ranks the elements of
+//      tile ti against the js-th slice of the tiles; partial ranks meet in one atomicAdd per element when JS > 1.
+//   3. rank_scatter_kernel: order[b][rank] = i.
+// Work per slice is N log(2048) + N (N / 2048) log(2048) compares instead of the N^2 of a plain rank count (30 720
+// tokens: 5.4 M instead of 944 M), still without multi-pass global traffic; measured in profiles/r02_sort.md.
 // ---------------------------------------------------------------------------------------------------------
-constexpr int kRankTile = 2048;  // composites staged per shared-memory tile (16 KB)
+constexpr int kSortTile = 2048;     // composites per shared-memory tile (16 KB)
+constexpr int kSortThreads = 1024;
+constexpr uint64_t kSortPad = ~0ull;   // above every composite (token index < N <= 2^31)
 
-__global__ void __launch_bounds__(kIT)
-rank_count_kernel(const uint64_t *__restrict__ comp, int N, int j_per_slice, int32_t *__restrict__ rank_out) {
-    __shared__ uint64_t tile[kRankTile];
-    const int b = blockIdx.y;
-    const int i = blockIdx.x * kIT + threadIdx.x;
-    const uint64_t *cb = comp + int64_t(b) * N;
-    const uint64_t mine = i < N ? cb[i] : 0ull;
-    const int j0 = blockIdx.z * j_per_slice, j1 = min(N, j0 + j_per_slice);
-    int cnt = 0;
-    for (int base = j0; base < j1; base += kRankTile) {
-        const int nt = min(kRankTile, j1 - base);
-        __syncthreads();
-        for (int t = threadIdx.x; t < nt; t += kIT) tile[t] = cb[base + t];
-        __syncthreads();
-        int t = 0;
-        for (; t + 4 <= nt; t += 4) {
-            cnt += (tile[t] < mine) + (tile[t + 1] < mine) + (tile[t + 2] < mine) + (tile[t + 3] < mine);
+__global__ void __launch_bounds__(kSortThreads)
+tile_sort_kernel(const uint64_t *__restrict__ comp, int N, uint64_t *__restrict__ sorted, int64_t *__restrict__ order,
+                 const float *__restrict__ pos, float *__restrict__ pos_sorted) {
+    __shared__ uint64_t s[kSortTile];
+    const int tid = threadIdx.x, b = blockIdx.y, base = blockIdx.x * kSortTile;
+    const int nt = min(kSortTile, N - base);
+    int n2 = 64;
+    while (n2 < nt) n2 <<= 1;
+    const uint64_t *cb = comp + int64_t(b) * N + base;
+    for (int t = tid; t < n2; t += kSortThreads) s[t] = t < nt ? cb[t] : kSortPad;
+    __syncthreads();
+    for (int k = 2; k <= n2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (n2 >> 1); t += kSortThreads) {
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int l = i | j;
+                const uint64_t x = s[i], y = s[l];
+                if ((x > y) == ((i & k) == 0)) { s[i] = y; s[l] = x; }
+            }
+            __syncthreads();
         }
-        for (; t < nt; ++t) cnt += (tile[t] < mine);
     }
-    if (i < N) {
-        if (gridDim.z == 1) rank_out[int64_t(b) * N + i] = cnt;
-        else atomicAdd(rank_out + int64_t(b) * N + i, cnt);
+    if (gridDim.x == 1) {     // the whole slice: finished
+        for (int t = tid; t < nt; t += kSortThreads) {
+            const int i = int(uint32_t(s[t]));
+            const int64_t dst = int64_t(b) * N + t;
+            order[dst] = i;
+            if (pos) reinterpret_cast<float2 *>(pos_sorted)[dst] = __ldg(reinterpret_cast<const float2 *>(pos) + int64_t(b) * N + i);
+        }
+    } else {
+        uint64_t *out = sorted + (int64_t(b) * gridDim.x + blockIdx.x) * kSortTile;
+        for (int t = tid; t < kSortTile; t += kSortThreads) out[t] = t < n2 ? s[t] : kSortPad;
+    }
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+tile_rank_kernel(const uint64_t *__restrict__ sorted, int N, int T, int tiles_per_slice, int32_t *__restrict__ rank_out) {
+    __shared__ uint64_t s[kSortTile];
+    const int tid = threadIdx.x, ti = blockIdx.x, b = blockIdx.y;
+    const uint64_t *sb = sorted + int64_t(b) * T * kSortTile;
+    const uint64_t e0 = sb[int64_t(ti) * kSortTile + tid], e1 = sb[int64_t(ti) * kSortTile + kSortThreads + tid];
+    const int j0 = blockIdx.z * tiles_per_slice, j1 = min(T, j0 + tiles_per_slice);
+    int c0 = 0, c1 = 0;
+    for (int tj = j0; tj < j1; ++tj) {
+        if (tj == ti) { c0 += tid; c1 += kSortThreads + tid; continue; }
+        __syncthreads();
+        for (int t = tid; t < kSortTile; t += kSortThreads) s[t] = sb[int64_t(tj) * kSortTile + t];
+        __syncthreads();
+        int p0 = 0, p1 = 0;     // lower_bound over 2048 entries (pads compare above everything)
+#pragma unroll
+        for (int step = kSortTile >> 1; step > 0; step >>= 1) {
+            p0 += s[p0 + step - 1] < e0 ? step : 0;
+            p1 += s[p1 + step - 1] < e1 ? step : 0;
+        }
+        c0 += p0 + (s[p0] < e0 ? 1 : 0);
+        c1 += p1 + (s[p1] < e1 ? 1 : 0);
+    }
+    if (e0 != kSortPad) {
+        int32_t *r = rank_out + int64_t(b) * N + int(uint32_t(e0));
+        if (gridDim.z == 1) *r = c0; else atomicAdd(r, c0);
+    }
+    if (e1 != kSortPad) {
+        int32_t *r = rank_out + int64_t(b) * N + int(uint32_t(e1));
+        if (gridDim.z == 1) *r = c1; else atomicAdd(r, c1);
     }
 }
 
@@ -581,22 +630,28 @@ using namespace affb200;
 static inline size_t al16(size_t x) { return (x + 15) & ~size_t(15); }
 static inline unsigned blocks_for(int64_t total) { return unsigned((total + kIT - 1) / kIT); }
 
-// workspace of the rank sort: composites u64[B*N] | partial ranks i32[B*N]
-static size_t sort_work_bytes(int64_t B, int64_t N) { return al16(size_t(B * N) * 8) + al16(size_t(B * N) * 4); }
+// workspace of the sort: composites u64[B*N] | ranks i32[B*N] | sorted tiles u64[B*T*2048] (slices longer than a tile)
+static size_t sort_work_bytes(int64_t B, int64_t N) {
+    const int64_t T = (N + kSortTile - 1) / kSortTile;
+    return al16(size_t(B * N) * 8) + al16(size_t(B * N) * 4) + (T > 1 ? size_t(B * T) * kSortTile * 8 : 0);
+}
 
-// comp -> order (and optionally pos_sorted); comp and rank live in `work`
+// comp -> order (and optionally pos_sorted); comp, rank and the sorted tiles live in `work` (rank follows comp)
 static int rank_sort(uint64_t *comp, int32_t *rank, int64_t B, int64_t N, int64_t *order, const float *pos,
                      float *pos_sorted, cudaStream_t st) {
-    const int ib = int((N + kIT - 1) / kIT);
-    int64_t ctas = int64_t(ib) * B;
+    const int T = int((N + kSortTile - 1) / kSortTile);
+    uint64_t *sorted = reinterpret_cast<uint64_t *>(reinterpret_cast<char *>(rank) + al16(size_t(B * N) * 4));
+    tile_sort_kernel<<<dim3(T, unsigned(B)), kSortThreads, 0, st>>>(comp, int(N), sorted, order, pos, pos_sorted);
+    if (T == 1) return check_launch("tile_sort", 1);
+    const int64_t ctas = int64_t(T) * B;
     int js = 1;
-    if (ctas < 2 * kNumSMs) js = int(std::min<int64_t>((2 * kNumSMs + ctas - 1) / ctas, (N + kRankTile - 1) / kRankTile));
-    if (js < 1) js = 1;
-    const int per = int((N + js - 1) / js);
+    if (ctas < 2 * kNumSMs) js = int(std::min<int64_t>((2 * kNumSMs + ctas - 1) / ctas, T));
+    const int per = (T + js - 1) / js;
+    js = (T + per - 1) / per;
     if (js > 1 && cudaMemsetAsync(rank, 0, size_t(B * N) * 4, st) != cudaSuccess) return check_launch("rank memset", 0);
-    rank_count_kernel<<<dim3(ib, unsigned(B), js), kIT, 0, st>>>(comp, int(N), per, rank);
+    tile_rank_kernel<<<dim3(T, unsigned(B), js), kSortThreads, 0, st>>>(sorted, int(N), T, per, rank);
     rank_scatter_kernel<<<blocks_for(B * N), kIT, 0, st>>>(rank, B * N, int(N), order, pos, pos_sorted);
-    return check_launch("rank_sort", 2);
+    return check_launch("rank_sort", 3);
 }
 
 static bool idx_dims_ok(const char *what, int64_t B, int64_t N) {

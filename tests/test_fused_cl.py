@@ -138,7 +138,8 @@ def test_plan_contents_against_a_direct_restatement():
     B, n, M = nbhd.shape
     pl = fused_cl.cl_plan(nbhd, mask, pe_idx, (2 * rpw + 1) ** 2)
     assert pl is not None
-    blk, hdr, ucl, qmask, pos16, stats, kb_cnt, kb_tok, q_pe = [None if t is None else t.cpu() for t in pl.keep]
+    blk, hdr, ucl, qmask, pos16, stats, kb_cnt, kb_tok, q_pe = [None if t is None else t.cpu() for t in pl.keep[:9]]
+    assert stats[3].item() == 0 and not pl.keep[9].any()      # no split tiles: second-half headers are zero
     nb, mk, pe, pos = nbhd.cpu(), mask.cpu(), pe_idx.cpu(), p_s.cpu()
     blocks = nb[:, :, ::8] // 8                               # [B, n, 6]: every group of 8 slots is one aligned block
     assert torch.equal(blk.long() & 0xffff, blocks)

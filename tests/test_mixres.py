@@ -148,3 +148,69 @@ def test_cuda_stage_config5_shape_bf16_runs_fused():
     assert torch.equal(outs[0][0], outs[1][0])
     assert torch.isfinite(outs[1][1]).all()
     assert rel(outs[1][1], outs[0][1].cpu()) < 2e-2
+    # under no_grad the stage kept the full 1023 x 1023 table and the block-structured forward evaluated pos_embed on
+    # the central rows its offsets reach; with gradients enabled the stage compacts the table instead (row-union
+    # kernels): the same numbers up to the bf16 rounding of two different kernels
+    from affb200 import fused_cl
+    obs = fused_cl.observed((1, n, 48))
+    assert obs is not None and obs["ok"] and 0 < obs["maxoff"] <= 255, obs
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        p2, o2 = layer(pos, feat, h, w, False)
+    assert torch.equal(p2, outs[1][0])
+    assert rel(o2.float().detach(), outs[1][1].cpu()) < 1e-2, rel(o2.float().detach(), outs[1][1].cpu())
+
+
+def _mixed_scale_positions(seed, h=256, w=512):
+    """token positions of a 4-scale split as the U-shaped model produces them (coarse tokens on an 8-unit grid, half of
+    each scale split into four children, parents kept): 2048 + 4096 + 8192 + 16384 = 30720 tokens"""
+    g = torch.Generator().manual_seed(seed)
+    ys, xs = torch.meshgrid(torch.arange(0, h, 8), torch.arange(0, w, 8), indexing="ij")
+    cur = torch.stack([xs.reshape(-1), ys.reshape(-1)], 1)
+    allp, alls = [], []
+    for s in range(4):
+        allp.append(cur)
+        alls.append(torch.full((cur.shape[0],), s))
+        if s == 3:
+            break
+        pick = torch.randn(cur.shape[0], generator=g).argsort()[cur.shape[0] // 2:]
+        par, half = cur[pick], 2 ** (2 - s)
+        cur = torch.stack([par, par + torch.tensor([half, 0]), par + torch.tensor([0, half]), par + torch.tensor([half, half])],
+                          1).reshape(-1, 2)
+    xy, sc = torch.cat(allp).float(), torch.cat(alls).float()
+    return torch.cat([sc[:, None], xy], 1).unsqueeze(0)
+
+
+@pytest.mark.gpu
+def test_cuda_stage_split_tiles_match_unfused():
+    """Mixed-resolution token sets put more than 64 key blocks behind some tiles of 64 tokens; those tiles carry one
+    union per half (AFFB200_CL_SPLIT) and the block-structured forward still serves the stage.  Checked against the
+    unfused operators on the same weights, on a draw that has split tiles."""
+    from affb200.aff_transformer import CudaOps
+    from affb200.mixres_neighbour import BasicLayer
+    from affb200 import fused as fa, fused_cl
+    from oracle.aff_ops_ref import fill_parameters_by_name
+    seen_split = 0
+    for seed in range(8):
+        pos = _mixed_scale_positions(seed).cuda()
+        n = pos.shape[1]
+        feat = torch.randn(1, n, 64, generator=torch.Generator().manual_seed(seed)).cuda()
+        outs, hits = [], []
+        for fused in (False, True):
+            ops = CudaOps()
+            ops.fused_attention = _counting(fa.fused_cluster_attention, hits) if fused else None
+            layer = BasicLayer(dim=64, cluster_size=8, nbhd_size=48, depth=1, num_heads=2, mlp_ratio=2., ops=ops)
+            fill_parameters_by_name(layer, seed=1)
+            layer.cuda().eval()
+            with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+                p, o = layer(pos, feat, 256, 512, False)
+            outs.append((p, o.float()))
+        st = fused_cl.last_eager_stats
+        assert hits == [True], (seed, st)
+        assert st[0] == 0 and st[1] == 0 and st[4] <= 64, st
+        assert torch.equal(outs[0][0], outs[1][0])
+        err = (outs[1][1] - outs[0][1]).norm(dim=2) / outs[0][1].norm(dim=2).clamp_min(1e-6)      # per token
+        assert rel(outs[1][1], outs[0][1].cpu()) < 2e-2 and err.max().item() < 0.06, (seed, st, err.max().item())
+        seen_split += int(st[3] > 0)
+        if seen_split >= 2:
+            break
+    assert seen_split >= 1, "no draw produced a tile with more than 64 blocks"
