@@ -377,8 +377,9 @@ class _AffRun:
                 q = torch.randn(B, n, hc, device=self.device).bfloat16()
                 kv = torch.randn(B, n, 2 * hc, device=self.device).bfloat16()
                 table = torch.randn(stage_table.shape[0], H, device=self.device).bfloat16()
-                calls = fused.raw_calls(q, kv, H, attn.scale, nbhd, pe_idx, mask, table, attn.blank_k, attn.blank_v,
-                                        pre_table=stage_table)
+                with torch.set_grad_enabled(not self.infer):     # inference builds forward-only plans
+                    calls = fused.raw_calls(q, kv, H, attn.scale, nbhd, pe_idx, mask, table, attn.blank_k, attn.blank_v,
+                                            pre_table=stage_table)
                 if calls is None:
                     continue
                 nidx = 8 * B * n * M * (3 if mask is not None else 2)
@@ -473,6 +474,8 @@ class MaskfinerUDSmallInfer(AffInfer):
         c = super().config(B, world)
         c.update(workload="maskfiner_ud_small_1024x2048_infer",
                  tokens_per_stage=[2048, 6144, 14336, 30720, 14336, 6144, 2048],
+                 l2="the patch-embedding activations (512 x 1024 x 32 fp32 = 64 MB, read and written by three passes) and "
+                    "~80 MB of bf16 weights exceed the 126 MB L2; inputs alternate between two images",
                  step="model.eval() forward of the 7-backbone chain, bf16 autocast; importance scores ~ N(0,1) per step "
                       "as the reference draws them (maskfiner_up_down.py:147-149)")
         return c

@@ -8,8 +8,9 @@ They are differentiable through autograd, run on CPU (and on CUDA), and accept a
 evaluate them in fp32/fp64 on inputs already rounded to the kernel's storage dtype.
 
 Parity pin: these ARE the reference's oracle expressions (no separate golden vectors exist in the reference:
-its tests use unseeded randn and print norms).  tests/golden/clusten_*.pt hold seeded inputs and the outputs of
-these expressions as produced in the build container (script: tests/golden/make_golden.py).
+its tests use unseeded randn and print norms).  They are held against the reference's own compiled CUDA kernels
+(oracle/_ref, tests/test_ref_cuda_parity.py) on the GPU box, and the parity tests evaluate them on seeded inputs
+generated in the test itself (tests/util.py) — there are no stored CLUSTEN fixtures.
 """
 import torch
 
