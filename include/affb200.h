@@ -379,6 +379,29 @@ int affb200_pe_feat_grad(const void *d_vals, const uint16_t *q_pe, const float *
 int affb200_table_grad_u16(const void *d_vals, const uint16_t *pe, int64_t B, int64_t H, int64_t NM, int64_t P,
                            float *d_table, int dtype, void *stream);
 
+/* Block-structured form for images of at most 128 tokens (csrc/fused_cld.cu): dense masked attention over the image,
+ * everything resident on chip — one CTA per (image, head) holds the image's K|V (TMA boxes), the packed positions and the
+ * head's table; a token's neighbourhood is a 16-bit membership word formed from plan->blk.  Replaces the same span of
+ * models/aff_transformer.py:120-155 as affb200_fused_cl_fwd/_bwd (stage 3 of the 224-pixel configs: 125 tokens).
+ *   table_t   [H][tab_stride] of `dtype`: entry (dy + w) * tw + (dx + w) of head h = bias of offset (dx, dy), for
+ *             w = rel_pos_width (or any smaller radius that covers every offset in use), tw = 2w + 1, tw*tw <= 16384,
+ *             tab_stride a multiple of 8 (rows 16-byte aligned)
+ *   blk, pos16, npad   plan->blk, plan->pos16 and its row length ceil(N/64)*64 (affb200_cl_qplan_build)
+ * Backward: ds_work [B][H][N][M] of `dtype` receives dS in ascending-block slot order (pair with plan->q_pe), blank_part
+ * [B][H][2][c] fp32 the per-image sums of d blank_k / d blank_v; dq / dk / dv are fully overwritten.  Head dim 32 only. */
+int affb200_fused_cld_fwd(const affb200_view *q, const affb200_view *k, const affb200_view *v, const affb200_view *out,
+                          const void *table_t, int64_t tab_stride, const float *blank_k, const float *blank_v,
+                          const uint16_t *blk, const uint32_t *pos16, int64_t npad, float *lse, int64_t B, int64_t H,
+                          int64_t N, int64_t M, int64_t c, int64_t rel_pos_width, int64_t table_width, float scale,
+                          int dtype, void *stream);
+int affb200_fused_cld_bwd(const affb200_view *q, const affb200_view *k, const affb200_view *v, const affb200_view *out,
+                          const affb200_view *dout, const affb200_view *dq, const affb200_view *dk,
+                          const affb200_view *dv, const void *table_t, int64_t tab_stride, const float *blank_k,
+                          const float *blank_v, const uint16_t *blk, const uint32_t *pos16, int64_t npad,
+                          const float *lse, void *ds_work, float *blank_part, int64_t B, int64_t H, int64_t N,
+                          int64_t M, int64_t c, int64_t rel_pos_width, int64_t table_width, float scale, int dtype,
+                          void *stream);
+
 /* Same operator for small token sets (N <= AFFB200_FUSED_IMG_MAX_N, M even and <= 96): one CTA per (image, head) keeps the
  * image's K and V resident in shared memory, walks 32-row query tiles, and in the backward accumulates dK and dV on
  * chip (no tile plans, no scatter launches, no P scratch).  affb200_fused_attn_img_prepare derives, once per

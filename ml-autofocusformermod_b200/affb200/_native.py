@@ -74,6 +74,10 @@ SIGNATURES = {
     "affb200_cl_qplan_build_split": (_int, [_ptr] * 4 + [_i64] * 5 + [_ptr] * 8 + [_ptr]),
     "affb200_cl_kplan_build": (_int, [_ptr] + [_i64] * 4 + [_ptr] * 3 + [_ptr]),
     "affb200_cl_pack_pe_sorted": (_int, [_ptr] * 3 + [_i64] * 3 + [_ptr] * 3),
+    "affb200_fused_cld_fwd": (_int, [_ptr] * 4 + [_ptr, _i64] + [_ptr] * 4 + [_i64, _ptr] + [_i64] * 7
+                              + [ctypes.c_float, _int, _ptr]),
+    "affb200_fused_cld_bwd": (_int, [_ptr] * 8 + [_ptr, _i64] + [_ptr] * 4 + [_i64] + [_ptr] * 3 + [_i64] * 7
+                              + [ctypes.c_float, _int, _ptr]),
     "affb200_fused_cl_bwd_grid": (_i64, [_i64] * 3),
     "affb200_fused_cl_bwd": (_int, [_ptr] * 8 + [_ptr] * 3 + [_ptr] + [_ptr] * 5 + [_i64] * 7
                              + [ctypes.c_float, _int, _ptr]),

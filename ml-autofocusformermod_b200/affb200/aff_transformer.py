@@ -343,6 +343,11 @@ class BasicLayer(nn.Module):
             member_idx, cluster_mask = None, None
             rel_pos = (pos[:, None, :, :] + rel_pos_width) - pos[:, :, None, :]          # b x n x n x d
             pe_idx = (rel_pos[..., 1] * table_width + rel_pos[..., 0]).long()
+            if getattr(ops, 'hint_geometry', None) is not None and pe_idx.is_cuda:
+                # all tokens as one neighbourhood of whole 8-row blocks: the block-structured kernels take it
+                nb = global_as_neighbourhood(pe_idx)
+                if nb is not None:
+                    ops.hint_geometry(nb[0], pos, rel_pos_width, table_width)
         else:
             if on_grid:
                 key = (b, n, h, w, str(pos.device), id(ops), COMPACT_ROWS_ABOVE)

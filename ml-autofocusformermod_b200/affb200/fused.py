@@ -352,6 +352,96 @@ class FusedClusterAttentionCl(Function):
                 db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt), None, None, None, None)
 
 
+def _table_t(table, w, tw, r, dt):
+    """[H][pad8((2r+1)^2)] table of dtype dt for the resident-key dense kernels: the rows of `table` [tw*tw, H] fp32 for
+    offsets |dx|, |dy| <= r, one contiguous row per head."""
+    H = table.shape[1]
+    n = (2 * r + 1) ** 2
+    out = torch.zeros((H, (n + 7) // 8 * 8), dtype=dt, device=table.device)
+    sub = table.view(tw, tw, H)[w - r:w + r + 1, w - r:w + r + 1] if r < w else table.view(tw, tw, H)
+    out[:, :n] = sub.reshape(n, H).t()
+    return out
+
+
+class FusedClusterAttentionCld(Function):
+    """Block-structured neighbourhoods of images with at most 128 tokens: dense masked attention over the image with
+    keys, positions and the bias table resident in shared memory (csrc/fused_cld.cu)."""
+
+    @staticmethod
+    def forward(ctx, q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx, pe_feat, clp, meta):
+        H, scale, r = meta
+        B, n, hc = q_lin.shape
+        c = hc // H
+        M = nbhd_idx.shape[2]
+        dev = q_lin.device
+        q_lin = q_lin.contiguous()
+        kv_lin = kv_lin.contiguous()
+        table = _table_of(pe_table, pe_w, pe_b, pe_feat)
+        tt = _table_t(table, clp.w, clp.tw, r, q_lin.dtype)
+        bk = blank_k.detach().float().contiguous()
+        bv = blank_v.detach().float().contiguous()
+        blk, pos16 = clp.keep[0], clp.keep[4]
+        with torch.cuda.device(dev):
+            out = torch.empty_like(q_lin)
+            lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_fused_cld_fwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), N.p(tt), tt.shape[1], N.p(bk),
+                N.p(bv), N.p(blk), N.p(pos16), clp.npad, N.p(lse), B, H, n, M, c, r, 2 * r + 1, float(scale),
+                N.dtype_enum(q_lin), N.stream_ptr(dev)), "fused_cld_fwd")
+        ctx.save_for_backward(q_lin, kv_lin, out, lse, tt, bk, bv)
+        ctx.clp = clp
+        ctx.M = M
+        ctx.meta = (H, scale, r, None if pe_table is None else pe_table.dtype, blank_k.dtype, table.shape[0])
+        ctx.pe_lin = None if pe_w is None else (pe_feat, pe_w.shape[1], pe_w.dtype, pe_b.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        q_lin, kv_lin, out, lse, tt, bk, bv = ctx.saved_tensors
+        H, scale, r, table_dt, blank_dt, P = ctx.meta
+        clp, M = ctx.clp, ctx.M
+        B, n, hc = q_lin.shape
+        c = hc // H
+        dev = q_lin.device
+        d_out = d_out.contiguous()
+        if d_out.dtype != q_lin.dtype:
+            d_out = d_out.to(q_lin.dtype)
+        blk, pos16 = clp.keep[0], clp.keep[4]
+        with torch.cuda.device(dev):
+            dq = torch.empty_like(q_lin)
+            dkv = torch.empty_like(kv_lin)
+            ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+            blank_part = torch.empty((B, H, 2, c), dtype=torch.float32, device=dev)
+            N.check(N.LIB.affb200_fused_cld_bwd(
+                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
+                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
+                _view(dq, n * hc, hc, c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c, c),
+                N.p(tt), tt.shape[1], N.p(bk), N.p(bv), N.p(blk), N.p(pos16), clp.npad, N.p(lse), N.p(ds),
+                N.p(blank_part), B, H, n, M, c, r, 2 * r + 1, float(scale), N.dtype_enum(q_lin), N.stream_ptr(dev)),
+                "fused_cld_bwd")
+            db = _col_sum(blank_part.view(B, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
+            dw = dpb = d_table = None
+            if ctx.pe_lin is not None:
+                pe_feat, F, w_dt, b_dt = ctx.pe_lin
+                dw, dpb = _pe_grad(ds, clp.q_pe, pe_feat, B, H, n * M, F, w_dt, b_dt)
+            else:
+                d_table = torch.empty((P, H), dtype=torch.float32, device=dev)
+                N.check(N.LIB.affb200_table_grad_u16(N.p(ds), N.p(clp.q_pe), B, H, n * M, P, N.p(d_table),
+                                                     N.dtype_enum(ds), N.stream_ptr(dev)), "table_grad_u16")
+        return (dq, dkv, None if d_table is None else d_table.to(table_dt), dw, dpb,
+                db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt), None, None, None, None)
+
+
+def _cld_radius(clp, n, c):
+    """table radius for the resident-key dense kernels, or None when they do not apply"""
+    from . import fused_cl
+    if n > fused_cl.CLD_MAX_N or c != 32 or os.environ.get("AFFB200_FUSED_CLD", "1") == "0":
+        return None
+    r = clp.sub_r if clp.sub_r is not None else clp.w
+    return r if (2 * r + 1) ** 2 <= 16384 else None
+
+
 _ctypes_sigs_done = False
 
 
@@ -393,11 +483,18 @@ def fused_cluster_attention(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, c
         return None
     plan = get_plan(nbhd_idx)
     cl_first = os.environ.get("AFFB200_CL_FIRST", "0") != "0"   # block-structured kernels also for small token sets
-    if (cl_first or not _use_img(n, nbhd_idx.shape[2])) and num_heads % 2 == 0 and num_heads * c <= 512:
-        from . import fused_cl
+    from . import fused_cl
+    needs_grad = torch.is_grad_enabled() and any(
+        t is not None and t.requires_grad for t in (q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v))
+    if n <= fused_cl.CLD_MAX_N and c == 32:      # small images: dense masked attention, everything resident
         clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, P)
-        needs_grad = torch.is_grad_enabled() and any(
-            t is not None and t.requires_grad for t in (q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v))
+        r = None if clp is None else _cld_radius(clp, n, c)
+        if r is not None and (pe_w is None or (n * nbhd_idx.shape[2]) % 8 == 0) and (clp.q_pe is not None or not needs_grad):
+            _note(n, num_heads, "resident-key dense")
+            return FusedClusterAttentionCld.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx,
+                                                  pe_feat, clp, (num_heads, scale, r))
+    if (cl_first or not _use_img(n, nbhd_idx.shape[2])) and num_heads % 2 == 0 and num_heads * c <= 512:
+        clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, P)
         if clp is not None and (pe_w is None or (n * nbhd_idx.shape[2]) % 8 == 0) and (clp.q_pe is not None or not needs_grad):
             _note(n, num_heads, "block-structured")
             return FusedClusterAttentionCl.apply(q_lin, kv_lin, pe_table, pe_w, pe_b, blank_k, blank_v, nbhd_idx,
@@ -457,8 +554,13 @@ def raw_calls(q_lin, kv_lin, num_heads, scale, nbhd_idx, pe_idx, cluster_mask, p
     dev = q_lin.device
     plan = get_plan(nbhd_idx)
     cl_first = os.environ.get("AFFB200_CL_FIRST", "0") != "0"
+    from . import fused_cl
+    if n <= fused_cl.CLD_MAX_N and c == 32:
+        clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, pe_table.shape[0])
+        r = None if clp is None else _cld_radius(clp, n, c)
+        if r is not None:
+            return _raw_calls_cld(clp, r, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, blank_v, pre_table)
     if (cl_first or not _use_img(n, M)) and H % 2 == 0 and H * c <= 512 and c in (16, 32):
-        from . import fused_cl
         clp = fused_cl.cl_plan(nbhd_idx, cluster_mask, pe_idx, pe_table.shape[0])
         if clp is not None:
             return _raw_calls_cl(clp, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, blank_v, pre_table)
@@ -548,6 +650,48 @@ def _raw_calls_cl(clp, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, bla
     fwd._keep = keep
     fwd.family = "block-structured"
     return fwd, (bwd if clp.q_pe is not None else None)   # tables above 32 768 rows: forward only
+
+
+def _raw_calls_cld(clp, r, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, blank_v, pre_table=None):
+    """(fwd, bwd) closures of the resident-key dense kernels; bwd = the backward kernel and the bias-generator gradient
+    from dS (what the model's backward launches, minus the column sums of the blank-token partials)."""
+    B, n, hc = q_lin.shape
+    c = hc // H
+    M = nbhd_idx.shape[2]
+    dev = q_lin.device
+    table = pe_table.detach().float().contiguous()
+    tt = _table_t(table, clp.w, clp.tw, r, q_lin.dtype)
+    bk, bv = blank_k.detach().float().contiguous(), blank_v.detach().float().contiguous()
+    out, dq, dkv, dout = torch.empty_like(q_lin), torch.empty_like(q_lin), torch.empty_like(kv_lin), torch.randn_like(q_lin)
+    lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
+    ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
+    blank_part = torch.empty((B, H, 2, c), dtype=torch.float32, device=dev)
+    d_table = torch.empty((table.shape[0], H), dtype=torch.float32, device=dev)
+    blk, pos16 = clp.keep[0], clp.keep[4]
+    de, sp = N.dtype_enum(q_lin), N.stream_ptr(dev)
+    keep = [clp, table, tt, bk, bv, out, dq, dkv, dout, lse, ds, blank_part, d_table]
+    pe_grad = _raw_pe_grad(pre_table, ds, clp.q_pe, B, H, n * M, keep)
+    V = lambda t, off=0, kv=False: _view(t, n * (2 * hc if kv else hc), 2 * hc if kv else hc, 2 * c if kv else c, off)
+
+    def fwd():
+        N.check(N.LIB.affb200_fused_cld_fwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), N.p(tt), tt.shape[1],
+                                            N.p(bk), N.p(bv), N.p(blk), N.p(pos16), clp.npad, N.p(lse), B, H, n, M, c, r,
+                                            2 * r + 1, float(scale), de, sp), "fused_cld_fwd")
+
+    def bwd():
+        N.check(N.LIB.affb200_fused_cld_bwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), V(dout), V(dq),
+                                            V(dkv, 0, True), V(dkv, c, True), N.p(tt), tt.shape[1], N.p(bk), N.p(bv),
+                                            N.p(blk), N.p(pos16), clp.npad, N.p(lse), N.p(ds), N.p(blank_part), B, H, n, M,
+                                            c, r, 2 * r + 1, float(scale), de, sp), "fused_cld_bwd")
+        if pe_grad is not None:
+            pe_grad()
+        else:
+            N.check(N.LIB.affb200_table_grad_u16(N.p(ds), N.p(clp.q_pe), B, H, n * M, table.shape[0], N.p(d_table), de, sp),
+                    "table_grad_u16")
+
+    fwd._keep = keep
+    fwd.family = "resident-key dense"
+    return fwd, (bwd if clp.q_pe is not None else None)
 
 
 def _raw_calls_img(q_lin, kv_lin, H, scale, nbhd_idx, pe_idx, cluster_mask, pe_table, blank_k, blank_v, pre_table=None):

@@ -20,6 +20,7 @@ CL_T = 64
 CL_UMAX = 64
 KBCAP_STEP = 16
 UCAP_SLACK = 3
+CLD_MAX_N = 128        # images up to this many tokens take the resident-key dense kernels (csrc/fused_cld.cu)
 UCAP_TWO_CTAS = 44     # largest union for which two CTAs of the forward kernel share an SM at head dim 32
 SUB_RADII = (31, 63, 127, 255)     # forward-only plans over a large table: the bias table is evaluated on the central
                                    # (2R+1)^2 rows only, R the smallest of these that covers every (token, key) offset
@@ -65,6 +66,7 @@ class ClPlan:
         self.kbcap = 0
         self.q_pe = None
         self.sub_r = None      # table radius the forward may use instead of w (see SUB_RADII), or None
+        self.npad = self.tiles * CL_T
 
     def byref(self):
         return ctypes.byref(self.struct)
@@ -139,7 +141,8 @@ def _build(nbhd_idx, mask, pe_idx, pos, w, tw, P, need_bwd=True):
                 N.check(N.LIB.affb200_cl_pack_pe_sorted(N.p(pe_c), N.p(mk_c), N.p(blk), B, n, M, N.p(q_pe), N.p(bad), sp),
                         "cl_pack_pe_sorted")
         sub_r = None
-        want_sub = (not need_bwd) and P > 32768
+        # a table radius below w serves the forward over large tables and the resident-key kernels of small images
+        want_sub = ((not need_bwd) and P > 32768) or n <= CLD_MAX_N
         if static:
             # a little room above the largest union seen: neighbourhoods of the data-dependent stages vary per batch
             ucap = min(CL_UMAX, obs["ucap"] + UCAP_SLACK)
