@@ -256,6 +256,125 @@ merge_bwd_f_kernel(const float *__restrict__ d_out, const float *__restrict__ ta
     mg_store<TF, CPL>(d_feat + row * C + lane * CPL, acc);
 }
 
+// The same gradient with a warp per ALIGNED BLOCK OF 8 source rows.  Neighbourhoods are whole clusters of 8 consecutive
+// rows (reference models/point_utils.py:203-206, aff_transformer.py:476-480), so the 8 rows of a block are referenced by
+// the same kept tokens, in slots j .. j+7 of each: the token's four d_out rows (the bulk of the traffic: 4*C fp32) are
+// loaded once and serve all 8 destination rows (the per-row kernel re-reads them 8 times: 7.7 GB through L2 at the first
+// merge of AFF-Tiny-1/5).  The structure is checked on the block's own CSR lists first (equal lengths, entry e + u for row
+// u); a block without it takes the per-row walk, so any index tensor gives the same sums in the same order.
+template <typename TF, typename TL, int CPL>
+__global__ void __launch_bounds__(kMT)
+merge_bwd_f8_kernel(const float *__restrict__ d_out, const float *__restrict__ table, const int64_t *__restrict__ pe_idx,
+                    const int64_t *__restrict__ mask, const TL *__restrict__ lp, const int32_t *__restrict__ off,
+                    const int32_t *__restrict__ ent, TF *__restrict__ d_feat, int64_t n_blocks, int Nq, int Nk, int M,
+                    FastDiv divM) {
+    constexpr int C = CPL * 32;
+    __shared__ float4 ts_all[kMW][4][8];
+    __shared__ int ti_all[kMW][4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t blk = int64_t(blockIdx.x) * kMW + warp;
+    if (blk >= n_blocks) return;
+    const int bpi = (Nk + 7) >> 3;
+    const int64_t b = blk / bpi;
+    const int r0 = int(blk - b * bpi) * 8;
+    const int nrow = min(8, Nk - r0);
+    const int32_t *o = off + b * (Nk + 1) + r0;
+    const int32_t *eb = ent + b * int64_t(Nq) * M;
+    const int64_t base = b * int64_t(Nq) * M;
+    const float *gb = d_out + b * int64_t(Nq) * 4 * C + lane * CPL;
+    const int kk = lane >> 3, u = lane & 7;
+    const int beg_u = u < nrow ? o[u] : 0, cnt_u = u < nrow ? o[u + 1] - beg_u : 0;
+    const int beg0 = __shfl_sync(0xffffffffu, beg_u, 0), cnt = __shfl_sync(0xffffffffu, cnt_u, 0);
+    // structure check
+    bool bad = u < nrow && cnt_u != cnt;
+    for (int k = kk; k < cnt && !bad; k += 4) {
+        const int e0 = __ldg(eb + beg0 + k);
+        if (u < nrow && u > 0 && __ldg(eb + beg_u + k) != e0 + u) bad = true;
+    }
+    if (__any_sync(0xffffffffu, bad)) {     // per-row walk (identical to merge_bwd_f_kernel)
+        for (int uu = 0; uu < nrow; ++uu) {
+            const int beg = o[uu], end = o[uu + 1];
+            float acc[CPL];
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) acc[c] = 0.f;
+            for (int k0 = beg; k0 < end; k0 += 32) {
+                const int k = k0 + lane;
+                int e = 0;
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (k < end) {
+                    e = __ldg(eb + k);
+                    if (!(mask && __ldg(mask + base + e) == 0)) t = __ldg(reinterpret_cast<const float4 *>(table) + __ldg(pe_idx + base + e));
+                }
+                const int n = min(32, end - k0);
+                for (int v = 0; v < n; ++v) {
+                    const int eu = __shfl_sync(0xffffffffu, e, v);
+                    const float tx = __shfl_sync(0xffffffffu, t.x, v), ty = __shfl_sync(0xffffffffu, t.y, v);
+                    const float tz = __shfl_sync(0xffffffffu, t.z, v), tw = __shfl_sync(0xffffffffu, t.w, v);
+                    const float *gi = gb + int64_t(divM.div(uint32_t(eu))) * 4 * C;
+                    float g0[CPL], g1[CPL], g2[CPL], g3[CPL];
+                    mg_load<float, CPL>(gi, g0);
+                    mg_load<float, CPL>(gi + C, g1);
+                    mg_load<float, CPL>(gi + 2 * C, g2);
+                    mg_load<float, CPL>(gi + 3 * C, g3);
+#pragma unroll
+                    for (int c = 0; c < CPL; ++c) acc[c] += tx * g0[c] + ty * g1[c] + tz * g2[c] + tw * g3[c];
+                }
+            }
+            const int64_t row = b * Nk + r0 + uu;
+            const float sc = lp ? Elem<TL>::to_acc(__ldg(lp + row)) : 1.f;
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) acc[c] *= sc;
+            mg_store<TF, CPL>(d_feat + row * C + lane * CPL, acc);
+        }
+        return;
+    }
+    float acc[8][CPL];
+#pragma unroll
+    for (int uu = 0; uu < 8; ++uu)
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) acc[uu][c] = 0.f;
+    float4(*ts)[8] = ts_all[warp];
+    int *ti = ti_all[warp];
+    for (int k0 = 0; k0 < cnt; k0 += 4) {
+        // lane (kk, u): the weight quadruple of (referencing token k0 + kk, destination row u)
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k0 + kk < cnt) {
+            const int e = __ldg(eb + beg0 + k0 + kk) + u;
+            if (u < nrow && !(mask && __ldg(mask + base + e) == 0)) t = __ldg(reinterpret_cast<const float4 *>(table) + __ldg(pe_idx + base + e));
+            if (u == 0) ti[kk] = int(divM.div(uint32_t(e)));
+        }
+        ts[kk][u] = t;
+        __syncwarp();
+        const int n = min(4, cnt - k0);
+        for (int v = 0; v < n; ++v) {
+            const float *gi = gb + int64_t(ti[v]) * 4 * C;
+            float g0[CPL], g1[CPL], g2[CPL], g3[CPL];
+            mg_load<float, CPL>(gi, g0);
+            mg_load<float, CPL>(gi + C, g1);
+            mg_load<float, CPL>(gi + 2 * C, g2);
+            mg_load<float, CPL>(gi + 3 * C, g3);
+#pragma unroll
+            for (int uu = 0; uu < 8; ++uu) {
+                const float4 tv = ts[v][uu];
+#pragma unroll
+                for (int c = 0; c < CPL; ++c) acc[uu][c] += tv.x * g0[c] + tv.y * g1[c] + tv.z * g2[c] + tv.w * g3[c];
+            }
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int uu = 0; uu < 8; ++uu) {
+        if (uu < nrow) {
+            const int64_t row = b * Nk + r0 + uu;
+            const float sc = lp ? Elem<TL>::to_acc(__ldg(lp + row)) : 1.f;
+            float outv[CPL];
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) outv[c] = acc[uu][c] * sc;
+            mg_store<TF, CPL>(d_feat + row * C + lane * CPL, outv);
+        }
+    }
+}
+
 template <typename F> static int mg_dispatch(int dtype, F &&f) {
     switch (dtype) {
         case AFFB200_F32: return f(float{});
@@ -347,9 +466,16 @@ extern "C" int affb200_merge_bwd(const float *d_out, const float *table, const i
                                                                          (const TF *)feat, d_wt, d_lp, n_tok, int(Nq), int(Nk), int(M));
                 if (int e = check_launch("merge_bwd_w")) return e;
                 if (!d_feat) return int(AFFB200_OK);
-                merge_bwd_f_kernel<TF, TL, CPL><<<unsigned((n_rows + kMW - 1) / kMW), kMT, 0, st>>>(
-                    d_out, table, pe_idx, mask, (const TL *)lp, csr_off, csr_ent, (TF *)d_feat, n_rows, int(Nq), int(Nk), int(M),
-                    FastDiv{uint32_t(M)});
+                if constexpr (CPL <= 8) {      // a warp per block of 8 source rows: d_out rows loaded once per referencing token
+                    const int64_t n_blocks = B * ((Nk + 7) / 8);
+                    merge_bwd_f8_kernel<TF, TL, CPL><<<unsigned((n_blocks + kMW - 1) / kMW), kMT, 0, st>>>(
+                        d_out, table, pe_idx, mask, (const TL *)lp, csr_off, csr_ent, (TF *)d_feat, n_blocks, int(Nq), int(Nk),
+                        int(M), FastDiv{uint32_t(M)});
+                } else {
+                    merge_bwd_f_kernel<TF, TL, CPL><<<unsigned((n_rows + kMW - 1) / kMW), kMT, 0, st>>>(
+                        d_out, table, pe_idx, mask, (const TL *)lp, csr_off, csr_ent, (TF *)d_feat, n_rows, int(Nq), int(Nk), int(M),
+                        FastDiv{uint32_t(M)});
+                }
                 return check_launch("merge_bwd_f");
             });
         });
