@@ -405,8 +405,9 @@ class _AffRun:
         try:
             import json
             tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_ncu_traffic.json")))
-            traffic = tj["per_launch_group"].get(top["kernel"], {}).get("dram_bytes")
-            traffic_src = "profiles/r02_ncu_traffic.json @ %s" % tj.get("commit")
+            if tj.get("model") == self.wl.model_name and tj.get("batch_per_gpu") == self.B:    # the capture's own shapes only
+                traffic = tj["per_launch_group"].get(top["kernel"], {}).get("dram_bytes")
+                traffic_src = "profiles/r02_ncu_traffic.json @ %s" % tj.get("commit")
         except Exception:
             traffic = None
         return {"bound": "hbm", "kernel": top["kernel"], "achieved": top["GBps"], "peak": peak, "unit": "GB/s",

@@ -326,24 +326,34 @@ class FusedClusterAttentionCl(Function):
             d_out = d_out.to(q_lin.dtype)
         with torch.cuda.device(dev):
             from .plan import guard_tensor
-            grid = N.LIB.affb200_fused_cl_bwd_grid(B, H, n)
             dq = torch.empty_like(q_lin)
             dkv = torch.empty_like(kv_lin)
             ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
             delta = torch.empty((B, H, n), dtype=torch.float32, device=dev)
-            blank_part = torch.empty((grid * 8, H, 2, c), dtype=torch.float32, device=dev)
-            N.check(N.LIB.affb200_fused_cl_bwd(
-                _view(q_lin, n * hc, hc, c), _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c),
-                _view(kv_lin, n * 2 * hc, 2 * hc, 2 * c, c), _view(out, n * hc, hc, c), _view(d_out, n * hc, hc, c),
-                _view(dq, n * hc, hc, c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c), _view(dkv, n * 2 * hc, 2 * hc, 2 * c, c),
-                N.p(table), N.p(bk), N.p(bv), clp.byref(), N.p(lse), N.p(delta), N.p(ds), N.p(blank_part),
-                N.p(guard_tensor(dev)), B, H, n, M, c, clp.w, clp.tw, float(scale), N.dtype_enum(q_lin),
-                N.stream_ptr(dev)), "fused_cl_bwd")
-            db = _col_sum(blank_part.view(grid * 8, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
+            # Optionally (AFFB200_BWD_L2_MB, see _bwd_chunk) the batch goes through in chunks of images small enough for the
+            # 126 MB L2, so that the key-major kernel and the bias gradient find Q / K|V / dO / dS of the chunk on chip.
+            cb = _bwd_chunk(B, n, hc, H, M, q_lin.element_size()) if ctx.pe_lin is not None else B
+            grids = [int(N.LIB.affb200_fused_cl_bwd_grid(min(cb, B - b0), H, n)) for b0 in range(0, B, cb)]
+            blank_part = torch.empty((sum(grids) * 8, H, 2, c), dtype=torch.float32, device=dev)
             dw = dpb = d_table = None
+            es, row0 = q_lin.element_size(), 0
+            for ci, b0 in enumerate(range(0, B, cb)):
+                bn = min(cb, B - b0)
+                V = lambda t, w_, off=0: _view(t, n * w_, w_, (2 * c if w_ == 2 * hc else c), b0 * n * w_ + off)
+                N.check(N.LIB.affb200_fused_cl_bwd(
+                    V(q_lin, hc), V(kv_lin, 2 * hc), V(kv_lin, 2 * hc, c), V(out, hc), V(d_out, hc),
+                    V(dq, hc), V(dkv, 2 * hc), V(dkv, 2 * hc, c),
+                    N.p(table), N.p(bk), N.p(bv), clp.byref_images(b0), N.p(lse[b0:]), N.p(delta[b0:]), N.p(ds[b0:]),
+                    N.p(blank_part[row0:]), N.p(guard_tensor(dev)), bn, H, n, M, c, clp.w, clp.tw, float(scale),
+                    N.dtype_enum(q_lin), N.stream_ptr(dev)), "fused_cl_bwd")
+                row0 += grids[ci] * 8
+                if ctx.pe_lin is not None:
+                    pe_feat, F, w_dt, b_dt = ctx.pe_lin
+                    w1, b1 = _pe_grad(ds[b0:b0 + bn], clp.q_pe[b0:b0 + bn], pe_feat, bn, H, n * M, F, torch.float32, torch.float32)
+                    dw, dpb = (w1, b1) if dw is None else (dw + w1, dpb + b1)     # fixed order over the chunks
+            db = _col_sum(blank_part.view(-1, H * 2 * c)).view(H, 2, c)   # fixed-order fp32 column sums
             if ctx.pe_lin is not None:
-                pe_feat, F, w_dt, b_dt = ctx.pe_lin
-                dw, dpb = _pe_grad(ds, clp.q_pe, pe_feat, B, H, n * M, F, w_dt, b_dt)
+                dw, dpb = dw.to(ctx.pe_lin[2]), dpb.to(ctx.pe_lin[3])
             else:
                 d_table = torch.empty((P, H), dtype=torch.float32, device=dev)
                 N.check(N.LIB.affb200_table_grad_u16(N.p(ds), N.p(clp.q_pe), B, H, n * M, P, N.p(d_table),
@@ -431,6 +441,18 @@ class FusedClusterAttentionCld(Function):
                                                      N.dtype_enum(ds), N.stream_ptr(dev)), "table_grad_u16")
         return (dq, dkv, None if d_table is None else d_table.to(table_dt), dw, dpb,
                 db[:, 0].reshape(-1).to(blank_dt), db[:, 1].reshape(-1).to(blank_dt), None, None, None, None)
+
+
+def _bwd_chunk(B, n, hc, H, M, es):
+    """images per backward chunk: the chunk's operands (q, kv, out, d_out, dq, dkv, dS) within AFFB200_BWD_L2_MB.
+    Off by default (0): measured inside the graph-replayed step, chunks of 72 / 110 MB cost 36.2 / 35.7 ms per step against
+    34.2 ms for the whole batch at once — the partial last wave of every chunk launch outweighs the second read of the
+    operands from HBM (1.98x the float-operand bytes, profiles/r02_ncu_traffic.json)."""
+    mb = float(os.environ.get("AFFB200_BWD_L2_MB", "0"))
+    if mb <= 0:
+        return B
+    per_image = n * hc * es * 8 + n * H * M * es + n * M * 2
+    return max(1, min(B, int(mb * 1e6 // per_image)))
 
 
 def _cld_radius(clp, n, c):
@@ -622,13 +644,17 @@ def _raw_calls_cl(clp, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, bla
     lse = torch.empty((B, H, n), dtype=torch.float32, device=dev)
     delta = torch.empty((B, H, n), dtype=torch.float32, device=dev)
     ds = torch.empty((B, H, n, M), dtype=q_lin.dtype, device=dev)
-    grid = N.LIB.affb200_fused_cl_bwd_grid(B, H, n)
-    blank_part = torch.empty((grid * 8, H, 2, c), dtype=torch.float32, device=dev)
+    cb = _bwd_chunk(B, n, hc, H, M, q_lin.element_size()) if (pre_table is not None and clp.q_pe is not None) else B
+    chunks = [(b0, min(cb, B - b0)) for b0 in range(0, B, cb)]
+    grids = [int(N.LIB.affb200_fused_cl_bwd_grid(bn, H, n)) for _, bn in chunks]
+    blank_part = torch.empty((sum(grids) * 8, H, 2, c), dtype=torch.float32, device=dev)
     d_table = torch.empty((table.shape[0], H), dtype=torch.float32, device=dev)
     guard = guard_tensor(dev)
     de, sp = N.dtype_enum(q_lin), N.stream_ptr(dev)
     keep = [clp, table, bk, bv, out, dq, dkv, dout, lse, delta, ds, blank_part, d_table]
-    pe_grad = _raw_pe_grad(pre_table, ds, clp.q_pe, B, H, n * M, keep)
+    pe_grads = [_raw_pe_grad(pre_table, ds[b0:b0 + bn], None if clp.q_pe is None else clp.q_pe[b0:b0 + bn], bn, H, n * M, keep)
+                for b0, bn in chunks]
+    pe_grad = pe_grads[0]
     V = lambda t, off=0, kv=False: _view(t, n * (2 * hc if kv else hc), 2 * hc if kv else hc, 2 * c if kv else c, off)
 
     def fwd():
@@ -637,12 +663,19 @@ def _raw_calls_cl(clp, q_lin, kv_lin, H, scale, nbhd_idx, pe_table, blank_k, bla
                                            float(scale), de, sp), "fused_cl_fwd")
 
     def bwd():
-        N.check(N.LIB.affb200_fused_cl_bwd(V(q_lin), V(kv_lin, 0, True), V(kv_lin, c, True), V(out), V(dout), V(dq),
-                                           V(dkv, 0, True), V(dkv, c, True), N.p(table), N.p(bk), N.p(bv), clp.byref(),
-                                           N.p(lse), N.p(delta), N.p(ds), N.p(blank_part), N.p(guard), B, H, n, M, c,
-                                           clp.w, clp.tw, float(scale), de, sp), "fused_cl_bwd")
+        row0 = 0
+        for (b0, bn), gr, pg in zip(chunks, grids, pe_grads):     # image chunks sized for the L2 (as the model's backward)
+            oq, okv = b0 * n * hc, b0 * n * 2 * hc
+            N.check(N.LIB.affb200_fused_cl_bwd(V(q_lin, oq), V(kv_lin, okv, True), V(kv_lin, okv + c, True), V(out, oq),
+                                               V(dout, oq), V(dq, oq), V(dkv, okv, True), V(dkv, okv + c, True), N.p(table),
+                                               N.p(bk), N.p(bv), clp.byref_images(b0), N.p(lse[b0:]), N.p(delta[b0:]),
+                                               N.p(ds[b0:]), N.p(blank_part[row0:]), N.p(guard), bn, H, n, M, c,
+                                               clp.w, clp.tw, float(scale), de, sp), "fused_cl_bwd")
+            row0 += gr * 8
+            if pg is not None:
+                pg()
         if pe_grad is not None:
-            pe_grad()
+            pass
         else:
             N.check(N.LIB.affb200_table_grad_u16(N.p(ds), N.p(clp.q_pe), B, H, n * M, table.shape[0], N.p(d_table), de, sp),
                     "table_grad_u16")

@@ -71,6 +71,27 @@ class ClPlan:
     def byref(self):
         return ctypes.byref(self.struct)
 
+    def byref_images(self, b0):
+        """the plan of images b0, b0+1, ... (every array is image-major: the same struct with offset pointers)"""
+        if b0 == 0:
+            return ctypes.byref(self.struct)
+        s, t = ClPlanStruct(), self.struct
+        nblk, nb = (self.n + 7) // 8, self.M // 8
+        s.ucap, s.kbcap = t.ucap, t.kbcap
+        s.q_hdr = t.q_hdr + 4 * b0 * self.tiles
+        s.q_ucl = t.q_ucl + 2 * b0 * self.tiles * CL_UMAX
+        s.q_mask = t.q_mask + 8 * b0 * self.npad
+        s.pos16 = t.pos16 + 4 * b0 * self.npad
+        s.blk = t.blk + 2 * b0 * self.n * nb
+        s.kb_cnt = t.kb_cnt + 4 * b0 * nblk if t.kb_cnt else None
+        s.kb_tok = t.kb_tok + 4 * b0 * nblk * t.kbcap if t.kb_tok else None
+        s.q_pe = t.q_pe + 2 * b0 * self.n * self.M if t.q_pe else None
+        s.q_hdr2 = t.q_hdr2 + 4 * b0 * self.tiles if t.q_hdr2 else None
+        s.q_ucl2 = t.q_ucl2 + 2 * b0 * self.tiles * CL_UMAX if t.q_ucl2 else None
+        self._chunk_structs = getattr(self, "_chunk_structs", {})
+        self._chunk_structs[b0] = s          # keeps the struct alive for the (asynchronous) launch
+        return ctypes.byref(s)
+
 
 def _radius(maxoff, w):
     for r in SUB_RADII:

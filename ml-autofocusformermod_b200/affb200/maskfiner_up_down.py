@@ -278,7 +278,11 @@ def _split_rows(tensors, key_col, n_groups, cache_key):
         sizes = counts[0].tolist()
         assert len(sizes) == n_groups, sizes
         _group_sizes[cache_key] = sizes
-    order = k8.argsort(dim=1, stable=True)
+    if k8.is_cuda:        # affb200_argsort_f32 (tile sort + rank merge): a fraction of torch's radix-sort launch chain
+        from .point_utils import argsort_stable
+        order = argsort_stable(k8.float())
+    else:
+        order = k8.argsort(dim=1, stable=True)
     out, at = [], 0
     for n in sizes:
         idx = order[:, at:at + n]

@@ -354,3 +354,31 @@ def test_resident_key_dense_pos_embed_form_and_old_kernels_agree(cld_calls, monk
         # dW / db are sums with heavy cancellation over the bf16-rounded dS of two different kernels (their exact relation
         # to each kernel's own dS is held in test_block_structured_pos_embed_form)
         assert rel_err(a, r.float()) < (5e-2 if nm in ("dW", "db") else 1e-2), (nm, rel_err(a, r.float()))
+
+
+def test_backward_in_image_chunks_gives_the_same_gradients(cl_calls, monkeypatch):
+    """AFFB200_BWD_L2_MB: the backward over chunks of images (plan arrays and operands offset per chunk) — d_q / d_kv
+    bit-equal to the whole batch at once, the bias-generator gradient equal up to the order of its partial sums"""
+    from affb200.fused import fused_cluster_attention
+    from affb200.aff_transformer import build_pe_lookup
+    nbhd, mask, pe_idx, rpw, _ = _setup(56, 56, 627, 5, 8, 48, 224)
+    pre_table = build_pe_lookup(224)[2].cuda()
+    B, n, H, c, dt = 5, 627, 4, 32, torch.bfloat16
+    res = []
+    for mb in ("0", "0.7"):        # 0.7 MB: two images per chunk (one image: 2 * 627 * 128 * 8 + ... = 0.33 MB)
+        monkeypatch.setenv("AFFB200_BWD_L2_MB", mb)
+        g = torch.Generator().manual_seed(17)
+        q = torch.randn(B, n, H * c, generator=g).to(dt).cuda().requires_grad_(True)
+        kv = torch.randn(B, n, 2 * H * c, generator=g).to(dt).cuda().requires_grad_(True)
+        W = (0.2 * torch.randn(H, 5, generator=g)).cuda().requires_grad_(True)
+        b = (0.2 * torch.randn(H, generator=g)).cuda().requires_grad_(True)
+        bk = torch.randn(H * c, generator=g).cuda().requires_grad_(True)
+        bv = torch.randn(H * c, generator=g).cuda().requires_grad_(True)
+        go = torch.randn(B, n, H * c, generator=g).to(dt).cuda()
+        out = fused_cluster_attention(q, kv, H, c ** -0.5, nbhd, pe_idx, mask, None, bk, bv, pos_embed=(pre_table, W, b))
+        out.backward(go)
+        res.append([q.grad, kv.grad, W.grad, b.grad, bk.grad, bv.grad])
+    assert cl_calls == [1, 1]
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+    for a, r in zip(res[1][2:], res[0][2:]):
+        assert rel_err(a, r) < 1e-5, rel_err(a, r)
