@@ -350,7 +350,9 @@ class BasicLayer(nn.Module):
                     ops.hint_geometry(nb[0], pos, rel_pos_width, table_width)
         else:
             if on_grid:
-                key = (b, n, h, w, str(pos.device), id(ops), COMPACT_ROWS_ABOVE)
+                key = (b, n, h, w, str(pos.device), id(ops), COMPACT_ROWS_ABOVE, id(pre_table), pre_table.dtype,
+                       torch.is_grad_enabled())   # (the cached tuple holds a table derived from pre_table; its version
+                # counter is left out on purpose: captured graphs hold the addresses of the cached index tensors)
                 if key not in self._grid_cache:
                     self._grid_cache.clear()
                     self._grid_cache[key] = self._index(pos, h, w, rel_pos_width, ops, pre_table)

@@ -155,6 +155,8 @@ class GraphedTrainStep:
         """Refresh the low-precision shadow from the fp32 parameters (call after changing parameters by hand, e.g.
         load_state_dict; the optimizer graph does it after every step)."""
         self.flat_lp.copy_(self.flat_param)
+        from .linear_ops import mark_shadow_fresh
+        mark_shadow_fresh(self.params)
 
     def _groups(self):
         """(caller's group, stepping group) pairs; the flat optimizer keeps the caller's non-empty groups in order"""
@@ -311,6 +313,8 @@ class GraphedForward:
                     sh.copy_(p.detach())
                 else:
                     p._affb200_lp = p.detach().to(self.autocast_dtype)
+        from .linear_ops import mark_shadow_fresh
+        mark_shadow_fresh(self.model.parameters())
 
     def _fwd(self):
         with torch.no_grad(), torch.autocast("cuda", dtype=self.autocast_dtype):

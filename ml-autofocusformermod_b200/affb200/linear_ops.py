@@ -47,9 +47,20 @@ def col_sum(x2d, into=None):
 
 
 def low_precision(p, dt):
-    """The parameter in the compute dtype: its registered shadow when there is one, else a cast."""
+    """The parameter in the compute dtype: its registered shadow when there is one and the parameter has not been written
+    since the shadow was refreshed (`_affb200_lp_ver` = the parameter's version counter at that time: load_state_dict, an
+    EMA copy or another optimizer bump it), else a cast."""
     s = getattr(p, "_affb200_lp", None)
-    return s if s is not None and s.dtype == dt else p.to(dt)
+    if s is not None and s.dtype == dt and getattr(p, "_affb200_lp_ver", -1) == p._version:
+        return s
+    return p.to(dt)
+
+
+def mark_shadow_fresh(params):
+    """record that the `_affb200_lp` shadows of these parameters hold their current values"""
+    for p in params:
+        if getattr(p, "_affb200_lp", None) is not None:
+            p._affb200_lp_ver = p._version
 
 
 def _sink(p):

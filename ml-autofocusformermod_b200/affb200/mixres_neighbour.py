@@ -87,7 +87,7 @@ class BasicLayer(nn.Module):
             nnc = min(int(round(self.nbhd_size / float(self.cluster_size))), k)
             self.nbhd_size = self.cluster_size * nnc      # rounded to a multiple of the cluster size (:482)
             if on_grid and self.training:
-                key = (b, n, h, w, str(pos.device), id(ops))
+                key = (b, n, h, w, str(pos.device), id(ops), torch.is_grad_enabled())
                 if key not in self._grid_cache:
                     self._grid_cache.clear()
                     self._grid_cache[key] = self._index(pos, h, w, ops)
